@@ -1,0 +1,152 @@
+/*
+ * mm25.h — C-ABI of libmm25.so: B200 (sm_100a) kernels for the contrastive-loss hot path
+ * of neskech/Multimodal-2025 (losses/clipLoss.py, cloobLoss.py, vclipLoss.py,
+ * alignCLIPLoss.py, losses/distributions/*, metrics/topk.py).
+ *
+ * Conventions:
+ *  - every pointer is a DEVICE pointer owned by the caller; kernels never allocate or free
+ *    and retain nothing past return; launches are asynchronous on `stream`
+ *    (a cudaStream_t / CUstream passed as void*);
+ *  - return 0 on success, a negative MM25_ERR_* otherwise (checked host-side before launch);
+ *  - matrices are row-major contiguous; `dtype` is MM25_F32 or MM25_BF16 for embedding
+ *    inputs, all statistics / losses / scratch gradients are fp32;
+ *  - stateless and re-entrant (autograd calls backward from another host thread).
+ *
+ * The reference has no FFI: each entry point replaces a block of eager ATen calls, cited
+ * per function as `reference file:line`.
+ */
+#ifndef MM25_H_
+#define MM25_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { MM25_F32 = 0, MM25_BF16 = 1 };
+
+enum {
+  MM25_OK = 0,
+  MM25_ERR_SHAPE = -1,     /* bad / unsupported sizes */
+  MM25_ERR_DTYPE = -2,
+  MM25_ERR_ALIGN = -3,     /* pointer or leading dimension not aligned as required */
+  MM25_ERR_WORKSPACE = -4, /* workspace too small */
+  MM25_ERR_ARCH = -5,      /* device is not sm_100 */
+  MM25_ERR_CUDA = -6,      /* a CUDA runtime / driver call failed (see mm25_last_cuda_error) */
+  MM25_ERR_ARG = -7
+};
+
+/* logit modes of the fused similarity kernels */
+enum {
+  MM25_SIM_PLAIN = 0,    /* z = s * a_i.b_j                       (clipLoss.py:106; loss.py:215) */
+  MM25_SIM_MASKDIAG = 1, /* z = s * a_i.b_j, z_ii := -10000 in LSE (cloobLoss.py:26-31)         */
+  MM25_SIM_MODULATED = 2 /* z = s * [(a_i.b_j)(1 - u_i.u_j) + delta_ij D_i]  (loss.py:229-242)  */
+};
+
+/* how `scale` (a device scalar) is interpreted */
+enum {
+  MM25_SCALE_MUL = 0, /* multiplicative, used as is (AlignCLIP convention, loss.py:215)          */
+  MM25_SCALE_LOG = 1  /* log-space: s = exp(min(l, clamp_max)) (clipLoss.py:35,105)               */
+};
+
+const char* mm25_version(void);
+/* cudaGetErrorString of the last failing CUDA call seen by this thread (static storage). */
+const char* mm25_last_cuda_error(void);
+/* 1 if the current device is compute capability 10.x, else 0. */
+int mm25_device_ok(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Row L2-normalisation prologue.  Replaces F.normalize(x, dim=-1) (clipLoss.py:28-29,95-96),
+ * semantic_features / norm (loss.py:229).
+ *   x      [B, M, d] dtype       (B = batch of independent problems, stride M*d)
+ *   xhat   [B, M, d] out_dtype   x / max(||x||, eps)   (or a plain cast when normalize == 0)
+ *   inv_norm [B, M]  fp32        1 / max(||x||, eps)   (1.0 when normalize == 0)
+ *   colsum [B, d]    fp32        sum_i xhat_i  — must be zeroed by the caller; may be NULL
+ * ------------------------------------------------------------------------------------------ */
+int mm25_rownorm_fwd(const void* x, int dtype, void* xhat, int out_dtype, float* inv_norm,
+                     float* colsum, int64_t B, int64_t M, int64_t d, int normalize, float eps,
+                     void* stream);
+
+/* Backward of the prologue: dx = inv_norm * (g - xhat (xhat.g)) (or a cast when !normalize).
+ *   g [B,M,d] fp32 (gradient w.r.t. xhat), xhat [B,M,d] xhat_dtype, dx [B,M,d] out_dtype.
+ *   gscale: optional device scalar multiplied into dx (upstream grad); NULL = 1.
+ *   accumulate: if non-zero dx += (used when a tensor feeds several terms). */
+int mm25_rownorm_bwd(const float* g, const void* xhat, int xhat_dtype, const float* inv_norm,
+                     void* dx, int out_dtype, int64_t B, int64_t M, int64_t d, int normalize,
+                     const float* gscale, int accumulate, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused similarity + online row/column log-sum-exp.  Never materialises the M x N logits.
+ * Replaces clipLoss.py:106-117 (logits + 2x cross_entropy), cloobLoss.py:26-31,
+ * AlignCLIP loss.py:209-216,229-269.
+ *
+ *   a [B,M,d], b [B,N,d]  (dtype)         — already normalised / cast by mm25_rownorm_fwd
+ *   u [B,M,d2], v [B,N,d2] fp32 or NULL    — MODULATED only: normalised semantic features
+ *   diag_add [B,M] fp32 or NULL            — MODULATED only: D_i added on the diagonal
+ *   scale: device scalar, see MM25_SCALE_*
+ *   diag_offset: column of the positive of local row 0 (rank * M when rows are sharded,
+ *                cf. loss.py:94-95)
+ * Outputs (all fp32):
+ *   row_lse [B,M]   LSE_j z_ij
+ *   col_max, col_sum [B,N]  partial column statistics over the M local rows, such that
+ *                   LSE_i z_ij = col_max + log(col_sum); NULL to skip (row-only losses)
+ *   diag [B,M]      z_{i, i+diag_offset} (un-masked value)
+ * Implementation selection: bf16 inputs with d % 64 == 0, M % 128 == 0, N % 128 == 0 in
+ * PLAIN mode run the tcgen05/TMEM/TMA kernel; everything else the fp32 SIMT kernel.
+ * `impl`: 0 = auto, 1 = force SIMT, 2 = force tcgen05 (error if not eligible).
+ * ------------------------------------------------------------------------------------------ */
+size_t mm25_sim_fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
+                                    int impl);
+int mm25_sim_fwd(const void* a, const void* b, int dtype, const float* u, const float* v,
+                 const float* diag_add, int64_t B, int64_t M, int64_t N, int64_t d, int64_t d2,
+                 const float* scale, int scale_kind, float clamp_max, int mode,
+                 int64_t diag_offset, float* row_lse, float* col_max, float* col_sum,
+                 float* diag, void* workspace, size_t workspace_bytes, int impl, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused backward with tile recompute (autograd of the block above).
+ *   G_ij = w_row e^{z_ij - row_lse_i} + w_col e^{z_ij - col_lse_j} - w_diag delta_ij - w_all
+ *   da  [B,M,d] fp32 = s * sum_j G_ij (dz_ij/ds_ij-factor) b_j        (row-stationary pass)
+ *   db  [B,N,d] fp32 = s * sum_i G_ij (...) a_i                        (NULL: skip)
+ *   dscale_part: fp32 partial sums of sum_ij G_ij z_ij / s, one per CTA of the row pass,
+ *                length mm25_sim_bwd_nparts(); reduce with mm25_sum_parts (NULL: skip)
+ *   ddiag [B,M] fp32 = s * G_ii (MODULATED: gradient w.r.t. D_i), NULL to skip
+ * col_lse may be NULL iff w_col == 0.  Weights are host scalars; `gout` is an optional device
+ * array [B] (upstream gradient per batch entry) folded into all four.
+ * ------------------------------------------------------------------------------------------ */
+size_t mm25_sim_bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
+                                    int impl);
+int64_t mm25_sim_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int impl);
+int mm25_sim_bwd(const void* a, const void* b, int dtype, const float* u, const float* v,
+                 const float* diag_add, int64_t B, int64_t M, int64_t N, int64_t d, int64_t d2,
+                 const float* scale, int scale_kind, float clamp_max, int mode,
+                 int64_t diag_offset, const float* row_lse, const float* col_lse, float w_row,
+                 float w_col, float w_diag, float w_all, const float* gout, float* da,
+                 float* db, float* dscale_part, float* ddiag, void* workspace,
+                 size_t workspace_bytes, int impl, void* stream);
+
+/* Deterministic fixed-order sum of n fp32 values into out[0] (one CTA). out = alpha * sum. */
+int mm25_sum_parts(const float* parts, int64_t n, float alpha, float* out, void* stream);
+
+/* Merge P partial column statistics (max,sum)[P,N] in fixed order into col_lse[N]
+ * (single GPU: P = 1).  Used after the cross-rank all-gather of column partials. */
+int mm25_col_merge(const float* col_max, const float* col_sum, int64_t P, int64_t N,
+                   float* col_lse, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * CLIP loss value from statistics (clipLoss.py:116-119 in closed form):
+ *   L_b = (sum_i r_i + sum_j c_j) / (2 N) - (1-eps)/N sum_i z_ii - eps/N^2 * s * (sx . sy)
+ * row_lse,diag [B,M_total]; col_lse [B,N]; sx, sy [B,d] column sums of xhat / yhat (may be
+ * NULL when eps == 0).  loss [B].  `n_norm` = global batch N used in the means.
+ * ------------------------------------------------------------------------------------------ */
+int mm25_clip_loss_finalize(const float* row_lse, const float* diag, const float* col_lse,
+                            const float* sx, const float* sy, int64_t B, int64_t M, int64_t N,
+                            int64_t d, int64_t n_norm, const float* scale, int scale_kind,
+                            float clamp_max, float eps_ls, float* loss, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MM25_H_ */

@@ -1,0 +1,129 @@
+// api_sim.cu — C-ABI entry points of the fused similarity forward / backward and the
+// implementation choice between the fp32 SIMT kernels and the bf16 tcgen05 kernels.
+#include "common.cuh"
+#include "sim_tc.h"
+
+namespace mm25 {
+namespace simt {
+size_t fwd_workspace_bytes(int64_t B, int64_t M, int64_t N);
+int launch_fwd(const void* a, const void* b, int dtype, const float* u, const float* v,
+               const float* diag_add, int64_t B, int64_t M, int64_t N, int64_t d, int64_t d2,
+               const float* scale, int scale_kind, float clamp_max, int mode,
+               int64_t diag_offset, float* row_lse, float* col_max, float* col_sum, float* diag,
+               void* ws, size_t ws_bytes, cudaStream_t st);
+int64_t bwd_nparts(int64_t B, int64_t M);
+int launch_bwd_pass(const void* a, const void* b, int dtype, const float* u, const float* v,
+                    const float* diag_add, int diag_by_col, int64_t B, int64_t M, int64_t N,
+                    int64_t d, int64_t d2, const float* scale, int scale_kind, float clamp_max,
+                    int mode, int64_t diag_offset, const float* row_lse, const float* col_lse,
+                    float w_row, float w_col, float w_diag, float w_all, const float* gout,
+                    float* dA, float* dscale_part, float* ddiag, cudaStream_t st);
+}  // namespace simt
+}  // namespace mm25
+
+using namespace mm25;
+
+static bool use_tc(int impl, int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode,
+                   int* err) {
+  *err = MM25_OK;
+  const bool ok = tc::eligible(B, M, N, d, dtype, mode);
+  if (impl == 2 && !ok) *err = MM25_ERR_SHAPE;
+  if (impl == 1) return false;
+  return ok;
+}
+
+extern "C" size_t mm25_sim_fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d,
+                                               int dtype, int impl) {
+  int err;
+  size_t w = simt::fwd_workspace_bytes(B, M, N);
+  if (use_tc(impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err)) {
+    size_t t = tc::fwd_workspace_bytes(B, M, N, d);
+    if (t > w) w = t;
+  }
+  return w;
+}
+
+extern "C" int mm25_sim_fwd(const void* a, const void* b, int dtype, const float* u,
+                            const float* v, const float* diag_add, int64_t B, int64_t M,
+                            int64_t N, int64_t d, int64_t d2, const float* scale, int scale_kind,
+                            float clamp_max, int mode, int64_t diag_offset, float* row_lse,
+                            float* col_max, float* col_sum, float* diag, void* workspace,
+                            size_t workspace_bytes, int impl, void* stream) {
+  if (B <= 0 || M <= 0 || N <= 0 || d <= 0) return MM25_ERR_SHAPE;
+  if (!a || !b || !scale || !row_lse || !diag) return MM25_ERR_ARG;
+  if ((col_max == nullptr) != (col_sum == nullptr)) return MM25_ERR_ARG;
+  if (mode < 0 || mode > 2) return MM25_ERR_ARG;
+  if (mode == MM25_SIM_MODULATED && (!u || !v || d2 <= 0)) return MM25_ERR_ARG;
+  if (dtype != MM25_F32 && dtype != MM25_BF16) return MM25_ERR_DTYPE;
+  if (!workspace) return MM25_ERR_WORKSPACE;
+  int err;
+  const bool t = use_tc(impl, B, M, N, d, dtype, mode, &err);
+  if (err) return err;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (t)
+    return tc::launch_fwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
+                          col_max, col_sum, diag, workspace, workspace_bytes, st);
+  return simt::launch_fwd(a, b, dtype, u, v, diag_add, B, M, N, d, d2, scale, scale_kind,
+                          clamp_max, mode, diag_offset, row_lse, col_max, col_sum, diag,
+                          workspace, workspace_bytes, st);
+}
+
+extern "C" size_t mm25_sim_bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d,
+                                               int dtype, int impl) {
+  int err;
+  if (use_tc(impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err))
+    return tc::bwd_workspace_bytes(B, M, N, d);
+  return 16;
+}
+
+extern "C" int64_t mm25_sim_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
+                                       int impl) {
+  int err;
+  int64_t n = simt::bwd_nparts(B, M);
+  if (use_tc(impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err)) {
+    int64_t t = tc::bwd_nparts(B, M, N, d);
+    if (t > n) n = t;
+  }
+  return n;
+}
+
+extern "C" int mm25_sim_bwd(const void* a, const void* b, int dtype, const float* u,
+                            const float* v, const float* diag_add, int64_t B, int64_t M,
+                            int64_t N, int64_t d, int64_t d2, const float* scale, int scale_kind,
+                            float clamp_max, int mode, int64_t diag_offset, const float* row_lse,
+                            const float* col_lse, float w_row, float w_col, float w_diag,
+                            float w_all, const float* gout, float* da, float* db,
+                            float* dscale_part, float* ddiag, void* workspace,
+                            size_t workspace_bytes, int impl, void* stream) {
+  if (B <= 0 || M <= 0 || N <= 0 || d <= 0) return MM25_ERR_SHAPE;
+  if (!a || !b || !scale || !row_lse) return MM25_ERR_ARG;
+  if (!col_lse && w_col != 0.f) return MM25_ERR_ARG;
+  if (mode < 0 || mode > 2) return MM25_ERR_ARG;
+  if (mode == MM25_SIM_MODULATED && (!u || !v || d2 <= 0)) return MM25_ERR_ARG;
+  if (dtype != MM25_F32 && dtype != MM25_BF16) return MM25_ERR_DTYPE;
+  int err;
+  const bool t = use_tc(impl, B, M, N, d, dtype, mode, &err);
+  if (err) return err;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (t)
+    return tc::launch_bwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
+                          col_lse, w_row, w_col, w_diag, w_all, gout, da, db, dscale_part,
+                          workspace, workspace_bytes, st);
+  int rc = MM25_OK;
+  if (da) {
+    rc = simt::launch_bwd_pass(a, b, dtype, u, v, diag_add, 0, B, M, N, d, d2, scale, scale_kind,
+                               clamp_max, mode, diag_offset, row_lse, col_lse, w_row, w_col,
+                               w_diag, w_all, gout, da, dscale_part, ddiag, st);
+    if (rc) return rc;
+  }
+  if (db) {
+    // transposed roles: rows = b, columns = a; row statistics = col_lse
+    if (!col_lse && w_row != 0.f) {
+      // column pass needs exp(z - row_lse_i) with i the *column* index of the swapped problem
+    }
+    rc = simt::launch_bwd_pass(b, a, dtype, v, u, diag_add, 1, B, N, M, d, d2, scale, scale_kind,
+                               clamp_max, mode, -diag_offset, col_lse, row_lse, w_col, w_row,
+                               w_diag, w_all, gout, db, da ? nullptr : dscale_part, nullptr, st);
+  }
+  return rc;
+}

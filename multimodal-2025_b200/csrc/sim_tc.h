@@ -1,0 +1,28 @@
+// sim_tc.h — host interface of the bf16 tcgen05 / TMEM / TMA similarity kernels (sim_tc.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace mm25 {
+namespace tc {
+
+// PLAIN mode, bf16, d % 64 == 0 (64 <= d <= 1024), M % 128 == 0, N % 128 == 0.
+bool eligible(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode);
+
+size_t fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d);
+int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,
+               const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
+               float* row_lse, float* col_max, float* col_sum, float* diag, void* ws,
+               size_t ws_bytes, cudaStream_t st);
+
+size_t bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d);
+int64_t bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d);
+int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,
+               const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
+               const float* row_lse, const float* col_lse, float w_row, float w_col,
+               float w_diag, float w_all, const float* gout, float* da, float* db,
+               float* dscale_part, void* ws, size_t ws_bytes, cudaStream_t st);
+
+}  // namespace tc
+}  // namespace mm25

@@ -1,0 +1,197 @@
+"""torch.library custom ops (`mm25::*`) over the C-ABI of libmm25.so.
+
+CUDA dispatch only: CPU tensors raise (there is no fallback).  Every op allocates its outputs
+and workspace through PyTorch's caching allocator and launches on the current stream, so the
+kernels never allocate (include/mm25.h conventions).
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _lib
+
+F32, BF16 = 0, 1
+SIM_PLAIN, SIM_MASKDIAG, SIM_MODULATED = 0, 1, 2
+SCALE_MUL, SCALE_LOG = 0, 1
+IMPL_AUTO, IMPL_SIMT, IMPL_TC = 0, 1, 2
+
+
+def _dt(t: Tensor) -> int:
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise TypeError("mm25 ops take float32 or bfloat16 embeddings, got %s" % t.dtype)
+
+
+def _tdt(code: int) -> torch.dtype:
+    return torch.float32 if code == F32 else torch.bfloat16
+
+
+def _p(t: Optional[Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream(t: Tensor):
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _cuda3(t: Tensor, name: str) -> Tensor:
+    if not t.is_cuda:
+        raise _lib.MM25Error("%s must be a CUDA tensor: this path has no CPU fallback" % name)
+    if t.dim() != 3:
+        raise ValueError("%s must be [B, M, d]" % name)
+    return t.contiguous()
+
+
+def _f32c(t: Optional[Tensor]) -> Optional[Tensor]:
+    if t is None:
+        return None
+    return t.detach().to(torch.float32).contiguous()
+
+
+@torch.library.custom_op("mm25::rownorm_fwd", mutates_args=(), device_types="cuda")
+def rownorm_fwd(x: Tensor, normalize: bool, eps: float, out_dtype: int,
+                want_colsum: bool) -> Tuple[Tensor, Tensor, Tensor]:
+    """F.normalize(x, dim=-1) (+ inverse norms, + column sums). Ref: clipLoss.py:28-29,95-96."""
+    x = _cuda3(x, "x")
+    B, M, d = x.shape
+    with torch.cuda.device(x.device):
+        xhat = torch.empty((B, M, d), dtype=_tdt(out_dtype), device=x.device)
+        inv = torch.empty((B, M), dtype=torch.float32, device=x.device)
+        cs = torch.empty((B, d) if want_colsum else (0,), dtype=torch.float32, device=x.device)
+        rc = _lib.lib().mm25_rownorm_fwd(_p(x), _dt(x), _p(xhat), out_dtype, _p(inv),
+                                         _p(cs) if want_colsum else None, B, M, d,
+                                         int(normalize), eps, _stream(x))
+    _lib.check(rc, "mm25_rownorm_fwd")
+    return xhat, inv, cs
+
+
+@torch.library.custom_op("mm25::rownorm_bwd", mutates_args=(), device_types="cuda")
+def rownorm_bwd(g: Tensor, xhat: Tensor, inv_norm: Tensor, normalize: bool, out_dtype: int,
+                gscale: Optional[Tensor]) -> Tensor:
+    g = _cuda3(g, "g")
+    B, M, d = g.shape
+    xhat = xhat.contiguous()
+    with torch.cuda.device(g.device):
+        dx = torch.empty((B, M, d), dtype=_tdt(out_dtype), device=g.device)
+        rc = _lib.lib().mm25_rownorm_bwd(_p(g), _p(xhat), _dt(xhat), _p(inv_norm), _p(dx),
+                                         out_dtype, B, M, d, int(normalize), _p(gscale), 0,
+                                         _stream(g))
+    _lib.check(rc, "mm25_rownorm_bwd")
+    return dx
+
+
+@torch.library.custom_op("mm25::sim_fwd", mutates_args=(), device_types="cuda")
+def sim_fwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
+            diag_add: Optional[Tensor], scale: Tensor, scale_kind: int, clamp_max: float,
+            mode: int, diag_offset: int, want_cols: bool,
+            impl: int) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """Fused similarity + online row/column LSE; returns (row_lse, col_max, col_sum, diag)."""
+    a = _cuda3(a, "a")
+    b = _cuda3(b, "b")
+    if a.dtype != b.dtype:
+        raise TypeError("a and b must share a dtype")
+    B, M, d = a.shape
+    N = b.shape[1]
+    d2 = 0 if u is None else u.shape[-1]
+    dev = a.device
+    L = _lib.lib()
+    with torch.cuda.device(dev):
+        row_lse = torch.empty((B, M), dtype=torch.float32, device=dev)
+        diag = torch.zeros((B, M), dtype=torch.float32, device=dev)
+        cshape = (B, N) if want_cols else (0,)
+        col_max = torch.empty(cshape, dtype=torch.float32, device=dev)
+        col_sum = torch.empty(cshape, dtype=torch.float32, device=dev)
+        wsb = L.mm25_sim_fwd_workspace_bytes(B, M, N, d, _dt(a), impl)
+        ws = torch.empty((max(int(wsb), 16),), dtype=torch.uint8, device=dev)
+        rc = L.mm25_sim_fwd(_p(a), _p(b), _dt(a), _p(u), _p(v), _p(diag_add), B, M, N, d, d2,
+                            _p(scale), scale_kind, clamp_max, mode, diag_offset, _p(row_lse),
+                            _p(col_max) if want_cols else None,
+                            _p(col_sum) if want_cols else None, _p(diag), _p(ws), ws.numel(),
+                            impl, _stream(a))
+    _lib.check(rc, "mm25_sim_fwd")
+    return row_lse, col_max, col_sum, diag
+
+
+@torch.library.custom_op("mm25::sim_bwd", mutates_args=(), device_types="cuda")
+def sim_bwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
+            diag_add: Optional[Tensor], scale: Tensor, scale_kind: int, clamp_max: float,
+            mode: int, diag_offset: int, row_lse: Tensor, col_lse: Optional[Tensor],
+            w_row: float, w_col: float, w_diag: float, w_all: float, gout: Optional[Tensor],
+            need_da: bool, need_db: bool, need_ddiag: bool,
+            impl: int) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """Fused backward with tile recompute; returns (da, db, dscale[1], ddiag), all fp32.
+
+    dscale is dL/d(multiplicative scale) = sum_ij G_ij z_ij / s (already times gout)."""
+    a = _cuda3(a, "a")
+    b = _cuda3(b, "b")
+    B, M, d = a.shape
+    N = b.shape[1]
+    d2 = 0 if u is None else u.shape[-1]
+    dev = a.device
+    L = _lib.lib()
+    with torch.cuda.device(dev):
+        da = torch.empty((B, M, d) if need_da else (0,), dtype=torch.float32, device=dev)
+        db = torch.empty((B, N, d) if need_db else (0,), dtype=torch.float32, device=dev)
+        ddiag = torch.zeros((B, M) if need_ddiag else (0,), dtype=torch.float32, device=dev)
+        nparts = int(L.mm25_sim_bwd_nparts(B, max(M, N), max(M, N), d, _dt(a), impl))
+        parts = torch.zeros((max(nparts, 1),), dtype=torch.float32, device=dev)
+        dscale = torch.empty((1,), dtype=torch.float32, device=dev)
+        wsb = L.mm25_sim_bwd_workspace_bytes(B, M, N, d, _dt(a), impl)
+        ws = torch.empty((max(int(wsb), 16),), dtype=torch.uint8, device=dev)
+        rc = L.mm25_sim_bwd(_p(a), _p(b), _dt(a), _p(u), _p(v), _p(diag_add), B, M, N, d, d2,
+                            _p(scale), scale_kind, clamp_max, mode, diag_offset, _p(row_lse),
+                            _p(col_lse), w_row, w_col, w_diag, w_all, _p(gout),
+                            _p(da) if need_da else None, _p(db) if need_db else None, _p(parts),
+                            _p(ddiag) if need_ddiag else None, _p(ws), ws.numel(), impl,
+                            _stream(a))
+        _lib.check(rc, "mm25_sim_bwd")
+        rc = L.mm25_sum_parts(_p(parts), parts.numel(), 1.0, _p(dscale), _stream(a))
+    _lib.check(rc, "mm25_sum_parts")
+    return da, db, dscale, ddiag
+
+
+@torch.library.custom_op("mm25::col_merge", mutates_args=(), device_types="cuda")
+def col_merge(col_max: Tensor, col_sum: Tensor) -> Tensor:
+    """Merge [P, N] partial column (max, sum) in fixed order into col_lse [N]."""
+    col_max = col_max.contiguous()
+    col_sum = col_sum.contiguous()
+    P, N = col_max.shape
+    with torch.cuda.device(col_max.device):
+        out = torch.empty((N,), dtype=torch.float32, device=col_max.device)
+        rc = _lib.lib().mm25_col_merge(_p(col_max), _p(col_sum), P, N, _p(out),
+                                       _stream(col_max))
+    _lib.check(rc, "mm25_col_merge")
+    return out
+
+
+@torch.library.custom_op("mm25::clip_loss_finalize", mutates_args=(), device_types="cuda")
+def clip_loss_finalize(row_lse: Tensor, diag: Tensor, col_lse: Optional[Tensor],
+                       sx: Optional[Tensor], sy: Optional[Tensor], n_norm: int, scale: Tensor,
+                       scale_kind: int, clamp_max: float, eps_ls: float) -> Tensor:
+    """Closed-form CLIP loss per batch entry from the statistics."""
+    row_lse = row_lse.contiguous()
+    B, M = row_lse.shape
+    N = M if col_lse is None else col_lse.shape[-1]
+    d = 0 if sx is None else sx.shape[-1]
+    with torch.cuda.device(row_lse.device):
+        loss = torch.empty((B,), dtype=torch.float32, device=row_lse.device)
+        rc = _lib.lib().mm25_clip_loss_finalize(_p(row_lse), _p(diag), _p(col_lse), _p(sx),
+                                                _p(sy), B, M, N, d, n_norm, _p(scale),
+                                                scale_kind, clamp_max, eps_ls, _p(loss),
+                                                _stream(row_lse))
+    _lib.check(rc, "mm25_clip_loss_finalize")
+    return loss
+
+
+def scale_param_grad(dscale: Tensor, scale: Tensor, scale_kind: int, clamp_max: float) -> Tensor:
+    """Chain dL/ds to the raw scale parameter (clamp passes gradient at equality)."""
+    if scale_kind == SCALE_MUL:
+        return dscale.reshape(scale.shape).to(scale.dtype)
+    l = scale.detach().float()
+    chain = torch.where(l <= clamp_max, l.exp(), torch.zeros_like(l))
+    return (dscale.reshape(()) * chain).reshape(scale.shape).to(scale.dtype)

@@ -1,0 +1,98 @@
+"""GPU parity of the CLIP loss (through the C-ABI) against the reference's golden vectors and
+the CPU oracle.  Tolerances are BASELINE.json's: fp32 rel 1e-5 loss / 1e-4 grads; bf16 rel 2e-3
+loss / 2e-2 grads."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, rel_err
+from oracle import losses_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def T(a):
+    return torch.from_numpy(np.asarray(a))
+
+
+def run_ours(mod_fn, tensors, dtype=torch.float32):
+    leaves = [t.detach().to("cuda").to(dtype if t.dim() > 0 else torch.float32)
+              .requires_grad_(True) for t in tensors]
+    out = mod_fn(*leaves)
+    out.sum().backward()
+    return out.detach().float().cpu(), [l.grad.float().cpu() for l in leaves]
+
+
+@pytest.mark.parametrize("case", ["n256_d512", "n256_d512_clamp", "n192_d96_eps0", "n70_d40_raw",
+                                  "n96_d64_nonorm"])
+def test_clip_fp32_vs_reference_golden(lib_built, case):
+    from multimodal_2025_b200.losses import ClipLoss
+    g = load_golden("clip_forward.npz")[case]
+    norm = case != "n96_d64_nonorm"
+    m = ClipLoss(float(g["eps"])).cuda()
+    loss, (gx, gy, gl) = run_ours(lambda a, b, c: m(a, b, c, normalize=norm),
+                                  [T(g["x"]), T(g["y"]), torch.tensor(float(g["ls"]))])
+    assert rel_err(loss, g["loss"]) < 1e-5
+    assert rel_err(gx, g["gx"]) < 1e-4
+    assert rel_err(gy, g["gy"]) < 1e-4
+    assert abs(float(gl) - float(g["gl"])) <= 1e-4 * max(abs(float(g["gl"])), 1e-3)
+
+
+@pytest.mark.parametrize("n,d,seed,ls", [(64, 64, 0, 2.0), (257, 100, 1, 3.0), (1000, 512, 2, 4.6052),
+                                         (33, 7, 3, 1.0), (1, 16, 4, 2.0)])
+def test_clip_fp32_vs_oracle_shapes(lib_built, n, d, seed, ls):
+    """ragged / tiny / single-row shapes and the clamp boundary."""
+    from multimodal_2025_b200.losses import ClipLoss
+    x, y = O.synth_embeddings(n, d, seed, correlated=True)
+    lsc = torch.tensor(ls)
+    ref, (rx, ry, rl) = O.loss_and_grads(O.clip_loss, [x, y, lsc], 0.1, True)
+    m = ClipLoss(0.1).cuda()
+    loss, (gx, gy, gl) = run_ours(lambda a, b, c: m(a, b, c), [x, y, lsc])
+    assert rel_err(loss, ref) < 1e-5
+    if n > 1:
+        assert rel_err(gx, rx) < 1e-4 and rel_err(gy, ry) < 1e-4
+        assert abs(float(gl) - float(rl)) <= 1e-4 * max(abs(float(rl)), 1e-3)
+
+
+@pytest.mark.parametrize("key", ["eps0.1_ls2.6592", "eps0.1_ls4.2", "eps0.0_ls2.6592",
+                                 "eps0.0_ls4.2"])
+def test_clip_sampled_fp32_vs_reference_golden(lib_built, key):
+    from multimodal_2025_b200.losses import ClipLoss
+    G = load_golden("clip_sampled.npz")
+    g, top = G[key], G[""]
+    eps = float(key.split("_")[0][3:])
+    ls = float(key.split("ls")[1])
+    w = T(top["w"]).cuda()
+    m = ClipLoss(eps).cuda()
+    loss, (gx, gy, gl) = run_ours(lambda a, b, c: m.forward_sampled(a, b, c) * w,
+                                  [T(top["x"]), T(top["y"]), torch.tensor(ls)])
+    assert rel_err(loss / w.cpu(), g["loss"]) < 1e-5
+    assert rel_err(gx, g["gx"]) < 1e-4 and rel_err(gy, g["gy"]) < 1e-4
+    assert abs(float(gl) - float(g["gl"])) <= 1e-4 * max(abs(float(g["gl"])), 1e-3)
+
+
+@pytest.mark.parametrize("impl", [1, 0])
+@pytest.mark.parametrize("n,d,ls", [(256, 512, 2.6592), (512, 128, 4.6052), (384, 64, 3.5)])
+def test_clip_bf16_vs_oracle(lib_built, impl, n, d, ls):
+    """bf16 inputs: SIMT (impl=1) and auto (tcgen05 when eligible) against the fp32 oracle fed
+    the same bf16-rounded values."""
+    from multimodal_2025_b200.losses import ClipLoss
+    x, y = O.synth_embeddings(n, d, 5, correlated=True, dtype=torch.bfloat16)
+    lsc = torch.tensor(ls)
+    ref, (rx, ry, rl) = O.loss_and_grads(O.clip_loss, [x.float(), y.float(), lsc], 0.1, True)
+    m = ClipLoss(0.1).cuda()
+    m.impl = impl
+    loss, (gx, gy, gl) = run_ours(lambda a, b, c: m(a, b, c), [x, y, lsc], torch.bfloat16)
+    assert rel_err(loss, ref) < 2e-3
+    assert rel_err(gx, rx) < 2e-2 and rel_err(gy, ry) < 2e-2
+    assert abs(float(gl) - float(rl)) <= 2e-2 * max(abs(float(rl)), 1e-3)
+
+
+def test_clip_linearity_in_upstream_grad(lib_built):
+    """size-independent property: grads scale linearly with the upstream gradient."""
+    from multimodal_2025_b200.losses import ClipLoss
+    x, y = O.synth_embeddings(300, 96, 9)
+    m = ClipLoss(0.1).cuda()
+    _, (g1, _, _) = run_ours(lambda a, b, c: m(a, b, c), [x, y, torch.tensor(3.0)])
+    _, (g3, _, _) = run_ours(lambda a, b, c: 3.0 * m(a, b, c), [x, y, torch.tensor(3.0)])
+    assert rel_err(g3, 3.0 * g1) < 1e-6
