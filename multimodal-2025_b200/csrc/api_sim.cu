@@ -23,10 +23,11 @@ int launch_bwd_pass(const void* a, const void* b, int dtype, const float* u, con
 
 using namespace mm25;
 
-static bool use_tc(int impl, int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode,
-                   int* err) {
+static bool use_tc(bool bwd, int impl, int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
+                   int mode, int* err) {
   *err = MM25_OK;
-  const bool ok = tc::eligible(B, M, N, d, dtype, mode);
+  const bool ok = bwd ? tc::eligible_bwd(B, M, N, d, dtype, mode)
+                      : tc::eligible_fwd(B, M, N, d, dtype, mode);
   if (impl == 2 && !ok) *err = MM25_ERR_SHAPE;
   if (impl == 1) return false;
   return ok;
@@ -36,7 +37,7 @@ extern "C" size_t mm25_sim_fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, 
                                                int dtype, int impl) {
   int err;
   size_t w = simt::fwd_workspace_bytes(B, M, N);
-  if (use_tc(impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err)) {
+  if (use_tc(false, impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err)) {
     size_t t = tc::fwd_workspace_bytes(B, M, N, d);
     if (t > w) w = t;
   }
@@ -57,7 +58,7 @@ extern "C" int mm25_sim_fwd(const void* a, const void* b, int dtype, const float
   if (dtype != MM25_F32 && dtype != MM25_BF16) return MM25_ERR_DTYPE;
   if (!workspace) return MM25_ERR_WORKSPACE;
   int err;
-  const bool t = use_tc(impl, B, M, N, d, dtype, mode, &err);
+  const bool t = use_tc(false, impl, B, M, N, d, dtype, mode, &err);
   if (err) return err;
   cudaStream_t st = (cudaStream_t)stream;
   if (t)
@@ -71,7 +72,7 @@ extern "C" int mm25_sim_fwd(const void* a, const void* b, int dtype, const float
 extern "C" size_t mm25_sim_bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d,
                                                int dtype, int impl) {
   int err;
-  if (use_tc(impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err))
+  if (use_tc(true, impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err))
     return tc::bwd_workspace_bytes(B, M, N, d);
   return 16;
 }
@@ -80,7 +81,7 @@ extern "C" int64_t mm25_sim_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t 
                                        int impl) {
   int err;
   int64_t n = simt::bwd_nparts(B, M);
-  if (use_tc(impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err)) {
+  if (use_tc(true, impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err)) {
     int64_t t = tc::bwd_nparts(B, M, N, d);
     if (t > n) n = t;
   }
@@ -102,7 +103,7 @@ extern "C" int mm25_sim_bwd(const void* a, const void* b, int dtype, const float
   if (mode == MM25_SIM_MODULATED && (!u || !v || d2 <= 0)) return MM25_ERR_ARG;
   if (dtype != MM25_F32 && dtype != MM25_BF16) return MM25_ERR_DTYPE;
   int err;
-  const bool t = use_tc(impl, B, M, N, d, dtype, mode, &err);
+  const bool t = use_tc(true, impl, B, M, N, d, dtype, mode, &err);
   if (err) return err;
   cudaStream_t st = (cudaStream_t)stream;
   if (t)

@@ -1,12 +1,416 @@
-// sim_tc.cu — placeholder until the tcgen05 kernels land (eligible() == false keeps every
-// call on the SIMT path).
-#include "common.cuh"
+// sim_tc.cu — bf16 tensor-core path of the fused similarity kernels (sm_100a):
+// TMA (128B-swizzled tiles) -> shared memory ring -> tcgen05.mma (fp32 accumulators in TMEM)
+// -> tcgen05.ld -> softmax-statistics / gradient epilogues in registers.
+//
+// Forward (this file, part 1): persistent CTAs; a work item is (128-row block, column segment).
+// The A row block stays resident in shared memory for the whole item, B tiles stream through a
+// 4-stage ring, 4 TMEM accumulator stages decouple the MMA warp from the 4 epilogue warps.
+#include "tc_common.cuh"
 #include "sim_tc.h"
-namespace mm25 { namespace tc {
-bool eligible(int64_t, int64_t, int64_t, int64_t, int, int) { return false; }
-size_t fwd_workspace_bytes(int64_t, int64_t, int64_t, int64_t) { return 0; }
-int launch_fwd(const void*, const void*, int64_t, int64_t, int64_t, int64_t, const float*, int, float, int64_t, float*, float*, float*, float*, void*, size_t, cudaStream_t) { return MM25_ERR_SHAPE; }
-size_t bwd_workspace_bytes(int64_t, int64_t, int64_t, int64_t) { return 0; }
+
+#include <mutex>
+
+namespace mm25 {
+namespace tc {
+
+constexpr int BM = 128, BN = 128, BK = 64;
+constexpr int MAX_KC = 8;            // d <= 512 keeps the A block resident (128 KB)
+constexpr int NST = 4;               // B ring stages (16 KB each)
+constexpr int NACC = 4;              // TMEM accumulator stages (128 columns each)
+constexpr int CHUNK_BYTES = BM * BK * 2;  // 16384
+constexpr int FWD_THREADS = 192;     // warp0 TMA, warp1 MMA, warps 2-5 epilogue
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+constexpr float SPREAD_LIMIT = 96.f;  // log2 units: larger in-block spread takes the slow path
+
+struct FwdSmem {
+  uint8_t a[MAX_KC * CHUNK_BYTES];
+  uint8_t b[NST * CHUNK_BYTES];
+  float colm[2][4][BN];
+  float cols[2][4][BN];
+  uint64_t a_full, a_empty;
+  uint64_t b_full[NST], b_empty[NST];
+  uint64_t acc_full[NACC], acc_empty[NACC];
+  uint32_t tmem_base;
+};
+
+// sum over the 32 lanes of e[j] for every j: afterwards lane j holds column j in e[0]
+__device__ __forceinline__ float butterfly_colsum(float (&e)[32], int lane) {
+#pragma unroll
+  for (int w = 16; w >= 1; w >>= 1) {
+    const bool up = (lane & w) != 0;
+#pragma unroll
+    for (int k = 0; k < w; ++k) {
+      const float send = up ? e[k] : e[k + w];
+      const float keep = up ? e[k + w] : e[k];
+      e[k] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+    }
+  }
+  return e[0];
+}
+
+__global__ void __launch_bounds__(FWD_THREADS, 1)
+sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                  const __grid_constant__ CUtensorMap tmap_b, int64_t M, int64_t N, int d,
+                  int nrb_per_batch, int total_rb, int nseg, int tps,
+                  const float* __restrict__ scale, int scale_kind, float clamp_max,
+                  int64_t diag_offset, float* __restrict__ row_pm, float* __restrict__ row_pl,
+                  float* __restrict__ col_pm, float* __restrict__ col_pl,
+                  float* __restrict__ diag, int force_slow) {
+  extern __shared__ uint8_t smem_raw[];
+  FwdSmem& sm = *reinterpret_cast<FwdSmem*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int KC = d / BK;
+  const int ntiles = (int)(N / BN);
+  const int nitems = total_rb * nseg;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&sm.a_full, 1);
+    mbar_init(&sm.a_empty, 1);
+    for (int i = 0; i < NST; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
+    for (int i = 0; i < NACC; ++i) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_empty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(&sm.tmem_base, 512);
+    if (lane == 0) { tma_prefetch_desc(&tmap_a); tma_prefetch_desc(&tmap_b); }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0) {
+      uint32_t bst = 0, bph = 0, aph = 0;
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+        const int rbg = item / nseg, seg = item % nseg;
+        const int bz = rbg / nrb_per_batch;
+        const int64_t arow = (int64_t)rbg * BM;  // row in the flattened [B*M, d] matrix
+        mbar_wait(&sm.a_empty, aph ^ 1);
+        aph ^= 1;
+        mbar_arrive_expect_tx(&sm.a_full, (uint32_t)(KC * CHUNK_BYTES));
+        for (int kc = 0; kc < KC; ++kc)
+          tma_load_2d(sm.a + kc * CHUNK_BYTES, &tmap_a, &sm.a_full, kc * BK, (int32_t)arow);
+        const int t0 = seg * tps, t1 = min(ntiles, t0 + tps);
+        for (int t = t0; t < t1; ++t) {
+          const int64_t brow = (int64_t)bz * N + (int64_t)t * BN;
+          for (int kc = 0; kc < KC; ++kc) {
+            mbar_wait(&sm.b_empty[bst], bph ^ 1);
+            mbar_arrive_expect_tx(&sm.b_full[bst], CHUNK_BYTES);
+            tma_load_2d(sm.b + bst * CHUNK_BYTES, &tmap_b, &sm.b_full[bst], kc * BK,
+                        (int32_t)brow);
+            if (++bst == NST) { bst = 0; bph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 0, 0);
+      uint32_t bst = 0, bph = 0, aph = 0, as = 0, accph = 0;
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+        const int seg = item % nseg;
+        mbar_wait(&sm.a_full, aph);
+        aph ^= 1;
+        tc_fence_after();
+        const int t0 = seg * tps, t1 = min(ntiles, t0 + tps);
+        for (int t = t0; t < t1; ++t) {
+          mbar_wait(&sm.acc_empty[as], accph ^ 1);
+          tc_fence_after();
+          const uint32_t dcol = tmem + as * BN;
+          for (int kc = 0; kc < KC; ++kc) {
+            mbar_wait(&sm.b_full[bst], bph);
+            tc_fence_after();
+            const uint32_t abase = smem_u32(sm.a + kc * CHUNK_BYTES);
+            const uint32_t bbase = smem_u32(sm.b + bst * CHUNK_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t ad = make_smem_desc(abase + k * 32, 16, 1024);
+              const uint64_t bd = make_smem_desc(bbase + k * 32, 16, 1024);
+              umma_bf16(dcol, ad, bd, idesc, (kc | k) != 0);
+            }
+            umma_commit(&sm.b_empty[bst]);
+            if (++bst == NST) { bst = 0; bph ^= 1; }
+          }
+          umma_commit(&sm.acc_full[as]);
+          if (++as == NACC) { as = 0; accph ^= 1; }
+        }
+        umma_commit(&sm.a_empty);
+      }
+    }
+  } else {
+    // ===================================================================== epilogue warps
+    const int q = warp & 3;        // TMEM lane quadrant this warp may read
+    const int ew = warp - 2;       // 0..3, staging slot
+    const float s = load_scale(scale, scale_kind, clamp_max);
+    const float c2 = s * LOG2E;
+    uint32_t as = 0, accph = 0, buf = 0;
+    for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+      const int rbg = item / nseg, seg = item % nseg;
+      const int bz = rbg / nrb_per_batch, rb = rbg % nrb_per_batch;
+      const int64_t row = (int64_t)rb * BM + q * 32 + lane;  // row inside this batch entry
+      const int64_t dcol = row + diag_offset;                // its positive column
+      float rm = -INFINITY, rl = 0.f;
+      const int t0 = seg * tps, t1 = min(ntiles, t0 + tps);
+      for (int t = t0; t < t1; ++t) {
+        const int64_t col0 = (int64_t)t * BN;
+        mbar_wait(&sm.acc_full[as], accph);
+        tc_fence_after();
+#pragma unroll 1
+        for (int ch = 0; ch < BN / 32; ++ch) {
+          float v[32];
+          tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + as * BN + ch * 32, v);
+          const int64_t cbase = col0 + ch * 32;
+          // positive logit (warp-uniform test: this chunk crosses the warp's diagonal range)
+          {
+            const int64_t d0 = (int64_t)rb * BM + q * 32 + diag_offset;
+            if (d0 + 31 >= cbase && d0 < cbase + 32) {
+              const int rel = (int)(dcol - cbase);
+              float dv = 0.f;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) dv = (j == rel) ? v[j] : dv;
+              if (rel >= 0 && rel < 32) diag[(int64_t)bz * M + row] = s * dv;
+            }
+          }
+          float tmx = v[0], tmn = v[0];
+#pragma unroll
+          for (int j = 1; j < 32; ++j) { tmx = fmaxf(tmx, v[j]); tmn = fminf(tmn, v[j]); }
+          const float bmx = warp_max(tmx), bmn = -warp_max(-tmn);
+          float e[32];
+          float cm;
+          if (!force_slow && (bmx - bmn) * c2 <= SPREAD_LIMIT) {
+            // fast path: one exp per logit, shared block shift
+            const float m2 = bmx * c2;
+            float rs = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) { e[j] = ex2_approx(fmaf(v[j], c2, -m2)); rs += e[j]; }
+            const float mn = fmaxf(rm, m2);
+            rl = rl * ex2_approx(rm - mn) + rs * ex2_approx(m2 - mn);
+            rm = mn;
+            cm = m2;
+          } else {
+            // robust path: per-row and per-column shifts (two exps per logit)
+            const float tm2 = tmx * c2;
+            const float mn = fmaxf(rm, tm2);
+            float rs = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) rs += ex2_approx(fmaf(v[j], c2, -mn));
+            rl = rl * ex2_approx(rm - mn) + rs;
+            rm = mn;
+            cm = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float cj = warp_max(v[j]) * c2;
+              e[j] = ex2_approx(fmaf(v[j], c2, -cj));
+              cm = (j == lane) ? cj : cm;
+            }
+          }
+          const float cs = butterfly_colsum(e, lane);
+          sm.colm[buf][ew][ch * 32 + lane] = cm;
+          sm.cols[buf][ew][ch * 32 + lane] = cs;
+        }
+        // all TMEM reads of this stage are complete (wait::ld inside the load helper)
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.acc_empty[as]);
+        if (++as == NACC) { as = 0; accph ^= 1; }
+        // merge the four 32-row groups of this tile; warp ew owns columns [32 ew, 32 ew + 32)
+        named_bar_sync(1, 128);
+        {
+          const int c = ew * 32 + lane;
+          float m = sm.colm[buf][0][c], l = sm.cols[buf][0][c];
+#pragma unroll
+          for (int g = 1; g < 4; ++g) {
+            const float m2 = sm.colm[buf][g][c], l2 = sm.cols[buf][g][c];
+            const float mn = fmaxf(m, m2);
+            l = l * ex2_approx(m - mn) + l2 * ex2_approx(m2 - mn);
+            m = mn;
+          }
+          const int64_t o = ((int64_t)bz * nrb_per_batch + rb) * N + col0 + c;
+          col_pm[o] = m;
+          col_pl[o] = l;
+        }
+        buf ^= 1;
+      }
+      const int64_t o = ((int64_t)bz * nseg + seg) * M + row;
+      row_pm[o] = rm;
+      row_pl[o] = rl;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+// partials are in log2-scaled units: value = 2^m * l
+__global__ void __launch_bounds__(256) fwd_tc_merge_kernel(
+    const float* __restrict__ row_pm, const float* __restrict__ row_pl, int nseg, int64_t M,
+    float* __restrict__ row_lse, const float* __restrict__ col_pm,
+    const float* __restrict__ col_pl, int nrb, int64_t N, float* __restrict__ col_max,
+    float* __restrict__ col_sum) {
+  const int bz = blockIdx.y;
+  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (t < M) {
+    float m = -INFINITY, l = 0.f;
+    for (int p = 0; p < nseg; ++p) {
+      const float m2 = row_pm[((int64_t)bz * nseg + p) * M + t];
+      const float l2 = row_pl[((int64_t)bz * nseg + p) * M + t];
+      const float mn = fmaxf(m, m2);
+      l = l * exp2f(m - mn) + l2 * exp2f(m2 - mn);
+      m = mn;
+    }
+    row_lse[(int64_t)bz * M + t] = (m + log2f(l)) * LN2;
+  }
+  if (col_max && t < N) {
+    float m = -INFINITY, l = 0.f;
+    for (int p = 0; p < nrb; ++p) {
+      const float m2 = col_pm[((int64_t)bz * nrb + p) * N + t];
+      const float l2 = col_pl[((int64_t)bz * nrb + p) * N + t];
+      const float mn = fmaxf(m, m2);
+      l = l * exp2f(m - mn) + l2 * exp2f(m2 - mn);
+      m = mn;
+    }
+    col_max[(int64_t)bz * N + t] = m * LN2;
+    col_sum[(int64_t)bz * N + t] = l;
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                   uint32_t box_rows, uint32_t box_cols) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) return MM25_ERR_CUDA;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (cols * 2) % 16) return MM25_ERR_ALIGN;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {cols * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim,
+                   gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? MM25_OK : MM25_ERR_CUDA;
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+bool eligible_fwd(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode) {
+  return dtype == MM25_BF16 && mode == MM25_SIM_PLAIN && d % BK == 0 && d >= BK &&
+         d <= MAX_KC * BK && M % BM == 0 && N % BN == 0 && B * M < (1ll << 31) &&
+         B * N < (1ll << 31);
+}
+
+struct FwdGeom { int nrb, total_rb, ntiles, nseg, tps, grid; };
+
+static FwdGeom fwd_geom(int64_t B, int64_t M, int64_t N) {
+  FwdGeom g;
+  g.nrb = (int)(M / BM);
+  g.total_rb = (int)(B * g.nrb);
+  g.ntiles = (int)(N / BN);
+  const int sms = sm_count();
+  int best = 1;
+  double best_eff = 0.0;
+  const int max_seg = g.ntiles >= 8 ? g.ntiles / 4 : 1;
+  for (int ns = 1; ns <= max_seg && ns <= 64; ++ns) {
+    const int tps = (g.ntiles + ns - 1) / ns;
+    const int nseg = (g.ntiles + tps - 1) / tps;
+    const long items = (long)g.total_rb * nseg;
+    const double waves = (double)((items + sms - 1) / sms);
+    const double eff = (double)items / (waves * sms);
+    if (eff > best_eff + 0.01) { best_eff = eff; best = nseg; }
+  }
+  g.nseg = best;
+  g.tps = (g.ntiles + best - 1) / best;
+  g.nseg = (g.ntiles + g.tps - 1) / g.tps;
+  const long items = (long)g.total_rb * g.nseg;
+  g.grid = (int)(items < sms ? items : sms);
+  return g;
+}
+
+size_t fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d) {
+  FwdGeom g = fwd_geom(B, M, N);
+  return sizeof(float) * 2 * (size_t)B * ((size_t)g.nseg * M + (size_t)g.nrb * N);
+}
+
+static int g_force_slow = 0;  // test hook: exercise the robust epilogue path
+void set_force_slow(int v) { g_force_slow = v; }
+
+int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,
+               const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
+               float* row_lse, float* col_max, float* col_sum, float* diag, void* ws,
+               size_t ws_bytes, cudaStream_t st) {
+  if (!eligible_fwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)) return MM25_ERR_SHAPE;
+  if (ws_bytes < fwd_workspace_bytes(B, M, N, d)) return MM25_ERR_WORKSPACE;
+  FwdGeom g = fwd_geom(B, M, N);
+  CUtensorMap ta, tb;
+  int rc = make_tmap_bf16(&ta, a, (uint64_t)(B * M), (uint64_t)d, BM, BK);
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tb, b, (uint64_t)(B * N), (uint64_t)d, BN, BK);
+  if (rc) return rc;
+  float* row_pm = (float*)ws;
+  float* row_pl = row_pm + (size_t)B * g.nseg * M;
+  float* col_pm = row_pl + (size_t)B * g.nseg * M;
+  float* col_pl = col_pm + (size_t)B * g.nrb * N;
+  const size_t smem = sizeof(FwdSmem) + 1024;
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_fwd_tc_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  sim_fwd_tc_kernel<<<g.grid, FWD_THREADS, smem, st>>>(
+      ta, tb, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind, clamp_max,
+      diag_offset, row_pm, row_pl, col_pm, col_pl, diag, g_force_slow);
+  MM25_LAUNCH_CHECK();
+  const int64_t mx = M > N ? M : N;
+  fwd_tc_merge_kernel<<<dim3((unsigned)ceil_div(mx, 256), (unsigned)B), 256, 0, st>>>(
+      row_pm, row_pl, g.nseg, M, row_lse, col_pm, col_pl, g.nrb, N, col_max, col_sum);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
+// backward on tensor cores: part 2 (not yet wired; bf16 backward runs the SIMT kernels)
+bool eligible_bwd(int64_t, int64_t, int64_t, int64_t, int, int) { return false; }
+size_t bwd_workspace_bytes(int64_t, int64_t, int64_t, int64_t) { return 16; }
 int64_t bwd_nparts(int64_t, int64_t, int64_t, int64_t) { return 0; }
-int launch_bwd(const void*, const void*, int64_t, int64_t, int64_t, int64_t, const float*, int, float, int64_t, const float*, const float*, float, float, float, float, const float*, float*, float*, float*, void*, size_t, cudaStream_t) { return MM25_ERR_SHAPE; }
-}}
+int launch_bwd(const void*, const void*, int64_t, int64_t, int64_t, int64_t, const float*, int,
+               float, int64_t, const float*, const float*, float, float, float, float,
+               const float*, float*, float*, float*, void*, size_t, cudaStream_t) {
+  return MM25_ERR_SHAPE;
+}
+
+}  // namespace tc
+}  // namespace mm25
+
+extern "C" void mm25_debug_force_slow_epilogue(int v) { mm25::tc::set_force_slow(v); }

@@ -8,7 +8,8 @@ namespace mm25 {
 namespace tc {
 
 // PLAIN mode, bf16, d % 64 == 0 (64 <= d <= 1024), M % 128 == 0, N % 128 == 0.
-bool eligible(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode);
+bool eligible_fwd(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode);
+bool eligible_bwd(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode);
 
 size_t fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d);
 int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,

@@ -83,7 +83,7 @@ def main():
     # ---- CLIP forward_sampled (clipLoss.py:24-79) ------------------------------------------
     g = torch.Generator().manual_seed(11)
     xs = torch.randn(3, 80, 48, generator=g)
-    ys = xs + 0.7 * torch.randn(3, 80, 48, generator=g)
+    ys = xs + 2.5 * torch.randn(3, 80, 48, generator=g)
     out = {}
     for eps in (0.1, 0.0):
         m = clip_mod.ClipLoss(eps)

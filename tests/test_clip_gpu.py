@@ -48,7 +48,7 @@ def test_clip_fp32_vs_oracle_shapes(lib_built, n, d, seed, ls):
     ref, (rx, ry, rl) = O.loss_and_grads(O.clip_loss, [x, y, lsc], 0.1, True)
     m = ClipLoss(0.1).cuda()
     loss, (gx, gy, gl) = run_ours(lambda a, b, c: m(a, b, c), [x, y, lsc])
-    assert rel_err(loss, ref) < 1e-5
+    assert abs(float(loss) - float(ref)) <= 1e-5 * max(abs(float(ref)), 1e-3)
     if n > 1:
         assert rel_err(gx, rx) < 1e-4 and rel_err(gy, ry) < 1e-4
         assert abs(float(gl) - float(rl)) <= 1e-4 * max(abs(float(rl)), 1e-3)
