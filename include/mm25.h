@@ -54,6 +54,10 @@ enum {
 const char* mm25_version(void);
 /* cudaGetErrorString of the last failing CUDA call seen by this thread (static storage). */
 const char* mm25_last_cuda_error(void);
+/* number of kernels this library has launched in this process (all threads). */
+long long mm25_launch_count(void);
+/* test hook: non-zero forces the robust (two-exp) epilogue path of the tcgen05 forward. */
+void mm25_debug_force_slow_epilogue(int on);
 /* 1 if the current device is compute capability 10.x, else 0. */
 int mm25_device_ok(void);
 

@@ -83,6 +83,8 @@ SIGNATURES = {
     "mm25_version": (ctypes.c_char_p, []),
     "mm25_last_cuda_error": (ctypes.c_char_p, []),
     "mm25_device_ok": (_int, []),
+    "mm25_launch_count": (ctypes.c_longlong, []),
+    "mm25_debug_force_slow_epilogue": (None, [_int]),
     "mm25_rownorm_fwd": (_int, [_vp, _int, _vp, _int, _vp, _vp, _i64, _i64, _i64, _int, _f32, _vp]),
     "mm25_rownorm_bwd": (_int, [_vp, _vp, _int, _vp, _vp, _int, _i64, _i64, _i64, _int, _vp, _int,
                                 _vp]),

@@ -24,7 +24,12 @@ void set_last_error(cudaError_t e);
     }                                            \
   } while (0)
 
-#define MM25_LAUNCH_CHECK() MM25_CUDA_CHECK(cudaGetLastError())
+void count_launch();
+#define MM25_LAUNCH_CHECK()                 \
+  do {                                      \
+    ::mm25::count_launch();                 \
+    MM25_CUDA_CHECK(cudaGetLastError());    \
+  } while (0)
 
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }

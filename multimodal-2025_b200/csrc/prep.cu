@@ -3,10 +3,14 @@
 //   closed-form CLIP loss value.  One warp per embedding row, 16-byte vector accesses.
 #include "common.cuh"
 
+#include <atomic>
+
 namespace mm25 {
 
 static thread_local cudaError_t g_last_err = cudaSuccess;
 void set_last_error(cudaError_t e) { g_last_err = e; }
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 // ---------------------------------------------------------------------------------------
 // row normalise: x [rows, d] -> xhat (TO), inv_norm.  Replaces F.normalize (clipLoss.py:95-96)
@@ -152,6 +156,7 @@ using namespace mm25;
 
 extern "C" const char* mm25_version(void) { return "mm25 0.1 (sm_100a)"; }
 extern "C" const char* mm25_last_cuda_error(void) { return cudaGetErrorString(g_last_err); }
+extern "C" long long mm25_launch_count(void) { return g_launches.load(); }
 extern "C" int mm25_device_ok(void) {
   int dev = 0, major = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 0;
