@@ -1,0 +1,407 @@
+#!/usr/bin/env python
+"""bench.py — CLIP-loss fwd+bwd pairs/s at B=32k d=512 bf16 (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 32768]
+
+A "step" is one forward+backward of the contrastive loss over one synthetic batch of
+L2-normalised bf16 embeddings.  `value` is timed with CUDA events per step with
+inputs resident in HBM and an L2 flush before every step; `e2e` goes through the public
+ClipLoss module with HOST (pinned) inputs, H2D inside the timed region and a D2H read of the loss.
+`--impl reference` times the CPU restatement of the reference (oracle/) on the host cores, on a
+bounded slab of the same workload.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "CLIP-loss fwd+bwd pairs/s at B=32k d=512, 1/2/4/8 B200; % of bf16 TC peak"
+LOGIT_SCALE = 2.6592  # log(1/0.07), CLIP init
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=10)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--n", type=int, default=32768, help="global batch (pairs)")
+    p.add_argument("--d", type=int, default=512)
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--slab-rows", type=int, default=1024, help="rows of the CPU sample slab")
+    return p.parse_args()
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            pk = json.load(f)
+        return {"bf16_tflops": pk.get("bf16_tflops", 1590.0),
+                "bf16_tflops_sustained": pk.get("bf16_tflops_sustained", 1400.0),
+                "hbm_gbs": pk.get("hbm_gbs", 6650.0), "source": "measured"}
+    return {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "hbm_gbs": 6650.0,
+            "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.gpu = gpu_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx = float(f[2])
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        med = sm[len(sm) // 2] if sm else None
+        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU baseline: the oracle restatement (kind "port") on a bounded slab of the same workload
+# ------------------------------------------------------------------------------------------
+def cpu_slab_step(x, y, ls, rows, eps=0.1):
+    """fwd+bwd of the CLIP loss terms owned by `rows` image rows against ALL N texts:
+    logits slab [rows, N] (1/(N/rows) of the full N x N work, same per-pair work), row CE with
+    label smoothing for those rows + the slab's share of the column CE, then backward.
+    Follows oracle.losses_oracle.clip_loss (reference clipLoss.py:94-119) on the slab."""
+    import torch
+    import torch.nn.functional as F
+    xs = x[:rows].detach().clone().requires_grad_(True)
+    yy = y.detach().clone().requires_grad_(True)
+    lsp = ls.detach().clone().requires_grad_(True)
+    xn = F.normalize(xs, dim=-1, p=2)
+    yn = F.normalize(yy, dim=-1, p=2)
+    s = lsp.clamp(max=4.6052).exp()
+    z = s.float() * xn.float() @ yn.t().float()                    # [rows, N]
+    labels = torch.arange(rows)
+    loss_img = F.cross_entropy(z, labels, label_smoothing=eps)
+    col = torch.logsumexp(z, dim=0).mean() - z.diagonal().mean()   # slab share of the text CE
+    loss = 0.5 * (loss_img + col)
+    loss.backward()
+    return float(loss.detach())
+
+
+def time_cpu_slab(n, d, rows, reps, threads):
+    import torch
+    from oracle import losses_oracle as O
+    torch.set_num_threads(threads)
+    x, y = O.synth_embeddings(n, d, 1234)
+    ls = torch.tensor(LOGIT_SCALE)
+    cpu_slab_step(x, y, ls, min(rows, 256))  # warm-up (thread pool, allocator)
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        cpu_slab_step(x, y, ls, rows)
+        ts.append(time.perf_counter() - t0)
+    return ts
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm (oracle port) on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    rows = min(args.slab_rows, args.n)
+    ts = time_cpu_slab(args.n, args.d, rows, args.warmup + args.steps, threads)[args.warmup:]
+    t = sum(ts) / len(ts)
+    frac = rows / float(args.n)
+    value = rows / t   # pairs/s: a slab of `rows` pairs' rows costs rows/N of a full step
+    out = {
+        "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3 / frac,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "impl": "reference",
+        "config": {"workload": "CLIP InfoNCE fwd+bwd, global B=%d d=%d, label_smoothing 0.1"
+                               % (args.n, args.d), "global_batch": args.n, "dim": args.d},
+        "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": threads, "kind": "port",
+                         "sample": "slab of %d of %d image rows x all %d texts (%.4f of one "
+                                   "step), fp32, torch CPU" % (rows, args.n, args.n, frac)},
+        "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out))
+
+
+# ------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from oracle import losses_oracle as O
+    import multimodal_2025_b200 as pkg
+    from multimodal_2025_b200 import ops, _lib
+    from multimodal_2025_b200.losses import ClipLoss
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (our arm) needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = _lib.lib()
+    assert L.mm25_device_ok() == 1, "not an sm_100 device"
+
+    n, d = args.n, args.d
+    n_local = n // world
+    # synthetic inputs: seeded on CPU, normalised, cast to bf16 AFTER normalising
+    x32, y32 = O.synth_embeddings(n, d, 1234)
+    sl = slice(rank * n_local, (rank + 1) * n_local)
+    x_host = x32[sl].to(torch.bfloat16).contiguous().pin_memory()
+    y_host = y32[sl].to(torch.bfloat16).contiguous().pin_memory()
+    del x32, y32
+    x = x_host.to(dev).requires_grad_(True)
+    y = y_host.to(dev).requires_grad_(True)
+    ls = torch.tensor(LOGIT_SCALE, device=dev, requires_grad=True)
+
+    if world > 1:
+        from multimodal_2025_b200.dist import ShardedClipLoss
+        crit = ShardedClipLoss(0.1).to(dev)
+    else:
+        crit = ClipLoss(0.1).to(dev)
+
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step(xi, yi):
+        xi.grad = None
+        yi.grad = None
+        ls.grad = None
+        loss = crit(xi, yi, ls)
+        loss.backward()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        """k steps, each bracketed by CUDA events after an L2 flush; returns summed ms."""
+        evs = []
+        for _ in range(k):
+            flush.zero_()
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in evs)
+
+    for _ in range(args.warmup):
+        step(x, y)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    c0 = L.mm25_launch_count()
+    t_wall0 = time.perf_counter()
+    ms = timed(lambda: step(x, y), args.steps)
+    barrier()
+    wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    launches = (L.mm25_launch_count() - c0) // args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    loss_val = float(crit(x, y, ls).detach())
+
+    # ---- e2e: public API, host inputs, H2D + D2H inside the timed region -------------------
+    xd = torch.empty_like(x_host, device=dev)
+    yd = torch.empty_like(y_host, device=dev)
+    loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        xd.copy_(x_host, non_blocking=True)
+        yd.copy_(y_host, non_blocking=True)
+        xi = xd.detach().requires_grad_(True)
+        yi = yd.detach().requires_grad_(True)
+        loss = step(xi, yi)
+        loss_host.copy_(loss.detach(), non_blocking=True)
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    ms_e2e = timed(e2e_step, args.steps)
+    barrier()
+
+    tm = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(tm[0]), float(tm[1])
+    ms_step = ms / args.steps
+    value = n / (ms_step * 1e-3)
+    e2e_value = n / (ms_e2e / args.steps * 1e-3)
+    return dict(world=world, rank=rank, dev=dev, n=n, d=d, n_local=n_local, x=x, y=y, ls=ls,
+                ms_step=ms_step, value=value, e2e_value=e2e_value, launches=int(launches),
+                clocks=clocks, loss=loss_val, wall_ms=wall_ms, flush=flush, ops=ops,
+                h2d=int(x_host.numel() * 2 * 2), dist=dist)
+
+
+def kernel_roofline(r, args, peaks):
+    """Per-kernel timing of the two fused kernels (CUDA events on the launch stream, L2 flushed
+    before each launch) -> roofline object of the dominant one."""
+    import torch
+    ops = r["ops"]
+    x, y, ls, flush = r["x"], r["y"], r["ls"], r["flush"]
+    M, N, d = r["n_local"], r["n"], r["d"]
+    with torch.no_grad():
+        xh, _, _ = ops.rownorm_fwd(x.detach().unsqueeze(0), True, 1e-12, ops.BF16, False)
+        yh, _, _ = ops.rownorm_fwd(y.detach().unsqueeze(0), True, 1e-12, ops.BF16, False)
+        if N != M:  # sharded run: rank-local rectangular block [M, N]
+            yh = yh.repeat(1, N // M, 1).contiguous()
+        sc = ls.detach().reshape(1).float()
+        off = r["rank"] * M
+
+        def fwd():
+            return ops.sim_fwd(xh, yh, None, None, None, sc, ops.SCALE_LOG, 4.6052,
+                               ops.SIM_PLAIN, off, True, ops.IMPL_AUTO)
+
+        row_lse, cmax, csum, _ = fwd()
+        col_lse = ops.col_merge(cmax.reshape(1, -1), csum.reshape(1, -1)).reshape(1, -1)
+        nn_ = float(N)
+
+        def bwd():
+            return ops.sim_bwd(xh, yh, None, None, None, sc, ops.SCALE_LOG, 4.6052,
+                               ops.SIM_PLAIN, off, row_lse, col_lse, 0.5 / nn_, 0.5 / nn_,
+                               0.9 / nn_, 0.1 / (nn_ * nn_), None, True, True, False,
+                               ops.IMPL_AUTO)
+
+        def t(fn, k):
+            tot = 0.0
+            for _ in range(k):
+                flush.zero_()
+                e0 = torch.cuda.Event(enable_timing=True)
+                e1 = torch.cuda.Event(enable_timing=True)
+                e0.record()
+                fn()
+                e1.record()
+                torch.cuda.synchronize()
+                tot += e0.elapsed_time(e1)
+            return tot / k
+
+        k = max(3, min(args.steps, 10))
+        fwd(); bwd()
+        ms_f, ms_b = t(fwd, k), t(bwd, k)
+    fl_f, fl_b = 2.0 * M * N * d, 4.0 * M * N * d
+    tf_f, tf_b = fl_f / (ms_f * 1e-3) / 1e12, fl_b / (ms_b * 1e-3) / 1e12
+    peak = peaks["bf16_tflops"]
+    dom = ("sim_bwd", tf_b, ms_b, fl_b) if ms_b >= ms_f else ("sim_fwd", tf_f, ms_f, fl_f)
+    return {
+        "bound": "tensor", "kernel": dom[0], "achieved": dom[1], "peak": peak,
+        "unit": "TFLOP/s", "frac": dom[1] / peak, "traffic": None,
+        "peak_source": peaks["source"] + " bf16_tflops (burst: kernel timed alone)",
+        "ms_per_launch": dom[2], "algorithmic_flops_per_launch": dom[3],
+        "kernels": {"sim_fwd": {"ms": ms_f, "tflops": tf_f, "frac": tf_f / peak,
+                                "flops": fl_f},
+                    "sim_bwd": {"ms": ms_b, "tflops": tf_b, "frac": tf_b / peak,
+                                "flops": fl_b}},
+    }
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    peaks = load_peaks()
+    r = run_ours(args)
+    roof = kernel_roofline(r, args, peaks)
+    world, rank = r["world"], r["rank"]
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        rows = min(args.slab_rows, args.n)
+        ts = time_cpu_slab(args.n, args.d, rows, 3, threads)
+        tbest = min(ts)
+        cpu = {"value": rows / tbest, "unit": "pairs/s", "cores": threads, "kind": "port",
+               "sample": "slab of %d of %d image rows x all %d texts (%.4f of one step), fp32 "
+                         "torch CPU, best of 3" % (rows, args.n, args.n, rows / args.n)}
+    if world > 1:
+        r["dist"].barrier()
+    if rank == 0:
+        flops = 6.0 * r["n"] * r["n"] * r["d"]
+        tf = flops / (r["ms_step"] * 1e-3) / 1e12 / world
+        out = {
+            "metric": METRIC, "value": r["value"], "unit": "pairs/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_step"],
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "CLIP InfoNCE fwd+bwd, global B=%d d=%d bf16, "
+                                   "label_smoothing 0.1, logit_scale log(1/0.07)"
+                                   % (r["n"], r["d"]),
+                       "global_batch": r["n"], "dim": r["d"], "per_gpu_rows": r["n_local"],
+                       "parallelism": "row-sharded x%d" % world if world > 1 else "single GPU",
+                       "l2_flush_between_steps": True},
+            "step_tflops_per_gpu_algorithmic_6N2d": tf,
+            "step_frac_of_bf16_peak": tf / peaks["bf16_tflops_sustained"],
+            "step_peak": "%s bf16_tflops_sustained" % peaks["source"],
+            "loss": r["loss"],
+            "clocks": r["clocks"],
+            "e2e": {"value": r["e2e_value"], "unit": "pairs/s",
+                    "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": 4},
+            "gpu_launches": r["launches"],
+            "roofline": roof,
+        }
+        if cpu is not None:
+            out["cpu_baseline"] = cpu
+        print(json.dumps(out))
+    if world > 1:
+        r["dist"].destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
