@@ -58,6 +58,12 @@ const char* mm25_last_cuda_error(void);
 long long mm25_launch_count(void);
 /* test hook: non-zero forces the robust (two-exp) epilogue path of the tcgen05 forward. */
 void mm25_debug_force_slow_epilogue(int on);
+/* test hook: cap (bytes) of the bf16 gradient panel of the tensor-core backward; 0 = default. */
+void mm25_debug_set_g_panel_bytes(size_t bytes);
+/* test hook: C[Mg,Ng] fp32 (+)= alpha * op(A) op(B) with the tcgen05 GEMM of the backward;
+ * a_mn / b_mn = 1 when the bf16 operand is stored [K, M] / [K, N] instead of [M, K] / [N, K]. */
+int mm25_debug_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, float* C, int64_t Mg,
+                         int64_t Ng, int64_t K, float alpha, int accumulate, void* stream);
 /* 1 if the current device is compute capability 10.x, else 0. */
 int mm25_device_ok(void);
 

@@ -16,7 +16,7 @@ LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libmm25.so")
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 
-SOURCES = ["prep.cu", "sim_simt.cu", "sim_tc.cu", "api_sim.cu", "hopfield.cu", "samplers.cu",
+SOURCES = ["prep.cu", "sim_simt.cu", "sim_tc.cu", "sim_tc_bwd.cu", "gemm_tc.cu", "api_sim.cu", "hopfield.cu", "samplers.cu",
            "topk.cu"]
 
 _lock = threading.Lock()
@@ -85,6 +85,8 @@ SIGNATURES = {
     "mm25_device_ok": (_int, []),
     "mm25_launch_count": (ctypes.c_longlong, []),
     "mm25_debug_force_slow_epilogue": (None, [_int]),
+    "mm25_debug_set_g_panel_bytes": (None, [_sz]),
+    "mm25_debug_gemm_bf16": (_int, [_vp, _int, _vp, _int, _vp, _i64, _i64, _i64, _f32, _int, _vp]),
     "mm25_rownorm_fwd": (_int, [_vp, _int, _vp, _int, _vp, _vp, _i64, _i64, _i64, _int, _f32, _vp]),
     "mm25_rownorm_bwd": (_int, [_vp, _vp, _int, _vp, _vp, _int, _i64, _i64, _i64, _int, _vp, _int,
                                 _vp]),

@@ -80,7 +80,7 @@ extern "C" size_t mm25_sim_bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, 
 extern "C" int64_t mm25_sim_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
                                        int impl) {
   int err;
-  int64_t n = simt::bwd_nparts(B, M);
+  int64_t n = simt::bwd_nparts(B, M > N ? M : N);
   if (use_tc(true, impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err)) {
     int64_t t = tc::bwd_nparts(B, M, N, d);
     if (t > n) n = t;

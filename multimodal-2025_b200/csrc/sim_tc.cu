@@ -5,34 +5,13 @@
 // Forward (this file, part 1): persistent CTAs; a work item is (128-row block, column segment).
 // The A row block stays resident in shared memory for the whole item, B tiles stream through a
 // 4-stage ring, 4 TMEM accumulator stages decouple the MMA warp from the 4 epilogue warps.
-#include "tc_common.cuh"
+#include "sim_tc_sweep.cuh"
 #include "sim_tc.h"
 
 #include <mutex>
 
 namespace mm25 {
 namespace tc {
-
-constexpr int BM = 128, BN = 128, BK = 64;
-constexpr int MAX_KC = 8;            // d <= 512 keeps the A block resident (128 KB)
-constexpr int NST = 4;               // B ring stages (16 KB each)
-constexpr int NACC = 4;              // TMEM accumulator stages (128 columns each)
-constexpr int CHUNK_BYTES = BM * BK * 2;  // 16384
-constexpr int FWD_THREADS = 192;     // warp0 TMA, warp1 MMA, warps 2-5 epilogue
-constexpr float LOG2E = 1.4426950408889634f;
-constexpr float LN2 = 0.6931471805599453f;
-constexpr float SPREAD_LIMIT = 96.f;  // log2 units: larger in-block spread takes the slow path
-
-struct FwdSmem {
-  uint8_t a[MAX_KC * CHUNK_BYTES];
-  uint8_t b[NST * CHUNK_BYTES];
-  float colm[2][4][BN];
-  float cols[2][4][BN];
-  uint64_t a_full, a_empty;
-  uint64_t b_full[NST], b_empty[NST];
-  uint64_t acc_full[NACC], acc_empty[NACC];
-  uint32_t tmem_base;
-};
 
 // sum over the 32 lanes of e[j] for every j: afterwards lane j holds column j in e[0]
 __device__ __forceinline__ float butterfly_colsum(float (&e)[32], int lane) {
@@ -61,87 +40,18 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
   FwdSmem& sm = *reinterpret_cast<FwdSmem*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int KC = d / BK;
   const int ntiles = (int)(N / BN);
   const int nitems = total_rb * nseg;
-
-  if (threadIdx.x == 0) {
-    mbar_init(&sm.a_full, 1);
-    mbar_init(&sm.a_empty, 1);
-    for (int i = 0; i < NST; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
-    for (int i = 0; i < NACC; ++i) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_empty[i], 4); }
-    fence_barrier_init();
-  }
-  if (warp == 0) {
-    tmem_alloc(&sm.tmem_base, 512);
-    if (lane == 0) { tma_prefetch_desc(&tmap_a); tma_prefetch_desc(&tmap_b); }
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
+  Sweep w;
+  w.KC = d / BK; w.ntiles = ntiles; w.nseg = nseg; w.tps = tps;
+  w.nrb_per_batch = nrb_per_batch; w.first_rbg = 0; w.num_rbg = total_rb; w.N = N;
+  sweep_setup(sm, &tmap_a, &tmap_b);
   const uint32_t tmem = sm.tmem_base;
 
   if (warp == 0) {
-    // ===================================================================== TMA producer
-    if (lane == 0) {
-      uint32_t bst = 0, bph = 0, aph = 0;
-      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-        const int rbg = item / nseg, seg = item % nseg;
-        const int bz = rbg / nrb_per_batch;
-        const int64_t arow = (int64_t)rbg * BM;  // row in the flattened [B*M, d] matrix
-        mbar_wait(&sm.a_empty, aph ^ 1);
-        aph ^= 1;
-        mbar_arrive_expect_tx(&sm.a_full, (uint32_t)(KC * CHUNK_BYTES));
-        for (int kc = 0; kc < KC; ++kc)
-          tma_load_2d(sm.a + kc * CHUNK_BYTES, &tmap_a, &sm.a_full, kc * BK, (int32_t)arow);
-        const int t0 = seg * tps, t1 = min(ntiles, t0 + tps);
-        for (int t = t0; t < t1; ++t) {
-          const int64_t brow = (int64_t)bz * N + (int64_t)t * BN;
-          for (int kc = 0; kc < KC; ++kc) {
-            mbar_wait(&sm.b_empty[bst], bph ^ 1);
-            mbar_arrive_expect_tx(&sm.b_full[bst], CHUNK_BYTES);
-            tma_load_2d(sm.b + bst * CHUNK_BYTES, &tmap_b, &sm.b_full[bst], kc * BK,
-                        (int32_t)brow);
-            if (++bst == NST) { bst = 0; bph ^= 1; }
-          }
-        }
-      }
-    }
+    if (lane == 0) sweep_producer(sm, &tmap_a, &tmap_b, w);
   } else if (warp == 1) {
-    // ===================================================================== MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 0, 0);
-      uint32_t bst = 0, bph = 0, aph = 0, as = 0, accph = 0;
-      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-        const int seg = item % nseg;
-        mbar_wait(&sm.a_full, aph);
-        aph ^= 1;
-        tc_fence_after();
-        const int t0 = seg * tps, t1 = min(ntiles, t0 + tps);
-        for (int t = t0; t < t1; ++t) {
-          mbar_wait(&sm.acc_empty[as], accph ^ 1);
-          tc_fence_after();
-          const uint32_t dcol = tmem + as * BN;
-          for (int kc = 0; kc < KC; ++kc) {
-            mbar_wait(&sm.b_full[bst], bph);
-            tc_fence_after();
-            const uint32_t abase = smem_u32(sm.a + kc * CHUNK_BYTES);
-            const uint32_t bbase = smem_u32(sm.b + bst * CHUNK_BYTES);
-#pragma unroll
-            for (int k = 0; k < BK / 16; ++k) {
-              const uint64_t ad = make_smem_desc(abase + k * 32, 16, 1024);
-              const uint64_t bd = make_smem_desc(bbase + k * 32, 16, 1024);
-              umma_bf16(dcol, ad, bd, idesc, (kc | k) != 0);
-            }
-            umma_commit(&sm.b_empty[bst]);
-            if (++bst == NST) { bst = 0; bph ^= 1; }
-          }
-          umma_commit(&sm.acc_full[as]);
-          if (++as == NACC) { as = 0; accph ^= 1; }
-        }
-        umma_commit(&sm.a_empty);
-      }
-    }
+    if (lane == 0) sweep_mma(sm, tmem, w);
   } else {
     // ===================================================================== epilogue warps
     const int q = warp & 3;        // TMEM lane quadrant this warp may read
@@ -400,15 +310,8 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   return MM25_OK;
 }
 
-// backward on tensor cores: part 2 (not yet wired; bf16 backward runs the SIMT kernels)
-bool eligible_bwd(int64_t, int64_t, int64_t, int64_t, int, int) { return false; }
-size_t bwd_workspace_bytes(int64_t, int64_t, int64_t, int64_t) { return 16; }
-int64_t bwd_nparts(int64_t, int64_t, int64_t, int64_t) { return 0; }
-int launch_bwd(const void*, const void*, int64_t, int64_t, int64_t, int64_t, const float*, int,
-               float, int64_t, const float*, const float*, float, float, float, float,
-               const float*, float*, float*, float*, void*, size_t, cudaStream_t) {
-  return MM25_ERR_SHAPE;
-}
+// shared with sim_tc_bwd.cu
+int tc_sm_count() { return sm_count(); }
 
 }  // namespace tc
 }  // namespace mm25

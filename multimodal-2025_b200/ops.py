@@ -138,7 +138,7 @@ def sim_bwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
         da = torch.empty((B, M, d) if need_da else (0,), dtype=torch.float32, device=dev)
         db = torch.empty((B, N, d) if need_db else (0,), dtype=torch.float32, device=dev)
         ddiag = torch.zeros((B, M) if need_ddiag else (0,), dtype=torch.float32, device=dev)
-        nparts = int(L.mm25_sim_bwd_nparts(B, max(M, N), max(M, N), d, _dt(a), impl))
+        nparts = int(L.mm25_sim_bwd_nparts(B, M, N, d, _dt(a), impl))
         parts = torch.zeros((max(nparts, 1),), dtype=torch.float32, device=dev)
         dscale = torch.empty((1,), dtype=torch.float32, device=dev)
         wsb = L.mm25_sim_bwd_workspace_bytes(B, M, N, d, _dt(a), impl)

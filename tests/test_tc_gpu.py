@@ -73,3 +73,26 @@ def test_tc_matches_simt_on_adversarial_range(lib_built):
     c_si = out_si[1] + out_si[2].log()
     assert torch.isfinite(c_tc).all()
     assert (c_tc - c_si).abs().max() < 2e-3
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1), (1, 0)])
+@pytest.mark.parametrize("Mg,Ng,K,acc", [(128, 256, 64, 0), (256, 512, 1024, 0), (512, 256, 320, 1)])
+def test_tc_gemm_layouts(lib_built, a_mn, b_mn, Mg, Ng, K, acc):
+    """the bf16 tcgen05 GEMM of the backward, all four operand-major combinations."""
+    from multimodal_2025_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator(device="cpu").manual_seed(Mg + K)
+    A = torch.randn(Mg, K, generator=g).cuda().bfloat16()
+    B = torch.randn(Ng, K, generator=g).cuda().bfloat16()
+    ref = 0.5 * (A.float() @ B.float().t())
+    C = torch.full((Mg, Ng), 1.0, device="cuda")
+    if acc:
+        ref = ref + 1.0
+    Am = A.t().contiguous() if a_mn else A.contiguous()
+    Bm = B.t().contiguous() if b_mn else B.contiguous()
+    rc = L.mm25_debug_gemm_bf16(Am.data_ptr(), a_mn, Bm.data_ptr(), b_mn, C.data_ptr(), Mg, Ng,
+                                K, 0.5, acc, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    err = (C - ref).abs().max().item()
+    assert err < 1e-2 * max(1.0, ref.abs().max().item() / 10), err
