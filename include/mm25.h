@@ -73,8 +73,11 @@ int mm25_device_ok(void);
  *   x      [B, M, d] dtype       (B = batch of independent problems, stride M*d)
  *   xhat   [B, M, d] out_dtype   x / max(||x||, eps)   (or a plain cast when normalize == 0)
  *   inv_norm [B, M]  fp32        1 / max(||x||, eps)   (1.0 when normalize == 0)
- *   colsum [B, d]    fp32        sum_i xhat_i  — must be zeroed by the caller; may be NULL
+ *   colsum           fp32        sum_i xhat_i in its first [B, d] floats; the buffer must hold
+ *                                mm25_rownorm_colsum_floats(B, M, d) floats (result + partials
+ *                                of the deterministic two-stage reduction); may be NULL
  * ------------------------------------------------------------------------------------------ */
+int64_t mm25_rownorm_colsum_floats(int64_t B, int64_t M, int64_t d);
 int mm25_rownorm_fwd(const void* x, int dtype, void* xhat, int out_dtype, float* inv_norm,
                      float* colsum, int64_t B, int64_t M, int64_t d, int normalize, float eps,
                      void* stream);

@@ -61,6 +61,60 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x,
   }
 }
 
+// stage 1 of the fast column sum: each CTA owns a strided set of rows, warps accumulate 16-byte
+// vectors in registers, fixed-order cross-warp sum -> partial [B][P][d]; stage 2 = colsum_kernel
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_part_kernel(const T* __restrict__ x,
+                                                          float* __restrict__ part, int64_t M,
+                                                          int d) {
+  constexpr int VW = 16 / sizeof(T);
+  extern __shared__ float red[];  // [8][d]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int P = gridDim.x;
+  const T* xb = x + (int64_t)blockIdx.y * M * d;
+  const int niter = d / (32 * VW);
+  float acc[64];
+#pragma unroll
+  for (int i = 0; i < 64; ++i) acc[i] = 0.f;
+  for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < M; r += (int64_t)P * 8) {
+    const T* xr = xb + r * d;
+#pragma unroll
+    for (int it = 0; it < 64 / VW; ++it) {
+      if (it < niter) {
+        const uint4 raw = *reinterpret_cast<const uint4*>(xr + (it * 32 + lane) * VW);
+        if constexpr (sizeof(T) == 4) {
+          acc[it * 4 + 0] += __uint_as_float(raw.x); acc[it * 4 + 1] += __uint_as_float(raw.y);
+          acc[it * 4 + 2] += __uint_as_float(raw.z); acc[it * 4 + 3] += __uint_as_float(raw.w);
+        } else {
+          const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            acc[it * 8 + 2 * u] += __uint_as_float(w[u] << 16);
+            acc[it * 8 + 2 * u + 1] += __uint_as_float(w[u] & 0xffff0000u);
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < 64 / VW; ++it)
+    if (it < niter)
+#pragma unroll
+      for (int u = 0; u < VW; ++u) red[warp * d + (it * 32 + lane) * VW + u] = acc[it * VW + u];
+  __syncthreads();
+  for (int c = threadIdx.x; c < d; c += 256) {
+    float sacc = 0.f;
+#pragma unroll
+    for (int w8 = 0; w8 < 8; ++w8) sacc += red[w8 * d + c];
+    part[((int64_t)blockIdx.y * P + blockIdx.x) * d + c] = sacc;
+  }
+}
+
+static int colsum_parts(int64_t M) {
+  int64_t p = (M + 7) / 8;
+  return (int)(p > 256 ? 256 : (p < 1 ? 1 : p));
+}
+
 // dx = inv * (g - xhat (xhat . g))   (backward of F.normalize away from the eps clamp)
 template <typename TH, typename TO>
 __global__ void __launch_bounds__(256) rownorm_bwd_kernel(const float* __restrict__ g,
@@ -115,35 +169,45 @@ __global__ void __launch_bounds__(256) col_merge_kernel(const float* __restrict_
   col_lse[j] = m + logf(l);
 }
 
-// one CTA per batch entry; fixed-order tree reduction -> deterministic
-__global__ void __launch_bounds__(256) clip_finalize_kernel(
+// one CTA (1024 threads) per batch entry; fixed-order tree reduction -> deterministic
+constexpr int FIN_T = 1024;
+__global__ void __launch_bounds__(FIN_T) clip_finalize_kernel(
     const float* __restrict__ row_lse, const float* __restrict__ diag,
     const float* __restrict__ col_lse, const float* __restrict__ sx,
     const float* __restrict__ sy, int64_t M, int64_t N, int d, int64_t n_norm,
     const float* __restrict__ scale, int scale_kind, float clamp_max, float eps_ls,
     float* __restrict__ loss) {
-  __shared__ double red[256];
+  __shared__ double red[FIN_T];
   const int b = blockIdx.x;
   row_lse += (int64_t)b * M;
   diag += (int64_t)b * M;
-  double acc = 0.0;
   const double nn = (double)n_norm;
-  for (int64_t i = threadIdx.x; i < M; i += 256)
-    acc += (double)row_lse[i] / (2.0 * nn) - (1.0 - (double)eps_ls) / nn * (double)diag[i];
+  const double wr = 1.0 / (2.0 * nn), wd = (1.0 - (double)eps_ls) / nn;
+  double acc0 = 0.0, acc1 = 0.0;
+  for (int64_t i = threadIdx.x; i < M; i += 2 * FIN_T) {
+    acc0 += (double)row_lse[i] * wr - wd * (double)diag[i];
+    const int64_t i2 = i + FIN_T;
+    if (i2 < M) acc1 += (double)row_lse[i2] * wr - wd * (double)diag[i2];
+  }
   if (col_lse) {
     col_lse += (int64_t)b * N;
-    for (int64_t j = threadIdx.x; j < N; j += 256) acc += (double)col_lse[j] / (2.0 * nn);
+    for (int64_t j = threadIdx.x; j < N; j += 2 * FIN_T) {
+      acc0 += (double)col_lse[j] * wr;
+      const int64_t j2 = j + FIN_T;
+      if (j2 < N) acc1 += (double)col_lse[j2] * wr;
+    }
   }
+  double acc = acc0 + acc1;
   if (eps_ls != 0.f && sx && sy) {
     const float s = load_scale(scale, scale_kind, clamp_max);
     double dot = 0.0;
-    for (int k = threadIdx.x; k < d; k += 256)
+    for (int k = threadIdx.x; k < d; k += FIN_T)
       dot += (double)sx[(int64_t)b * d + k] * (double)sy[(int64_t)b * d + k];
     acc -= (double)eps_ls / (nn * nn) * (double)s * dot;
   }
   red[threadIdx.x] = acc;
   __syncthreads();
-  for (int s = 128; s > 0; s >>= 1) {
+  for (int s = FIN_T / 2; s > 0; s >>= 1) {
     if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
     __syncthreads();
   }
@@ -165,6 +229,10 @@ extern "C" int mm25_device_ok(void) {
   return major == 10;
 }
 
+extern "C" int64_t mm25_rownorm_colsum_floats(int64_t B, int64_t M, int64_t d) {
+  return B * d * (1 + (int64_t)colsum_parts(M));
+}
+
 extern "C" int mm25_rownorm_fwd(const void* x, int dtype, void* xhat, int out_dtype,
                                 float* inv_norm, float* colsum, int64_t B, int64_t M, int64_t d,
                                 int normalize, float eps, void* stream) {
@@ -184,12 +252,27 @@ extern "C" int mm25_rownorm_fwd(const void* x, int dtype, void* xhat, int out_dt
 #undef RN
   MM25_LAUNCH_CHECK();
   if (colsum) {
+    const int vw = out_dtype == MM25_F32 ? 4 : 8;
     dim3 g2((unsigned)ceil_div(d, 32), (unsigned)B);
-    if (out_dtype == MM25_F32)
+    if (d % (32 * vw) == 0 && d <= 2048 && M >= 64) {
+      // two-stage: partials live behind the [B, d] result inside the caller's buffer
+      const int P = colsum_parts(M);
+      float* part = colsum + B * d;
+      dim3 g1((unsigned)P, (unsigned)B);
+      const size_t sh = sizeof(float) * 8 * (size_t)d;
+      if (out_dtype == MM25_F32)
+        colsum_part_kernel<float><<<g1, 256, sh, st>>>((const float*)xhat, part, M, (int)d);
+      else
+        colsum_part_kernel<__nv_bfloat16><<<g1, 256, sh, st>>>((const __nv_bfloat16*)xhat, part,
+                                                               M, (int)d);
+      MM25_LAUNCH_CHECK();
+      colsum_kernel<float><<<g2, 256, 0, st>>>(part, colsum, P, (int)d);
+    } else if (out_dtype == MM25_F32) {
       colsum_kernel<float><<<g2, 256, 0, st>>>((const float*)xhat, colsum, M, (int)d);
-    else
+    } else {
       colsum_kernel<__nv_bfloat16><<<g2, 256, 0, st>>>((const __nv_bfloat16*)xhat, colsum, M,
                                                       (int)d);
+    }
     MM25_LAUNCH_CHECK();
   }
   return MM25_OK;
@@ -242,7 +325,7 @@ extern "C" int mm25_clip_loss_finalize(const float* row_lse, const float* diag,
                                        void* stream) {
   if (!row_lse || !diag || !loss || B <= 0 || M <= 0) return MM25_ERR_ARG;
   if (eps_ls != 0.f && (!sx || !sy || !scale)) return MM25_ERR_ARG;
-  clip_finalize_kernel<<<(unsigned)B, 256, 0, (cudaStream_t)stream>>>(
+  clip_finalize_kernel<<<(unsigned)B, FIN_T, 0, (cudaStream_t)stream>>>(
       row_lse, diag, col_lse, sx, sy, M, N, (int)d, n_norm, scale, scale_kind, clamp_max,
       eps_ls, loss);
   MM25_LAUNCH_CHECK();

@@ -55,7 +55,8 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
   } else {
     // ===================================================================== epilogue warps
     const int q = warp & 3;        // TMEM lane quadrant this warp may read
-    const int ew = warp - 2;       // 0..3, staging slot
+    const int ew = warp - 2;       // 0..7
+    const int half = ew >> 2;      // which half of the tile's columns this warp handles
     const float s = load_scale(scale, scale_kind, clamp_max);
     const float c2 = s * LOG2E;
     uint32_t as = 0, accph = 0, buf = 0;
@@ -71,7 +72,7 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         mbar_wait(&sm.acc_full[as], accph);
         tc_fence_after();
 #pragma unroll 1
-        for (int ch = 0; ch < BN / 32; ++ch) {
+        for (int ch = half * 2; ch < half * 2 + 2; ++ch) {
           float v[32];
           tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + as * BN + ch * 32, v);
           const int64_t cbase = col0 + ch * 32;
@@ -120,8 +121,8 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
             }
           }
           const float cs = butterfly_colsum(e, lane);
-          sm.colm[buf][ew][ch * 32 + lane] = cm;
-          sm.cols[buf][ew][ch * 32 + lane] = cs;
+          sm.colm[buf][q][ch * 32 + lane] = cm;
+          sm.cols[buf][q][ch * 32 + lane] = cs;
         }
         // all TMEM reads of this stage are complete (wait::ld inside the load helper)
         tc_fence_before();
@@ -129,8 +130,8 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         if (lane == 0) mbar_arrive(&sm.acc_empty[as]);
         if (++as == NACC) { as = 0; accph ^= 1; }
         // merge the four 32-row groups of this tile; warp ew owns columns [32 ew, 32 ew + 32)
-        named_bar_sync(1, 128);
-        {
+        named_bar_sync(1, 32 * NEPI);
+        if (ew < 4) {
           const int c = ew * 32 + lane;
           float m = sm.colm[buf][0][c], l = sm.cols[buf][0][c];
 #pragma unroll
@@ -146,7 +147,7 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
         buf ^= 1;
       }
-      const int64_t o = ((int64_t)bz * nseg + seg) * M + row;
+      const int64_t o = ((int64_t)bz * nseg * 2 + seg * 2 + half) * M + row;
       row_pm[o] = rm;
       row_pl[o] = rl;
     }
@@ -157,39 +158,53 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
   if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
-// partials are in log2-scaled units: value = 2^m * l
+// partials are in log2-scaled units: value = 2^m * l.  Block = 32 elements x 8 partial lanes;
+// lane k merges partials k, k+8, ... in order, then the 8 lanes are merged in order.
+__device__ __forceinline__ void lse2_merge(float& m, float& l, float m2, float l2) {
+  const float mn = fmaxf(m, m2);
+  if (mn == -INFINITY) return;
+  l = l * exp2f(m - mn) + l2 * exp2f(m2 - mn);
+  m = mn;
+}
+
 __global__ void __launch_bounds__(256) fwd_tc_merge_kernel(
     const float* __restrict__ row_pm, const float* __restrict__ row_pl, int nseg, int64_t M,
     float* __restrict__ row_lse, const float* __restrict__ col_pm,
     const float* __restrict__ col_pl, int nrb, int64_t N, float* __restrict__ col_max,
     float* __restrict__ col_sum) {
+  __shared__ float sm_m[8][33], sm_l[8][33];
   const int bz = blockIdx.y;
-  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (t < M) {
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t t = (int64_t)blockIdx.x * 32 + tx;
+  {
     float m = -INFINITY, l = 0.f;
-    for (int p = 0; p < nseg; ++p) {
-      const float m2 = row_pm[((int64_t)bz * nseg + p) * M + t];
-      const float l2 = row_pl[((int64_t)bz * nseg + p) * M + t];
-      const float mn = fmaxf(m, m2);
-      l = l * exp2f(m - mn) + l2 * exp2f(m2 - mn);
-      m = mn;
+    if (t < M)
+      for (int p = ty; p < nseg; p += 8)
+        lse2_merge(m, l, row_pm[((int64_t)bz * nseg + p) * M + t],
+                   row_pl[((int64_t)bz * nseg + p) * M + t]);
+    sm_m[ty][tx] = m; sm_l[ty][tx] = l;
+    __syncthreads();
+    if (ty == 0 && t < M) {
+      for (int k = 1; k < 8; ++k) lse2_merge(m, l, sm_m[k][tx], sm_l[k][tx]);
+      row_lse[(int64_t)bz * M + t] = (m + log2f(l)) * LN2;
     }
-    row_lse[(int64_t)bz * M + t] = (m + log2f(l)) * LN2;
+    __syncthreads();
   }
-  if (col_max && t < N) {
+  if (col_max) {
     float m = -INFINITY, l = 0.f;
-    for (int p = 0; p < nrb; ++p) {
-      const float m2 = col_pm[((int64_t)bz * nrb + p) * N + t];
-      const float l2 = col_pl[((int64_t)bz * nrb + p) * N + t];
-      const float mn = fmaxf(m, m2);
-      l = l * exp2f(m - mn) + l2 * exp2f(m2 - mn);
-      m = mn;
+    if (t < N)
+      for (int p = ty; p < nrb; p += 8)
+        lse2_merge(m, l, col_pm[((int64_t)bz * nrb + p) * N + t],
+                   col_pl[((int64_t)bz * nrb + p) * N + t]);
+    sm_m[ty][tx] = m; sm_l[ty][tx] = l;
+    __syncthreads();
+    if (ty == 0 && t < N) {
+      for (int k = 1; k < 8; ++k) lse2_merge(m, l, sm_m[k][tx], sm_l[k][tx]);
+      col_max[(int64_t)bz * N + t] = m * LN2;
+      col_sum[(int64_t)bz * N + t] = l;
     }
-    col_max[(int64_t)bz * N + t] = m * LN2;
-    col_sum[(int64_t)bz * N + t] = l;
   }
 }
-
 
 // ------------------------------------------------------------------------------------------
 // host side
@@ -274,7 +289,7 @@ static FwdGeom fwd_geom(int64_t B, int64_t M, int64_t N) {
 
 size_t fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d) {
   FwdGeom g = fwd_geom(B, M, N);
-  return sizeof(float) * 2 * (size_t)B * ((size_t)g.nseg * M + (size_t)g.nrb * N);
+  return sizeof(float) * 2 * (size_t)B * ((size_t)g.nseg * 2 * M + (size_t)g.nrb * N);
 }
 
 static int g_force_slow = 0;  // test hook: exercise the robust epilogue path
@@ -293,8 +308,8 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   rc = make_tmap_bf16(&tb, b, (uint64_t)(B * N), (uint64_t)d, BN, BK);
   if (rc) return rc;
   float* row_pm = (float*)ws;
-  float* row_pl = row_pm + (size_t)B * g.nseg * M;
-  float* col_pm = row_pl + (size_t)B * g.nseg * M;
+  float* row_pl = row_pm + (size_t)B * g.nseg * 2 * M;
+  float* col_pm = row_pl + (size_t)B * g.nseg * 2 * M;
   float* col_pl = col_pm + (size_t)B * g.nrb * N;
   const size_t smem = sizeof(FwdSmem) + 1024;
   MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_fwd_tc_kernel,
@@ -304,8 +319,8 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
       diag_offset, row_pm, row_pl, col_pm, col_pl, diag, g_force_slow);
   MM25_LAUNCH_CHECK();
   const int64_t mx = M > N ? M : N;
-  fwd_tc_merge_kernel<<<dim3((unsigned)ceil_div(mx, 256), (unsigned)B), 256, 0, st>>>(
-      row_pm, row_pl, g.nseg, M, row_lse, col_pm, col_pl, g.nrb, N, col_max, col_sum);
+  fwd_tc_merge_kernel<<<dim3((unsigned)ceil_div(mx, 32), (unsigned)B), 256, 0, st>>>(
+      row_pm, row_pl, g.nseg * 2, M, row_lse, col_pm, col_pl, g.nrb, N, col_max, col_sum);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

@@ -44,6 +44,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (lane == 0) sweep_mma(sm, tmem, w);
   } else {
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
     const float s = load_scale(scale, scale_kind, clamp_max);
     const float c2 = s * LOG2E;
     const float go = gout ? __ldg(gout) : 1.f;
@@ -62,7 +63,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         mbar_wait(&sm.acc_full[as], accph);
         tc_fence_after();
 #pragma unroll 1
-        for (int ch = 0; ch < BN / 32; ++ch) {
+        for (int ch = half * 2; ch < half * 2 + 2; ++ch) {
           float v[32];
           tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + as * BN + ch * 32, v);
           const int64_t cbase = col0 + ch * 32;
@@ -104,10 +105,13 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // d(loss)/d(scale) partial of this CTA: sum G.z/s = sum G.v (times the upstream gradient)
     ds = warp_sum(ds) * go;
     if (lane == 0) sm.colm[0][0][warp - 2] = ds;
-    named_bar_sync(1, 128);
-    if (warp == 2 && lane == 0 && dscale_part)
-      dscale_part[blockIdx.x] = sm.colm[0][0][0] + sm.colm[0][0][1] + sm.colm[0][0][2] +
-                                sm.colm[0][0][3];
+    named_bar_sync(1, 32 * NEPI);
+    if (warp == 2 && lane == 0 && dscale_part) {
+      float tot = 0.f;
+#pragma unroll
+      for (int k = 0; k < NEPI; ++k) tot += sm.colm[0][0][k];
+      dscale_part[blockIdx.x] = tot;
+    }
   }
   tc_fence_before();
   __syncthreads();

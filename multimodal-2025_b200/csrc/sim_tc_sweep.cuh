@@ -12,7 +12,8 @@ constexpr int MAX_KC = 8;            // d <= 512 keeps the A block resident (128
 constexpr int NST = 4;               // B ring stages (16 KB each)
 constexpr int NACC = 4;              // TMEM accumulator stages (128 columns each)
 constexpr int CHUNK_BYTES = BM * BK * 2;  // 16384
-constexpr int FWD_THREADS = 192;     // warp0 TMA, warp1 MMA, warps 2-5 epilogue
+constexpr int NEPI = 8;              // epilogue warps: 2 per SM sub-partition
+constexpr int FWD_THREADS = 64 + 32 * NEPI;  // warp0 TMA, warp1 MMA, warps 2.. epilogue
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 constexpr float SPREAD_LIMIT = 96.f;  // log2 units: larger in-block spread takes the slow path
@@ -42,7 +43,7 @@ __device__ __forceinline__ void sweep_setup(FwdSmem& sm, const CUtensorMap* ta,
     mbar_init(&sm.a_full, 1);
     mbar_init(&sm.a_empty, 1);
     for (int i = 0; i < NST; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
-    for (int i = 0; i < NACC; ++i) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_empty[i], 4); }
+    for (int i = 0; i < NACC; ++i) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_empty[i], NEPI); }
     fence_barrier_init();
   }
   if (warp == 0) {

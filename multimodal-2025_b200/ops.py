@@ -62,12 +62,13 @@ def rownorm_fwd(x: Tensor, normalize: bool, eps: float, out_dtype: int,
     with torch.cuda.device(x.device):
         xhat = torch.empty((B, M, d), dtype=_tdt(out_dtype), device=x.device)
         inv = torch.empty((B, M), dtype=torch.float32, device=x.device)
-        cs = torch.empty((B, d) if want_colsum else (0,), dtype=torch.float32, device=x.device)
+        ncs = int(_lib.lib().mm25_rownorm_colsum_floats(B, M, d)) if want_colsum else 0
+        cs = torch.empty((ncs,), dtype=torch.float32, device=x.device)
         rc = _lib.lib().mm25_rownorm_fwd(_p(x), _dt(x), _p(xhat), out_dtype, _p(inv),
                                          _p(cs) if want_colsum else None, B, M, d,
                                          int(normalize), eps, _stream(x))
     _lib.check(rc, "mm25_rownorm_fwd")
-    return xhat, inv, cs
+    return xhat, inv, (cs[:B * d].reshape(B, d).clone() if want_colsum else cs)
 
 
 @torch.library.custom_op("mm25::rownorm_bwd", mutates_args=(), device_types="cuda")
