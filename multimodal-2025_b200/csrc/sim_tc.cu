@@ -72,7 +72,7 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         mbar_wait(&sm.acc_full[as], accph);
         tc_fence_after();
 #pragma unroll 1
-        for (int ch = half * 2; ch < half * 2 + 2; ++ch) {
+        for (int ch = half * CH_PER_WARP; ch < (half + 1) * CH_PER_WARP; ++ch) {
           float v[32];
           tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + as * BN + ch * 32, v);
           const int64_t cbase = col0 + ch * 32;
@@ -131,8 +131,8 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         if (++as == NACC) { as = 0; accph ^= 1; }
         // merge the four 32-row groups of this tile; warp ew owns columns [32 ew, 32 ew + 32)
         named_bar_sync(1, 32 * NEPI);
-        if (ew < 4) {
-          const int c = ew * 32 + lane;
+        {
+          const int c = ew * 32 + lane;   // 8 warps x 32 lanes = the tile's 256 columns
           float m = sm.colm[buf][0][c], l = sm.cols[buf][0][c];
 #pragma unroll
           for (int g = 1; g < 4; ++g) {
@@ -256,7 +256,7 @@ static int sm_count() {
 
 bool eligible_fwd(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode) {
   return dtype == MM25_BF16 && mode == MM25_SIM_PLAIN && d % BK == 0 && d >= BK &&
-         d <= MAX_KC * BK && M % BM == 0 && N % BN == 0 && B * M < (1ll << 31) &&
+         d <= MAX_KC * BK && M % BM == 0 && N % BN == 0 && NEPI * 32 == BN && B * M < (1ll << 31) &&
          B * N < (1ll << 31);
 }
 

@@ -63,7 +63,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         mbar_wait(&sm.acc_full[as], accph);
         tc_fence_after();
 #pragma unroll 1
-        for (int ch = half * 2; ch < half * 2 + 2; ++ch) {
+        for (int ch = half * CH_PER_WARP; ch < (half + 1) * CH_PER_WARP; ++ch) {
           float v[32];
           tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + as * BN + ch * 32, v);
           const int64_t cbase = col0 + ch * 32;

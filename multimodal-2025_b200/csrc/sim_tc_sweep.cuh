@@ -1,34 +1,37 @@
-// sim_tc_sweep.cuh — shared pieces of the "row block resident, column tiles streaming" tcgen05
-// kernels (forward statistics kernel and backward G-panel kernel): tile constants, shared-memory
-// layout, the TMA producer loop and the MMA issuer loop.
+// sim_tc_sweep.cuh — shared pieces of the S-tile sweep kernels (forward statistics kernel and
+// backward G-panel kernel): tile constants, shared-memory layout, the TMA producer loop and the
+// MMA issuer loop.  A work item is (128-row block, column segment); every 128 x 256 S tile is a
+// K-loop over d in 64-wide chunks, A and B chunks streamed together through a 4-stage ring
+// (192 KB in flight: the v1 kernel with a resident A block and 16 KB B stages was bound by
+// prefetch depth and by 128-wide UMMA operand bandwidth, profiles/r1_v1_ncu_summary.md).
 #pragma once
 #include "tc_common.cuh"
 
 namespace mm25 {
 namespace tc {
 
-constexpr int BM = 128, BN = 128, BK = 64;
-constexpr int MAX_KC = 8;            // d <= 512 keeps the A block resident (128 KB)
-constexpr int NST = 4;               // B ring stages (16 KB each)
-constexpr int NACC = 4;              // TMEM accumulator stages (128 columns each)
-constexpr int CHUNK_BYTES = BM * BK * 2;  // 16384
+constexpr int BM = 128, BN = 256, BK = 64;
+constexpr int MAX_KC = 16;           // d <= 1024
+constexpr int NST = 4;               // ring stages (A 16 KB + B 32 KB each)
+constexpr int NACC = 2;              // TMEM accumulator stages (256 columns each)
+constexpr int A_BYTES = BM * BK * 2;  // 16384
+constexpr int B_BYTES = BN * BK * 2;  // 32768
 constexpr int NEPI = 8;              // epilogue warps: 2 per SM sub-partition
 constexpr int FWD_THREADS = 64 + 32 * NEPI;  // warp0 TMA, warp1 MMA, warps 2.. epilogue
+constexpr int CH_PER_WARP = BN / 32 / 2;     // 32-column chunks each epilogue warp handles
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 constexpr float SPREAD_LIMIT = 96.f;  // log2 units: larger in-block spread takes the slow path
 
 struct FwdSmem {
-  uint8_t a[MAX_KC * CHUNK_BYTES];
-  uint8_t b[NST * CHUNK_BYTES];
+  uint8_t a[NST][A_BYTES];
+  uint8_t b[NST][B_BYTES];
   float colm[2][4][BN];
   float cols[2][4][BN];
-  uint64_t a_full, a_empty;
-  uint64_t b_full[NST], b_empty[NST];
+  uint64_t full[NST], empty[NST];
   uint64_t acc_full[NACC], acc_empty[NACC];
   uint32_t tmem_base;
 };
-
 
 // work decomposition: items = (row block, column segment); row blocks [first_rbg, first_rbg+num_rbg)
 struct Sweep {
@@ -40,9 +43,7 @@ __device__ __forceinline__ void sweep_setup(FwdSmem& sm, const CUtensorMap* ta,
                                             const CUtensorMap* tb) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    mbar_init(&sm.a_full, 1);
-    mbar_init(&sm.a_empty, 1);
-    for (int i = 0; i < NST; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
+    for (int i = 0; i < NST; ++i) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 1); }
     for (int i = 0; i < NACC; ++i) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_empty[i], NEPI); }
     fence_barrier_init();
   }
@@ -58,25 +59,21 @@ __device__ __forceinline__ void sweep_setup(FwdSmem& sm, const CUtensorMap* ta,
 // one elected thread of warp 0
 __device__ __forceinline__ void sweep_producer(FwdSmem& sm, const CUtensorMap* ta,
                                                const CUtensorMap* tb, const Sweep& w) {
-  uint32_t bst = 0, bph = 0, aph = 0;
+  uint32_t st = 0, ph = 0;
   const int nitems = w.num_rbg * w.nseg;
   for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
     const int rbg = w.first_rbg + item / w.nseg, seg = item % w.nseg;
     const int bz = rbg / w.nrb_per_batch;
-    const int64_t arow = (int64_t)rbg * BM;  // row in the flattened [B*M, d] matrix
-    mbar_wait(&sm.a_empty, aph ^ 1);
-    aph ^= 1;
-    mbar_arrive_expect_tx(&sm.a_full, (uint32_t)(w.KC * CHUNK_BYTES));
-    for (int kc = 0; kc < w.KC; ++kc)
-      tma_load_2d(sm.a + kc * CHUNK_BYTES, ta, &sm.a_full, kc * BK, (int32_t)arow);
+    const int32_t arow = (int32_t)((int64_t)rbg * BM);  // row in the flattened [B*M, d] matrix
     const int t0 = seg * w.tps, t1 = min(w.ntiles, t0 + w.tps);
     for (int t = t0; t < t1; ++t) {
-      const int64_t brow = (int64_t)bz * w.N + (int64_t)t * BN;
+      const int32_t brow = (int32_t)((int64_t)bz * w.N + (int64_t)t * BN);
       for (int kc = 0; kc < w.KC; ++kc) {
-        mbar_wait(&sm.b_empty[bst], bph ^ 1);
-        mbar_arrive_expect_tx(&sm.b_full[bst], CHUNK_BYTES);
-        tma_load_2d(sm.b + bst * CHUNK_BYTES, tb, &sm.b_full[bst], kc * BK, (int32_t)brow);
-        if (++bst == NST) { bst = 0; bph ^= 1; }
+        mbar_wait(&sm.empty[st], ph ^ 1);
+        mbar_arrive_expect_tx(&sm.full[st], A_BYTES + B_BYTES);
+        tma_load_2d(sm.a[st], ta, &sm.full[st], kc * BK, arow);
+        tma_load_2d(sm.b[st], tb, &sm.full[st], kc * BK, brow);
+        if (++st == NST) { st = 0; ph ^= 1; }
       }
     }
   }
@@ -85,36 +82,32 @@ __device__ __forceinline__ void sweep_producer(FwdSmem& sm, const CUtensorMap* t
 // one elected thread of warp 1
 __device__ __forceinline__ void sweep_mma(FwdSmem& sm, uint32_t tmem, const Sweep& w) {
   constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 0, 0);
-  uint32_t bst = 0, bph = 0, aph = 0, as = 0, accph = 0;
+  uint32_t st = 0, ph = 0, as = 0, accph = 0;
   const int nitems = w.num_rbg * w.nseg;
   for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
     const int seg = item % w.nseg;
-    mbar_wait(&sm.a_full, aph);
-    aph ^= 1;
-    tc_fence_after();
     const int t0 = seg * w.tps, t1 = min(w.ntiles, t0 + w.tps);
     for (int t = t0; t < t1; ++t) {
       mbar_wait(&sm.acc_empty[as], accph ^ 1);
       tc_fence_after();
       const uint32_t dcol = tmem + as * BN;
       for (int kc = 0; kc < w.KC; ++kc) {
-        mbar_wait(&sm.b_full[bst], bph);
+        mbar_wait(&sm.full[st], ph);
         tc_fence_after();
-        const uint32_t abase = smem_u32(sm.a + kc * CHUNK_BYTES);
-        const uint32_t bbase = smem_u32(sm.b + bst * CHUNK_BYTES);
+        const uint32_t abase = smem_u32(sm.a[st]);
+        const uint32_t bbase = smem_u32(sm.b[st]);
 #pragma unroll
         for (int k = 0; k < BK / 16; ++k) {
           const uint64_t ad = make_smem_desc(abase + k * 32, 16, 1024);
           const uint64_t bd = make_smem_desc(bbase + k * 32, 16, 1024);
           umma_bf16(dcol, ad, bd, idesc, (kc | k) != 0);
         }
-        umma_commit(&sm.b_empty[bst]);
-        if (++bst == NST) { bst = 0; bph ^= 1; }
+        umma_commit(&sm.empty[st]);
+        if (++st == NST) { st = 0; ph ^= 1; }
       }
       umma_commit(&sm.acc_full[as]);
       if (++as == NACC) { as = 0; accph ^= 1; }
     }
-    umma_commit(&sm.a_empty);
   }
 }
 

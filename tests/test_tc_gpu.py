@@ -28,10 +28,10 @@ def make(B, M, N, d, seed, spread=1.0):
 
 
 @pytest.mark.parametrize("B,M,N,d,off,ls,force_slow", [
-    (1, 128, 128, 64, 0, 2.0, 0),
+    (1, 128, 256, 64, 0, 2.0, 0),
     (1, 256, 256, 512, 0, 2.6592, 0),
     (1, 1024, 1024, 512, 0, 4.6052, 0),
-    (2, 256, 384, 128, 128, 3.0, 0),
+    (2, 256, 512, 128, 128, 3.0, 0),
     (1, 512, 2048, 256, 1024, 4.6052, 0),
     (1, 256, 256, 512, 0, 4.6052, 1),
     (3, 128, 256, 64, 0, 1.0, 1),
