@@ -1,0 +1,158 @@
+"""Row-sharded CLIP loss across the GPUs of one NVSwitch box (one process per GPU, NCCL).
+
+The reference has no working multi-process path; its semantic precedent is
+`gather_features(..., gather_with_grad=True)` + `local_loss=False` in
+AlignCLIP/align_clip/loss.py:20-64,103-114.  Algorithm:
+
+  forward   rank r owns rows [r n, (r+1) n) of both modalities (n = N / P)
+            1. local row-normalise; all-reduce the [d] column sums (label-smoothing term)
+            2. all-gather Yhat (bf16/fp32, N d elements in total)
+            3. fused kernel on the local block [n, N]: complete row LSE, per-column partial
+               (max, sum) over the local rows, positives at column offset r n (loss.py:94-95)
+            4. all-gather the [N] column partials, merge in fixed rank order (deterministic)
+            5. all-reduce the scalar partial losses
+  backward  recompute the local block; dXhat_local is complete locally; the partial
+            dYhat_all [N, d] is reduce-scattered (sum) so each rank receives its own rows;
+            d(scale) is all-reduced.
+
+The returned loss is the GLOBAL loss (identical on every rank) and the gradients are those of
+the global loss w.r.t. the local shards (times the upstream gradient, assumed equal on all
+ranks) — what `gather_with_grad=True, local_loss=False` computes divided by P.  `grad_scale`
+multiplies them (set it to P to reproduce open_clip's sum-over-ranks convention).
+
+Kernels are reached through `backend` (default: multimodal_2025_b200.ops, CUDA only); tests
+inject a CPU stand-in to exercise the collective logic under gloo.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+_EPS_NORM = 1e-12
+
+
+def _all_gather_cat(t: torch.Tensor, group) -> torch.Tensor:
+    """[n, ...] per rank -> [P n, ...] (rank order)."""
+    world = dist.get_world_size(group)
+    t = t.contiguous()
+    out = torch.empty((world * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    if dist.get_backend(group) == "gloo":
+        parts = list(out.chunk(world, dim=0))
+        dist.all_gather(parts, t, group=group)
+    else:
+        dist.all_gather_into_tensor(out, t, group=group)
+    return out
+
+
+def _reduce_scatter_sum(t: torch.Tensor, group) -> torch.Tensor:
+    """[P n, ...] per rank -> sum over ranks of the local [n, ...] slice."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    t = t.contiguous()
+    n = t.shape[0] // world
+    if dist.get_backend(group) == "gloo":  # gloo has no reduce_scatter
+        dist.all_reduce(t, group=group)
+        return t[rank * n:(rank + 1) * n].clone()
+    out = torch.empty((n,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    dist.reduce_scatter_tensor(out, t, group=group)
+    return out
+
+
+class _ShardedClipFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, img, txt, logits_scale, eps_ls, normalize, clamp_max, group, backend,
+                grad_scale, impl):
+        B = backend
+        world = dist.get_world_size(group)
+        rank = dist.get_rank(group)
+        in_dtype = img.dtype
+        if in_dtype not in (torch.float32, torch.bfloat16):
+            img, txt = img.float(), txt.float()
+        if txt.dtype != img.dtype:
+            txt = txt.to(img.dtype)
+        cdt = B.BF16 if img.dtype == torch.bfloat16 else B.F32
+        n, d = img.shape
+        N = n * world
+        want_cs = eps_ls != 0.0
+        xhat, invx, sx = B.rownorm_fwd(img.unsqueeze(0), normalize, _EPS_NORM, cdt, want_cs)
+        yhat, invy, sy = B.rownorm_fwd(txt.unsqueeze(0), normalize, _EPS_NORM, cdt, want_cs)
+        scale32 = logits_scale.detach().reshape(1).to(torch.float32).contiguous()
+        # (2) all-gather the other modality
+        yall = _all_gather_cat(yhat[0], group).unsqueeze(0)
+        # (3) local block
+        row_lse, cmax, csum, diag = B.sim_fwd(xhat, yall, None, None, None, scale32,
+                                              B.SCALE_LOG, clamp_max, B.SIM_PLAIN, rank * n,
+                                              True, impl)
+        # (4) column statistics: gather partials, merge in rank order
+        stats = _all_gather_cat(torch.stack([cmax[0], csum[0]], 0).unsqueeze(0), group)
+        col_lse = B.col_merge(stats[:, 0].contiguous(), stats[:, 1].contiguous())  # [N]
+        # (5) scalar pieces
+        part = B.clip_loss_finalize(row_lse, diag, col_lse[rank * n:(rank + 1) * n]
+                                    .reshape(1, n).contiguous(), None, None, N, scale32,
+                                    B.SCALE_LOG, clamp_max, eps_ls)
+        red = part.reshape(1).clone()
+        if want_cs:
+            svec = torch.cat([sx.reshape(-1), sy.reshape(-1)])
+            dist.all_reduce(svec, group=group)
+            sxg, syg = svec[:d], svec[d:]
+        dist.all_reduce(red, group=group)
+        loss = red.reshape(())
+        if want_cs:
+            s = scale32.clamp(max=clamp_max).exp().reshape(())
+            loss = loss - (eps_ls / float(N) ** 2) * s * (sxg * syg).sum()
+        ctx.save_for_backward(xhat, yhat, yall, invx, invy, row_lse, col_lse, scale32,
+                              logits_scale)
+        ctx.cfg = (eps_ls, normalize, clamp_max, group, backend, grad_scale, impl, in_dtype,
+                   rank, n, N)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        (xhat, yhat, yall, invx, invy, row_lse, col_lse, scale32,
+         logits_scale) = ctx.saved_tensors
+        (eps_ls, normalize, clamp_max, group, B, grad_scale, impl, in_dtype, rank, n,
+         N) = ctx.cfg
+        nn_ = float(N)
+        g = (gout.detach().to(torch.float32).reshape(1) * grad_scale).contiguous()
+        da, db, dscale, _ = B.sim_bwd(xhat, yall, None, None, None, scale32, B.SCALE_LOG,
+                                      clamp_max, B.SIM_PLAIN, rank * n, row_lse,
+                                      col_lse.reshape(1, N), 0.5 / nn_, 0.5 / nn_,
+                                      (1.0 - eps_ls) / nn_, eps_ls / (nn_ * nn_), g, True, True,
+                                      False, impl)
+        dy_local = _reduce_scatter_sum(db[0], group).unsqueeze(0)
+        out_dt = B.BF16 if in_dtype == torch.bfloat16 else B.F32
+        dimg = B.rownorm_bwd(da, xhat, invx, normalize, out_dt, None)[0].to(in_dtype)
+        dtxt = B.rownorm_bwd(dy_local, yhat, invy, normalize, out_dt, None)[0].to(in_dtype)
+        dls = None
+        if ctx.needs_input_grad[2]:
+            dist.all_reduce(dscale, group=group)
+            dls = B.scale_param_grad(dscale, logits_scale, B.SCALE_LOG, clamp_max)
+        return dimg, dtxt, dls, None, None, None, None, None, None, None
+
+
+class ShardedClipLoss(nn.Module):
+    """ClipLoss (reference losses/clipLoss.py:81-121) with the batch row-sharded over a process
+    group: every rank passes its LOCAL [n, d] image and text shards (same n on all ranks) and
+    receives the loss of the GLOBAL batch of P n pairs."""
+
+    def __init__(self, label_smoothing: float = 0.1, group=None, grad_scale: float = 1.0,
+                 backend=None):
+        super().__init__()
+        self.label_smoothing = label_smoothing
+        self.register_buffer("smoothing", torch.tensor(self.label_smoothing))
+        self.group = group
+        self.grad_scale = grad_scale
+        self.backend = backend
+        self.impl = 0
+
+    def forward(self, image_features, text_features, logits_scale, normalize=True):
+        backend = self.backend
+        if backend is None:
+            from . import ops as backend
+        group = self.group if self.group is not None else dist.group.WORLD
+        if not torch.is_tensor(logits_scale):
+            logits_scale = torch.tensor(float(logits_scale), device=image_features.device)
+        return _ShardedClipFn.apply(image_features, text_features, logits_scale,
+                                    float(self.label_smoothing), bool(normalize), 4.6052, group,
+                                    backend, float(self.grad_scale), int(self.impl))

@@ -1,0 +1,82 @@
+"""TEST INFRASTRUCTURE: a dense torch-CPU stand-in for `multimodal_2025_b200.ops`, used only to
+exercise the collective / merge logic of dist.ShardedClipLoss under gloo (no GPU in CI).
+It restates each op's contract (include/mm25.h) with materialised logits."""
+import torch
+
+F32, BF16 = 0, 1
+SIM_PLAIN, SIM_MASKDIAG, SIM_MODULATED = 0, 1, 2
+SCALE_MUL, SCALE_LOG = 0, 1
+
+
+def _s(scale, kind, clamp):
+    return scale.clamp(max=clamp).exp() if kind == SCALE_LOG else scale
+
+
+def rownorm_fwd(x, normalize, eps, out_dtype, want_colsum):
+    xf = x.float()
+    inv = 1.0 / xf.norm(dim=-1).clamp_min(eps) if normalize else torch.ones(x.shape[:2])
+    xhat = (xf * inv.unsqueeze(-1)).to(torch.float32 if out_dtype == F32 else torch.bfloat16)
+    cs = xhat.float().sum(dim=1) if want_colsum else torch.empty(0)
+    return xhat, inv, cs
+
+
+def sim_fwd(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offset, want_cols,
+            impl):
+    z = _s(scale, scale_kind, clamp_max) * (a.float() @ b.float().transpose(1, 2))
+    M = a.shape[1]
+    idx = torch.arange(M)
+    diag = z[:, idx, idx + diag_offset]
+    cmax = z.max(dim=1).values
+    csum = (z - cmax.unsqueeze(1)).exp().sum(dim=1)
+    return torch.logsumexp(z, dim=2), cmax, csum, diag
+
+
+def col_merge(col_max, col_sum):
+    m = col_max.max(dim=0).values
+    return m + (col_sum * (col_max - m).exp()).sum(dim=0).log()
+
+
+def clip_loss_finalize(row_lse, diag, col_lse, sx, sy, n_norm, scale, scale_kind, clamp_max,
+                       eps_ls):
+    n = float(n_norm)
+    out = row_lse.double().sum(1) / (2 * n) - (1 - eps_ls) / n * diag.double().sum(1)
+    if col_lse is not None:
+        out = out + col_lse.double().sum(1) / (2 * n)
+    if eps_ls != 0 and sx is not None:
+        out = out - eps_ls / n ** 2 * _s(scale, scale_kind, clamp_max).double() * \
+            (sx.double() * sy.double()).sum(1)
+    return out.float()
+
+
+def sim_bwd(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offset, row_lse,
+            col_lse, w_row, w_col, w_diag, w_all, gout, need_da, need_db, need_ddiag, impl):
+    s = _s(scale, scale_kind, clamp_max)
+    dot = a.float() @ b.float().transpose(1, 2)
+    z = s * dot
+    G = w_row * (z - row_lse.unsqueeze(2)).exp() + w_col * (z - col_lse.unsqueeze(1)).exp() - w_all
+    M = a.shape[1]
+    idx = torch.arange(M)
+    G[:, idx, idx + diag_offset] -= w_diag
+    go = gout.reshape(-1, 1, 1) if gout is not None else 1.0
+    G = G * go
+    da = s * (G @ b.float())
+    db = s * (G.transpose(1, 2) @ a.float())
+    dscale = (G * dot).sum().reshape(1)
+    return da, db, dscale, torch.empty(0)
+
+
+def rownorm_bwd(g, xhat, inv_norm, normalize, out_dtype, gscale):
+    h = xhat.float()
+    if normalize:
+        dx = (g - h * (h * g).sum(-1, keepdim=True)) * inv_norm.unsqueeze(-1)
+    else:
+        dx = g
+    return dx.to(torch.float32 if out_dtype == F32 else torch.bfloat16)
+
+
+def scale_param_grad(dscale, scale, scale_kind, clamp_max):
+    if scale_kind == SCALE_MUL:
+        return dscale.reshape(scale.shape)
+    l = scale.detach().float()
+    return (dscale.reshape(()) * torch.where(l <= clamp_max, l.exp(), torch.zeros_like(l))
+            ).reshape(scale.shape)

@@ -1,0 +1,50 @@
+"""Launched by test_dist_gpu.py under torch.distributed.run: sharded CLIP loss over NCCL vs the
+CPU oracle on the full batch (rank 0 prints OK / FAIL)."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"])
+    lr = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dev = torch.device("cuda", lr)
+    dist.init_process_group("nccl", device_id=dev)
+    from multimodal_2025_b200.dist import ShardedClipLoss
+    from oracle import losses_oracle as O
+    ok = True
+    for dtype, n, d, tl, tg in ((torch.float32, 96, 64, 1e-5, 1e-4),
+                                (torch.bfloat16, 512, 512, 2e-3, 2e-2)):
+        N = n * world
+        x, y = O.synth_embeddings(N, d, 11, correlated=True, dtype=dtype)
+        ls = torch.tensor(3.0)
+        ref, (rx, ry, rl) = O.loss_and_grads(O.clip_loss, [x.float(), y.float(), ls], 0.1, True)
+        sl = slice(rank * n, (rank + 1) * n)
+        xl = x[sl].to(dev).requires_grad_(True)
+        yl = y[sl].to(dev).requires_grad_(True)
+        lp = ls.to(dev).requires_grad_(True)
+        loss = ShardedClipLoss(0.1).to(dev)(xl, yl, lp)
+        loss.backward()
+        torch.cuda.synchronize()
+        el = abs(float(loss) - float(ref)) / abs(float(ref))
+        egx = float((xl.grad.float().cpu() - rx[sl]).norm() / rx[sl].norm())
+        egy = float((yl.grad.float().cpu() - ry[sl]).norm() / ry[sl].norm())
+        egl = abs(float(lp.grad) - float(rl)) / abs(float(rl))
+        good = el < tl and egx < tg and egy < tg and egl < tg
+        print("rank %d %s N=%d loss_rel=%.2e gx=%.2e gy=%.2e gl=%.2e %s" %
+              (rank, dtype, N, el, egx, egy, egl, "OK" if good else "FAIL"), flush=True)
+        ok = ok and good
+    t = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    dist.destroy_process_group()
+    sys.exit(0 if int(t) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,72 @@
+"""CPU, world_size 2 over gloo: the sharded-loss collective logic (all-gather, column-partial
+merge, reduce-scatter, scalar all-reduces) against the single-process oracle."""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import ROOT
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q, eps, n, d, ls):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import cpu_backend
+        from multimodal_2025_b200.dist import ShardedClipLoss
+        from oracle import losses_oracle as O
+        x, y = O.synth_embeddings(n * world, d, 7, correlated=True)
+        x = x * 1.7  # exercise the normalise backward
+        sl = slice(rank * n, (rank + 1) * n)
+        xl = x[sl].clone().requires_grad_(True)
+        yl = y[sl].clone().requires_grad_(True)
+        lsp = torch.tensor(ls, requires_grad=True)
+        crit = ShardedClipLoss(eps, backend=cpu_backend)
+        loss = crit(xl, yl, lsp)
+        (2.0 * loss).backward()
+        q.put((rank, float(loss.detach()), xl.grad.clone(), yl.grad.clone(), float(lsp.grad)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("eps,ls", [(0.1, 2.6592), (0.0, 5.0)])
+def test_sharded_clip_world2_gloo(eps, ls):
+    from oracle import losses_oracle as O
+    world, n, d = 2, 48, 32
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, eps, n, d, ls))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    x, y = O.synth_embeddings(n * world, d, 7, correlated=True)
+    x = x * 1.7
+    ref, (rx, ry, rl) = O.loss_and_grads(lambda a, b, c: 2.0 * O.clip_loss(a, b, c, eps, True),
+                                         [x, y, torch.tensor(ls)])
+    for rank, loss, gx, gy, gl in res:
+        assert abs(2.0 * loss - float(ref)) < 1e-5 * abs(float(ref))
+        sl = slice(rank * n, (rank + 1) * n)
+        assert (gx - rx[sl]).norm() < 1e-4 * rx[sl].norm()
+        assert (gy - ry[sl]).norm() < 1e-4 * ry[sl].norm()
+        assert abs(gl - float(rl)) <= 1e-4 * max(abs(float(rl)), 1e-6)
