@@ -152,7 +152,8 @@ int mm25_col_merge(const float* col_max, const float* col_sum, int64_t P, int64_
  * CLIP loss value from statistics (clipLoss.py:116-119 in closed form):
  *   L_b = (sum_i r_i + sum_j c_j) / (2 N) - (1-eps)/N sum_i z_ii - eps/N^2 * s * (sx . sy)
  * row_lse,diag [B,M_total]; col_lse [B,N]; sx, sy [B,d] column sums of xhat / yhat (may be
- * NULL when eps == 0).  loss [B].  `n_norm` = global batch N used in the means.
+ * NULL when eps == 0, or to leave
+ * the smoothing dot term to the caller as the sharded loss does).  loss [B].  `n_norm` = global batch N used in the means.
  * ------------------------------------------------------------------------------------------ */
 int mm25_clip_loss_finalize(const float* row_lse, const float* diag, const float* col_lse,
                             const float* sx, const float* sy, int64_t B, int64_t M, int64_t N,

@@ -324,7 +324,8 @@ extern "C" int mm25_clip_loss_finalize(const float* row_lse, const float* diag,
                                        float clamp_max, float eps_ls, float* loss,
                                        void* stream) {
   if (!row_lse || !diag || !loss || B <= 0 || M <= 0) return MM25_ERR_ARG;
-  if (eps_ls != 0.f && (!sx || !sy || !scale)) return MM25_ERR_ARG;
+  if ((sx == nullptr) != (sy == nullptr)) return MM25_ERR_ARG;
+  if (eps_ls != 0.f && sx && !scale) return MM25_ERR_ARG;
   clip_finalize_kernel<<<(unsigned)B, FIN_T, 0, (cudaStream_t)stream>>>(
       row_lse, diag, col_lse, sx, sy, M, N, (int)d, n_norm, scale, scale_kind, clamp_max,
       eps_ls, loss);
