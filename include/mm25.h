@@ -160,6 +160,22 @@ int mm25_clip_loss_finalize(const float* row_lse, const float* diag, const float
                             int64_t d, int64_t n_norm, const float* scale, int scale_kind,
                             float clamp_max, float eps_ls, float* loss, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * CLOOB Hopfield retrieval, backward (cloobLoss.py:43-47; forward = mm25_sim_fwd row LSE +
+ * the row pass of mm25_sim_bwd with w_row = 1 + mm25_rownorm_fwd).  All fp32.
+ *   out[rows, d] = sum_cols G1 bm1[cols] (+ G2 bm2[cols]),
+ *   p = exp(beta a.b - lse[q]),  G1 = beta p (a2.b2 - D[q]),  G2 = p,
+ *   q = row (stat_by_col = 0) or column (stat_by_col = 1) of the [M, N] tile grid.
+ * dQ: a=Q b=K a2=dO b2=K bm1=K bm2=NULL stat_by_col=0;  dK: a=K b=Q a2=K b2=dO bm1=Q bm2=dO, 1.
+ * mm25_rowdot: out[i] = x_i . y_i  (D_q = dO_q . O_q).
+ * ------------------------------------------------------------------------------------------ */
+int mm25_rowdot(const float* x, const float* y, float* out, int64_t rows, int64_t d,
+                void* stream);
+int mm25_hopfield_bwd_pass(const float* a, const float* b, const float* a2, const float* b2,
+                           const float* bm1, const float* bm2, int64_t M, int64_t N, int64_t d,
+                           float beta, const float* lse, const float* D, int stat_by_col,
+                           float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(NT) sim_bwd_kernel(
   const int dchunk = blockIdx.x, rb = blockIdx.y, bz = blockIdx.z;
   a += (int64_t)bz * M * d;
   b += (int64_t)bz * N * d;
-  row_lse += (int64_t)bz * M;
+  if (row_lse) row_lse += (int64_t)bz * M;
   if (col_lse) col_lse += (int64_t)bz * N;
   if (MODE == MM25_SIM_MODULATED) {
     u += (int64_t)bz * M * d2;
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(NT) sim_bwd_kernel(
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int64_t row = row0 + ty * 4 + i;
-    rl[i] = row < M ? row_lse[row] : 0.f;
+    rl[i] = (row_lse && row < M) ? row_lse[row] : 0.f;
   }
 
   for (int jb = 0; jb < njb; ++jb) {

@@ -1,0 +1,136 @@
+"""Drop-in for the reference `losses/cloobLoss.py` (CLOOB: Hopfield retrieval + InfoLOOB,
+https://arxiv.org/pdf/2110.11316).  Same free functions and `CLOOBLoss(inv_tau, scale_hopfield,
+device)` module; nothing N x N is materialised:
+
+  hopfield(Q, K, beta)   = rownorm( softmax_rows(beta Q K^T) K )^T      (cloobLoss.py:43-47)
+  infoloob_loss(x, y, .) = -mean_i k_ii + mean_i LSE_j k'_ij,  k = inv_tau x y^T,
+                           k'_ii = -10000                                (cloobLoss.py:24-32)
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from .. import ops
+
+
+def _scalar(v, dev):
+    return torch.tensor([float(v)], dtype=torch.float32, device=dev)
+
+
+class _HopfieldFn(torch.autograd.Function):
+    """U[Nq, d] = rownorm(softmax(beta Q K^T) K)."""
+
+    @staticmethod
+    def forward(ctx, q, k, beta):
+        in_dtype = q.dtype
+        qf = q.detach().float().contiguous()
+        kf = k.detach().float().contiguous()
+        sc = _scalar(beta, q.device)
+        q3, k3 = qf.unsqueeze(0), kf.unsqueeze(0)
+        lse, _, _, _ = ops.sim_fwd(q3, k3, None, None, None, sc, ops.SCALE_MUL, 0.0,
+                                   ops.SIM_PLAIN, 0, False, ops.IMPL_SIMT)
+        # softmax-weighted sum = row pass with G = exp(z - lse); the kernel returns beta * O
+        o, _, _, _ = ops.sim_bwd(q3, k3, None, None, None, sc, ops.SCALE_MUL, 0.0,
+                                 ops.SIM_PLAIN, 0, lse, None, 1.0, 0.0, 0.0, 0.0, None, True,
+                                 False, False, ops.IMPL_SIMT)
+        o = o / float(beta)
+        u, inv, _ = ops.rownorm_fwd(o, True, 1e-30, ops.F32, False)
+        ctx.save_for_backward(qf, kf, o[0], u[0], inv, lse[0])
+        ctx.beta = float(beta)
+        ctx.in_dtype = in_dtype
+        return u[0].to(in_dtype)
+
+    @staticmethod
+    def backward(ctx, du):
+        qf, kf, o, u, inv, lse = ctx.saved_tensors
+        beta = ctx.beta
+        du = du.detach().float().contiguous()
+        do = ops.rownorm_bwd(du.unsqueeze(0), u.unsqueeze(0), inv, True, ops.F32, None)[0]
+        D = ops.rowdot(do, o)
+        dq = dk = None
+        if ctx.needs_input_grad[0]:
+            dq = ops.hopfield_bwd_pass(qf, kf, do, kf, kf, None, beta, lse, D, False)
+            dq = dq.to(ctx.in_dtype)
+        if ctx.needs_input_grad[1]:
+            dk = ops.hopfield_bwd_pass(kf, qf, kf, do, qf, do, beta, lse, D, True)
+            dk = dk.to(ctx.in_dtype)
+        return dq, dk, None
+
+
+class _InfoLoobFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, y, inv_tau):
+        in_dtype = x.dtype
+        xf = x.detach().float().contiguous().unsqueeze(0)
+        yf = y.detach().float().contiguous().unsqueeze(0)
+        sc = _scalar(inv_tau, x.device)
+        lse, _, _, diag = ops.sim_fwd(xf, yf, None, None, None, sc, ops.SCALE_MUL, 0.0,
+                                      ops.SIM_MASKDIAG, 0, False, ops.IMPL_SIMT)
+        n = xf.shape[1]
+        # -mean(diag) + mean(lse): one deterministic reduction kernel (weights 1/2n * 2)
+        loss = ops.clip_loss_finalize(lse * 2.0, diag, None, None, None, n, sc, ops.SCALE_MUL,
+                                      0.0, 0.0)
+        ctx.save_for_backward(xf, yf, lse, sc)
+        ctx.in_dtype = in_dtype
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, gout):
+        xf, yf, lse, sc = ctx.saved_tensors
+        n = float(xf.shape[1])
+        g = gout.detach().float().reshape(1).contiguous()
+        da, db, _, _ = ops.sim_bwd(xf, yf, None, None, None, sc, ops.SCALE_MUL, 0.0,
+                                   ops.SIM_MASKDIAG, 0, lse, None, 1.0 / n, 0.0, 1.0 / n, 0.0,
+                                   g, ctx.needs_input_grad[0], ctx.needs_input_grad[1], False,
+                                   ops.IMPL_SIMT)
+        dx = da[0].to(ctx.in_dtype) if ctx.needs_input_grad[0] else None
+        dy = db[0].to(ctx.in_dtype) if ctx.needs_input_grad[1] else None
+        return dx, dy, None
+
+
+def hopfield(state_patterns, stored_patterns, scale_hopfield):
+    """Retrieved, column-normalised patterns [d, N_state] (reference cloobLoss.py:43-47)."""
+    return _HopfieldFn.apply(state_patterns, stored_patterns, float(scale_hopfield)).T
+
+
+def hopfield_retrieval(image_features, text_features, scale_hopfield):
+    """reference cloobLoss.py:35-40."""
+    patterns_xx = hopfield(state_patterns=image_features, stored_patterns=image_features,
+                           scale_hopfield=scale_hopfield)
+    patterns_yy = hopfield(state_patterns=text_features, stored_patterns=text_features,
+                           scale_hopfield=scale_hopfield)
+    patterns_xy = hopfield(state_patterns=text_features, stored_patterns=image_features,
+                           scale_hopfield=scale_hopfield)
+    patterns_yx = hopfield(state_patterns=image_features, stored_patterns=text_features,
+                           scale_hopfield=scale_hopfield)
+    return patterns_xx, patterns_yy, patterns_xy, patterns_yx
+
+
+def infoloob_loss(x, y, i, inv_tau, device=None):
+    """InfoLOOB (reference cloobLoss.py:24-32).  `i` is the positives mask of the reference
+    signature; the fused kernel assumes it is the identity (as cloob_loss passes it) and never
+    reads it, so no N x N mask has to exist (pass None)."""
+    return _InfoLoobFn.apply(x, y, float(inv_tau))
+
+
+def cloob_loss(image_features, text_features, inv_tau, scale_hopfield, device=None):
+    """reference cloobLoss.py:10-21."""
+    p_xx, p_yy, p_xy, p_yx = hopfield_retrieval(image_features, text_features, scale_hopfield)
+    loss_img = infoloob_loss(p_xx.T, p_xy.T, None, inv_tau=inv_tau, device=device)
+    loss_txt = infoloob_loss(p_yy.T, p_yx.T, None, inv_tau=inv_tau, device=device)
+    return (loss_img + loss_txt) / 2
+
+
+class CLOOBLoss(nn.Module):
+
+    def __init__(self, inv_tau, scale_hopfield, device):
+        super().__init__()
+        self.inv_tau = inv_tau
+        self.scale_hopfield = scale_hopfield
+        self.device = device
+
+    def forward(self, image_features, text_features):
+        return cloob_loss(
+            image_features, text_features, self.inv_tau, self.scale_hopfield, self.device
+        )

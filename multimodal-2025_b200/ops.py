@@ -189,6 +189,37 @@ def clip_loss_finalize(row_lse: Tensor, diag: Tensor, col_lse: Optional[Tensor],
     return loss
 
 
+@torch.library.custom_op("mm25::rowdot", mutates_args=(), device_types="cuda")
+def rowdot(x: Tensor, y: Tensor) -> Tensor:
+    """out[i] = x_i . y_i for fp32 [rows, d] matrices."""
+    x = x.contiguous()
+    y = y.contiguous()
+    rows, d = x.shape
+    with torch.cuda.device(x.device):
+        out = torch.empty((rows,), dtype=torch.float32, device=x.device)
+        rc = _lib.lib().mm25_rowdot(_p(x), _p(y), _p(out), rows, d, _stream(x))
+    _lib.check(rc, "mm25_rowdot")
+    return out
+
+
+@torch.library.custom_op("mm25::hopfield_bwd_pass", mutates_args=(), device_types="cuda")
+def hopfield_bwd_pass(a: Tensor, b: Tensor, a2: Tensor, b2: Tensor, bm1: Tensor,
+                      bm2: Optional[Tensor], beta: float, lse: Tensor, D: Tensor,
+                      stat_by_col: bool) -> Tensor:
+    """One row-stationary pass of the Hopfield-retrieval backward (fp32, see include/mm25.h)."""
+    a, b, a2, b2, bm1 = (t.contiguous() for t in (a, b, a2, b2, bm1))
+    M, d = a.shape
+    N = b.shape[0]
+    with torch.cuda.device(a.device):
+        out = torch.empty((M, d), dtype=torch.float32, device=a.device)
+        rc = _lib.lib().mm25_hopfield_bwd_pass(_p(a), _p(b), _p(a2), _p(b2), _p(bm1),
+                                               _p(bm2.contiguous()) if bm2 is not None else None,
+                                               M, N, d, beta, _p(lse), _p(D), int(stat_by_col),
+                                               _p(out), _stream(a))
+    _lib.check(rc, "mm25_hopfield_bwd_pass")
+    return out
+
+
 def scale_param_grad(dscale: Tensor, scale: Tensor, scale_kind: int, clamp_max: float) -> Tensor:
     """Chain dL/ds to the raw scale parameter (clamp passes gradient at equality)."""
     if scale_kind == SCALE_MUL:
