@@ -308,7 +308,8 @@ def kernel_roofline(r, args, peaks):
 
         def fwd():
             return ops.sim_fwd(xh, yh, None, None, None, sc, ops.SCALE_LOG, 4.6052,
-                               ops.SIM_PLAIN, off, True, ops.IMPL_AUTO)
+                               ops.SIM_PLAIN, off, True, ops.IMPL_AUTO,
+                               ops.DOT_BOUND_NORMALIZED)
 
         row_lse, cmax, csum, _ = fwd()
         col_lse = ops.col_merge(cmax.reshape(1, -1), csum.reshape(1, -1)).reshape(1, -1)
@@ -318,7 +319,7 @@ def kernel_roofline(r, args, peaks):
             return ops.sim_bwd(xh, yh, None, None, None, sc, ops.SCALE_LOG, 4.6052,
                                ops.SIM_PLAIN, off, row_lse, col_lse, 0.5 / nn_, 0.5 / nn_,
                                0.9 / nn_, 0.1 / (nn_ * nn_), None, True, True, False,
-                               ops.IMPL_AUTO)
+                               ops.IMPL_AUTO, ops.DOT_BOUND_NORMALIZED)
 
         def t(fn, k):
             tot = 0.0

@@ -109,6 +109,10 @@ int mm25_rownorm_bwd(const float* g, const void* xhat, int xhat_dtype, const flo
  * Implementation selection: bf16 inputs with d % 64 == 0, M % 128 == 0, N % 128 == 0 in
  * PLAIN mode run the tcgen05/TMEM/TMA kernel; everything else the fp32 SIMT kernel.
  * `impl`: 0 = auto, 1 = force SIMT, 2 = force tcgen05 (error if not eligible).
+ * `dot_bound`: a caller-guaranteed bound on |a_i . b_j| (1.01 for rows normalised by
+ * mm25_rownorm_fwd), or <= 0 when unknown.  With a bound and 2 dot_bound |s| log2(e) <= 96 the
+ * tcgen05 kernels use a static softmax shift (one exp per logit, no running maximum); results
+ * are the same statistics either way.
  * ------------------------------------------------------------------------------------------ */
 size_t mm25_sim_fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
                                     int impl);
@@ -116,7 +120,8 @@ int mm25_sim_fwd(const void* a, const void* b, int dtype, const float* u, const 
                  const float* diag_add, int64_t B, int64_t M, int64_t N, int64_t d, int64_t d2,
                  const float* scale, int scale_kind, float clamp_max, int mode,
                  int64_t diag_offset, float* row_lse, float* col_max, float* col_sum,
-                 float* diag, void* workspace, size_t workspace_bytes, int impl, void* stream);
+                 float* diag, void* workspace, size_t workspace_bytes, int impl, float dot_bound,
+                 void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused backward with tile recompute (autograd of the block above).
@@ -138,7 +143,7 @@ int mm25_sim_bwd(const void* a, const void* b, int dtype, const float* u, const 
                  int64_t diag_offset, const float* row_lse, const float* col_lse, float w_row,
                  float w_col, float w_diag, float w_all, const float* gout, float* da,
                  float* db, float* dscale_part, float* ddiag, void* workspace,
-                 size_t workspace_bytes, int impl, void* stream);
+                 size_t workspace_bytes, int impl, float dot_bound, void* stream);
 
 /* Deterministic fixed-order sum of n fp32 values into out[0] (one CTA). out = alpha * sum. */
 int mm25_sum_parts(const float* parts, int64_t n, float alpha, float* out, void* stream);

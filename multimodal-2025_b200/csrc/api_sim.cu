@@ -49,7 +49,7 @@ extern "C" int mm25_sim_fwd(const void* a, const void* b, int dtype, const float
                             int64_t N, int64_t d, int64_t d2, const float* scale, int scale_kind,
                             float clamp_max, int mode, int64_t diag_offset, float* row_lse,
                             float* col_max, float* col_sum, float* diag, void* workspace,
-                            size_t workspace_bytes, int impl, void* stream) {
+                            size_t workspace_bytes, int impl, float dot_bound, void* stream) {
   if (B <= 0 || M <= 0 || N <= 0 || d <= 0) return MM25_ERR_SHAPE;
   if (!a || !b || !scale || !row_lse || !diag) return MM25_ERR_ARG;
   if ((col_max == nullptr) != (col_sum == nullptr)) return MM25_ERR_ARG;
@@ -63,7 +63,7 @@ extern "C" int mm25_sim_fwd(const void* a, const void* b, int dtype, const float
   cudaStream_t st = (cudaStream_t)stream;
   if (t)
     return tc::launch_fwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
-                          col_max, col_sum, diag, workspace, workspace_bytes, st);
+                          col_max, col_sum, diag, workspace, workspace_bytes, dot_bound, st);
   return simt::launch_fwd(a, b, dtype, u, v, diag_add, B, M, N, d, d2, scale, scale_kind,
                           clamp_max, mode, diag_offset, row_lse, col_max, col_sum, diag,
                           workspace, workspace_bytes, st);
@@ -95,7 +95,7 @@ extern "C" int mm25_sim_bwd(const void* a, const void* b, int dtype, const float
                             const float* col_lse, float w_row, float w_col, float w_diag,
                             float w_all, const float* gout, float* da, float* db,
                             float* dscale_part, float* ddiag, void* workspace,
-                            size_t workspace_bytes, int impl, void* stream) {
+                            size_t workspace_bytes, int impl, float dot_bound, void* stream) {
   if (B <= 0 || M <= 0 || N <= 0 || d <= 0) return MM25_ERR_SHAPE;
   if (!a || !b || !scale || !row_lse) return MM25_ERR_ARG;
   if (!col_lse && w_col != 0.f) return MM25_ERR_ARG;
@@ -109,7 +109,7 @@ extern "C" int mm25_sim_bwd(const void* a, const void* b, int dtype, const float
   if (t)
     return tc::launch_bwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
                           col_lse, w_row, w_col, w_diag, w_all, gout, da, db, dscale_part,
-                          workspace, workspace_bytes, st);
+                          workspace, workspace_bytes, dot_bound, st);
   int rc = MM25_OK;
   if (da) {
     rc = simt::launch_bwd_pass(a, b, dtype, u, v, diag_add, 0, B, M, N, d, d2, scale, scale_kind,

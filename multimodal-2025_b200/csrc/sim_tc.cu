@@ -35,7 +35,7 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                   const float* __restrict__ scale, int scale_kind, float clamp_max,
                   int64_t diag_offset, float* __restrict__ row_pm, float* __restrict__ row_pl,
                   float* __restrict__ col_pm, float* __restrict__ col_pl,
-                  float* __restrict__ diag, int force_slow) {
+                  float* __restrict__ diag, int force_slow, float dot_bound) {
   extern __shared__ uint8_t smem_raw[];
   FwdSmem& sm = *reinterpret_cast<FwdSmem*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -59,22 +59,28 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int half = ew >> 2;      // which half of the tile's columns this warp handles
     const float s = load_scale(scale, scale_kind, clamp_max);
     const float c2 = s * LOG2E;
+    const float m2s = dot_bound * fabsf(c2);
+    const bool fast_static = !force_slow && dot_bound > 0.f && 2.f * m2s <= SPREAD_LIMIT;
     uint32_t as = 0, accph = 0, buf = 0;
     for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
       const int rbg = item / nseg, seg = item % nseg;
       const int bz = rbg / nrb_per_batch, rb = rbg % nrb_per_batch;
       const int64_t row = (int64_t)rb * BM + q * 32 + lane;  // row inside this batch entry
       const int64_t dcol = row + diag_offset;                // its positive column
-      float rm = -INFINITY, rl = 0.f;
+      float rm = fast_static ? m2s : -INFINITY, rl = 0.f;
       const int t0 = seg * tps, t1 = min(ntiles, t0 + tps);
       for (int t = t0; t < t1; ++t) {
         const int64_t col0 = (int64_t)t * BN;
         mbar_wait(&sm.acc_full[as], accph);
         tc_fence_after();
-#pragma unroll 1
-        for (int ch = half * CH_PER_WARP; ch < (half + 1) * CH_PER_WARP; ++ch) {
+        const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + as * BN +
+                               half * CH_PER_WARP * 32;
+
+        auto process = [&](uint32_t (&r)[32], int chl) {
+          const int ch = half * CH_PER_WARP + chl;
           float v[32];
-          tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + as * BN + ch * 32, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
           const int64_t cbase = col0 + ch * 32;
           // positive logit (warp-uniform test: this chunk crosses the warp's diagonal range)
           {
@@ -87,42 +93,68 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
               if (rel >= 0 && rel < 32) diag[(int64_t)bz * M + row] = s * dv;
             }
           }
-          float tmx = v[0], tmn = v[0];
-#pragma unroll
-          for (int j = 1; j < 32; ++j) { tmx = fmaxf(tmx, v[j]); tmn = fminf(tmn, v[j]); }
-          const float bmx = warp_max(tmx), bmn = -warp_max(-tmn);
           float e[32];
           float cm;
-          if (!force_slow && (bmx - bmn) * c2 <= SPREAD_LIMIT) {
-            // fast path: one exp per logit, shared block shift
-            const float m2 = bmx * c2;
+          if (fast_static) {
+            // static shift m2s >= every z log2e: one exp per logit, no running maximum
             float rs = 0.f;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) { e[j] = ex2_approx(fmaf(v[j], c2, -m2)); rs += e[j]; }
-            const float mn = fmaxf(rm, m2);
-            rl = rl * ex2_approx(rm - mn) + rs * ex2_approx(m2 - mn);
-            rm = mn;
-            cm = m2;
+            for (int j = 0; j < 32; ++j) { e[j] = ex2_approx(fmaf(v[j], c2, -m2s)); rs += e[j]; }
+            rl += rs;
+            cm = m2s;
           } else {
-            // robust path: per-row and per-column shifts (two exps per logit)
-            const float tm2 = tmx * c2;
-            const float mn = fmaxf(rm, tm2);
-            float rs = 0.f;
+            float tmx = v[0], tmn = v[0];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) rs += ex2_approx(fmaf(v[j], c2, -mn));
-            rl = rl * ex2_approx(rm - mn) + rs;
-            rm = mn;
-            cm = 0.f;
+            for (int j = 1; j < 32; ++j) { tmx = fmaxf(tmx, v[j]); tmn = fminf(tmn, v[j]); }
+            const float bmx = warp_max(tmx), bmn = -warp_max(-tmn);
+            const float hi2 = fmaxf(bmx * c2, bmn * c2), lo2 = fminf(bmx * c2, bmn * c2);
+            if (!force_slow && hi2 - lo2 <= SPREAD_LIMIT) {
+              // fast path: one exp per logit, shared block shift
+              const float m2 = hi2;
+              float rs = 0.f;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float cj = warp_max(v[j]) * c2;
-              e[j] = ex2_approx(fmaf(v[j], c2, -cj));
-              cm = (j == lane) ? cj : cm;
+              for (int j = 0; j < 32; ++j) { e[j] = ex2_approx(fmaf(v[j], c2, -m2)); rs += e[j]; }
+              const float mn = fmaxf(rm, m2);
+              rl = rl * ex2_approx(rm - mn) + rs * ex2_approx(m2 - mn);
+              rm = mn;
+              cm = m2;
+            } else {
+              // robust path: per-row and per-column shifts (two exps per logit)
+              float tz = v[0] * c2;
+#pragma unroll
+              for (int j = 1; j < 32; ++j) tz = fmaxf(tz, v[j] * c2);
+              const float mn = fmaxf(rm, tz);
+              float rs = 0.f;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) rs += ex2_approx(fmaf(v[j], c2, -mn));
+              rl = rl * ex2_approx(rm - mn) + rs;
+              rm = mn;
+              cm = 0.f;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const float cj = warp_max(v[j] * c2);
+                e[j] = ex2_approx(fmaf(v[j], c2, -cj));
+                cm = (j == lane) ? cj : cm;
+              }
             }
           }
           const float cs = butterfly_colsum(e, lane);
           sm.colm[buf][q][ch * 32 + lane] = cm;
           sm.cols[buf][q][ch * 32 + lane] = cs;
+        };
+
+        static_assert(CH_PER_WARP % 2 == 0, "pipeline is unrolled by two");
+        uint32_t ra[32], rb_[32];
+        tmem_ld_32x32_issue(tbase, ra);
+        tmem_ld_wait(ra);
+#pragma unroll
+        for (int c = 0; c < CH_PER_WARP; c += 2) {
+          tmem_ld_32x32_issue(tbase + (c + 1) * 32, rb_);
+          process(ra, c);
+          tmem_ld_wait(rb_);
+          if (c + 2 < CH_PER_WARP) tmem_ld_32x32_issue(tbase + (c + 2) * 32, ra);
+          process(rb_, c + 1);
+          if (c + 2 < CH_PER_WARP) tmem_ld_wait(ra);
         }
         // all TMEM reads of this stage are complete (wait::ld inside the load helper)
         tc_fence_before();
@@ -229,7 +261,7 @@ static PFN_encodeTiled get_encode() {
 }
 
 int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
-                   uint32_t box_rows, uint32_t box_cols) {
+                   uint32_t box_rows, uint32_t box_cols, int swizzle_bytes) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) return MM25_ERR_CUDA;
   if ((reinterpret_cast<uintptr_t>(base) & 15) || (cols * 2) % 16) return MM25_ERR_ALIGN;
@@ -238,7 +270,8 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t c
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim,
-                   gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? MM25_OK : MM25_ERR_CUDA;
 }
@@ -298,7 +331,7 @@ void set_force_slow(int v) { g_force_slow = v; }
 int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,
                const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
                float* row_lse, float* col_max, float* col_sum, float* diag, void* ws,
-               size_t ws_bytes, cudaStream_t st) {
+               size_t ws_bytes, float dot_bound, cudaStream_t st) {
   if (!eligible_fwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)) return MM25_ERR_SHAPE;
   if (ws_bytes < fwd_workspace_bytes(B, M, N, d)) return MM25_ERR_WORKSPACE;
   FwdGeom g = fwd_geom(B, M, N);
@@ -316,7 +349,7 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   sim_fwd_tc_kernel<<<g.grid, FWD_THREADS, smem, st>>>(
       ta, tb, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind, clamp_max,
-      diag_offset, row_pm, row_pl, col_pm, col_pl, diag, g_force_slow);
+      diag_offset, row_pm, row_pl, col_pm, col_pl, diag, g_force_slow, dot_bound);
   MM25_LAUNCH_CHECK();
   const int64_t mx = M > N ? M : N;
   fwd_tc_merge_kernel<<<dim3((unsigned)ceil_div(mx, 32), (unsigned)B), 256, 0, st>>>(

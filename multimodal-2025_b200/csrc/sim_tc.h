@@ -7,6 +7,8 @@
 namespace mm25 {
 namespace tc {
 
+// `dot_bound`: caller-guaranteed bound on |a_i . b_j| (e.g. 1.01 for rows normalised by
+// mm25_rownorm_fwd); <= 0 = unknown.  Enables the static-shift one-exp epilogues.
 // PLAIN mode, bf16, d % 64 == 0 (64 <= d <= 1024), M % 128 == 0, N % 128 == 0.
 bool eligible_fwd(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode);
 bool eligible_bwd(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode);
@@ -15,7 +17,7 @@ size_t fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d);
 int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,
                const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
                float* row_lse, float* col_max, float* col_sum, float* diag, void* ws,
-               size_t ws_bytes, cudaStream_t st);
+               size_t ws_bytes, float dot_bound, cudaStream_t st);
 
 size_t bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d);
 int64_t bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d);
@@ -23,7 +25,7 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
                const float* row_lse, const float* col_lse, float w_row, float w_col,
                float w_diag, float w_all, const float* gout, float* da, float* db,
-               float* dscale_part, void* ws, size_t ws_bytes, cudaStream_t st);
+               float* dscale_part, void* ws, size_t ws_bytes, float dot_bound, cudaStream_t st);
 
 }  // namespace tc
 }  // namespace mm25

@@ -18,17 +18,38 @@ namespace tc {
 
 int tc_sm_count();
 
+// Cc[j] = gout * s * w_col * 2^(m2 - c_j log2e): the column factor of the one-exp gradient
+// (static-shift path, see sim_grad_tc_kernel).  One thread per column.
+__global__ void __launch_bounds__(256)
+grad_col_coef_kernel(const float* __restrict__ col_lse, int64_t N, const float* __restrict__ scale,
+                     int scale_kind, float clamp_max, const float* __restrict__ gout, float w_col,
+                     float dot_bound, float* __restrict__ Cc) {
+  const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (j >= N) return;
+  const float s = load_scale(scale, scale_kind, clamp_max);
+  const float m2 = dot_bound * fabsf(s) * LOG2E;
+  const float go = gout ? __ldg(gout) : 1.f;
+  Cc[j] = go * s * w_col * exp2f(m2 - col_lse[j] * LOG2E);
+}
+
+// Epilogue paths:
+//  * static shift (one exp per logit): when the caller bounds |a_i.b_j| <= dot_bound and
+//    2 dot_bound |s| log2e <= SPREAD_LIMIT, every 2^(z log2e - m2) with m2 = dot_bound |s| log2e
+//    lies in [2^-96, 1], so  G' = E (R_i + C_j) - K  with E = 2^(z log2e - m2),
+//    R_i = gs w_row 2^(m2 - r_i log2e), C_j = gs w_col 2^(m2 - c_j log2e) (both <= 2^96).
+//  * general (two exps per logit): any range (s up to the 100 clamp, un-normalised inputs).
 __global__ void __launch_bounds__(FWD_THREADS, 1)
 sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                   const __grid_constant__ CUtensorMap tmap_b, int64_t M, int64_t N, int d,
+                   const __grid_constant__ CUtensorMap tmap_b,
+                   const __grid_constant__ CUtensorMap tmap_g, int64_t M, int64_t N, int d,
                    int first_rb, int num_rb, int nseg, int tps, const float* __restrict__ scale,
                    int scale_kind, float clamp_max, int64_t diag_offset,
                    const float* __restrict__ row_lse, const float* __restrict__ col_lse,
                    float w_row, float w_col, float w_diag, float w_all,
-                   const float* __restrict__ gout, __nv_bfloat16* __restrict__ G,
-                   float* __restrict__ dscale_part) {
+                   const float* __restrict__ gout, float* __restrict__ dscale_part,
+                   const float* __restrict__ Cc, float dot_bound) {
   extern __shared__ uint8_t smem_raw[];
-  FwdSmem& sm = *reinterpret_cast<FwdSmem*>(
+  GradSmem& sm = *reinterpret_cast<GradSmem*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   Sweep w;
@@ -44,57 +65,135 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (lane == 0) sweep_mma(sm, tmem, w);
   } else {
     const int q = warp & 3;
-    const int half = (warp - 2) >> 2;
+    const int ew = warp - 2;
+    const int half = ew >> 2;
     const float s = load_scale(scale, scale_kind, clamp_max);
     const float c2 = s * LOG2E;
     const float go = gout ? __ldg(gout) : 1.f;
     const float gs = go * s;
-    float ds = 0.f;
+    const float m2 = dot_bound * fabsf(c2);
+    const bool fast = Cc != nullptr && dot_bound > 0.f && 2.f * m2 <= SPREAD_LIMIT;
+    const float k_all = gs * w_all, k_diag = gs * w_diag;
+    // per-column operand of the epilogue: C_j (static shift) or c_j (general), staged per warp
+    const float* colv = fast ? Cc : col_lse;
+    float* ccw = sm.ccw[ew];
+    uint8_t* stage = sm.stage[ew];
+    // 64B swizzle of the staging rows: 16-byte chunk c of row r lives at chunk c ^ ((r >> 1) & 3)
+    const uint32_t st_row = smem_u32(stage) + lane * 64;
+    const uint32_t st_xor = (lane >> 1) & 3;
+    if (lane == 0) tma_prefetch_desc(&tmap_g);
+    float ds = 0.f;  // fast: sum G' v (= gout s sum G v); general: sum G v
     uint32_t as = 0, accph = 0;
     for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
       const int rb = first_rb + item / nseg, seg = item % nseg;
       const int64_t row = (int64_t)rb * BM + q * 32 + lane;
       const int64_t dcol = row + diag_offset;
       const float r2 = __ldg(row_lse + row) * LOG2E;
-      __nv_bfloat16* grow = G + (int64_t)(row - (int64_t)first_rb * BM) * N;
+      const float Ri = gs * w_row * exp2f(m2 - r2);
+      const int32_t grow0 = (int32_t)((int64_t)(rb - first_rb) * BM + q * 32);  // panel row
       const int t0 = seg * tps, t1 = min(w.ntiles, t0 + tps);
+      float4 cnext = __ldg(reinterpret_cast<const float4*>(
+          colv + (int64_t)t0 * BN + half * (BN / 2) + lane * 4));
       for (int t = t0; t < t1; ++t) {
         const int64_t col0 = (int64_t)t * BN;
+        // stage this tile's column operands (all lanes are past the previous tile's reads)
+        __syncwarp();
+        *reinterpret_cast<float4*>(ccw + lane * 4) = cnext;
+        __syncwarp();
+        if (t + 1 < t1)
+          cnext = __ldg(reinterpret_cast<const float4*>(
+              colv + (int64_t)(t + 1) * BN + half * (BN / 2) + lane * 4));
         mbar_wait(&sm.acc_full[as], accph);
         tc_fence_after();
-#pragma unroll 1
-        for (int ch = half * CH_PER_WARP; ch < (half + 1) * CH_PER_WARP; ++ch) {
-          float v[32];
-          tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + as * BN + ch * 32, v);
-          const int64_t cbase = col0 + ch * 32;
+        const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + as * BN +
+                               half * CH_PER_WARP * 32;
+
+        auto process = [&](uint32_t (&r)[32], int chl) {
+          const int64_t cbase = col0 + (half * CH_PER_WARP + chl) * 32;
           const int rel = (int)min((int64_t)64, max((int64_t)-1, dcol - cbase));
-          const float4* cl4 = reinterpret_cast<const float4*>(col_lse + cbase);
+          const float4* cc4 = reinterpret_cast<const float4*>(ccw + chl * 32);
           uint32_t packed[16];
+          if (fast) {
+            // warp-uniform: does this chunk cross the warp's positives?
+            const int64_t d0 = (int64_t)rb * BM + q * 32 + diag_offset;
+            const bool has_diag = (d0 + 31 >= cbase) && (d0 < cbase + 32);
 #pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            const float4 cc = __ldg(cl4 + j4);
-            const float cj[4] = {cc.x, cc.y, cc.z, cc.w};
-            float gq[4];
+            for (int j4 = 0; j4 < 8; ++j4) {
+              const float4 cc = cc4[j4];
+              const float cj[4] = {cc.x, cc.y, cc.z, cc.w};
+              float gq[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const int j = j4 * 4 + u;
-              const float zl = v[j] * c2;
-              float gg = w_row * ex2_approx(zl - r2) + w_col * ex2_approx(fmaf(-cj[u], LOG2E, zl));
-              gg -= w_all;
-              gg -= (j == rel) ? w_diag : 0.f;
-              ds = fmaf(gg, v[j], ds);
-              gq[u] = gg * gs;
+              for (int u = 0; u < 4; ++u) {
+                const int j = j4 * 4 + u;
+                const float vj = __uint_as_float(r[j]);
+                const float E = ex2_approx(fmaf(vj, c2, -m2));
+                float gg = fmaf(E, Ri + cj[u], -k_all);
+                if (has_diag) gg -= (j == rel) ? k_diag : 0.f;
+                ds = fmaf(gg, vj, ds);
+                gq[u] = gg;
+              }
+              __nv_bfloat162 lo = __floats2bfloat162_rn(gq[0], gq[1]);
+              __nv_bfloat162 hi = __floats2bfloat162_rn(gq[2], gq[3]);
+              packed[j4 * 2] = *reinterpret_cast<uint32_t*>(&lo);
+              packed[j4 * 2 + 1] = *reinterpret_cast<uint32_t*>(&hi);
             }
-            __nv_bfloat162 lo = __floats2bfloat162_rn(gq[0], gq[1]);
-            __nv_bfloat162 hi = __floats2bfloat162_rn(gq[2], gq[3]);
-            packed[j4 * 2] = *reinterpret_cast<uint32_t*>(&lo);
-            packed[j4 * 2 + 1] = *reinterpret_cast<uint32_t*>(&hi);
-          }
-          uint4* dst = reinterpret_cast<uint4*>(grow + cbase);
+          } else {
 #pragma unroll
-          for (int u = 0; u < 4; ++u)
-            dst[u] = make_uint4(packed[4 * u], packed[4 * u + 1], packed[4 * u + 2],
-                                packed[4 * u + 3]);
+            for (int j4 = 0; j4 < 8; ++j4) {
+              const float4 cc = cc4[j4];
+              const float cj[4] = {cc.x, cc.y, cc.z, cc.w};
+              float gq[4];
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                const int j = j4 * 4 + u;
+                const float vj = __uint_as_float(r[j]);
+                const float zl = vj * c2;
+                float gg = w_row * ex2_approx(zl - r2) +
+                           w_col * ex2_approx(fmaf(-cj[u], LOG2E, zl));
+                gg -= w_all;
+                gg -= (j == rel) ? w_diag : 0.f;
+                ds = fmaf(gg, vj, ds);
+                gq[u] = gg * gs;
+              }
+              __nv_bfloat162 lo = __floats2bfloat162_rn(gq[0], gq[1]);
+              __nv_bfloat162 hi = __floats2bfloat162_rn(gq[2], gq[3]);
+              packed[j4 * 2] = *reinterpret_cast<uint32_t*>(&lo);
+              packed[j4 * 2 + 1] = *reinterpret_cast<uint32_t*>(&hi);
+            }
+          }
+          // the previous TMA store of this warp must be done reading the staging buffer
+          if (lane == 0) tma_store_wait_read<0>();
+          __syncwarp();
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const uint32_t addr = st_row + ((u ^ st_xor) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr),
+                         "r"(packed[4 * u]), "r"(packed[4 * u + 1]), "r"(packed[4 * u + 2]),
+                         "r"(packed[4 * u + 3])
+                         : "memory");
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmap_g, stage, (int32_t)cbase, grow0);
+            tma_store_commit();
+          }
+        };
+
+        // software pipeline over the warp's chunks: the TMEM load of chunk c+1 is in flight
+        // while chunk c is processed
+        static_assert(CH_PER_WARP % 2 == 0, "pipeline is unrolled by two");
+        uint32_t ra[32], rb_[32];
+        tmem_ld_32x32_issue(tbase, ra);
+        tmem_ld_wait(ra);
+#pragma unroll
+        for (int c = 0; c < CH_PER_WARP; c += 2) {
+          tmem_ld_32x32_issue(tbase + (c + 1) * 32, rb_);
+          process(ra, c);
+          tmem_ld_wait(rb_);
+          if (c + 2 < CH_PER_WARP) tmem_ld_32x32_issue(tbase + (c + 2) * 32, ra);
+          process(rb_, c + 1);
+          if (c + 2 < CH_PER_WARP) tmem_ld_wait(ra);
         }
         tc_fence_before();
         __syncwarp();
@@ -102,14 +201,15 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         if (++as == NACC) { as = 0; accph ^= 1; }
       }
     }
-    // d(loss)/d(scale) partial of this CTA: sum G.z/s = sum G.v (times the upstream gradient)
-    ds = warp_sum(ds) * go;
-    if (lane == 0) sm.colm[0][0][warp - 2] = ds;
+    if (lane == 0) tma_store_wait_all<0>();
+    // d(loss)/d(scale) partial of this CTA: gout * sum G.z/s = gout * sum G.v
+    ds = warp_sum(ds) * (fast ? (s != 0.f ? 1.f / s : 0.f) : go);
+    if (lane == 0) sm.red[ew] = ds;
     named_bar_sync(1, 32 * NEPI);
     if (warp == 2 && lane == 0 && dscale_part) {
       float tot = 0.f;
 #pragma unroll
-      for (int k = 0; k < NEPI; ++k) tot += sm.colm[0][0][k];
+      for (int k = 0; k < NEPI; ++k) tot += sm.red[k];
       dscale_part[blockIdx.x] = tot;
     }
   }
@@ -134,7 +234,8 @@ static int64_t panel_rows(int64_t M, int64_t N) {
 }
 
 size_t bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d) {
-  return (size_t)panel_rows(M, N) * (size_t)N * 2 + 256;
+  // bf16 G panel + the [N] column factors of the static-shift epilogue
+  return (size_t)panel_rows(M, N) * (size_t)N * 2 + 256 + (size_t)N * sizeof(float) + 256;
 }
 
 int64_t bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d) {
@@ -146,15 +247,21 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
                const float* row_lse, const float* col_lse, float w_row, float w_col,
                float w_diag, float w_all, const float* gout, float* da, float* db,
-               float* dscale_part, void* ws, size_t ws_bytes, cudaStream_t st) {
+               float* dscale_part, void* ws, size_t ws_bytes, float dot_bound,
+               cudaStream_t st) {
   if (!eligible_bwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)) return MM25_ERR_SHAPE;
   if (!col_lse) return MM25_ERR_ARG;
   if (ws_bytes < bwd_workspace_bytes(B, M, N, d)) return MM25_ERR_WORKSPACE;
   __nv_bfloat16* G = reinterpret_cast<__nv_bfloat16*>(
       (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255));
   const int64_t R = panel_rows(M, N);
+  float* Cc = nullptr;
+  if (dot_bound > 0.f) {
+    Cc = reinterpret_cast<float*>(
+        (reinterpret_cast<uintptr_t>(G) + (size_t)R * (size_t)N * 2 + 255) & ~uintptr_t(255));
+  }
   const int sms = tc_sm_count();
-  const size_t smem = sizeof(FwdSmem) + 1024;
+  const size_t smem = sizeof(GradSmem) + 1024;
   MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_grad_tc_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const __nv_bfloat16* ab = (const __nv_bfloat16*)a;
@@ -168,6 +275,12 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
     if (rc) return rc;
     rc = make_tmap_bf16(&tb, b_b, (uint64_t)N, (uint64_t)d, BN, BK);
     if (rc) return rc;
+    if (Cc) {
+      grad_col_coef_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(
+          col_lse + bz * N, N, scale, scale_kind, clamp_max, gout ? gout + bz : nullptr, w_col,
+          dot_bound, Cc);
+      MM25_LAUNCH_CHECK();
+    }
     for (int64_t p0 = 0; p0 < M; p0 += R) {
       const int64_t rows = (M - p0 < R) ? (M - p0) : R;
       const int num_rb = (int)(rows / BM), ntiles = (int)(N / BN);
@@ -191,10 +304,14 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
       if (dscale_part) {
         MM25_CUDA_CHECK(cudaMemsetAsync(dscale_part + part, 0, sizeof(float) * sms, st));
       }
+      CUtensorMap tg;  // the [rows, N] bf16 panel, stored in 32 x 32 boxes (64B swizzle)
+      rc = make_tmap_bf16(&tg, G, (uint64_t)rows, (uint64_t)N, 32, 32, 64);
+      if (rc) return rc;
       sim_grad_tc_kernel<<<grid, FWD_THREADS, smem, st>>>(
-          ta, tb, M, N, (int)d, (int)(p0 / BM), num_rb, nseg, tps, scale, scale_kind, clamp_max,
+          ta, tb, tg, M, N, (int)d, (int)(p0 / BM), num_rb, nseg, tps, scale, scale_kind, clamp_max,
           diag_offset, row_lse + bz * M, col_lse + bz * N, w_row, w_col, w_diag, w_all,
-          gout ? gout + bz : nullptr, G, dscale_part ? dscale_part + part : nullptr);
+          gout ? gout + bz : nullptr, dscale_part ? dscale_part + part : nullptr, Cc,
+          dot_bound);
       MM25_LAUNCH_CHECK();
       part += sms;
       if (da) {

@@ -33,13 +33,27 @@ struct FwdSmem {
   uint32_t tmem_base;
 };
 
+// gradient-panel kernel: same rings; per-warp staging of the bf16 G chunk for the TMA store
+// (32 rows x 64 B, 64B-swizzled) and of the column factors of the warp's 128 columns.
+struct GradSmem {
+  uint8_t a[NST][A_BYTES];
+  uint8_t b[NST][B_BYTES];
+  uint8_t stage[NEPI][2048];
+  float ccw[NEPI][BN / 2];
+  float red[NEPI];
+  uint64_t full[NST], empty[NST];
+  uint64_t acc_full[NACC], acc_empty[NACC];
+  uint32_t tmem_base;
+};
+
 // work decomposition: items = (row block, column segment); row blocks [first_rbg, first_rbg+num_rbg)
 struct Sweep {
   int KC, ntiles, nseg, tps, nrb_per_batch, first_rbg, num_rbg;
   int64_t N;
 };
 
-__device__ __forceinline__ void sweep_setup(FwdSmem& sm, const CUtensorMap* ta,
+template <class SM>
+__device__ __forceinline__ void sweep_setup(SM& sm, const CUtensorMap* ta,
                                             const CUtensorMap* tb) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -57,7 +71,8 @@ __device__ __forceinline__ void sweep_setup(FwdSmem& sm, const CUtensorMap* ta,
 }
 
 // one elected thread of warp 0
-__device__ __forceinline__ void sweep_producer(FwdSmem& sm, const CUtensorMap* ta,
+template <class SM>
+__device__ __forceinline__ void sweep_producer(SM& sm, const CUtensorMap* ta,
                                                const CUtensorMap* tb, const Sweep& w) {
   uint32_t st = 0, ph = 0;
   const int nitems = w.num_rbg * w.nseg;
@@ -80,7 +95,8 @@ __device__ __forceinline__ void sweep_producer(FwdSmem& sm, const CUtensorMap* t
 }
 
 // one elected thread of warp 1
-__device__ __forceinline__ void sweep_mma(FwdSmem& sm, uint32_t tmem, const Sweep& w) {
+template <class SM>
+__device__ __forceinline__ void sweep_mma(SM& sm, uint32_t tmem, const Sweep& w) {
   constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 0, 0);
   uint32_t st = 0, ph = 0, as = 0, accph = 0;
   const int nitems = w.num_rbg * w.nseg;

@@ -83,7 +83,7 @@ class _ShardedClipFn(torch.autograd.Function):
         # (3) local block
         row_lse, cmax, csum, diag = B.sim_fwd(xhat, yall, None, None, None, scale32,
                                               B.SCALE_LOG, clamp_max, B.SIM_PLAIN, rank * n,
-                                              True, impl)
+                                              True, impl, 1.01 if normalize else 0.0)
         # (4) column statistics: gather partials, merge in rank order
         stats = _all_gather_cat(torch.stack([cmax[0], csum[0]], 0).unsqueeze(0), group)
         col_lse = B.col_merge(stats[:, 0].contiguous(), stats[:, 1].contiguous())  # [N]
@@ -119,7 +119,7 @@ class _ShardedClipFn(torch.autograd.Function):
                                       clamp_max, B.SIM_PLAIN, rank * n, row_lse,
                                       col_lse.reshape(1, N), 0.5 / nn_, 0.5 / nn_,
                                       (1.0 - eps_ls) / nn_, eps_ls / (nn_ * nn_), g, True, True,
-                                      False, impl)
+                                      False, impl, 1.01 if normalize else 0.0)
         dy_local = _reduce_scatter_sum(db[0], group).unsqueeze(0)
         out_dt = B.BF16 if in_dtype == torch.bfloat16 else B.F32
         dimg = B.rownorm_bwd(da, xhat, invx, normalize, out_dt, None)[0].to(in_dtype)

@@ -35,9 +35,10 @@ class _ClipLossFn(torch.autograd.Function):
         yhat, invy, sy = ops.rownorm_fwd(txt, normalize, _EPS_NORM, cdt, want_cs)
         scale32 = logits_scale.detach().reshape(1).to(torch.float32).contiguous()
         B, M, _ = xhat.shape
+        bound = ops.DOT_BOUND_NORMALIZED if normalize else 0.0
         row_lse, cmax, csum, diag = ops.sim_fwd(xhat, yhat, None, None, None, scale32,
                                                 scale_kind, clamp_max, ops.SIM_PLAIN, 0, True,
-                                                impl)
+                                                impl, bound)
         col_lse = ops.col_merge(cmax.reshape(1, -1), csum.reshape(1, -1)).reshape(B, -1)
         loss = ops.clip_loss_finalize(row_lse, diag, col_lse, sx if want_cs else None,
                                       sy if want_cs else None, M, scale32, scale_kind,
@@ -57,7 +58,7 @@ class _ClipLossFn(torch.autograd.Function):
             xhat, yhat, None, None, None, scale32, scale_kind, clamp_max, ops.SIM_PLAIN, 0,
             row_lse, col_lse, 0.5 / n, 0.5 / n, (1.0 - eps_ls) / n, eps_ls / (n * n), gout,
             ctx.needs_input_grad[0] or ctx.needs_input_grad[2], ctx.needs_input_grad[1], False,
-            impl)
+            impl, ops.DOT_BOUND_NORMALIZED if normalize else 0.0)
         out_dt = ops.BF16 if in_dtype == torch.bfloat16 else ops.F32
         dimg = dtxt = dls = None
         if ctx.needs_input_grad[0]:

@@ -17,6 +17,8 @@ F32, BF16 = 0, 1
 SIM_PLAIN, SIM_MASKDIAG, SIM_MODULATED = 0, 1, 2
 SCALE_MUL, SCALE_LOG = 0, 1
 IMPL_AUTO, IMPL_SIMT, IMPL_TC = 0, 1, 2
+# |xhat_i . yhat_j| for rows normalised by rownorm_fwd (bf16 rounding included)
+DOT_BOUND_NORMALIZED = 1.01
 
 
 def _dt(t: Tensor) -> int:
@@ -90,8 +92,9 @@ def rownorm_bwd(g: Tensor, xhat: Tensor, inv_norm: Tensor, normalize: bool, out_
 def sim_fwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
             diag_add: Optional[Tensor], scale: Tensor, scale_kind: int, clamp_max: float,
             mode: int, diag_offset: int, want_cols: bool,
-            impl: int) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
-    """Fused similarity + online row/column LSE; returns (row_lse, col_max, col_sum, diag)."""
+            impl: int, dot_bound: float = 0.0) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """Fused similarity + online row/column LSE; returns (row_lse, col_max, col_sum, diag).
+    `dot_bound`: bound on |a_i.b_j| if the caller knows one (include/mm25.h), else 0."""
     a = _cuda3(a, "a")
     b = _cuda3(b, "b")
     if a.dtype != b.dtype:
@@ -113,7 +116,7 @@ def sim_fwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
                             _p(scale), scale_kind, clamp_max, mode, diag_offset, _p(row_lse),
                             _p(col_max) if want_cols else None,
                             _p(col_sum) if want_cols else None, _p(diag), _p(ws), ws.numel(),
-                            impl, _stream(a))
+                            impl, dot_bound, _stream(a))
     _lib.check(rc, "mm25_sim_fwd")
     return row_lse, col_max, col_sum, diag
 
@@ -124,7 +127,7 @@ def sim_bwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
             mode: int, diag_offset: int, row_lse: Tensor, col_lse: Optional[Tensor],
             w_row: float, w_col: float, w_diag: float, w_all: float, gout: Optional[Tensor],
             need_da: bool, need_db: bool, need_ddiag: bool,
-            impl: int) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+            impl: int, dot_bound: float = 0.0) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
     """Fused backward with tile recompute; returns (da, db, dscale[1], ddiag), all fp32.
 
     dscale is dL/d(multiplicative scale) = sum_ij G_ij z_ij / s (already times gout)."""
@@ -149,7 +152,7 @@ def sim_bwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
                             _p(col_lse), w_row, w_col, w_diag, w_all, _p(gout),
                             _p(da) if need_da else None, _p(db) if need_db else None, _p(parts),
                             _p(ddiag) if need_ddiag else None, _p(ws), ws.numel(), impl,
-                            _stream(a))
+                            dot_bound, _stream(a))
         _lib.check(rc, "mm25_sim_bwd")
         rc = L.mm25_sum_parts(_p(parts), parts.numel(), 1.0, _p(dscale), _stream(a))
     _lib.check(rc, "mm25_sum_parts")

@@ -21,7 +21,7 @@ def rownorm_fwd(x, normalize, eps, out_dtype, want_colsum):
 
 
 def sim_fwd(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offset, want_cols,
-            impl):
+            impl, dot_bound=0.0):
     z = _s(scale, scale_kind, clamp_max) * (a.float() @ b.float().transpose(1, 2))
     M = a.shape[1]
     idx = torch.arange(M)
@@ -49,7 +49,8 @@ def clip_loss_finalize(row_lse, diag, col_lse, sx, sy, n_norm, scale, scale_kind
 
 
 def sim_bwd(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offset, row_lse,
-            col_lse, w_row, w_col, w_diag, w_all, gout, need_da, need_db, need_ddiag, impl):
+            col_lse, w_row, w_col, w_diag, w_all, gout, need_da, need_db, need_ddiag, impl,
+            dot_bound=0.0):
     s = _s(scale, scale_kind, clamp_max)
     dot = a.float() @ b.float().transpose(1, 2)
     z = s * dot

@@ -57,6 +57,28 @@ def test_tc_forward_stats(lib_built, B, M, N, d, off, ls, force_slow):
     assert (col_lse - c).abs().max() < 2e-3
 
 
+@pytest.mark.parametrize("B,M,N,d,off,ls", [
+    (1, 256, 256, 512, 0, 2.6592),
+    (2, 256, 512, 128, 128, 3.4),
+    (1, 1024, 2048, 256, 512, 1.0),
+    (1, 256, 256, 64, 0, 4.6052),   # bound given but s too large: must take the general path
+])
+def test_tc_forward_stats_static_shift(lib_built, B, M, N, d, off, ls):
+    """caller-supplied |a.b| bound -> static-shift epilogue (one exp, no running max)."""
+    from multimodal_2025_b200 import ops
+    a, b = make(B, M, N, d, 4, spread=2.0)
+    scale = torch.tensor([ls], device="cuda")
+    row_lse, cmax, csum, diag = ops.sim_fwd(a, b, None, None, None, scale, ops.SCALE_LOG,
+                                            4.6052, ops.SIM_PLAIN, off, True, ops.IMPL_TC,
+                                            ops.DOT_BOUND_NORMALIZED)
+    s = float(torch.tensor(min(ls, 4.6052)).exp())
+    r, c, dg = ref_stats(a, b, s, off)
+    col_lse = cmax + csum.log()
+    assert torch.allclose(diag, dg, atol=2e-3 * s, rtol=0)
+    assert (row_lse - r).abs().max() < 2e-3
+    assert (col_lse - c).abs().max() < 2e-3
+
+
 def test_tc_matches_simt_on_adversarial_range(lib_built):
     """duplicates (cos = 1) next to unrelated pairs at s = 100: > 87 nats inside one block."""
     from multimodal_2025_b200 import ops
