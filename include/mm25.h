@@ -64,6 +64,12 @@ void mm25_debug_set_g_panel_bytes(size_t bytes);
  * a_mn / b_mn = 1 when the bf16 operand is stored [K, M] / [K, N] instead of [M, K] / [N, K]. */
 int mm25_debug_gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, float* C, int64_t Mg,
                          int64_t Ng, int64_t K, float alpha, int accumulate, void* stream);
+/* test hook: two GEMMs sharing Ng in one grouped launch, C0[M0,Ng] = op(A0) op(B0) and
+ * C1[M1,Ng] = op(A1) op(B1) (the dA / dB pair of the tensor-core backward). */
+int mm25_debug_gemm_grouped(const void* A0, int a0_mn, const void* B0, int b0_mn, float* C0,
+                            int64_t M0, int64_t K0, const void* A1, int a1_mn, const void* B1,
+                            int b1_mn, float* C1, int64_t M1, int64_t K1, int64_t Ng,
+                            void* stream);
 /* 1 if the current device is compute capability 10.x, else 0. */
 int mm25_device_ok(void);
 

@@ -1,4 +1,4 @@
-// gemm_tc.cu — bf16 tcgen05 GEMM used by the tensor-core backward:
+// gemm_tc.cu — bf16 tcgen05 GEMMs of the tensor-core backward:
 //     C[Mg, Ng] (fp32)  (+)=  alpha * Aop[Mg, K] * Bop[K, Ng]
 // Operands are fed by TMA straight from their natural row-major storage, so each of them may
 // be "K-major" (memory [rows = M/N index, cols = K]) or "MN-major" (memory [rows = K,
@@ -6,6 +6,15 @@
 //   dA = G  . Yhat   : A = G   K-major  [R, N],   B = Yhat MN-major [N, d]
 //   dB = G^T. Xhat   : A = G   MN-major [R, N],   B = Xhat MN-major [R, d]
 // Tile 128 x 256 x 64, 4-stage TMA ring, 2 TMEM accumulator stages, persistent CTAs.
+//
+// One launch runs up to TWO problems that share Ng (the "grouped" kernel): with separate
+// launches each problem pays its own wave quantisation (256 and 512 tiles on 148 SMs: 86 %),
+// together 1024 cost units level out at 7 per SM (98.8 %).  Work is assigned by a static
+// host-computed schedule (deterministic, no atomics): CTAs form groups of Ng/256 neighbours
+// that walk the same list of m-blocks, CTA g of a group owning n-tile g, so the two CTAs that
+// read one G tile run side by side and share it in L2.  Every group first takes its m-blocks
+// of the long-K problem round-robin, then a contiguous run of m-blocks of the short-K problem
+// sized by water-filling.
 #include "tc_common.cuh"
 #include "gemm_tc.h"
 
@@ -27,22 +36,63 @@ struct Smem {
   uint64_t acc_full[NACC], acc_empty[NACC];
   uint32_t tmem_base;
 };
+
+struct Problem {
+  CUtensorMap ta, tb;
+  float* C;
+  int64_t ldc;
+  int nk;          // K / BK
+  int mblocks;     // Mg / BM
+  int a_mn, b_mn;
+  int accumulate;
+  float alpha;
+};
+
+// groups [0, r) are class A, the rest class B; problem 0 is walked round-robin over groups
+// (nb0 blocks each), problem 1 in contiguous runs (ns blocks each, class A runs first).
+struct Schedule {
+  int group;       // CTAs per group = Ng / BN
+  int ngroups;
+  int r;
+  int nbA, nbB;
+  int nsA, nsB;
+};
+
+struct Params {
+  Problem p[2];
+  Schedule s;
+  const float* alpha_dev;
+};
+
+// job k of group `grp`: which problem and which m-block; false when the list is exhausted
+__device__ __forceinline__ bool job_at(const Params& P, int grp, int k, int* prob, int* mb) {
+  const Schedule& s = P.s;
+  const bool A = grp < s.r;
+  const int nb = A ? s.nbA : s.nbB;
+  if (k < nb) {
+    *prob = 0;
+    *mb = grp + k * s.ngroups;
+    return *mb < P.p[0].mblocks;
+  }
+  const int ks = k - nb;
+  const int ns = A ? s.nsA : s.nsB;
+  if (ks >= ns) return false;
+  const int base = A ? grp * s.nsA : s.r * s.nsA + (grp - s.r) * s.nsB;
+  *prob = 1;
+  *mb = base + ks;
+  return *mb < P.p[1].mblocks;
+}
 }  // namespace g
 
-template <int A_MN, int B_MN>
 __global__ void __launch_bounds__(g::THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
-               const __grid_constant__ CUtensorMap tmap_b, float* __restrict__ C, int64_t ldc,
-               int Mg, int Ng, int K, float alpha, const float* __restrict__ alpha_dev,
-               int accumulate) {
+gemm_grouped_kernel(const __grid_constant__ g::Params P) {
   using namespace g;
   extern __shared__ uint8_t smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                       ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tiles_m = Mg / BM, tiles_n = Ng / BN;
-  const int ntiles = tiles_m * tiles_n;
-  const int nk = K / BK;
+  const int grp = blockIdx.x / P.s.group, nt = blockIdx.x % P.s.group;
+  const int n0 = nt * BN;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < NST; ++i) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 1); }
@@ -51,7 +101,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
   }
   if (warp == 0) {
     tmem_alloc(&sm.tmem_base, 512);
-    if (lane == 0) { tma_prefetch_desc(&tmap_a); tma_prefetch_desc(&tmap_b); }
+    if (lane == 0) {
+      tma_prefetch_desc(&P.p[0].ta); tma_prefetch_desc(&P.p[0].tb);
+      tma_prefetch_desc(&P.p[1].ta); tma_prefetch_desc(&P.p[1].tb);
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -61,26 +114,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
   if (warp == 0) {
     if (lane == 0) {
       uint32_t st = 0, ph = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        // n fastest: consecutive CTAs share the A rows (G is the big operand)
-        const int m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
-        for (int kb = 0; kb < nk; ++kb) {
+      int prob, mb;
+      for (int k = 0; job_at(P, grp, k, &prob, &mb); ++k) {
+        const Problem& pr = P.p[prob];
+        const int m0 = mb * BM;
+        for (int kb = 0; kb < pr.nk; ++kb) {
           const int k0 = kb * BK;
           mbar_wait(&sm.empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&sm.full[st], A_BYTES + B_BYTES);
-          if (A_MN) {
+          if (pr.a_mn) {
 #pragma unroll
             for (int at = 0; at < BM / 64; ++at)
-              tma_load_2d(sm.a[st] + at * 8192, &tmap_a, &sm.full[st], m0 + at * 64, k0);
+              tma_load_2d(sm.a[st] + at * 8192, &pr.ta, &sm.full[st], m0 + at * 64, k0);
           } else {
-            tma_load_2d(sm.a[st], &tmap_a, &sm.full[st], k0, m0);
+            tma_load_2d(sm.a[st], &pr.ta, &sm.full[st], k0, m0);
           }
-          if (B_MN) {
+          if (pr.b_mn) {
 #pragma unroll
             for (int at = 0; at < BN / 64; ++at)
-              tma_load_2d(sm.b[st] + at * 8192, &tmap_b, &sm.full[st], n0 + at * 64, k0);
+              tma_load_2d(sm.b[st] + at * 8192, &pr.tb, &sm.full[st], n0 + at * 64, k0);
           } else {
-            tma_load_2d(sm.b[st], &tmap_b, &sm.full[st], k0, n0);
+            tma_load_2d(sm.b[st], &pr.tb, &sm.full[st], k0, n0);
           }
           if (++st == NST) { st = 0; ph ^= 1; }
         }
@@ -88,9 +142,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
       uint32_t st = 0, ph = 0, as = 0, accph = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      int prob, mb;
+      for (int k = 0; job_at(P, grp, k, &prob, &mb); ++k) {
+        const Problem& pr = P.p[prob];
+        const int a_mn = pr.a_mn, b_mn = pr.b_mn, nk = pr.nk;
+        const uint32_t idesc = make_idesc_bf16(BM, BN, a_mn, b_mn);
+        // K-major: +32 B per 16 k inside the 128 B swizzle row; SBO = 8 rows.
+        // MN-major: +16 k-rows (2048 B); LBO = next 64-wide MN atom, SBO = 8 k-rows.
+        const uint32_t a_step = a_mn ? 2048 : 32, a_lbo = a_mn ? 8192 : 16;
+        const uint32_t b_step = b_mn ? 2048 : 32, b_lbo = b_mn ? 8192 : 16;
         mbar_wait(&sm.acc_empty[as], accph ^ 1);
         tc_fence_after();
         const uint32_t dcol = tmem + as * BN;
@@ -100,14 +161,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
           const uint32_t abase = smem_u32(sm.a[st]);
           const uint32_t bbase = smem_u32(sm.b[st]);
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            // K-major: +32 B per 16 k inside the 128 B swizzle row; SBO = 8 rows.
-            // MN-major: +16 k-rows (2048 B); LBO = next 64-wide MN atom, SBO = 8 k-rows.
-            const uint64_t ad = A_MN ? make_smem_desc(abase + k * 2048, 8192, 1024)
-                                     : make_smem_desc(abase + k * 32, 16, 1024);
-            const uint64_t bd = B_MN ? make_smem_desc(bbase + k * 2048, 8192, 1024)
-                                     : make_smem_desc(bbase + k * 32, 16, 1024);
-            umma_bf16(dcol, ad, bd, idesc, (kb | k) != 0);
+          for (int kk = 0; kk < BK / 16; ++kk) {
+            const uint64_t ad = make_smem_desc(abase + kk * a_step, a_lbo, 1024);
+            const uint64_t bd = make_smem_desc(bbase + kk * b_step, b_lbo, 1024);
+            umma_bf16(dcol, ad, bd, idesc, (kb | kk) != 0);
           }
           umma_commit(&sm.empty[st]);
           if (++st == NST) { st = 0; ph ^= 1; }
@@ -118,11 +175,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
   } else {
     const int q = warp & 3;
-    const float al = alpha * (alpha_dev ? __ldg(alpha_dev) : 1.f);
+    const float ad = P.alpha_dev ? __ldg(P.alpha_dev) : 1.f;
     uint32_t as = 0, accph = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const int m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
-      float* crow = C + (int64_t)(m0 + q * 32 + lane) * ldc + n0;
+    int prob, mb;
+    for (int k = 0; job_at(P, grp, k, &prob, &mb); ++k) {
+      const Problem& pr = P.p[prob];
+      const float al = pr.alpha * ad;
+      const int accumulate = pr.accumulate;
+      float* crow = pr.C + (int64_t)(mb * BM + q * 32 + lane) * pr.ldc + n0;
       mbar_wait(&sm.acc_full[as], accph);
       tc_fence_after();
 #pragma unroll 1
@@ -165,41 +225,93 @@ static int sm_count_g() {
 
 bool gemm_eligible(int64_t Mg, int64_t Ng, int64_t K) {
   return Mg > 0 && Ng > 0 && K > 0 && Mg % g::BM == 0 && Ng % g::BN == 0 && K % g::BK == 0 &&
-         Mg < (1ll << 31) && Ng < (1ll << 31) && K < (1ll << 31);
+         Ng / g::BN <= 16 && Mg < (1ll << 31) && Ng < (1ll << 31) && K < (1ll << 31);
 }
 
-template <int A_MN, int B_MN>
-static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, float* C, int64_t ldc,
-                    int64_t Mg, int64_t Ng, int64_t K, float alpha, const float* alpha_dev,
-                    int accumulate, cudaStream_t st) {
+static int fill_problem(g::Problem* p, const GemmDesc& d, int64_t Ng) {
+  int rc;
+  if (d.a_mn) rc = make_tmap_bf16(&p->ta, d.A, (uint64_t)d.K, (uint64_t)d.Mg, 64, 64);
+  else rc = make_tmap_bf16(&p->ta, d.A, (uint64_t)d.Mg, (uint64_t)d.K, g::BM, 64);
+  if (rc) return rc;
+  if (d.b_mn) rc = make_tmap_bf16(&p->tb, d.B, (uint64_t)d.K, (uint64_t)Ng, 64, 64);
+  else rc = make_tmap_bf16(&p->tb, d.B, (uint64_t)Ng, (uint64_t)d.K, g::BN, 64);
+  if (rc) return rc;
+  p->C = d.C;
+  p->ldc = d.ldc;
+  p->nk = (int)(d.K / g::BK);
+  p->mblocks = (int)(d.Mg / g::BM);
+  p->a_mn = d.a_mn;
+  p->b_mn = d.b_mn;
+  p->accumulate = d.accumulate;
+  p->alpha = d.alpha;
+  return MM25_OK;
+}
+
+// static schedule: problem 0 = the one with the longer K (costlier blocks), see file header
+void gemm_schedule(int64_t mb0, int64_t nk0, int64_t mb1, int64_t nk1, int ngroups, int* r,
+                   int* nbA, int* nbB, int* nsA, int* nsB) {
+  const int64_t q = mb0 / ngroups, rem = mb0 % ngroups;
+  *r = (int)rem;
+  *nbA = (int)(q + (rem ? 1 : 0));
+  *nbB = (int)q;
+  if (rem == 0) { *r = ngroups; *nbA = (int)q; }
+  *nsA = *nsB = 0;
+  if (mb1 <= 0) return;
+  // water-filling over the finishing level T (in k-blocks)
+  const int64_t la = (int64_t)(*nbA) * nk0, lb = (int64_t)(*nbB) * nk0;
+  const int64_t na = *r, nb = ngroups - *r;
+  int64_t T = (mb0 * nk0 + mb1 * nk1 + ngroups - 1) / ngroups;
+  if (T < la) T = la;
+  for (;;) {
+    const int64_t xa = T > la ? (T - la) / nk1 : 0, xb = T > lb ? (T - lb) / nk1 : 0;
+    if (na * xa + nb * xb >= mb1) { *nsA = (int)xa; *nsB = (int)xb; return; }
+    // next level at which some group can take one more block
+    const int64_t ta = la + (xa + 1) * nk1, tb = lb + (xb + 1) * nk1;
+    T = (nb > 0 && tb < ta) ? tb : ta;
+  }
+}
+
+int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float* alpha_dev,
+                 cudaStream_t st) {
+  if (!d0 && !d1) return MM25_OK;
+  if (!d0) { d0 = d1; d1 = nullptr; }
+  if (d1 && d1->K > d0->K) { const GemmDesc* t = d0; d0 = d1; d1 = t; }
+  if (!gemm_eligible(d0->Mg, Ng, d0->K)) return MM25_ERR_SHAPE;
+  if (d1 && !gemm_eligible(d1->Mg, Ng, d1->K)) return MM25_ERR_SHAPE;
+  g::Params P;
+  memset(&P, 0, sizeof(P));
+  int rc = fill_problem(&P.p[0], *d0, Ng);
+  if (rc) return rc;
+  if (d1) {
+    rc = fill_problem(&P.p[1], *d1, Ng);
+    if (rc) return rc;
+  } else {
+    P.p[1] = P.p[0];
+    P.p[1].mblocks = 0;
+  }
+  P.alpha_dev = alpha_dev;
+  const int group = (int)(Ng / g::BN);
+  int ngroups = sm_count_g() / group;
+  const int64_t total_mb = P.p[0].mblocks + (int64_t)P.p[1].mblocks;
+  if (ngroups > total_mb) ngroups = (int)total_mb;
+  if (ngroups < 1) ngroups = 1;
+  P.s.group = group;
+  P.s.ngroups = ngroups;
+  gemm_schedule(P.p[0].mblocks, P.p[0].nk, P.p[1].mblocks, P.p[1].nk, ngroups, &P.s.r,
+                &P.s.nbA, &P.s.nbB, &P.s.nsA, &P.s.nsB);
   const size_t smem = sizeof(g::Smem) + 1024;
-  MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<A_MN, B_MN>,
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_grouped_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int64_t ntiles = (Mg / g::BM) * (Ng / g::BN);
-  const int grid = (int)(ntiles < sm_count_g() ? ntiles : sm_count_g());
-  gemm_tc_kernel<A_MN, B_MN><<<grid, g::THREADS, smem, st>>>(
-      ta, tb, C, ldc, (int)Mg, (int)Ng, (int)K, alpha, alpha_dev, accumulate);
+  gemm_grouped_kernel<<<ngroups * group, g::THREADS, smem, st>>>(P);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }
 
-// a_rows/a_cols (b_rows/b_cols): the row-major bf16 matrix as stored in memory.
 int gemm_bf16(const void* A, int a_mn, const void* Bm, int b_mn, float* C, int64_t ldc,
               int64_t Mg, int64_t Ng, int64_t K, float alpha, const float* alpha_dev,
               int accumulate, cudaStream_t st) {
-  if (!gemm_eligible(Mg, Ng, K)) return MM25_ERR_SHAPE;
-  CUtensorMap ta, tb;
-  int rc;
-  if (a_mn) rc = make_tmap_bf16(&ta, A, (uint64_t)K, (uint64_t)Mg, 64, 64);
-  else rc = make_tmap_bf16(&ta, A, (uint64_t)Mg, (uint64_t)K, g::BM, 64);
-  if (rc) return rc;
-  if (b_mn) rc = make_tmap_bf16(&tb, Bm, (uint64_t)K, (uint64_t)Ng, 64, 64);
-  else rc = make_tmap_bf16(&tb, Bm, (uint64_t)Ng, (uint64_t)K, g::BN, 64);
-  if (rc) return rc;
-  if (a_mn && b_mn) return launch_t<1, 1>(ta, tb, C, ldc, Mg, Ng, K, alpha, alpha_dev, accumulate, st);
-  if (a_mn) return launch_t<1, 0>(ta, tb, C, ldc, Mg, Ng, K, alpha, alpha_dev, accumulate, st);
-  if (b_mn) return launch_t<0, 1>(ta, tb, C, ldc, Mg, Ng, K, alpha, alpha_dev, accumulate, st);
-  return launch_t<0, 0>(ta, tb, C, ldc, Mg, Ng, K, alpha, alpha_dev, accumulate, st);
+  GemmDesc d{A, Bm, C, ldc, Mg, K, a_mn, b_mn, accumulate, alpha};
+  return gemm_grouped(&d, nullptr, Ng, alpha_dev, st);
 }
 
 }  // namespace tc
@@ -211,4 +323,14 @@ extern "C" int mm25_debug_gemm_bf16(const void* A, int a_mn, const void* B, int 
                                     int accumulate, void* stream) {
   return mm25::tc::gemm_bf16(A, a_mn, B, b_mn, C, Ng, Mg, Ng, K, alpha, nullptr, accumulate,
                              (cudaStream_t)stream);
+}
+
+// debug / test entry: two problems sharing Ng in one launch (C0 = A0 op B0, C1 = A1 op B1)
+extern "C" int mm25_debug_gemm_grouped(const void* A0, int a0_mn, const void* B0, int b0_mn,
+                                       float* C0, int64_t M0, int64_t K0, const void* A1,
+                                       int a1_mn, const void* B1, int b1_mn, float* C1,
+                                       int64_t M1, int64_t K1, int64_t Ng, void* stream) {
+  mm25::tc::GemmDesc d0{A0, B0, C0, Ng, M0, K0, a0_mn, b0_mn, 0, 1.f};
+  mm25::tc::GemmDesc d1{A1, B1, C1, Ng, M1, K1, a1_mn, b1_mn, 0, 1.f};
+  return mm25::tc::gemm_grouped(&d0, &d1, Ng, nullptr, (cudaStream_t)stream);
 }

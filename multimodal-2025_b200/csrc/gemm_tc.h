@@ -1,4 +1,4 @@
-// gemm_tc.h — host interface of the bf16 tcgen05 GEMM (gemm_tc.cu).
+// gemm_tc.h — host interface of the bf16 tcgen05 GEMMs (gemm_tc.cu).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -6,7 +6,26 @@
 namespace mm25 {
 namespace tc {
 bool gemm_eligible(int64_t Mg, int64_t Ng, int64_t K);
-// C[Mg,Ng] fp32 (+)= alpha * alpha_dev[0] * Aop * Bop.  a_mn / b_mn: operand stored [K, MN].
+
+// One problem  C[Mg, Ng] fp32 (+)= alpha * Aop[Mg, K] * Bop[K, Ng]  (bf16 operands).
+// a_mn / b_mn = 1: the operand is stored [K, Mg] / [K, Ng] instead of [Mg, K] / [Ng, K].
+struct GemmDesc {
+  const void* A;
+  const void* B;
+  float* C;
+  int64_t ldc;
+  int64_t Mg, K;
+  int a_mn, b_mn;
+  int accumulate;
+  float alpha;
+};
+
+// Up to two problems sharing Ng in ONE persistent launch with a static balanced schedule
+// (either pointer may be NULL).  alpha_dev: optional device scalar multiplied into both.
+int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float* alpha_dev,
+                 cudaStream_t st);
+
+// single problem (wrapper over gemm_grouped)
 int gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, float* C, int64_t ldc,
               int64_t Mg, int64_t Ng, int64_t K, float alpha, const float* alpha_dev,
               int accumulate, cudaStream_t st);

@@ -314,13 +314,12 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
           dot_bound);
       MM25_LAUNCH_CHECK();
       part += sms;
-      if (da) {
-        rc = gemm_bf16(G, 0, b_b, 1, da + (bz * M + p0) * d, d, rows, d, N, 1.f, nullptr, 0, st);
-        if (rc) return rc;
-      }
-      if (db) {
-        rc = gemm_bf16(G, 1, a_b + p0 * d, 1, db + bz * N * d, d, N, d, rows, 1.f, nullptr,
-                       p0 > 0 ? 1 : 0, st);
+      {
+        // dA[panel] = G . Yhat and dB += G^T . Xhat[panel] in one grouped launch
+        GemmDesc ga{G, b_b, da ? da + (bz * M + p0) * d : nullptr, d, rows, N, 0, 1, 0, 1.f};
+        GemmDesc gb{G, a_b + p0 * d, db ? db + bz * N * d : nullptr, d, N, rows, 1, 1,
+                    p0 > 0 ? 1 : 0, 1.f};
+        rc = gemm_grouped(da ? &ga : nullptr, db ? &gb : nullptr, d, nullptr, st);
         if (rc) return rc;
       }
     }

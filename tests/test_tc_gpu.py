@@ -118,3 +118,27 @@ def test_tc_gemm_layouts(lib_built, a_mn, b_mn, Mg, Ng, K, acc):
     torch.cuda.synchronize()
     err = (C - ref).abs().max().item()
     assert err < 1e-2 * max(1.0, ref.abs().max().item() / 10), err
+
+
+@pytest.mark.parametrize("M0,K0,M1,K1,Ng", [(256, 2048, 2048, 256, 512), (128, 512, 512, 128, 256),
+                                            (1024, 4096, 4096, 1024, 512), (384, 640, 640, 384, 1024)])
+def test_tc_gemm_grouped_pair(lib_built, M0, K0, M1, K1, Ng):
+    """dA = G . Y (K-major x MN-major) and dB = G^T . X (MN x MN) in one scheduled launch."""
+    from multimodal_2025_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator(device="cpu").manual_seed(M0 + K0)
+    G = torch.randn(M0, K0, generator=g).cuda().bfloat16()      # [R, N]
+    Y = torch.randn(K0, Ng, generator=g).cuda().bfloat16()      # [N, d]
+    X = torch.randn(K1, Ng, generator=g).cuda().bfloat16()      # [R, d]
+    assert M1 == K0 and K1 == M0
+    C0 = torch.zeros(M0, Ng, device="cuda")
+    C1 = torch.zeros(M1, Ng, device="cuda")
+    rc = L.mm25_debug_gemm_grouped(G.data_ptr(), 0, Y.data_ptr(), 1, C0.data_ptr(), M0, K0,
+                                   G.data_ptr(), 1, X.data_ptr(), 1, C1.data_ptr(), M1, K1, Ng,
+                                   torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    r0 = G.float() @ Y.float()
+    r1 = G.float().t() @ X.float()
+    assert (C0 - r0).abs().max().item() < 1e-2 * max(1.0, r0.abs().max().item() / 10)
+    assert (C1 - r1).abs().max().item() < 1e-2 * max(1.0, r1.abs().max().item() / 10)
