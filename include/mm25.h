@@ -187,6 +187,53 @@ int mm25_hopfield_bwd_pass(const float* a, const float* b, const float* a2, cons
                            float beta, const float* lse, const float* D, int stat_by_col,
                            float* out, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * vCLIP sampling path (losses/vclipLoss.py:98-121, losses/distributions/*.py, power_spherical).
+ * All tensors fp32.  Sample layout is sample-major [S, B, d] as the reference returns
+ * (VonMisesFisher.py:238-239).  Noise: pass the draws the reference would make (parity mode)
+ * or NULL to generate them in-kernel with Philox4x32-10 keyed by `seed` (the backward
+ * regenerates the same noise from the same seed).
+ * ------------------------------------------------------------------------------------------ */
+/* ProjectedNormal.rsample (ProjectedNormal.py:41-49): out = (mu + sigma*eps)/||.||;
+ * eps_in [S,B,d] or NULL; inv_norm [S,B] (saved for the backward). */
+int mm25_sample_projnormal_fwd(const float* mu, const float* sigma, const float* eps_in,
+                               uint64_t seed, int64_t S, int64_t B, int64_t d, float* out,
+                               float* inv_norm, void* stream);
+/* its backward: dmu, dsigma [B,d] (sum over the S samples). */
+int mm25_sample_projnormal_bwd(const float* gout, const float* y, const float* inv_norm,
+                               const float* eps_in, uint64_t seed, int64_t S, int64_t B,
+                               int64_t d, float* dmu, float* dsigma, void* stream);
+/* x = [t, sqrt(1-t^2) v/nv], y = Householder(e1 -> loc) x.  t [S,B], loc [B,d], v_in [S,B,d-1]
+ * or NULL.  nv = max(||v||, v_clamp) + v_add; u = (e1-loc)/(max(||e1-loc||, h_clamp) + h_add);
+ * 1-t^2 clamped below by omt2_min when omt2_min >= 0.
+ * vMF (VonMisesFisher.py:181-183,224-236): 1e-10, 0, 1e-10, 0, -1.
+ * PowerSpherical (power_spherical _TTransform/_HouseholderRotationTransform): 0, 1e-7, 0, 1e-7, 1e-7. */
+int mm25_sphere_sample_fwd(const float* t, const float* loc, const float* v_in, uint64_t seed,
+                           int64_t S, int64_t B, int64_t d, float v_clamp, float v_add,
+                           float h_clamp, float h_add, float omt2_min, float* out, void* stream);
+/* backward: dloc [B,d] (sum over samples) and dt [S,B] from gout, the samples y, t and loc. */
+int mm25_sphere_sample_bwd(const float* gout, const float* y, const float* t, const float* loc,
+                           int64_t S, int64_t B, int64_t d, float v_clamp, float v_add,
+                           float h_clamp, float h_add, float omt2_min, float* dloc, float* dt,
+                           void* stream);
+/* Wood's rejection sampler of the vMF marginal (VonMisesFisher.py:184-222): w [S,B].
+ * prop_eps/prop_u [B,P]: injected Beta((d-1)/2,(d-1)/2) / Uniform proposals scanned in order
+ * (count[b] = accepted, missing entries NaN); NULL: Philox. */
+int mm25_vmf_sample_w(const float* kappa, int64_t d, int64_t S, int64_t B, uint64_t seed,
+                      const float* prop_eps, const float* prop_u, int64_t P, float* w_out,
+                      int* count, void* stream);
+/* z[s,b] ~ Beta(alpha_b, beta_b) (PowerSpherical marginal, t = 2z-1). */
+int mm25_beta_sample(const float* alpha, const float* beta, int64_t S, int64_t B, uint64_t seed,
+                     float* z, void* stream);
+/* implicit-reparameterisation gradient dz/dalpha of Beta draws (what the backward of
+ * torch.distributions.Beta.rsample evaluates: (1-z) * dirichlet_grad_one(z, alpha, alpha+beta)). */
+int mm25_beta_grad(const float* z, const float* alpha, const float* beta, int64_t S, int64_t B,
+                   float* dz_dalpha, void* stream);
+/* log I_nu(kappa) and log I_{nu+1}(kappa) in fp64 (VonMisesFisher.py:19-62 mpmath round trip);
+ * either output may be NULL. */
+int mm25_log_bessel(const double* kappa, int64_t n, double nu, double* log_i_nu,
+                    double* log_i_nu1, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

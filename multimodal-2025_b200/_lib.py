@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(LIB_DIR, "libmm25.so")
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 
 SOURCES = ["prep.cu", "sim_simt.cu", "sim_tc.cu", "sim_tc_bwd.cu", "gemm_tc.cu", "api_sim.cu",
-           "hopfield.cu", "samplers.cu", "bessel.cu", "topk.cu"]
+           "hopfield.cu", "samplers.cu", "beta_vmf.cu", "bessel.cu", "topk.cu"]
 
 _lock = threading.Lock()
 _lib = None
@@ -77,6 +77,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 _i64, _int, _f32, _vp, _sz = (ctypes.c_int64, ctypes.c_int, ctypes.c_float, ctypes.c_void_p,
                               ctypes.c_size_t)
+_u64, _f64 = ctypes.c_uint64, ctypes.c_double
 
 # name -> (restype, argtypes); must list every symbol include/mm25.h declares
 SIGNATURES = {
@@ -101,6 +102,17 @@ SIGNATURES = {
     "mm25_sim_bwd": (_int, [_vp, _vp, _int, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp, _int,
                             _f32, _int, _i64, _vp, _vp, _f32, _f32, _f32, _f32, _vp, _vp, _vp, _vp,
                             _vp, _vp, _sz, _int, _f32, _vp]),
+    "mm25_sample_projnormal_fwd": (_int, [_vp, _vp, _vp, _u64, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "mm25_sample_projnormal_bwd": (_int, [_vp, _vp, _vp, _vp, _u64, _i64, _i64, _i64, _vp, _vp,
+                                          _vp]),
+    "mm25_sphere_sample_fwd": (_int, [_vp, _vp, _vp, _u64, _i64, _i64, _i64, _f32, _f32, _f32,
+                                      _f32, _f32, _vp, _vp]),
+    "mm25_sphere_sample_bwd": (_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _f32, _f32,
+                                      _f32, _f32, _vp, _vp, _vp]),
+    "mm25_vmf_sample_w": (_int, [_vp, _i64, _i64, _i64, _u64, _vp, _vp, _i64, _vp, _vp, _vp]),
+    "mm25_beta_sample": (_int, [_vp, _vp, _i64, _i64, _u64, _vp, _vp]),
+    "mm25_beta_grad": (_int, [_vp, _vp, _vp, _i64, _i64, _vp, _vp]),
+    "mm25_log_bessel": (_int, [_vp, _i64, _f64, _vp, _vp, _vp]),
     "mm25_rowdot": (_int, [_vp, _vp, _vp, _i64, _i64, _vp]),
     "mm25_hopfield_bwd_pass": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _vp,
                                       _vp, _int, _vp, _vp]),

@@ -1,0 +1,62 @@
+// philox.cuh — Philox4x32-10 counter-based RNG (Salmon et al., SC'11) for the sampler kernels.
+// Stateless: the 128-bit counter is (element index, stream id) and the key is the 64-bit seed,
+// so forward and backward kernels regenerate identical noise without storing it.
+#pragma once
+#include <stdint.h>
+
+namespace mm25 {
+namespace rng {
+
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+  const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+  const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+  const uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+  c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+}
+
+// 4 x 32 random bits for counter (idx, stream) under key `seed`
+__device__ __forceinline__ void philox4(uint64_t seed, uint64_t idx, uint64_t stream,
+                                        uint32_t (&out)[4]) {
+  uint32_t c[4] = {(uint32_t)idx, (uint32_t)(idx >> 32), (uint32_t)stream,
+                   (uint32_t)(stream >> 32)};
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    philox_round(c, k0, k1);
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) out[i] = c[i];
+}
+
+// uniform in (0, 1]: never 0, so log() is finite
+__device__ __forceinline__ float u01(uint32_t x) {
+  return ((float)(x >> 8) + 1.0f) * (1.0f / 16777216.0f);
+}
+
+// 4 standard normals (Box-Muller) for counter (idx, stream)
+__device__ __forceinline__ void normal4(uint64_t seed, uint64_t idx, uint64_t stream,
+                                        float (&z)[4]) {
+  uint32_t r[4];
+  philox4(seed, idx, stream, r);
+#pragma unroll
+  for (int p = 0; p < 2; ++p) {
+    const float u1 = u01(r[2 * p]), u2 = u01(r[2 * p + 1]);
+    const float rad = sqrtf(-2.0f * __logf(u1));
+    float sn, cs;
+    __sincosf(6.283185307179586f * u2, &sn, &cs);
+    z[2 * p] = rad * cs;
+    z[2 * p + 1] = rad * sn;
+  }
+}
+
+// element k of a row of standard normals: rows are keyed by `row`, 4 elements per counter
+__device__ __forceinline__ float normal_at(uint64_t seed, uint64_t row, int k, uint64_t stream) {
+  float z[4];
+  normal4(seed, row * 0x100000ull + (uint64_t)(k >> 2), stream, z);
+  return z[k & 3];
+}
+
+}  // namespace rng
+}  // namespace mm25

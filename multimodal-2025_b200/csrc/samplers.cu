@@ -1,0 +1,380 @@
+// samplers.cu — HBM-bound warp-per-row kernels of the vCLIP sampling path.
+//   ProjectedNormal.rsample          losses/distributions/ProjectedNormal.py:41-49
+//   [t, sqrt(1-t^2) v] + Householder VonMisesFisher.py:180-183,224-236; power_spherical
+//                                    _TTransform / _HouseholderRotationTransform
+// One warp owns one output row [d] (forward) or one distribution row b over all S samples
+// (backward, so the parameter gradients reduce in registers / shared memory without atomics).
+// Rows are processed in groups of 4 consecutive elements per lane: 16-byte loads / stores when
+// d % 4 == 0, scalar otherwise.  Noise is either injected by the caller (parity mode: the
+// deterministic transform is compared with the reference given identical draws) or generated
+// in-kernel with Philox4x32-10 keyed by (seed, row, element) and regenerated in the backward.
+#include "common.cuh"
+#include "philox.cuh"
+
+namespace mm25 {
+
+struct F4 { float v[4]; };
+
+__device__ __forceinline__ F4 load4(const float* __restrict__ p, int k0, int d, bool vec) {
+  F4 r;
+  if (vec) {
+    const float4 t = *reinterpret_cast<const float4*>(p + k0);
+    r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w;
+  } else {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) r.v[e] = (k0 + e < d) ? p[k0 + e] : 0.f;
+  }
+  return r;
+}
+__device__ __forceinline__ void store4(float* __restrict__ p, int k0, int d, bool vec,
+                                       const F4& r) {
+  if (vec) {
+    *reinterpret_cast<float4*>(p + k0) = make_float4(r.v[0], r.v[1], r.v[2], r.v[3]);
+  } else {
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+      if (k0 + e < d) p[k0 + e] = r.v[e];
+  }
+}
+
+constexpr uint64_t STREAM_PN = 0x504e;      // ProjectedNormal noise
+constexpr uint64_t STREAM_SPHERE = 0x5348;  // tangent noise of the spherical samplers
+
+// ------------------------------------------------------------------------------------------
+// ProjectedNormal: y[s,b,:] = (mu_b + sigma_b * eps) / ||.||       (no eps in the norm, :49)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+projnormal_fwd_kernel(const float* __restrict__ mu, const float* __restrict__ sigma,
+                      const float* __restrict__ eps_in, uint64_t seed, int64_t S, int64_t B,
+                      int d, float* __restrict__ out, float* __restrict__ inv_norm) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= S * B) return;
+  const int64_t b = row % B;
+  const bool vec = (d & 3) == 0;
+  const float* mr = mu + b * d;
+  const float* sr = sigma + b * d;
+  const int ngroups = (d + 3) >> 2;
+  float ss = 0.f;
+  for (int g = lane; g < ngroups; g += 32) {
+    const int k0 = g * 4;
+    const F4 m = load4(mr, k0, d, vec), sg = load4(sr, k0, d, vec);
+    F4 e;
+    if (eps_in) e = load4(eps_in + row * d, k0, d, vec);
+    else rng::normal4(seed, (uint64_t)row * 0x100000ull + (uint64_t)g, STREAM_PN, e.v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float v = (k0 + i < d) ? fmaf(sg.v[i], e.v[i], m.v[i]) : 0.f;
+      ss = fmaf(v, v, ss);
+    }
+  }
+  ss = warp_sum(ss);
+  const float inv = 1.f / sqrtf(ss);
+  for (int g = lane; g < ngroups; g += 32) {
+    const int k0 = g * 4;
+    const F4 m = load4(mr, k0, d, vec), sg = load4(sr, k0, d, vec);
+    F4 e;
+    if (eps_in) e = load4(eps_in + row * d, k0, d, vec);
+    else rng::normal4(seed, (uint64_t)row * 0x100000ull + (uint64_t)g, STREAM_PN, e.v);
+    F4 y;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) y.v[i] = fmaf(sg.v[i], e.v[i], m.v[i]) * inv;
+    store4(out + row * d, k0, d, vec, y);
+  }
+  if (lane == 0 && inv_norm) inv_norm[row] = inv;
+}
+
+// backward: dv = (g - y (y.g)) * inv;  dmu_b = sum_s dv;  dsigma_b = sum_s dv * eps.
+// One warp per b; the [d] accumulators live in shared memory (2 d floats per warp).
+__global__ void __launch_bounds__(256)
+projnormal_bwd_kernel(const float* __restrict__ gout, const float* __restrict__ y,
+                      const float* __restrict__ inv_norm, const float* __restrict__ eps_in,
+                      uint64_t seed, int64_t S, int64_t B, int d, float* __restrict__ dmu,
+                      float* __restrict__ dsigma) {
+  extern __shared__ float acc_sm[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t b = (int64_t)blockIdx.x * 8 + warp;
+  if (b >= B) return;
+  const bool vec = (d & 3) == 0;
+  const int ngroups = (d + 3) >> 2;
+  const int dpad = ngroups * 4;
+  float* am = acc_sm + (size_t)warp * 2 * dpad;
+  float* as = am + dpad;
+  for (int k = lane; k < dpad; k += 32) { am[k] = 0.f; as[k] = 0.f; }
+  __syncwarp();
+  for (int64_t s = 0; s < S; ++s) {
+    const int64_t row = s * B + b;
+    const float* gr = gout + row * d;
+    const float* yr = y + row * d;
+    float dot = 0.f;
+    for (int g = lane; g < ngroups; g += 32) {
+      const F4 gg = load4(gr, g * 4, d, vec), yy = load4(yr, g * 4, d, vec);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dot = fmaf(gg.v[i], yy.v[i], dot);
+    }
+    dot = warp_sum(dot);
+    const float inv = inv_norm[row];
+    for (int g = lane; g < ngroups; g += 32) {
+      const int k0 = g * 4;
+      const F4 gg = load4(gr, k0, d, vec), yy = load4(yr, k0, d, vec);
+      F4 e;
+      if (eps_in) e = load4(eps_in + row * d, k0, d, vec);
+      else rng::normal4(seed, (uint64_t)row * 0x100000ull + (uint64_t)g, STREAM_PN, e.v);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float dv = (gg.v[i] - yy.v[i] * dot) * inv;
+        am[k0 + i] += dv;
+        as[k0 + i] = fmaf(dv, e.v[i], as[k0 + i]);
+      }
+    }
+  }
+  __syncwarp();
+  for (int g = lane; g < ngroups; g += 32) {
+    F4 a, c;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { a.v[i] = am[g * 4 + i]; c.v[i] = as[g * 4 + i]; }
+    if (dmu) store4(dmu + b * d, g * 4, d, vec, a);
+    if (dsigma) store4(dsigma + b * d, g * 4, d, vec, c);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Spherical samplers (vMF and PowerSpherical share the geometry):
+//   x = [t, c * v / nv],  c = sqrt(1 - t^2) (optionally clamped), nv = max(||v||, v_clamp) + v_add
+//   u = (e1 - loc) / den, den = max(||e1 - loc||, h_clamp) + h_add;   y = x - 2 (x.u) u
+// vMF  (VonMisesFisher.py:181-183,224-236): v_clamp = h_clamp = 1e-10, adds 0, no clamp on c.
+// PowerSpherical (App. B): v_add = h_add = omt2_min = 1e-7, clamps 0.
+// The tangent noise of output element k >= 1 is v_in[row, k-1] (injected) or Philox keyed by k.
+// ------------------------------------------------------------------------------------------
+struct SphereCfg {
+  float v_clamp, v_add, h_clamp, h_add, omt2_min;  // omt2_min < 0: no clamp on 1 - t^2
+};
+
+__device__ __forceinline__ F4 sphere_noise4(const float* __restrict__ v_in, int64_t row, int k0,
+                                            int d, uint64_t seed, int g) {
+  F4 e;
+  if (v_in) {
+    const float* vr = v_in + row * (int64_t)(d - 1);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int k = k0 + i;
+      e.v[i] = (k >= 1 && k < d) ? vr[k - 1] : 0.f;
+    }
+  } else {
+    rng::normal4(seed, (uint64_t)row * 0x100000ull + (uint64_t)g, STREAM_SPHERE, e.v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (k0 + i < 1 || k0 + i >= d) e.v[i] = 0.f;
+  }
+  return e;
+}
+
+__global__ void __launch_bounds__(256)
+sphere_fwd_kernel(const float* __restrict__ t_in, const float* __restrict__ loc,
+                  const float* __restrict__ v_in, uint64_t seed, int64_t S, int64_t B, int d,
+                  SphereCfg cfg, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= S * B) return;
+  const int64_t b = row % B;
+  const bool vec = (d & 3) == 0;
+  const float* mr = loc + b * d;
+  const int ngroups = (d + 3) >> 2;
+  float vv = 0.f, vmu = 0.f, mm = 0.f;
+  for (int g = lane; g < ngroups; g += 32) {
+    const int k0 = g * 4;
+    const F4 m = load4(mr, k0, d, vec);
+    const F4 e = sphere_noise4(v_in, row, k0, d, seed, g);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      vv = fmaf(e.v[i], e.v[i], vv);
+      vmu = fmaf(e.v[i], m.v[i], vmu);
+      if (k0 + i >= 1) mm = fmaf(m.v[i], m.v[i], mm);
+    }
+  }
+  vv = warp_sum(vv); vmu = warp_sum(vmu); mm = warp_sum(mm);
+  const float mu0 = mr[0];
+  const float t = t_in[row];
+  const float omt2 = 1.f - t * t;
+  const float c = sqrtf(cfg.omt2_min >= 0.f ? fmaxf(omt2, cfg.omt2_min) : omt2);
+  const float cn = c / (fmaxf(sqrtf(vv), cfg.v_clamp) + cfg.v_add);
+  const float w0 = 1.f - mu0;
+  const float den = fmaxf(sqrtf(fmaf(w0, w0, mm)), cfg.h_clamp) + cfg.h_add;
+  const float xw = t * w0 - cn * vmu;      // x . (e1 - loc)
+  const float f = 2.f * xw / (den * den);  // y = x - f * (e1 - loc)
+  for (int g = lane; g < ngroups; g += 32) {
+    const int k0 = g * 4;
+    const F4 m = load4(mr, k0, d, vec);
+    const F4 e = sphere_noise4(v_in, row, k0, d, seed, g);
+    F4 y;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int k = k0 + i;
+      const float x = (k == 0) ? t : cn * e.v[i];
+      const float w = (k == 0) ? w0 : -m.v[i];
+      y.v[i] = fmaf(-f, w, x);
+    }
+    store4(out + row * d, k0, d, vec, y);
+  }
+}
+
+// backward: one warp per b over all S samples.  dloc [B,d] (sum over s), dt [S,B].
+__global__ void __launch_bounds__(256)
+sphere_bwd_kernel(const float* __restrict__ gout, const float* __restrict__ y,
+                  const float* __restrict__ t_in, const float* __restrict__ loc, int64_t S,
+                  int64_t B, int d, SphereCfg cfg, float* __restrict__ dloc,
+                  float* __restrict__ dt) {
+  extern __shared__ float acc_sm[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t b = (int64_t)blockIdx.x * 8 + warp;
+  if (b >= B) return;
+  const bool vec = (d & 3) == 0;
+  const int ngroups = (d + 3) >> 2;
+  const int dpad = ngroups * 4;
+  float* A = acc_sm + (size_t)warp * dpad;  // sum_s dL/du
+  for (int k = lane; k < dpad; k += 32) A[k] = 0.f;
+  const float* mr = loc + b * d;
+  float mm = 0.f;
+  for (int g = lane; g < ngroups; g += 32) {
+    const F4 m = load4(mr, g * 4, d, vec);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (g * 4 + i >= 1) mm = fmaf(m.v[i], m.v[i], mm);
+  }
+  mm = warp_sum(mm);
+  const float w0 = 1.f - mr[0];
+  const float nw = sqrtf(fmaf(w0, w0, mm));
+  const float den = fmaxf(nw, cfg.h_clamp) + cfg.h_add;
+  const float iden = 1.f / den;
+  const float uu = (nw * iden) * (nw * iden);
+  __syncwarp();
+  for (int64_t s = 0; s < S; ++s) {
+    const int64_t row = s * B + b;
+    const float* gr = gout + row * d;
+    const float* yr = y + row * d;
+    float yu = 0.f, gu = 0.f;
+    for (int g = lane; g < ngroups; g += 32) {
+      const int k0 = g * 4;
+      const F4 gg = load4(gr, k0, d, vec), yy = load4(yr, k0, d, vec), m = load4(mr, k0, d, vec);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float u = ((k0 + i == 0) ? w0 : -m.v[i]) * iden;
+        yu = fmaf(yy.v[i], u, yu);
+        gu = fmaf(gg.v[i], u, gu);
+      }
+    }
+    yu = warp_sum(yu); gu = warp_sum(gu);
+    const float xu = yu * (1.f - 2.f * uu);
+    float sgx = 0.f, gx0 = 0.f;
+    for (int g = lane; g < ngroups; g += 32) {
+      const int k0 = g * 4;
+      const F4 gg = load4(gr, k0, d, vec), yy = load4(yr, k0, d, vec), m = load4(mr, k0, d, vec);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int k = k0 + i;
+        if (k < d) {
+          const float u = ((k == 0) ? w0 : -m.v[i]) * iden;
+          const float x = fmaf(-2.f * yu, u, yy.v[i]);
+          const float gx = fmaf(-2.f * gu, u, gg.v[i]);
+          A[k] += -2.f * (xu * gg.v[i] + gu * x);
+          if (k == 0) gx0 = gx; else sgx = fmaf(gx, x, sgx);
+        }
+      }
+    }
+    sgx = warp_sum(sgx);
+    gx0 = __shfl_sync(0xffffffffu, gx0, 0);
+    if (lane == 0 && dt) {
+      const float t = t_in[row];
+      const float omt2 = 1.f - t * t;
+      const bool clamped = cfg.omt2_min >= 0.f && !(omt2 > cfg.omt2_min);
+      dt[row] = clamped ? gx0 : gx0 - t / omt2 * sgx;
+    }
+  }
+  __syncwarp();
+  if (dloc) {
+    // u = w / den(w):  dL/dw = A / den - w (w.A) / (den^2 nw) when the norm is not clamped
+    float wa = 0.f;
+    for (int g = lane; g < ngroups; g += 32) {
+      const F4 m = load4(mr, g * 4, d, vec);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int k = g * 4 + i;
+        if (k < d) wa = fmaf((k == 0) ? w0 : -m.v[i], A[k], wa);
+      }
+    }
+    wa = warp_sum(wa);
+    const float corr = (nw > cfg.h_clamp && nw > 0.f) ? wa * iden * iden / nw : 0.f;
+    for (int g = lane; g < ngroups; g += 32) {
+      const F4 m = load4(mr, g * 4, d, vec);
+      F4 o;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int k = g * 4 + i;
+        const float w = (k == 0) ? w0 : -m.v[i];
+        const float dw = (k < d) ? A[k] * iden - w * corr : 0.f;
+        o.v[i] = -dw;  // w = e1 - loc
+      }
+      store4(dloc + b * d, g * 4, d, vec, o);
+    }
+  }
+}
+
+}  // namespace mm25
+
+using namespace mm25;
+
+extern "C" int mm25_sample_projnormal_fwd(const float* mu, const float* sigma,
+                                          const float* eps_in, uint64_t seed, int64_t S,
+                                          int64_t B, int64_t d, float* out, float* inv_norm,
+                                          void* stream) {
+  if (S <= 0 || B <= 0 || d <= 0 || d > (1 << 20)) return MM25_ERR_SHAPE;
+  if (!mu || !sigma || !out) return MM25_ERR_ARG;
+  projnormal_fwd_kernel<<<(unsigned)ceil_div(S * B, 8), 256, 0, (cudaStream_t)stream>>>(
+      mu, sigma, eps_in, seed, S, B, (int)d, out, inv_norm);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
+extern "C" int mm25_sample_projnormal_bwd(const float* gout, const float* y,
+                                          const float* inv_norm, const float* eps_in,
+                                          uint64_t seed, int64_t S, int64_t B, int64_t d,
+                                          float* dmu, float* dsigma, void* stream) {
+  if (S <= 0 || B <= 0 || d <= 0 || d > 4096) return MM25_ERR_SHAPE;
+  if (!gout || !y || !inv_norm) return MM25_ERR_ARG;
+  const size_t sh = sizeof(float) * 8 * 2 * (size_t)((d + 3) / 4 * 4);
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(projnormal_bwd_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+  projnormal_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, sh, (cudaStream_t)stream>>>(
+      gout, y, inv_norm, eps_in, seed, S, B, (int)d, dmu, dsigma);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
+extern "C" int mm25_sphere_sample_fwd(const float* t, const float* loc, const float* v_in,
+                                      uint64_t seed, int64_t S, int64_t B, int64_t d,
+                                      float v_clamp, float v_add, float h_clamp, float h_add,
+                                      float omt2_min, float* out, void* stream) {
+  if (S <= 0 || B <= 0 || d < 2 || d > (1 << 20)) return MM25_ERR_SHAPE;
+  if (!t || !loc || !out) return MM25_ERR_ARG;
+  SphereCfg cfg{v_clamp, v_add, h_clamp, h_add, omt2_min};
+  sphere_fwd_kernel<<<(unsigned)ceil_div(S * B, 8), 256, 0, (cudaStream_t)stream>>>(
+      t, loc, v_in, seed, S, B, (int)d, cfg, out);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
+extern "C" int mm25_sphere_sample_bwd(const float* gout, const float* y, const float* t,
+                                      const float* loc, int64_t S, int64_t B, int64_t d,
+                                      float v_clamp, float v_add, float h_clamp, float h_add,
+                                      float omt2_min, float* dloc, float* dt, void* stream) {
+  if (S <= 0 || B <= 0 || d < 2 || d > 8192) return MM25_ERR_SHAPE;
+  if (!gout || !y || !t || !loc) return MM25_ERR_ARG;
+  SphereCfg cfg{v_clamp, v_add, h_clamp, h_add, omt2_min};
+  const size_t sh = sizeof(float) * 8 * (size_t)((d + 3) / 4 * 4);
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(sphere_bwd_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+  sphere_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, sh, (cudaStream_t)stream>>>(
+      gout, y, t, loc, S, B, (int)d, cfg, dloc, dt);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}

@@ -230,3 +230,135 @@ def scale_param_grad(dscale: Tensor, scale: Tensor, scale_kind: int, clamp_max: 
     l = scale.detach().float()
     chain = torch.where(l <= clamp_max, l.exp(), torch.zeros_like(l))
     return (dscale.reshape(()) * chain).reshape(scale.shape).to(scale.dtype)
+
+
+# ------------------------------------------------------------------------------------------------
+# vCLIP sampling path (include/mm25.h "vCLIP sampling path").  All fp32, sample-major [S, B, d].
+# ------------------------------------------------------------------------------------------------
+VMF_CFG = (1e-10, 0.0, 1e-10, 0.0, -1.0)      # VonMisesFisher.py:181-183,224-236
+POWER_SPHERICAL_CFG = (0.0, 1e-7, 0.0, 1e-7, 1e-7)  # power_spherical _EPS (unverified)
+
+
+def _f32dev(t: Tensor, name: str) -> Tensor:
+    if not t.is_cuda:
+        raise _lib.MM25Error("%s must be a CUDA tensor: this path has no CPU fallback" % name)
+    return t.detach().to(torch.float32).contiguous()
+
+
+@torch.library.custom_op("mm25::projnormal_fwd", mutates_args=(), device_types="cuda")
+def projnormal_fwd(mu: Tensor, sigma: Tensor, eps_in: Optional[Tensor], seed: int,
+                   S: int) -> Tuple[Tensor, Tensor]:
+    """ProjectedNormal.rsample((S,)) (ProjectedNormal.py:41-49) -> (samples [S,B,d], 1/norm [S,B])."""
+    mu, sigma = _f32dev(mu, "mu"), _f32dev(sigma, "sigma")
+    B, d = mu.shape
+    eps = None if eps_in is None else _f32dev(eps_in, "eps_in")
+    with torch.cuda.device(mu.device):
+        out = torch.empty((S, B, d), dtype=torch.float32, device=mu.device)
+        inv = torch.empty((S, B), dtype=torch.float32, device=mu.device)
+        rc = _lib.lib().mm25_sample_projnormal_fwd(_p(mu), _p(sigma), _p(eps), seed, S, B, d,
+                                                   _p(out), _p(inv), _stream(mu))
+    _lib.check(rc, "mm25_sample_projnormal_fwd")
+    return out, inv
+
+
+@torch.library.custom_op("mm25::projnormal_bwd", mutates_args=(), device_types="cuda")
+def projnormal_bwd(g: Tensor, y: Tensor, inv_norm: Tensor, eps_in: Optional[Tensor],
+                   seed: int) -> Tuple[Tensor, Tensor]:
+    g, y = _f32dev(g, "g"), _f32dev(y, "y")
+    S, B, d = y.shape
+    eps = None if eps_in is None else _f32dev(eps_in, "eps_in")
+    with torch.cuda.device(y.device):
+        dmu = torch.empty((B, d), dtype=torch.float32, device=y.device)
+        dsg = torch.empty((B, d), dtype=torch.float32, device=y.device)
+        rc = _lib.lib().mm25_sample_projnormal_bwd(_p(g), _p(y), _p(inv_norm), _p(eps), seed, S,
+                                                   B, d, _p(dmu), _p(dsg), _stream(y))
+    _lib.check(rc, "mm25_sample_projnormal_bwd")
+    return dmu, dsg
+
+
+@torch.library.custom_op("mm25::sphere_fwd", mutates_args=(), device_types="cuda")
+def sphere_fwd(t: Tensor, loc: Tensor, v_in: Optional[Tensor], seed: int, v_clamp: float,
+               v_add: float, h_clamp: float, h_add: float, omt2_min: float) -> Tensor:
+    """[t, sqrt(1-t^2) v/|v|] reflected so that e1 -> loc; t [S,B], loc [B,d] -> [S,B,d]."""
+    t, loc = _f32dev(t, "t"), _f32dev(loc, "loc")
+    S, B = t.shape
+    d = loc.shape[-1]
+    v = None if v_in is None else _f32dev(v_in, "v_in")
+    with torch.cuda.device(loc.device):
+        out = torch.empty((S, B, d), dtype=torch.float32, device=loc.device)
+        rc = _lib.lib().mm25_sphere_sample_fwd(_p(t), _p(loc), _p(v), seed, S, B, d, v_clamp,
+                                               v_add, h_clamp, h_add, omt2_min, _p(out),
+                                               _stream(loc))
+    _lib.check(rc, "mm25_sphere_sample_fwd")
+    return out
+
+
+@torch.library.custom_op("mm25::sphere_bwd", mutates_args=(), device_types="cuda")
+def sphere_bwd(g: Tensor, y: Tensor, t: Tensor, loc: Tensor, v_clamp: float, v_add: float,
+               h_clamp: float, h_add: float, omt2_min: float) -> Tuple[Tensor, Tensor]:
+    g, y, t, loc = _f32dev(g, "g"), _f32dev(y, "y"), _f32dev(t, "t"), _f32dev(loc, "loc")
+    S, B, d = y.shape
+    with torch.cuda.device(y.device):
+        dloc = torch.empty((B, d), dtype=torch.float32, device=y.device)
+        dt = torch.empty((S, B), dtype=torch.float32, device=y.device)
+        rc = _lib.lib().mm25_sphere_sample_bwd(_p(g), _p(y), _p(t), _p(loc), S, B, d, v_clamp,
+                                               v_add, h_clamp, h_add, omt2_min, _p(dloc), _p(dt),
+                                               _stream(y))
+    _lib.check(rc, "mm25_sphere_sample_bwd")
+    return dloc, dt
+
+
+@torch.library.custom_op("mm25::vmf_sample_w", mutates_args=(), device_types="cuda")
+def vmf_sample_w(kappa: Tensor, d: int, S: int, seed: int, prop_eps: Optional[Tensor],
+                 prop_u: Optional[Tensor]) -> Tuple[Tensor, Tensor]:
+    """Wood rejection sampler (VonMisesFisher.py:184-222) -> (w [S,B], accepted count [B])."""
+    kappa = _f32dev(kappa, "kappa").reshape(-1)
+    B = kappa.numel()
+    pe = None if prop_eps is None else _f32dev(prop_eps, "prop_eps")
+    pu = None if prop_u is None else _f32dev(prop_u, "prop_u")
+    P = 0 if pe is None else pe.shape[-1]
+    with torch.cuda.device(kappa.device):
+        w = torch.empty((S, B), dtype=torch.float32, device=kappa.device)
+        cnt = torch.full((B,), S, dtype=torch.int32, device=kappa.device)
+        rc = _lib.lib().mm25_vmf_sample_w(_p(kappa), d, S, B, seed, _p(pe), _p(pu), P, _p(w),
+                                          _p(cnt), _stream(kappa))
+    _lib.check(rc, "mm25_vmf_sample_w")
+    return w, cnt
+
+
+@torch.library.custom_op("mm25::beta_sample", mutates_args=(), device_types="cuda")
+def beta_sample(alpha: Tensor, beta: Tensor, S: int, seed: int) -> Tensor:
+    alpha, beta = _f32dev(alpha, "alpha").reshape(-1), _f32dev(beta, "beta").reshape(-1)
+    B = alpha.numel()
+    with torch.cuda.device(alpha.device):
+        z = torch.empty((S, B), dtype=torch.float32, device=alpha.device)
+        rc = _lib.lib().mm25_beta_sample(_p(alpha), _p(beta), S, B, seed, _p(z), _stream(alpha))
+    _lib.check(rc, "mm25_beta_sample")
+    return z
+
+
+@torch.library.custom_op("mm25::beta_grad", mutates_args=(), device_types="cuda")
+def beta_grad(z: Tensor, alpha: Tensor, beta: Tensor) -> Tensor:
+    """dz/dalpha of z ~ Beta(alpha, beta) (implicit reparameterisation, as torch's Beta.rsample)."""
+    z = _f32dev(z, "z")
+    alpha, beta = _f32dev(alpha, "alpha").reshape(-1), _f32dev(beta, "beta").reshape(-1)
+    S, B = z.shape
+    with torch.cuda.device(z.device):
+        out = torch.empty((S, B), dtype=torch.float32, device=z.device)
+        rc = _lib.lib().mm25_beta_grad(_p(z), _p(alpha), _p(beta), S, B, _p(out), _stream(z))
+    _lib.check(rc, "mm25_beta_grad")
+    return out
+
+
+@torch.library.custom_op("mm25::log_bessel", mutates_args=(), device_types="cuda")
+def log_bessel(kappa: Tensor, nu: float) -> Tuple[Tensor, Tensor]:
+    """(log I_nu(kappa), log I_{nu+1}(kappa)) in fp64 (replaces the mpmath round trip)."""
+    if not kappa.is_cuda:
+        raise _lib.MM25Error("kappa must be a CUDA tensor: this path has no CPU fallback")
+    k = kappa.detach().to(torch.float64).contiguous()
+    with torch.cuda.device(k.device):
+        o0 = torch.empty_like(k)
+        o1 = torch.empty_like(k)
+        rc = _lib.lib().mm25_log_bessel(_p(k), k.numel(), nu, _p(o0), _p(o1), _stream(k))
+    _lib.check(rc, "mm25_log_bessel")
+    return o0, o1
