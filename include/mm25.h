@@ -234,6 +234,14 @@ int mm25_beta_grad(const float* z, const float* alpha, const float* beta, int64_
 int mm25_log_bessel(const double* kappa, int64_t n, double nu, double* log_i_nu,
                     double* log_i_nu1, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Top-k retrieval indices (metrics/topk.py:43-48 `similarities.topk(k).indices`).
+ * scores [Q, N] fp32 with row stride ld; out_idx [Q, k] int64 and (optional) out_val [Q, k], sorted
+ * by descending score, ties lowest index first, NaN largest (torch order).  k <= 2048, k <= N.
+ * ------------------------------------------------------------------------------------------ */
+int mm25_topk_rows(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_t k,
+                   int64_t* out_idx, float* out_val, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

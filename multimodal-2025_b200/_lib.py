@@ -113,6 +113,7 @@ SIGNATURES = {
     "mm25_beta_sample": (_int, [_vp, _vp, _i64, _i64, _u64, _vp, _vp]),
     "mm25_beta_grad": (_int, [_vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "mm25_log_bessel": (_int, [_vp, _i64, _f64, _vp, _vp, _vp]),
+    "mm25_topk_rows": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
     "mm25_rowdot": (_int, [_vp, _vp, _vp, _i64, _i64, _vp]),
     "mm25_hopfield_bwd_pass": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _vp,
                                       _vp, _int, _vp, _vp]),

@@ -362,3 +362,22 @@ def log_bessel(kappa: Tensor, nu: float) -> Tuple[Tensor, Tensor]:
         rc = _lib.lib().mm25_log_bessel(_p(k), k.numel(), nu, _p(o0), _p(o1), _stream(k))
     _lib.check(rc, "mm25_log_bessel")
     return o0, o1
+
+
+@torch.library.custom_op("mm25::topk_rows", mutates_args=(), device_types="cuda")
+def topk_rows(scores: Tensor, k: int) -> Tuple[Tensor, Tensor]:
+    """(indices int64 [Q,k], values [Q,k]) of the k largest entries per row of fp32 scores,
+    sorted descending (metrics/topk.py:43-48); exact, ties lowest index first."""
+    if not scores.is_cuda:
+        raise _lib.MM25Error("scores must be a CUDA tensor: this path has no CPU fallback")
+    s = scores.detach().to(torch.float32)
+    if s.dim() == 1:
+        s = s.unsqueeze(0)
+    s = s.contiguous()
+    Q, N = s.shape
+    with torch.cuda.device(s.device):
+        idx = torch.empty((Q, k), dtype=torch.int64, device=s.device)
+        val = torch.empty((Q, k), dtype=torch.float32, device=s.device)
+        rc = _lib.lib().mm25_topk_rows(_p(s), Q, N, N, k, _p(idx), _p(val), _stream(s))
+    _lib.check(rc, "mm25_topk_rows")
+    return idx, val

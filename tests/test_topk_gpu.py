@@ -1,0 +1,56 @@
+"""GPU: top-k retrieval indices (metrics/topk.py).  Bit-exact against torch.topk on tie-free
+fp32 score rows, against the reference's golden indices, and the reference's own KAT."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("Q,N,k", [(4, 1000, 1), (4, 1000, 5), (3, 1000, 10), (3, 1000, 100),
+                                   (2, 65536, 100), (2, 65536, 1), (5, 257, 257), (1, 3, 2),
+                                   (2, 70001, 2048)])
+def test_topk_indices_bit_exact_vs_torch(lib_built, Q, N, k):
+    from multimodal_2025_b200 import ops
+    g = torch.Generator().manual_seed(N + k)
+    # tie-free rows: a random permutation of distinct values
+    base = torch.linspace(-3.0, 3.0, N)
+    scores = torch.stack([base[torch.randperm(N, generator=g)] for _ in range(Q)])
+    ref = torch.topk(scores, k, dim=1)
+    idx, val = ops.topk_rows(scores.cuda(), k)
+    assert torch.equal(idx.cpu(), ref.indices)
+    assert torch.equal(val.cpu(), ref.values)
+
+
+def test_topk_ties_and_special_values(lib_built):
+    from multimodal_2025_b200 import ops
+    s = torch.tensor([[1.0, 3.0, 3.0, -0.0, 0.0, float("inf"), 3.0, float("-inf")],
+                      [2.0, 2.0, 2.0, 2.0, 2.0, 2.0, 2.0, 2.0]])
+    idx, val = ops.topk_rows(s.cuda(), 4)
+    assert idx[0].tolist() == [5, 1, 2, 6]          # ties: lowest index first
+    assert idx[1].tolist() == [0, 1, 2, 3]
+    ref = torch.topk(s, 4, dim=1)
+    assert torch.equal(val.cpu(), ref.values)       # as a set of values torch agrees
+
+
+def test_topk_reference_golden_and_kat(lib_built):
+    from multimodal_2025_b200.metrics import top_k_score, top_k_similarities
+    G = load_golden("topk.npz")
+    top = G[""]
+    texts = torch.from_numpy(top["texts"]).cuda()
+    images = torch.from_numpy(top["images"]).cuda()
+    # the reference's __main__ KAT (metrics/topk.py:87-106)
+    emb1 = torch.tensor([[1.0, 0.0], [0.9, 0.1], [0.0, 1.0]]).cuda()
+    kat = top_k_similarities(emb1, torch.tensor([1.0, 0.0]).cuda(), k=2)
+    assert [i for i, _ in kat] == top["kat_idx"].tolist()
+    assert np.allclose([s for _, s in kat], top["kat_sim"], rtol=1e-6)
+    pairs = [([texts[3 * i], texts[3 * i + 1], texts[3 * i + 2]], images[i]) for i in range(100)]
+    for k in (1, 5, 10, 100):
+        acc, info = top_k_score(pairs, k)
+        assert info["correct"] == int(G["k%d" % k]["correct"]) and info["total"] == 100
+        assert acc == float(G["k%d" % k]["acc"])
+        got = np.array([[i for i, _ in top_k_similarities(texts, images[q], k)]
+                        for q in range(0, 100, 9)])
+        assert np.array_equal(got, G["k%d" % k]["idx"][::9])
