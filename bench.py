@@ -35,6 +35,7 @@ def parse_args():
     p.add_argument("--n", type=int, default=32768, help="global batch (pairs)")
     p.add_argument("--d", type=int, default=512)
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-graph", action="store_true", help="eager launches instead of a CUDA graph")
     p.add_argument("--slab-rows", type=int, default=1024, help="rows of the CPU sample slab")
     return p.parse_args()
 
@@ -249,17 +250,35 @@ def run_ours(args):
     for _ in range(args.warmup):
         step(x, y)
     barrier()
+    # one CUDA graph of the whole fwd+bwd (multimodal_2025_b200.graphs); --no-graph = eager
+    graphed, graph_note = None, "eager"
+    launches_per_step = None
+    if not args.no_graph:
+        try:
+            from multimodal_2025_b200.graphs import GraphedLossStep
+            c0 = L.mm25_launch_count()
+            graphed = GraphedLossStep(crit, x, y, ls, warmup=1)
+            # launches recorded into the graph = launches of ONE eager step (warm-up 1 + capture)
+            launches_per_step = (L.mm25_launch_count() - c0) // 2
+            graph_note = "cuda-graph replay"
+        except Exception as e:  # capture unsupported -> measure the eager path, say so
+            graphed, graph_note = None, "eager (graph capture failed: %s)" % type(e).__name__
+    run_step = (lambda: graphed()) if graphed is not None else (lambda: step(x, y))
+    for _ in range(args.warmup):
+        run_step()
+    barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     c0 = L.mm25_launch_count()
     t_wall0 = time.perf_counter()
-    ms = timed(lambda: step(x, y), args.steps)
+    ms = timed(run_step, args.steps)
     barrier()
     wall_ms = (time.perf_counter() - t_wall0) * 1e3
-    launches = (L.mm25_launch_count() - c0) // args.steps
+    launches = launches_per_step if graphed is not None else \
+        (L.mm25_launch_count() - c0) // args.steps
     clocks = sampler.stop() if rank == 0 else None
-    loss_val = float(crit(x, y, ls).detach())
+    loss_val = float(graphed.loss) if graphed is not None else float(crit(x, y, ls).detach())
 
     # ---- e2e: public API, host inputs, H2D + D2H inside the timed region -------------------
     xd = torch.empty_like(x_host, device=dev)
@@ -267,6 +286,10 @@ def run_ours(args):
     loss_host = torch.empty((), dtype=torch.float32).pin_memory()
 
     def e2e_step():
+        if graphed is not None:  # H2D straight into the graph's static inputs, replay, D2H
+            loss, _, _, _ = graphed(x_host, y_host)
+            loss_host.copy_(loss, non_blocking=True)
+            return
         xd.copy_(x_host, non_blocking=True)
         yd.copy_(y_host, non_blocking=True)
         xi = xd.detach().requires_grad_(True)
@@ -280,6 +303,11 @@ def run_ours(args):
     ms_e2e = timed(e2e_step, args.steps)
     barrier()
 
+    coll_note = "none (single GPU)"
+    if world > 1:
+        import multimodal_2025_b200.dist as mdist
+        coll_note = ("nccl all-gather(Yhat) + all-gather(col stats) + all-reduce(scalars); dY: "
+                     + str(mdist.LAST_BACKWARD_PATH))
     tm = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
@@ -290,7 +318,8 @@ def run_ours(args):
     return dict(world=world, rank=rank, dev=dev, n=n, d=d, n_local=n_local, x=x, y=y, ls=ls,
                 ms_step=ms_step, value=value, e2e_value=e2e_value, launches=int(launches),
                 clocks=clocks, loss=loss_val, wall_ms=wall_ms, flush=flush, ops=ops,
-                h2d=int(x_host.numel() * 2 * 2), dist=dist)
+                h2d=int(x_host.numel() * 2 * 2), dist=dist, graph_note=graph_note,
+                coll_note=coll_note)
 
 
 def kernel_roofline(r, args, peaks):
@@ -388,7 +417,8 @@ def main():
                                    % (r["n"], r["d"]),
                        "global_batch": r["n"], "dim": r["d"], "per_gpu_rows": r["n_local"],
                        "parallelism": "row-sharded x%d" % world if world > 1 else "single GPU",
-                       "l2_flush_between_steps": True},
+                       "l2_flush_between_steps": True, "launch": r["graph_note"],
+                       "collectives": r["coll_note"]},
             "step_tflops_per_gpu_algorithmic_6N2d": tf,
             "step_frac_of_bf16_peak": tf / peaks["bf16_tflops_sustained"],
             "step_peak": "%s bf16_tflops_sustained" % peaks["source"],

@@ -151,6 +151,21 @@ int mm25_sim_bwd(const void* a, const void* b, int dtype, const float* u, const 
                  float* db, float* dscale_part, float* ddiag, void* workspace,
                  size_t workspace_bytes, int impl, float dot_bound, void* stream);
 
+/* Fused backward + reduce-scatter for the row-sharded loss (tcgen05 path, PLAIN mode, B = 1):
+ * as mm25_sim_bwd, but instead of writing the partial db [N, d] of this rank, rows
+ * [q N/P, (q+1) N/P) of it are ADDED (fp32 red.global over NVLink) into db_peers[q], the
+ * peer-mapped [N/P, d] gradient buffer of rank q (symmetric memory; HOST array of P device
+ * pointers).  The buffers must be zeroed and a cross-rank barrier passed before the call, and a
+ * barrier must follow it before they are read.  Replaces the reduce-scatter that autograd of
+ * `gather_features(gather_with_grad=True)` performs (AlignCLIP/align_clip/loss.py:49-51).
+ * The summation order across ranks is not fixed (fp32 atomics). */
+int mm25_sim_bwd_rs(const void* a, const void* b, int dtype, int64_t M, int64_t N, int64_t d,
+                    const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
+                    const float* row_lse, const float* col_lse, float w_row, float w_col,
+                    float w_diag, float w_all, const float* gout, float* da,
+                    float* const* db_peers, int64_t npeers, float* dscale_part, void* workspace,
+                    size_t workspace_bytes, float dot_bound, void* stream);
+
 /* Deterministic fixed-order sum of n fp32 values into out[0] (one CTA). out = alpha * sum. */
 int mm25_sum_parts(const float* parts, int64_t n, float alpha, float* out, void* stream);
 

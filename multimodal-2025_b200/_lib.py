@@ -113,6 +113,9 @@ SIGNATURES = {
     "mm25_beta_sample": (_int, [_vp, _vp, _i64, _i64, _u64, _vp, _vp]),
     "mm25_beta_grad": (_int, [_vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "mm25_log_bessel": (_int, [_vp, _i64, _f64, _vp, _vp, _vp]),
+    "mm25_sim_bwd_rs": (_int, [_vp, _vp, _int, _i64, _i64, _i64, _vp, _int, _f32, _i64, _vp, _vp,
+                               _f32, _f32, _f32, _f32, _vp, _vp, _vp, _i64, _vp, _vp, _sz, _f32,
+                               _vp]),
     "mm25_topk_rows": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
     "mm25_rowdot": (_int, [_vp, _vp, _vp, _i64, _i64, _vp]),
     "mm25_hopfield_bwd_pass": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _vp,

@@ -88,14 +88,14 @@ extern "C" int64_t mm25_sim_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t 
   return n;
 }
 
-extern "C" int mm25_sim_bwd(const void* a, const void* b, int dtype, const float* u,
-                            const float* v, const float* diag_add, int64_t B, int64_t M,
-                            int64_t N, int64_t d, int64_t d2, const float* scale, int scale_kind,
-                            float clamp_max, int mode, int64_t diag_offset, const float* row_lse,
-                            const float* col_lse, float w_row, float w_col, float w_diag,
-                            float w_all, const float* gout, float* da, float* db,
-                            float* dscale_part, float* ddiag, void* workspace,
-                            size_t workspace_bytes, int impl, float dot_bound, void* stream) {
+static int sim_bwd_impl(const void* a, const void* b, int dtype, const float* u, const float* v,
+                        const float* diag_add, int64_t B, int64_t M, int64_t N, int64_t d,
+                        int64_t d2, const float* scale, int scale_kind, float clamp_max, int mode,
+                        int64_t diag_offset, const float* row_lse, const float* col_lse,
+                        float w_row, float w_col, float w_diag, float w_all, const float* gout,
+                        float* da, float* db, float* dscale_part, float* ddiag, void* workspace,
+                        size_t workspace_bytes, int impl, float dot_bound,
+                        float* const* db_peers, int npeers, void* stream) {
   if (B <= 0 || M <= 0 || N <= 0 || d <= 0) return MM25_ERR_SHAPE;
   if (!a || !b || !scale || !row_lse) return MM25_ERR_ARG;
   if (!col_lse && w_col != 0.f) return MM25_ERR_ARG;
@@ -109,7 +109,8 @@ extern "C" int mm25_sim_bwd(const void* a, const void* b, int dtype, const float
   if (t)
     return tc::launch_bwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
                           col_lse, w_row, w_col, w_diag, w_all, gout, da, db, dscale_part,
-                          workspace, workspace_bytes, dot_bound, st);
+                          workspace, workspace_bytes, dot_bound, db_peers, npeers, st);
+  if (db_peers) return MM25_ERR_SHAPE;  // the fused reduce-scatter exists on the tcgen05 path only
   int rc = MM25_OK;
   if (da) {
     rc = simt::launch_bwd_pass(a, b, dtype, u, v, diag_add, 0, B, M, N, d, d2, scale, scale_kind,
@@ -119,12 +120,39 @@ extern "C" int mm25_sim_bwd(const void* a, const void* b, int dtype, const float
   }
   if (db) {
     // transposed roles: rows = b, columns = a; row statistics = col_lse
-    if (!col_lse && w_row != 0.f) {
-      // column pass needs exp(z - row_lse_i) with i the *column* index of the swapped problem
-    }
     rc = simt::launch_bwd_pass(b, a, dtype, v, u, diag_add, 1, B, N, M, d, d2, scale, scale_kind,
                                clamp_max, mode, -diag_offset, col_lse, row_lse, w_col, w_row,
                                w_diag, w_all, gout, db, da ? nullptr : dscale_part, nullptr, st);
   }
   return rc;
+}
+
+extern "C" int mm25_sim_bwd(const void* a, const void* b, int dtype, const float* u,
+                            const float* v, const float* diag_add, int64_t B, int64_t M,
+                            int64_t N, int64_t d, int64_t d2, const float* scale, int scale_kind,
+                            float clamp_max, int mode, int64_t diag_offset, const float* row_lse,
+                            const float* col_lse, float w_row, float w_col, float w_diag,
+                            float w_all, const float* gout, float* da, float* db,
+                            float* dscale_part, float* ddiag, void* workspace,
+                            size_t workspace_bytes, int impl, float dot_bound, void* stream) {
+  return sim_bwd_impl(a, b, dtype, u, v, diag_add, B, M, N, d, d2, scale, scale_kind, clamp_max,
+                      mode, diag_offset, row_lse, col_lse, w_row, w_col, w_diag, w_all, gout, da,
+                      db, dscale_part, ddiag, workspace, workspace_bytes, impl, dot_bound,
+                      nullptr, 0, stream);
+}
+
+extern "C" int mm25_sim_bwd_rs(const void* a, const void* b, int dtype, int64_t M, int64_t N,
+                               int64_t d, const float* scale, int scale_kind, float clamp_max,
+                               int64_t diag_offset, const float* row_lse, const float* col_lse,
+                               float w_row, float w_col, float w_diag, float w_all,
+                               const float* gout, float* da, float* const* db_peers,
+                               int64_t npeers, float* dscale_part, void* workspace,
+                               size_t workspace_bytes, float dot_bound, void* stream) {
+  if (!db_peers || npeers < 1 || npeers > 16) return MM25_ERR_ARG;
+  for (int64_t i = 0; i < npeers; ++i)
+    if (!db_peers[i]) return MM25_ERR_ARG;
+  return sim_bwd_impl(a, b, dtype, nullptr, nullptr, nullptr, 1, M, N, d, 0, scale, scale_kind,
+                      clamp_max, MM25_SIM_PLAIN, diag_offset, row_lse, col_lse, w_row, w_col,
+                      w_diag, w_all, gout, da, nullptr, dscale_part, nullptr, workspace,
+                      workspace_bytes, 2, dot_bound, db_peers, (int)npeers, stream);
 }

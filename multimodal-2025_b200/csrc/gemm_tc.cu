@@ -46,6 +46,11 @@ struct Problem {
   int a_mn, b_mn;
   int accumulate;
   float alpha;
+  // scatter mode (fused reduce-scatter): m-block rows [q R, (q+1) R) are ADDED (red.global) into
+  // peer[q] + (row - q R) * ldc — peer-mapped fp32 buffers of the other ranks over NVLink
+  int scatter;
+  int rows_per_rank;
+  float* peer[GEMM_MAX_PEERS];
 };
 
 // groups [0, r) are class A, the rest class B; problem 0 is walked round-robin over groups
@@ -182,7 +187,15 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
       const Problem& pr = P.p[prob];
       const float al = pr.alpha * ad;
       const int accumulate = pr.accumulate;
-      float* crow = pr.C + (int64_t)(mb * BM + q * 32 + lane) * pr.ldc + n0;
+      const int grow = mb * BM + q * 32 + lane;
+      float* crow;
+      if (pr.scatter) {
+        const int owner = (mb * BM) / pr.rows_per_rank;  // BM divides rows_per_rank
+        crow = pr.peer[owner] + (int64_t)(grow - owner * pr.rows_per_rank) * pr.ldc + n0;
+      } else {
+        crow = pr.C + (int64_t)grow * pr.ldc + n0;
+      }
+      const int scatter = pr.scatter;
       mbar_wait(&sm.acc_full[as], accph);
       tc_fence_after();
 #pragma unroll 1
@@ -194,6 +207,12 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
         for (int j = 0; j < 8; ++j) {
           float4 o = make_float4(v[4 * j] * al, v[4 * j + 1] * al, v[4 * j + 2] * al,
                                  v[4 * j + 3] * al);
+          if (scatter) {
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j),
+                         "f"(o.x), "f"(o.y), "f"(o.z), "f"(o.w)
+                         : "memory");
+            continue;
+          }
           if (accumulate) {
             const float4 c = dst[j];
             o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
@@ -244,6 +263,15 @@ static int fill_problem(g::Problem* p, const GemmDesc& d, int64_t Ng) {
   p->b_mn = d.b_mn;
   p->accumulate = d.accumulate;
   p->alpha = d.alpha;
+  p->scatter = 0;
+  if (d.peers) {
+    if (d.npeers < 1 || d.npeers > GEMM_MAX_PEERS || d.rows_per_rank <= 0 ||
+        d.rows_per_rank % g::BM != 0 || d.rows_per_rank * d.npeers != d.Mg)
+      return MM25_ERR_SHAPE;
+    p->scatter = 1;
+    p->rows_per_rank = (int)d.rows_per_rank;
+    for (int i = 0; i < d.npeers; ++i) p->peer[i] = d.peers[i];
+  }
   return MM25_OK;
 }
 
@@ -310,7 +338,7 @@ int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float
 int gemm_bf16(const void* A, int a_mn, const void* Bm, int b_mn, float* C, int64_t ldc,
               int64_t Mg, int64_t Ng, int64_t K, float alpha, const float* alpha_dev,
               int accumulate, cudaStream_t st) {
-  GemmDesc d{A, Bm, C, ldc, Mg, K, a_mn, b_mn, accumulate, alpha};
+  GemmDesc d{A, Bm, C, ldc, Mg, K, a_mn, b_mn, accumulate, alpha, nullptr, 0, 0};
   return gemm_grouped(&d, nullptr, Ng, alpha_dev, st);
 }
 
@@ -330,7 +358,7 @@ extern "C" int mm25_debug_gemm_grouped(const void* A0, int a0_mn, const void* B0
                                        float* C0, int64_t M0, int64_t K0, const void* A1,
                                        int a1_mn, const void* B1, int b1_mn, float* C1,
                                        int64_t M1, int64_t K1, int64_t Ng, void* stream) {
-  mm25::tc::GemmDesc d0{A0, B0, C0, Ng, M0, K0, a0_mn, b0_mn, 0, 1.f};
-  mm25::tc::GemmDesc d1{A1, B1, C1, Ng, M1, K1, a1_mn, b1_mn, 0, 1.f};
+  mm25::tc::GemmDesc d0{A0, B0, C0, Ng, M0, K0, a0_mn, b0_mn, 0, 1.f, nullptr, 0, 0};
+  mm25::tc::GemmDesc d1{A1, B1, C1, Ng, M1, K1, a1_mn, b1_mn, 0, 1.f, nullptr, 0, 0};
   return mm25::tc::gemm_grouped(&d0, &d1, Ng, nullptr, (cudaStream_t)stream);
 }

@@ -18,7 +18,13 @@ struct GemmDesc {
   int a_mn, b_mn;
   int accumulate;
   float alpha;
+  // optional fused reduce-scatter: C is ignored and rows [q R, (q+1) R) of the result are
+  // added (fp32 red.global over NVLink) into peers[q][row - q R, :]; npeers * R == Mg
+  float* const* peers;
+  int npeers;
+  int64_t rows_per_rank;
 };
+constexpr int GEMM_MAX_PEERS = 16;
 
 // Up to two problems sharing Ng in ONE persistent launch with a static balanced schedule
 // (either pointer may be NULL).  alpha_dev: optional device scalar multiplied into both.

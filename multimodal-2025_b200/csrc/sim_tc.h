@@ -25,7 +25,8 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
                const float* row_lse, const float* col_lse, float w_row, float w_col,
                float w_diag, float w_all, const float* gout, float* da, float* db,
-               float* dscale_part, void* ws, size_t ws_bytes, float dot_bound, cudaStream_t st);
+               float* dscale_part, void* ws, size_t ws_bytes, float dot_bound,
+               float* const* db_peers, int npeers, cudaStream_t st);
 
 }  // namespace tc
 }  // namespace mm25

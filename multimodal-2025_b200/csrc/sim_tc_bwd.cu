@@ -13,6 +13,8 @@
 #include "sim_tc.h"
 #include "gemm_tc.h"
 
+#include <cstdlib>
+
 namespace mm25 {
 namespace tc {
 
@@ -248,8 +250,9 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                const float* row_lse, const float* col_lse, float w_row, float w_col,
                float w_diag, float w_all, const float* gout, float* da, float* db,
                float* dscale_part, void* ws, size_t ws_bytes, float dot_bound,
-               cudaStream_t st) {
+               float* const* db_peers, int npeers, cudaStream_t st) {
   if (!eligible_bwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)) return MM25_ERR_SHAPE;
+  if (db_peers && (B != 1 || npeers < 1 || N % npeers != 0)) return MM25_ERR_SHAPE;
   if (!col_lse) return MM25_ERR_ARG;
   if (ws_bytes < bwd_workspace_bytes(B, M, N, d)) return MM25_ERR_WORKSPACE;
   __nv_bfloat16* G = reinterpret_cast<__nv_bfloat16*>(
@@ -316,10 +319,19 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
       part += sms;
       {
         // dA[panel] = G . Yhat and dB += G^T . Xhat[panel] in one grouped launch
-        GemmDesc ga{G, b_b, da ? da + (bz * M + p0) * d : nullptr, d, rows, N, 0, 1, 0, 1.f};
+        GemmDesc ga{G, b_b, da ? da + (bz * M + p0) * d : nullptr, d, rows, N, 0, 1, 0, 1.f,
+                    nullptr, 0, 0};
         GemmDesc gb{G, a_b + p0 * d, db ? db + bz * N * d : nullptr, d, N, rows, 1, 1,
-                    p0 > 0 ? 1 : 0, 1.f};
-        rc = gemm_grouped(da ? &ga : nullptr, db ? &gb : nullptr, d, nullptr, st);
+                    p0 > 0 ? 1 : 0, 1.f, db_peers, npeers, db_peers ? N / npeers : 0};
+        const bool have_db = db != nullptr || db_peers != nullptr;
+        static const bool split = getenv("MM25_GEMM_SPLIT") != nullptr;  // A/B switch
+        if (split) {
+          rc = gemm_grouped(da ? &ga : nullptr, nullptr, d, nullptr, st);
+          if (rc) return rc;
+          rc = gemm_grouped(nullptr, have_db ? &gb : nullptr, d, nullptr, st);
+        } else {
+          rc = gemm_grouped(da ? &ga : nullptr, have_db ? &gb : nullptr, d, nullptr, st);
+        }
         if (rc) return rc;
       }
     }

@@ -59,6 +59,29 @@ def _reduce_scatter_sum(t: torch.Tensor, group) -> torch.Tensor:
     return out
 
 
+_SYMM_CACHE = {}
+LAST_BACKWARD_PATH = None  # "fused gemm+reduce-scatter (peer memory)" or "nccl reduce-scatter"
+
+
+def _symm_grad_buffer(n: int, d: int, device, group):
+    """[n, d] fp32 buffer in symmetric memory (peer-mapped on every rank of `group`) that the
+    fused backward scatter-adds dY into.  Returns (tensor, handle) or None when symmetric
+    memory cannot be set up (then the NCCL reduce-scatter is used)."""
+    key = (n, d, device.index, id(group))
+    if key in _SYMM_CACHE:
+        return _SYMM_CACHE[key]
+    out = None
+    try:
+        import torch.distributed._symmetric_memory as symm_mem
+        buf = symm_mem.empty((n, d), dtype=torch.float32, device=device)
+        hdl = symm_mem.rendezvous(buf, group)
+        out = (buf, hdl)
+    except Exception:  # no NVLink peer access / unsupported allocator: keep the NCCL path
+        out = None
+    _SYMM_CACHE[key] = out
+    return out
+
+
 class _ShardedClipFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, img, txt, logits_scale, eps_ls, normalize, clamp_max, group, backend,
@@ -84,21 +107,23 @@ class _ShardedClipFn(torch.autograd.Function):
         row_lse, cmax, csum, diag = B.sim_fwd(xhat, yall, None, None, None, scale32,
                                               B.SCALE_LOG, clamp_max, B.SIM_PLAIN, rank * n,
                                               True, impl, 1.01 if normalize else 0.0)
-        # (4) column statistics: gather partials, merge in rank order
-        stats = _all_gather_cat(torch.stack([cmax[0], csum[0]], 0).unsqueeze(0), group)
-        col_lse = B.col_merge(stats[:, 0].contiguous(), stats[:, 1].contiguous())  # [N]
-        # (5) scalar pieces
+        # (4) ONE all-gather carries the column partials (max, sum)[N] and each rank's scalar
+        #     pieces (column sums of xhat / yhat for the smoothing term); everything is then
+        #     merged / summed locally in rank order (deterministic, one collective fewer)
+        extra = torch.cat([sx.reshape(-1), sy.reshape(-1)]) if want_cs else cmax.new_zeros(0)
+        payload = torch.cat([cmax[0], csum[0], extra]).unsqueeze(0)
+        gathered = _all_gather_cat(payload, group)                      # [P, 2N (+ 2d)]
+        col_lse = B.col_merge(gathered[:, :N].contiguous(), gathered[:, N:2 * N].contiguous())
+        # (5) scalar pieces of the loss: local rows + local columns, then one small all-reduce
         part = B.clip_loss_finalize(row_lse, diag, col_lse[rank * n:(rank + 1) * n]
                                     .reshape(1, n).contiguous(), None, None, N, scale32,
                                     B.SCALE_LOG, clamp_max, eps_ls)
         red = part.reshape(1).clone()
-        if want_cs:
-            svec = torch.cat([sx.reshape(-1), sy.reshape(-1)])
-            dist.all_reduce(svec, group=group)
-            sxg, syg = svec[:d], svec[d:]
         dist.all_reduce(red, group=group)
         loss = red.reshape(())
         if want_cs:
+            sxg = gathered[:, 2 * N:2 * N + d].sum(dim=0)
+            syg = gathered[:, 2 * N + d:2 * N + 2 * d].sum(dim=0)
             s = scale32.clamp(max=clamp_max).exp().reshape(())
             loss = loss - (eps_ls / float(N) ** 2) * s * (sxg * syg).sum()
         ctx.save_for_backward(xhat, yhat, yall, invx, invy, row_lse, col_lse, scale32,
@@ -115,12 +140,33 @@ class _ShardedClipFn(torch.autograd.Function):
          N) = ctx.cfg
         nn_ = float(N)
         g = (gout.detach().to(torch.float32).reshape(1) * grad_scale).contiguous()
-        da, db, dscale, _ = B.sim_bwd(xhat, yall, None, None, None, scale32, B.SCALE_LOG,
-                                      clamp_max, B.SIM_PLAIN, rank * n, row_lse,
-                                      col_lse.reshape(1, N), 0.5 / nn_, 0.5 / nn_,
-                                      (1.0 - eps_ls) / nn_, eps_ls / (nn_ * nn_), g, True, True,
-                                      False, impl, 1.01 if normalize else 0.0)
-        dy_local = _reduce_scatter_sum(db[0], group).unsqueeze(0)
+        bound = 1.01 if normalize else 0.0
+        weights = (0.5 / nn_, 0.5 / nn_, (1.0 - eps_ls) / nn_, eps_ls / (nn_ * nn_))
+        symm = None
+        if (hasattr(B, "sim_bwd_rs") and xhat.is_cuda and xhat.dtype == torch.bfloat16 and
+                dist.get_backend(group) == "nccl" and B.tc_eligible_bwd(xhat, yall)):
+            symm = _symm_grad_buffer(n, xhat.shape[-1], xhat.device, group)
+        global LAST_BACKWARD_PATH
+        LAST_BACKWARD_PATH = ("fused gemm+reduce-scatter (NVLink peer memory)" if symm is not None
+                              else "nccl reduce-scatter")
+        if symm is not None:
+            # GEMM -> reduce-scatter in ONE kernel: the dB tiles are added straight into the
+            # owner rank's buffer over NVLink peer memory (no NCCL reduce-scatter, no [N, d]
+            # fp32 partial in HBM)
+            buf, hdl = symm
+            buf.zero_()
+            hdl.barrier(channel=0)
+            da, dscale = B.sim_bwd_rs(xhat, yall, scale32, B.SCALE_LOG, clamp_max, rank * n,
+                                      row_lse, col_lse.reshape(1, N), *weights, g,
+                                      [int(p) for p in hdl.buffer_ptrs], bound)
+            hdl.barrier(channel=1)
+            dy_local = buf.unsqueeze(0)
+        else:
+            da, db, dscale, _ = B.sim_bwd(xhat, yall, None, None, None, scale32, B.SCALE_LOG,
+                                          clamp_max, B.SIM_PLAIN, rank * n, row_lse,
+                                          col_lse.reshape(1, N), *weights, g, True, True, False,
+                                          impl, bound)
+            dy_local = _reduce_scatter_sum(db[0], group).unsqueeze(0)
         out_dt = B.BF16 if in_dtype == torch.bfloat16 else B.F32
         dimg = B.rownorm_bwd(da, xhat, invx, normalize, out_dt, None)[0].to(in_dtype)
         dtxt = B.rownorm_bwd(dy_local, yhat, invy, normalize, out_dt, None)[0].to(in_dtype)

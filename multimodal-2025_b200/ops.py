@@ -6,7 +6,7 @@ kernels never allocate (include/mm25.h conventions).
 """
 from __future__ import annotations
 
-from typing import Optional, Tuple
+from typing import List, Optional, Tuple
 
 import torch
 from torch import Tensor
@@ -381,3 +381,45 @@ def topk_rows(scores: Tensor, k: int) -> Tuple[Tensor, Tensor]:
         rc = _lib.lib().mm25_topk_rows(_p(s), Q, N, N, k, _p(idx), _p(val), _stream(s))
     _lib.check(rc, "mm25_topk_rows")
     return idx, val
+
+
+@torch.library.custom_op("mm25::sim_bwd_rs", mutates_args=(), device_types="cuda")
+def sim_bwd_rs(a: Tensor, b: Tensor, scale: Tensor, scale_kind: int, clamp_max: float,
+               diag_offset: int, row_lse: Tensor, col_lse: Tensor, w_row: float, w_col: float,
+               w_diag: float, w_all: float, gout: Optional[Tensor], peer_ptrs: List[int],
+               dot_bound: float) -> Tuple[Tensor, Tensor]:
+    """Fused backward + reduce-scatter (include/mm25.h mm25_sim_bwd_rs): returns (da, dscale);
+    the partial db of this rank is added into the peers' [N/P, d] fp32 buffers `peer_ptrs`."""
+    a = _cuda3(a, "a")
+    b = _cuda3(b, "b")
+    _, M, d = a.shape
+    N = b.shape[1]
+    dev = a.device
+    L = _lib.lib()
+    P = len(peer_ptrs)
+    import ctypes
+    table = (ctypes.c_void_p * P)(*peer_ptrs)
+    with torch.cuda.device(dev):
+        da = torch.empty((1, M, d), dtype=torch.float32, device=dev)
+        nparts = int(L.mm25_sim_bwd_nparts(1, M, N, d, _dt(a), IMPL_TC))
+        parts = torch.zeros((max(nparts, 1),), dtype=torch.float32, device=dev)
+        dscale = torch.empty((1,), dtype=torch.float32, device=dev)
+        wsb = L.mm25_sim_bwd_workspace_bytes(1, M, N, d, _dt(a), IMPL_TC)
+        ws = torch.empty((max(int(wsb), 16),), dtype=torch.uint8, device=dev)
+        rc = L.mm25_sim_bwd_rs(_p(a), _p(b), _dt(a), M, N, d, _p(scale), scale_kind, clamp_max,
+                               diag_offset, _p(row_lse), _p(col_lse), w_row, w_col, w_diag, w_all,
+                               _p(gout), _p(da), table, P, _p(parts), _p(ws), ws.numel(),
+                               dot_bound, _stream(a))
+        _lib.check(rc, "mm25_sim_bwd_rs")
+        rc = L.mm25_sum_parts(_p(parts), parts.numel(), 1.0, _p(dscale), _stream(a))
+    _lib.check(rc, "mm25_sum_parts")
+    return da, dscale
+
+
+def tc_eligible_bwd(a: Tensor, b: Tensor) -> bool:
+    """True when the tcgen05 backward (and so the fused reduce-scatter) takes these operands
+    (sim_tc_bwd.cu eligible_bwd: bf16, d % 256 == 0, d <= 1024, M % 128 == 0, N % 256 == 0)."""
+    M, d = a.shape[-2], a.shape[-1]
+    N = b.shape[-2]
+    return (a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and d % 256 == 0 and
+            d <= 1024 and M % 128 == 0 and N % 256 == 0)
