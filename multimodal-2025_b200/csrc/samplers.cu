@@ -43,6 +43,9 @@ constexpr uint64_t STREAM_SPHERE = 0x5348;  // tangent noise of the spherical sa
 // ------------------------------------------------------------------------------------------
 // ProjectedNormal: y[s,b,:] = (mu_b + sigma_b * eps) / ||.||       (no eps in the norm, :49)
 // ------------------------------------------------------------------------------------------
+// MAXG > 0: the row (<= 128 MAXG elements) stays in registers between the norm pass and the
+// write pass, so parameters are read and noise generated once; MAXG == 0: generic two-pass.
+template <int MAXG>
 __global__ void __launch_bounds__(256)
 projnormal_fwd_kernel(const float* __restrict__ mu, const float* __restrict__ sigma,
                       const float* __restrict__ eps_in, uint64_t seed, int64_t S, int64_t B,
@@ -56,30 +59,55 @@ projnormal_fwd_kernel(const float* __restrict__ mu, const float* __restrict__ si
   const float* sr = sigma + b * d;
   const int ngroups = (d + 3) >> 2;
   float ss = 0.f;
-  for (int g = lane; g < ngroups; g += 32) {
+  F4 cache[MAXG > 0 ? MAXG : 1];
+  auto value = [&](int g) {
     const int k0 = g * 4;
     const F4 m = load4(mr, k0, d, vec), sg = load4(sr, k0, d, vec);
     F4 e;
     if (eps_in) e = load4(eps_in + row * d, k0, d, vec);
     else rng::normal4(seed, (uint64_t)row * 0x100000ull + (uint64_t)g, STREAM_PN, e.v);
+    F4 v;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float v = (k0 + i < d) ? fmaf(sg.v[i], e.v[i], m.v[i]) : 0.f;
-      ss = fmaf(v, v, ss);
+    for (int i = 0; i < 4; ++i) v.v[i] = (k0 + i < d) ? fmaf(sg.v[i], e.v[i], m.v[i]) : 0.f;
+    return v;
+  };
+  if (MAXG > 0) {
+#pragma unroll
+    for (int c = 0; c < MAXG; ++c) {
+      const int g = lane + 32 * c;
+      if (g < ngroups) {
+        cache[c] = value(g);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ss = fmaf(cache[c].v[i], cache[c].v[i], ss);
+      }
+    }
+  } else {
+    for (int g = lane; g < ngroups; g += 32) {
+      const F4 v = value(g);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) ss = fmaf(v.v[i], v.v[i], ss);
     }
   }
   ss = warp_sum(ss);
   const float inv = 1.f / sqrtf(ss);
-  for (int g = lane; g < ngroups; g += 32) {
-    const int k0 = g * 4;
-    const F4 m = load4(mr, k0, d, vec), sg = load4(sr, k0, d, vec);
-    F4 e;
-    if (eps_in) e = load4(eps_in + row * d, k0, d, vec);
-    else rng::normal4(seed, (uint64_t)row * 0x100000ull + (uint64_t)g, STREAM_PN, e.v);
-    F4 y;
+  if (MAXG > 0) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) y.v[i] = fmaf(sg.v[i], e.v[i], m.v[i]) * inv;
-    store4(out + row * d, k0, d, vec, y);
+    for (int c = 0; c < MAXG; ++c) {
+      const int g = lane + 32 * c;
+      if (g < ngroups) {
+        F4 y;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) y.v[i] = cache[c].v[i] * inv;
+        store4(out + row * d, g * 4, d, vec, y);
+      }
+    }
+  } else {
+    for (int g = lane; g < ngroups; g += 32) {
+      F4 y = value(g);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) y.v[i] *= inv;
+      store4(out + row * d, g * 4, d, vec, y);
+    }
   }
   if (lane == 0 && inv_norm) inv_norm[row] = inv;
 }
@@ -169,6 +197,7 @@ __device__ __forceinline__ F4 sphere_noise4(const float* __restrict__ v_in, int6
   return e;
 }
 
+template <int MAXG>
 __global__ void __launch_bounds__(256)
 sphere_fwd_kernel(const float* __restrict__ t_in, const float* __restrict__ loc,
                   const float* __restrict__ v_in, uint64_t seed, int64_t S, int64_t B, int d,
@@ -181,16 +210,28 @@ sphere_fwd_kernel(const float* __restrict__ t_in, const float* __restrict__ loc,
   const float* mr = loc + b * d;
   const int ngroups = (d + 3) >> 2;
   float vv = 0.f, vmu = 0.f, mm = 0.f;
-  for (int g = lane; g < ngroups; g += 32) {
-    const int k0 = g * 4;
-    const F4 m = load4(mr, k0, d, vec);
-    const F4 e = sphere_noise4(v_in, row, k0, d, seed, g);
+  F4 ce[MAXG > 0 ? MAXG : 1], cm[MAXG > 0 ? MAXG : 1];
+  auto accumulate = [&](const F4& e, const F4& m, int k0) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       vv = fmaf(e.v[i], e.v[i], vv);
       vmu = fmaf(e.v[i], m.v[i], vmu);
       if (k0 + i >= 1) mm = fmaf(m.v[i], m.v[i], mm);
     }
+  };
+  if (MAXG > 0) {
+#pragma unroll
+    for (int c = 0; c < MAXG; ++c) {
+      const int g = lane + 32 * c;
+      if (g < ngroups) {
+        cm[c] = load4(mr, g * 4, d, vec);
+        ce[c] = sphere_noise4(v_in, row, g * 4, d, seed, g);
+        accumulate(ce[c], cm[c], g * 4);
+      }
+    }
+  } else {
+    for (int g = lane; g < ngroups; g += 32)
+      accumulate(sphere_noise4(v_in, row, g * 4, d, seed, g), load4(mr, g * 4, d, vec), g * 4);
   }
   vv = warp_sum(vv); vmu = warp_sum(vmu); mm = warp_sum(mm);
   const float mu0 = mr[0];
@@ -202,10 +243,7 @@ sphere_fwd_kernel(const float* __restrict__ t_in, const float* __restrict__ loc,
   const float den = fmaxf(sqrtf(fmaf(w0, w0, mm)), cfg.h_clamp) + cfg.h_add;
   const float xw = t * w0 - cn * vmu;      // x . (e1 - loc)
   const float f = 2.f * xw / (den * den);  // y = x - f * (e1 - loc)
-  for (int g = lane; g < ngroups; g += 32) {
-    const int k0 = g * 4;
-    const F4 m = load4(mr, k0, d, vec);
-    const F4 e = sphere_noise4(v_in, row, k0, d, seed, g);
+  auto emit = [&](const F4& e, const F4& m, int k0) {
     F4 y;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -215,6 +253,16 @@ sphere_fwd_kernel(const float* __restrict__ t_in, const float* __restrict__ loc,
       y.v[i] = fmaf(-f, w, x);
     }
     store4(out + row * d, k0, d, vec, y);
+  };
+  if (MAXG > 0) {
+#pragma unroll
+    for (int c2 = 0; c2 < MAXG; ++c2) {
+      const int g = lane + 32 * c2;
+      if (g < ngroups) emit(ce[c2], cm[c2], g * 4);
+    }
+  } else {
+    for (int g = lane; g < ngroups; g += 32)
+      emit(sphere_noise4(v_in, row, g * 4, d, seed, g), load4(mr, g * 4, d, vec), g * 4);
   }
 }
 
@@ -329,8 +377,14 @@ extern "C" int mm25_sample_projnormal_fwd(const float* mu, const float* sigma,
                                           void* stream) {
   if (S <= 0 || B <= 0 || d <= 0 || d > (1 << 20)) return MM25_ERR_SHAPE;
   if (!mu || !sigma || !out) return MM25_ERR_ARG;
-  projnormal_fwd_kernel<<<(unsigned)ceil_div(S * B, 8), 256, 0, (cudaStream_t)stream>>>(
-      mu, sigma, eps_in, seed, S, B, (int)d, out, inv_norm);
+  const unsigned grid = (unsigned)ceil_div(S * B, 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t gpl = ceil_div(ceil_div(d, 4), 32);  // 4-element groups per lane
+#define PN(G) projnormal_fwd_kernel<G><<<grid, 256, 0, st>>>(mu, sigma, eps_in, seed, S, B, \
+                                                             (int)d, out, inv_norm)
+  if (gpl <= 1) PN(1); else if (gpl <= 2) PN(2); else if (gpl <= 4) PN(4);
+  else if (gpl <= 8) PN(8); else PN(0);
+#undef PN
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }
@@ -357,8 +411,13 @@ extern "C" int mm25_sphere_sample_fwd(const float* t, const float* loc, const fl
   if (S <= 0 || B <= 0 || d < 2 || d > (1 << 20)) return MM25_ERR_SHAPE;
   if (!t || !loc || !out) return MM25_ERR_ARG;
   SphereCfg cfg{v_clamp, v_add, h_clamp, h_add, omt2_min};
-  sphere_fwd_kernel<<<(unsigned)ceil_div(S * B, 8), 256, 0, (cudaStream_t)stream>>>(
-      t, loc, v_in, seed, S, B, (int)d, cfg, out);
+  const unsigned grid = (unsigned)ceil_div(S * B, 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t gpl = ceil_div(ceil_div(d, 4), 32);
+#define SP(G) sphere_fwd_kernel<G><<<grid, 256, 0, st>>>(t, loc, v_in, seed, S, B, (int)d, cfg, out)
+  if (gpl <= 1) SP(1); else if (gpl <= 2) SP(2); else if (gpl <= 4) SP(4);
+  else if (gpl <= 8) SP(8); else SP(0);
+#undef SP
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

@@ -23,13 +23,17 @@ class _ClipLossFn(torch.autograd.Function):
     """loss[B] of B independent CLIP problems; inputs [B, M, d]."""
 
     @staticmethod
-    def forward(ctx, img, txt, logits_scale, eps_ls, normalize, clamp_max, scale_kind, impl):
+    def forward(ctx, img, txt, logits_scale, eps_ls, normalize, clamp_max, scale_kind, impl,
+                compute_bf16=False):
         in_dtype = img.dtype
         if in_dtype not in (torch.float32, torch.bfloat16):
             img, txt = img.float(), txt.float()
         if txt.dtype != img.dtype:
             txt = txt.to(img.dtype)
-        cdt = ops.BF16 if img.dtype == torch.bfloat16 else ops.F32
+        # compute_bf16: fp32 inputs are normalised in fp32 and rounded to bf16 ONCE for the
+        # tensor-core kernels (what autocast does to the reference's matmul); statistics, loss
+        # and gradients stay fp32.  Default: compute in the input dtype (fp32 -> 1e-5 contract).
+        cdt = ops.BF16 if (img.dtype == torch.bfloat16 or compute_bf16) else ops.F32
         want_cs = eps_ls != 0.0
         xhat, invx, sx = ops.rownorm_fwd(img, normalize, _EPS_NORM, cdt, want_cs)
         yhat, invy, sy = ops.rownorm_fwd(txt, normalize, _EPS_NORM, cdt, want_cs)
@@ -67,16 +71,16 @@ class _ClipLossFn(torch.autograd.Function):
             dtxt = ops.rownorm_bwd(db, yhat, invy, normalize, out_dt, None).to(in_dtype)
         if ctx.needs_input_grad[2]:
             dls = ops.scale_param_grad(dscale, logits_scale, scale_kind, clamp_max)
-        return dimg, dtxt, dls, None, None, None, None, None
+        return dimg, dtxt, dls, None, None, None, None, None, None
 
 
 def clip_loss_batched(img, txt, logits_scale, eps_ls, normalize, clamp_max,
-                      scale_kind=ops.SCALE_LOG, impl=ops.IMPL_AUTO):
+                      scale_kind=ops.SCALE_LOG, impl=ops.IMPL_AUTO, compute_bf16=False):
     """[B, M, d] x2 -> loss [B] (fp32)."""
     if not torch.is_tensor(logits_scale):
         logits_scale = torch.tensor(float(logits_scale), device=img.device)
     return _ClipLossFn.apply(img, txt, logits_scale, float(eps_ls), bool(normalize),
-                             float(clamp_max), int(scale_kind), int(impl))
+                             float(clamp_max), int(scale_kind), int(impl), bool(compute_bf16))
 
 
 class ClipLoss(nn.Module):
@@ -90,6 +94,15 @@ class ClipLoss(nn.Module):
         self.label_smoothing = label_smoothing
         self.register_buffer("smoothing", torch.tensor(self.label_smoothing))
         self.impl = ops.IMPL_AUTO
+        # None: compute in the input dtype (reference semantics).  torch.bfloat16: fp32 inputs
+        # run the bf16 tcgen05 kernels (bf16 contract 2e-3 / 2e-2); also taken under
+        # torch.autocast(dtype=torch.bfloat16), where the reference's matmul is bf16 as well.
+        self.compute_dtype = None
+
+    def _bf16(self):
+        return self.compute_dtype == torch.bfloat16 or (
+            torch.is_autocast_enabled("cuda") and
+            torch.get_autocast_dtype("cuda") == torch.bfloat16)
 
     def forward_sampled(self, image_features: torch.Tensor, text_features: torch.Tensor,
                         logits_scale: torch.Tensor):
@@ -97,12 +110,13 @@ class ClipLoss(nn.Module):
         (reference clipLoss.py:24-79)."""
         B1, B2, E = image_features.shape
         return clip_loss_batched(image_features, text_features, logits_scale,
-                                 self.label_smoothing, True, 3.912, impl=self.impl)
+                                 self.label_smoothing, True, 3.912, impl=self.impl,
+                                 compute_bf16=self._bf16())
 
     def forward(self, image_features: torch.Tensor, text_features: torch.Tensor,
                 logits_scale: torch.Tensor, normalize=True):
         """Scalar fp32 loss; clamp 4.6052 (reference clipLoss.py:81-121)."""
         loss = clip_loss_batched(image_features.unsqueeze(0), text_features.unsqueeze(0),
                                  logits_scale, self.label_smoothing, normalize, 4.6052,
-                                 impl=self.impl)
+                                 impl=self.impl, compute_bf16=self._bf16())
         return loss.reshape(())

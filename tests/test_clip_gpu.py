@@ -123,3 +123,30 @@ def test_clip_bf16_tc_multi_panel_and_sampled(lib_built):
     assert rel_err(l1, l0) < 2e-3
     assert rel_err(gx1, gx0) < 2e-2 and rel_err(gy1, gy0) < 2e-2
     assert abs(float(gl1) - float(gl0)) <= 2e-2 * abs(float(gl0))
+
+
+def test_clip_fp32_inputs_bf16_compute(lib_built):
+    """compute_dtype=bf16: fp32 inputs on the tcgen05 kernels (bf16 contract), forward and
+    forward_sampled; also picked up under torch.autocast(bf16)."""
+    from multimodal_2025_b200.losses import ClipLoss
+    x, y = O.synth_embeddings(512, 256, 21, correlated=True)
+    lsc = torch.tensor(2.6592)
+    ref, (rx, ry, rl) = O.loss_and_grads(O.clip_loss, [x, y, lsc], 0.1, True)
+    m = ClipLoss(0.1).cuda()
+    m.compute_dtype = torch.bfloat16
+    loss, (gx, gy, gl) = run_ours(lambda a, b, c: m(a, b, c), [x, y, lsc])
+    assert rel_err(loss, ref) < 2e-3
+    assert rel_err(gx, rx) < 2e-2 and rel_err(gy, ry) < 2e-2
+    assert abs(float(gl) - float(rl)) <= 2e-2 * abs(float(rl))
+    m2 = ClipLoss(0.1).cuda()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        loss2, _ = run_ours(lambda a, b, c: m2(a, b, c), [x, y, lsc])
+    assert float(loss2) == float(loss)
+    g = torch.Generator().manual_seed(4)
+    xs = torch.randn(3, 256, 256, generator=g)
+    ys = xs + 1.5 * torch.randn(3, 256, 256, generator=g)
+    refs, (rxs, rys, rls) = O.loss_and_grads(lambda a, b, c: O.clip_loss_sampled(a, b, c, 0.1),
+                                             [xs, ys, lsc])
+    ls_, (gxs, gys, gls) = run_ours(lambda a, b, c: m.forward_sampled(a, b, c), [xs, ys, lsc])
+    assert rel_err(ls_, refs) < 2e-3
+    assert rel_err(gxs, rxs) < 2e-2 and rel_err(gys, rys) < 2e-2
