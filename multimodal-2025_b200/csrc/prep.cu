@@ -110,9 +110,105 @@ __global__ void __launch_bounds__(256) colsum_part_kernel(const T* __restrict__ 
   }
 }
 
+// Fused row normalise + stage 1 of the column sums, 4-element vector accesses: each warp walks a
+// strided set of rows with the row held in registers (d <= 2048, d % 128 == 0), writes xhat and
+// 1/norm, and keeps per-lane column partial sums that are reduced across the CTA's warps in
+// fixed order -> part [B][P][d].  One pass over x instead of three (normalise, re-read xhat for
+// the column sums).
+template <typename T> struct Vec4 {};
+template <> struct Vec4<float> {
+  static __device__ __forceinline__ void load(const float* p, float (&v)[4]) {
+    const float4 t = *reinterpret_cast<const float4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  static __device__ __forceinline__ void store(float* p, const float (&v)[4]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+template <> struct Vec4<__nv_bfloat16> {
+  static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&v)[4]) {
+    const uint2 t = *reinterpret_cast<const uint2*>(p);
+    v[0] = __uint_as_float(t.x << 16); v[1] = __uint_as_float(t.x & 0xffff0000u);
+    v[2] = __uint_as_float(t.y << 16); v[3] = __uint_as_float(t.y & 0xffff0000u);
+  }
+  static __device__ __forceinline__ void store(__nv_bfloat16* p, const float (&v)[4]) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+    uint2 t;
+    t.x = *reinterpret_cast<uint32_t*>(&lo); t.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(p) = t;
+  }
+};
+
+constexpr int RN_MAXIT = 16;  // d <= 16 * 128
+
+template <typename TI, typename TO, bool CS>
+__global__ void __launch_bounds__(256)
+rownorm_fused_kernel(const TI* __restrict__ x, TO* __restrict__ xhat,
+                     float* __restrict__ inv_norm, float* __restrict__ part, int64_t M, int d,
+                     int normalize, float eps) {
+  extern __shared__ float red[];  // [8][d] when CS
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int P = gridDim.x;
+  const int niter = d >> 7;
+  const int64_t base = (int64_t)blockIdx.y * M;
+  float acc[CS ? RN_MAXIT : 1][4];
+  if (CS) {
+#pragma unroll
+    for (int it = 0; it < RN_MAXIT; ++it)
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc[it][u] = 0.f;
+  }
+  for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < M; r += (int64_t)P * 8) {
+    const TI* xr = x + (base + r) * d;
+    TO* o = xhat + (base + r) * d;
+    float v[RN_MAXIT][4];
+    float ss = 0.f;
+#pragma unroll
+    for (int it = 0; it < RN_MAXIT; ++it)
+      if (it < niter) {
+        Vec4<TI>::load(xr + (it * 32 + lane) * 4, v[it]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) ss = fmaf(v[it][u], v[it][u], ss);
+      }
+    float inv = 1.f;
+    if (normalize) {
+      ss = warp_sum(ss);
+      inv = 1.f / fmaxf(sqrtf(ss), eps);
+    }
+#pragma unroll
+    for (int it = 0; it < RN_MAXIT; ++it)
+      if (it < niter) {
+        float w[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) w[u] = v[it][u] * inv;
+        Vec4<TO>::store(o + (it * 32 + lane) * 4, w);
+        if (CS) {
+          // sums are over the ROUNDED xhat (what the similarity kernels read)
+#pragma unroll
+          for (int u = 0; u < 4; ++u) acc[it][u] += to_f32<TO>(from_f32<TO>(w[u]));
+        }
+      }
+    if (lane == 0 && inv_norm) inv_norm[base + r] = inv;
+  }
+  if (CS) {
+#pragma unroll
+    for (int it = 0; it < RN_MAXIT; ++it)
+      if (it < niter)
+#pragma unroll
+        for (int u = 0; u < 4; ++u) red[warp * d + (it * 32 + lane) * 4 + u] = acc[it][u];
+    __syncthreads();
+    for (int c = threadIdx.x; c < d; c += 256) {
+      float sacc = 0.f;
+#pragma unroll
+      for (int w8 = 0; w8 < 8; ++w8) sacc += red[w8 * d + c];
+      part[((int64_t)blockIdx.y * P + blockIdx.x) * d + c] = sacc;
+    }
+  }
+}
+
 static int colsum_parts(int64_t M) {
   int64_t p = (M + 7) / 8;
-  return (int)(p > 256 ? 256 : (p < 1 ? 1 : p));
+  return (int)(p > 592 ? 592 : (p < 1 ? 1 : p));  // up to 4 CTAs per SM
 }
 
 // dx = inv * (g - xhat (xhat . g))   (backward of F.normalize away from the eps clamp)
@@ -183,21 +279,22 @@ __global__ void __launch_bounds__(FIN_T) clip_finalize_kernel(
   diag += (int64_t)b * M;
   const double nn = (double)n_norm;
   const double wr = 1.0 / (2.0 * nn), wd = (1.0 - (double)eps_ls) / nn;
-  double acc0 = 0.0, acc1 = 0.0;
-  for (int64_t i = threadIdx.x; i < M; i += 2 * FIN_T) {
-    acc0 += (double)row_lse[i] * wr - wd * (double)diag[i];
-    const int64_t i2 = i + FIN_T;
-    if (i2 < M) acc1 += (double)row_lse[i2] * wr - wd * (double)diag[i2];
+  // per-thread sums in compensated fp32 (fp64 adds are slow on this part), combined in fp64
+  float sr = 0.f, cr = 0.f, sd = 0.f, cd = 0.f, sc = 0.f, cc = 0.f;
+  auto kadd = [](float& s_, float& c_, float v) {
+    const float yv = v - c_, t = s_ + yv;
+    c_ = (t - s_) - yv;
+    s_ = t;
+  };
+  for (int64_t i = threadIdx.x; i < M; i += FIN_T) {
+    kadd(sr, cr, row_lse[i]);
+    kadd(sd, cd, diag[i]);
   }
   if (col_lse) {
     col_lse += (int64_t)b * N;
-    for (int64_t j = threadIdx.x; j < N; j += 2 * FIN_T) {
-      acc0 += (double)col_lse[j] * wr;
-      const int64_t j2 = j + FIN_T;
-      if (j2 < N) acc1 += (double)col_lse[j2] * wr;
-    }
+    for (int64_t j = threadIdx.x; j < N; j += FIN_T) kadd(sc, cc, col_lse[j]);
   }
-  double acc = acc0 + acc1;
+  double acc = ((double)sr + (double)sc) * wr - wd * (double)sd;
   if (eps_ls != 0.f && sx && sy) {
     const float s = load_scale(scale, scale_kind, clamp_max);
     double dot = 0.0;
@@ -240,6 +337,40 @@ extern "C" int mm25_rownorm_fwd(const void* x, int dtype, void* xhat, int out_dt
   if (!x || !xhat) return MM25_ERR_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t rows = B * M;
+  if (dtype != MM25_F32 && dtype != MM25_BF16) return MM25_ERR_DTYPE;
+  if (out_dtype != MM25_F32 && out_dtype != MM25_BF16) return MM25_ERR_DTYPE;
+  if (d % 128 == 0 && d <= RN_MAXIT * 128 && M >= 64) {
+    // fused vectorised path (+ column-sum partials behind the [B, d] result)
+    const int P = colsum_parts(M);
+    float* part = colsum ? colsum + B * d : nullptr;
+    dim3 g1((unsigned)P, (unsigned)B);
+    const size_t sh = colsum ? sizeof(float) * 8 * (size_t)d : 0;
+#define RF(TI, TO)                                                                            \
+  do {                                                                                        \
+    if (colsum) {                                                                             \
+      MM25_CUDA_CHECK(cudaFuncSetAttribute(rownorm_fused_kernel<TI, TO, true>,                \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize,       \
+                                           (int)sh));                                         \
+      rownorm_fused_kernel<TI, TO, true><<<g1, 256, sh, st>>>(                                \
+          (const TI*)x, (TO*)xhat, inv_norm, part, M, (int)d, normalize, eps);                \
+    } else {                                                                                  \
+      rownorm_fused_kernel<TI, TO, false><<<g1, 256, 0, st>>>(                                \
+          (const TI*)x, (TO*)xhat, inv_norm, nullptr, M, (int)d, normalize, eps);             \
+    }                                                                                         \
+  } while (0)
+    if (dtype == MM25_F32 && out_dtype == MM25_F32) RF(float, float);
+    else if (dtype == MM25_F32 && out_dtype == MM25_BF16) RF(float, __nv_bfloat16);
+    else if (dtype == MM25_BF16 && out_dtype == MM25_BF16) RF(__nv_bfloat16, __nv_bfloat16);
+    else RF(__nv_bfloat16, float);
+#undef RF
+    MM25_LAUNCH_CHECK();
+    if (colsum) {
+      dim3 g2((unsigned)ceil_div(d, 32), (unsigned)B);
+      colsum_kernel<float><<<g2, 256, 0, st>>>(part, colsum, P, (int)d);
+      MM25_LAUNCH_CHECK();
+    }
+    return MM25_OK;
+  }
   dim3 grid((unsigned)ceil_div(rows, 8));
 #define RN(TI, TO)                                                                         \
   rownorm_fwd_kernel<TI, TO><<<grid, 256, 0, st>>>((const TI*)x, (TO*)xhat, inv_norm, rows, \
@@ -247,32 +378,16 @@ extern "C" int mm25_rownorm_fwd(const void* x, int dtype, void* xhat, int out_dt
   if (dtype == MM25_F32 && out_dtype == MM25_F32) RN(float, float);
   else if (dtype == MM25_F32 && out_dtype == MM25_BF16) RN(float, __nv_bfloat16);
   else if (dtype == MM25_BF16 && out_dtype == MM25_BF16) RN(__nv_bfloat16, __nv_bfloat16);
-  else if (dtype == MM25_BF16 && out_dtype == MM25_F32) RN(__nv_bfloat16, float);
-  else return MM25_ERR_DTYPE;
+  else RN(__nv_bfloat16, float);
 #undef RN
   MM25_LAUNCH_CHECK();
   if (colsum) {
-    const int vw = out_dtype == MM25_F32 ? 4 : 8;
     dim3 g2((unsigned)ceil_div(d, 32), (unsigned)B);
-    if (d % (32 * vw) == 0 && d <= 2048 && M >= 64) {
-      // two-stage: partials live behind the [B, d] result inside the caller's buffer
-      const int P = colsum_parts(M);
-      float* part = colsum + B * d;
-      dim3 g1((unsigned)P, (unsigned)B);
-      const size_t sh = sizeof(float) * 8 * (size_t)d;
-      if (out_dtype == MM25_F32)
-        colsum_part_kernel<float><<<g1, 256, sh, st>>>((const float*)xhat, part, M, (int)d);
-      else
-        colsum_part_kernel<__nv_bfloat16><<<g1, 256, sh, st>>>((const __nv_bfloat16*)xhat, part,
-                                                               M, (int)d);
-      MM25_LAUNCH_CHECK();
-      colsum_kernel<float><<<g2, 256, 0, st>>>(part, colsum, P, (int)d);
-    } else if (out_dtype == MM25_F32) {
+    if (out_dtype == MM25_F32)
       colsum_kernel<float><<<g2, 256, 0, st>>>((const float*)xhat, colsum, M, (int)d);
-    } else {
+    else
       colsum_kernel<__nv_bfloat16><<<g2, 256, 0, st>>>((const __nv_bfloat16*)xhat, colsum, M,
                                                       (int)d);
-    }
     MM25_LAUNCH_CHECK();
   }
   return MM25_OK;

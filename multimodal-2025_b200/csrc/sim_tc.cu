@@ -199,25 +199,28 @@ __device__ __forceinline__ void lse2_merge(float& m, float& l, float m2, float l
   m = mn;
 }
 
-__global__ void __launch_bounds__(256) fwd_tc_merge_kernel(
+// block = 32 elements x 32 partial lanes: lane ty merges partials ty, ty+32, ... in order, then
+// the 32 lanes are merged in order (fixed order -> deterministic).  1024 threads per 32 columns
+// keep ~64 MB of partials streaming at HBM speed.
+__global__ void __launch_bounds__(1024) fwd_tc_merge_kernel(
     const float* __restrict__ row_pm, const float* __restrict__ row_pl, int nseg, int64_t M,
     float* __restrict__ row_lse, const float* __restrict__ col_pm,
     const float* __restrict__ col_pl, int nrb, int64_t N, float* __restrict__ col_max,
     float* __restrict__ col_sum) {
-  __shared__ float sm_m[8][33], sm_l[8][33];
+  __shared__ float sm_m[32][33], sm_l[32][33];
   const int bz = blockIdx.y;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int64_t t = (int64_t)blockIdx.x * 32 + tx;
   {
     float m = -INFINITY, l = 0.f;
     if (t < M)
-      for (int p = ty; p < nseg; p += 8)
+      for (int p = ty; p < nseg; p += 32)
         lse2_merge(m, l, row_pm[((int64_t)bz * nseg + p) * M + t],
                    row_pl[((int64_t)bz * nseg + p) * M + t]);
     sm_m[ty][tx] = m; sm_l[ty][tx] = l;
     __syncthreads();
     if (ty == 0 && t < M) {
-      for (int k = 1; k < 8; ++k) lse2_merge(m, l, sm_m[k][tx], sm_l[k][tx]);
+      for (int k = 1; k < 32; ++k) lse2_merge(m, l, sm_m[k][tx], sm_l[k][tx]);
       row_lse[(int64_t)bz * M + t] = (m + log2f(l)) * LN2;
     }
     __syncthreads();
@@ -225,13 +228,13 @@ __global__ void __launch_bounds__(256) fwd_tc_merge_kernel(
   if (col_max) {
     float m = -INFINITY, l = 0.f;
     if (t < N)
-      for (int p = ty; p < nrb; p += 8)
+      for (int p = ty; p < nrb; p += 32)
         lse2_merge(m, l, col_pm[((int64_t)bz * nrb + p) * N + t],
                    col_pl[((int64_t)bz * nrb + p) * N + t]);
     sm_m[ty][tx] = m; sm_l[ty][tx] = l;
     __syncthreads();
     if (ty == 0 && t < N) {
-      for (int k = 1; k < 8; ++k) lse2_merge(m, l, sm_m[k][tx], sm_l[k][tx]);
+      for (int k = 1; k < 32; ++k) lse2_merge(m, l, sm_m[k][tx], sm_l[k][tx]);
       col_max[(int64_t)bz * N + t] = m * LN2;
       col_sum[(int64_t)bz * N + t] = l;
     }
@@ -352,7 +355,7 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
       diag_offset, row_pm, row_pl, col_pm, col_pl, diag, g_force_slow, dot_bound);
   MM25_LAUNCH_CHECK();
   const int64_t mx = M > N ? M : N;
-  fwd_tc_merge_kernel<<<dim3((unsigned)ceil_div(mx, 32), (unsigned)B), 256, 0, st>>>(
+  fwd_tc_merge_kernel<<<dim3((unsigned)ceil_div(mx, 32), (unsigned)B), 1024, 0, st>>>(
       row_pm, row_pl, g.nseg * 2, M, row_lse, col_pm, col_pl, g.nrb, N, col_max, col_sum);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
