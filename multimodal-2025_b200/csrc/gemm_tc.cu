@@ -41,8 +41,10 @@ struct Problem {
   CUtensorMap ta, tb;
   float* C;
   int64_t ldc;
-  int nk;          // K / BK
+  int nk;          // k-blocks (of BK) per JOB = (K / BK) / ksplit
   int mblocks;     // Mg / BM
+  int ksplit;      // split-K factor: jobs = mblocks * ksplit, job j -> (m-block j % mblocks,
+                   // k-part j / mblocks); partial tiles are added with red.global (C zeroed)
   int a_mn, b_mn;
   int accumulate;
   float alpha;
@@ -70,22 +72,28 @@ struct Params {
 };
 
 // job k of group `grp`: which problem and which m-block; false when the list is exhausted
-__device__ __forceinline__ bool job_at(const Params& P, int grp, int k, int* prob, int* mb) {
+__device__ __forceinline__ bool job_at(const Params& P, int grp, int k, int* prob, int* mb,
+                                       int* kb0) {
   const Schedule& s = P.s;
   const bool A = grp < s.r;
   const int nb = A ? s.nbA : s.nbB;
+  int job;
   if (k < nb) {
     *prob = 0;
-    *mb = grp + k * s.ngroups;
-    return *mb < P.p[0].mblocks;
+    job = grp + k * s.ngroups;
+  } else {
+    const int ks = k - nb;
+    const int ns = A ? s.nsA : s.nsB;
+    if (ks >= ns) return false;
+    const int base = A ? grp * s.nsA : s.r * s.nsA + (grp - s.r) * s.nsB;
+    *prob = 1;
+    job = base + ks;
   }
-  const int ks = k - nb;
-  const int ns = A ? s.nsA : s.nsB;
-  if (ks >= ns) return false;
-  const int base = A ? grp * s.nsA : s.r * s.nsA + (grp - s.r) * s.nsB;
-  *prob = 1;
-  *mb = base + ks;
-  return *mb < P.p[1].mblocks;
+  const Problem& pr = P.p[*prob];
+  if (job >= pr.mblocks * pr.ksplit) return false;
+  *mb = job % pr.mblocks;
+  *kb0 = (job / pr.mblocks) * pr.nk;
+  return true;
 }
 }  // namespace g
 
@@ -119,12 +127,12 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
   if (warp == 0) {
     if (lane == 0) {
       uint32_t st = 0, ph = 0;
-      int prob, mb;
-      for (int k = 0; job_at(P, grp, k, &prob, &mb); ++k) {
+      int prob, mb, kb0;
+      for (int k = 0; job_at(P, grp, k, &prob, &mb, &kb0); ++k) {
         const Problem& pr = P.p[prob];
         const int m0 = mb * BM;
         for (int kb = 0; kb < pr.nk; ++kb) {
-          const int k0 = kb * BK;
+          const int k0 = (kb0 + kb) * BK;
           mbar_wait(&sm.empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&sm.full[st], A_BYTES + B_BYTES);
           if (pr.a_mn) {
@@ -148,8 +156,8 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
   } else if (warp == 1) {
     if (lane == 0) {
       uint32_t st = 0, ph = 0, as = 0, accph = 0;
-      int prob, mb;
-      for (int k = 0; job_at(P, grp, k, &prob, &mb); ++k) {
+      int prob, mb, kb0;
+      for (int k = 0; job_at(P, grp, k, &prob, &mb, &kb0); ++k) {
         const Problem& pr = P.p[prob];
         const int a_mn = pr.a_mn, b_mn = pr.b_mn, nk = pr.nk;
         const uint32_t idesc = make_idesc_bf16(BM, BN, a_mn, b_mn);
@@ -182,8 +190,8 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
     const int q = warp & 3;
     const float ad = P.alpha_dev ? __ldg(P.alpha_dev) : 1.f;
     uint32_t as = 0, accph = 0;
-    int prob, mb;
-    for (int k = 0; job_at(P, grp, k, &prob, &mb); ++k) {
+    int prob, mb, kb0;
+    for (int k = 0; job_at(P, grp, k, &prob, &mb, &kb0); ++k) {
       const Problem& pr = P.p[prob];
       const float al = pr.alpha * ad;
       const int accumulate = pr.accumulate;
@@ -195,7 +203,7 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
       } else {
         crow = pr.C + (int64_t)grow * pr.ldc + n0;
       }
-      const int scatter = pr.scatter;
+      const int scatter = pr.scatter | (pr.ksplit > 1);  // both add with red.global
       mbar_wait(&sm.acc_full[as], accph);
       tc_fence_after();
 #pragma unroll 1
@@ -259,6 +267,7 @@ static int fill_problem(g::Problem* p, const GemmDesc& d, int64_t Ng) {
   p->ldc = d.ldc;
   p->nk = (int)(d.K / g::BK);
   p->mblocks = (int)(d.Mg / g::BM);
+  p->ksplit = 1;
   p->a_mn = d.a_mn;
   p->b_mn = d.b_mn;
   p->accumulate = d.accumulate;
@@ -325,8 +334,25 @@ int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float
   if (ngroups < 1) ngroups = 1;
   P.s.group = group;
   P.s.ngroups = ngroups;
-  gemm_schedule(P.p[0].mblocks, P.p[0].nk, P.p[1].mblocks, P.p[1].nk, ngroups, &P.s.r,
-                &P.s.nbA, &P.s.nbB, &P.s.nsA, &P.s.nsB);
+  // split-K for an under-filled long-K problem (e.g. the dA GEMM of a row shard: 32 m-blocks
+  // of 512 k-blocks on 74 CTA groups): its jobs become (m-block, k-part) and the partial tiles
+  // are added into a zeroed C with red.global — otherwise one long job bounds the makespan.
+  if (!P.p[0].scatter && P.p[0].mblocks < ngroups && P.p[0].nk >= 128 && P.p[0].ldc == Ng) {
+    int ks = 1;
+    while (P.p[0].mblocks * ks < ngroups && ks < 8 && P.p[0].nk % (2 * ks) == 0 &&
+           P.p[0].nk / (2 * ks) >= 32)
+      ks *= 2;
+    if (ks > 1) {
+      P.p[0].ksplit = ks;
+      P.p[0].nk /= ks;
+      if (!P.p[0].accumulate)
+        MM25_CUDA_CHECK(cudaMemsetAsync(P.p[0].C, 0,
+                                        sizeof(float) * (size_t)d0->Mg * (size_t)P.p[0].ldc, st));
+    }
+  }
+  gemm_schedule((int64_t)P.p[0].mblocks * P.p[0].ksplit, P.p[0].nk,
+                (int64_t)P.p[1].mblocks * P.p[1].ksplit, P.p[1].nk, ngroups, &P.s.r, &P.s.nbA,
+                &P.s.nbB, &P.s.nsA, &P.s.nsB);
   const size_t smem = sizeof(g::Smem) + 1024;
   MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_grouped_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -121,7 +121,8 @@ def test_tc_gemm_layouts(lib_built, a_mn, b_mn, Mg, Ng, K, acc):
 
 
 @pytest.mark.parametrize("M0,K0,M1,K1,Ng", [(256, 2048, 2048, 256, 512), (128, 512, 512, 128, 256),
-                                            (1024, 4096, 4096, 1024, 512), (384, 640, 640, 384, 1024)])
+                                            (1024, 4096, 4096, 1024, 512), (384, 640, 640, 384, 1024),
+                                            (512, 16384, 16384, 512, 512)])  # last: split-K
 def test_tc_gemm_grouped_pair(lib_built, M0, K0, M1, K1, Ng):
     """dA = G . Y (K-major x MN-major) and dB = G^T . X (MN x MN) in one scheduled launch."""
     from multimodal_2025_b200 import _lib

@@ -23,6 +23,12 @@ def step():
     loss = crit(x, y, ls); loss.backward(); return loss
 for _ in range(5): step()
 torch.cuda.synchronize(); dist.barrier()
+if os.environ.get("MM25_PROFILE_GRAPH", "1") == "1":
+    from multimodal_2025_b200.graphs import GraphedLossStep
+    graphed = GraphedLossStep(crit, x, y, ls, warmup=1)
+    step = lambda: graphed()
+    for _ in range(5): step()
+    torch.cuda.synchronize(); dist.barrier()
 from torch.profiler import profile, ProfilerActivity
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(3): step()
@@ -31,7 +37,7 @@ if rank == 0:
     evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
     evs.sort(key=lambda e: e.time_range.start)
     # last step only: split by the first rownorm kernel occurrences
-    starts = [i for i, e in enumerate(evs) if "rownorm_fwd" in e.name]
+    starts = [i for i, e in enumerate(evs) if "rownorm_f" in e.name]
     first = starts[-2] if len(starts) >= 2 else 0
     last = evs[first:]
     t0 = last[0].time_range.start
