@@ -119,6 +119,13 @@ int mm25_rownorm_bwd(const float* g, const void* xhat, int xhat_dtype, const flo
  * mm25_rownorm_fwd), or <= 0 when unknown.  With a bound and 2 dot_bound |s| log2(e) <= 96 the
  * tcgen05 kernels use a static softmax shift (one exp per logit, no running maximum); results
  * are the same statistics either way.
+ * `e_keep`, `e_flag` (both or neither; NULL to skip): a [B*M, N] bf16 buffer and a device int.
+ * When the tcgen05 static-shift path runs it also stores E_ij = 2^(z_ij log2e - dot_bound |s|
+ * log2e) there and sets *e_flag = 1 (0 on any other path, buffer then untouched).  Handing both
+ * to mm25_sim_bwd with the same scale and dot_bound replaces the S-tile recompute of the
+ * backward by an elementwise pass over E (2 B read + 2 B written per logit); the buffer is
+ * CONSUMED (overwritten by G').  This is the activation autograd would have saved
+ * (clipLoss.py:106 keeps the fp32 logits); at B = 32768 it is 2 GiB of the 180 GB.
  * ------------------------------------------------------------------------------------------ */
 size_t mm25_sim_fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
                                     int impl);
@@ -127,7 +134,7 @@ int mm25_sim_fwd(const void* a, const void* b, int dtype, const float* u, const 
                  const float* scale, int scale_kind, float clamp_max, int mode,
                  int64_t diag_offset, float* row_lse, float* col_max, float* col_sum,
                  float* diag, void* workspace, size_t workspace_bytes, int impl, float dot_bound,
-                 void* stream);
+                 void* e_keep, int* e_flag, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused backward with tile recompute (autograd of the block above).
@@ -139,9 +146,13 @@ int mm25_sim_fwd(const void* a, const void* b, int dtype, const float* u, const 
  *   ddiag [B,M] fp32 = s * G_ii (MODULATED: gradient w.r.t. D_i), NULL to skip
  * col_lse may be NULL iff w_col == 0.  Weights are host scalars; `gout` is an optional device
  * array [B] (upstream gradient per batch entry) folded into all four.
+ * `e_keep`, `e_flag`: the pair mm25_sim_fwd filled (NULL, NULL = always recompute).  With them
+ * the workspace shrinks to the column factors (`with_e` = 1 in the size query) and, when the
+ * flag is up, d loss / d scale is taken as (a . da) / s instead of from the logits — so da or
+ * db must be requested whenever dscale_part is (else the call recomputes as if NULL).
  * ------------------------------------------------------------------------------------------ */
 size_t mm25_sim_bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
-                                    int impl);
+                                    int impl, int with_e);
 int64_t mm25_sim_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int impl);
 int mm25_sim_bwd(const void* a, const void* b, int dtype, const float* u, const float* v,
                  const float* diag_add, int64_t B, int64_t M, int64_t N, int64_t d, int64_t d2,
@@ -149,7 +160,8 @@ int mm25_sim_bwd(const void* a, const void* b, int dtype, const float* u, const 
                  int64_t diag_offset, const float* row_lse, const float* col_lse, float w_row,
                  float w_col, float w_diag, float w_all, const float* gout, float* da,
                  float* db, float* dscale_part, float* ddiag, void* workspace,
-                 size_t workspace_bytes, int impl, float dot_bound, void* stream);
+                 size_t workspace_bytes, int impl, float dot_bound, void* e_keep,
+                 const int* e_flag, void* stream);
 
 /* Fused backward + reduce-scatter for the row-sharded loss (tcgen05 path, PLAIN mode, B = 1):
  * as mm25_sim_bwd, but instead of writing the partial db [N, d] of this rank, rows
@@ -164,7 +176,8 @@ int mm25_sim_bwd_rs(const void* a, const void* b, int dtype, int64_t M, int64_t 
                     const float* row_lse, const float* col_lse, float w_row, float w_col,
                     float w_diag, float w_all, const float* gout, float* da,
                     float* const* db_peers, int64_t npeers, float* dscale_part, void* workspace,
-                    size_t workspace_bytes, float dot_bound, void* stream);
+                    size_t workspace_bytes, float dot_bound, void* e_keep, const int* e_flag,
+                    void* stream);
 
 /* Deterministic fixed-order sum of n fp32 values into out[0] (one CTA). out = alpha * sum. */
 int mm25_sum_parts(const float* parts, int64_t n, float alpha, float* out, void* stream);

@@ -96,12 +96,13 @@ SIGNATURES = {
                                 _vp]),
     "mm25_sim_fwd_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64, _int, _int]),
     "mm25_sim_fwd": (_int, [_vp, _vp, _int, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp, _int,
-                            _f32, _int, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _int, _f32, _vp]),
-    "mm25_sim_bwd_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64, _int, _int]),
+                            _f32, _int, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _int, _f32, _vp, _vp,
+                            _vp]),
+    "mm25_sim_bwd_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64, _int, _int, _int]),
     "mm25_sim_bwd_nparts": (_i64, [_i64, _i64, _i64, _i64, _int, _int]),
     "mm25_sim_bwd": (_int, [_vp, _vp, _int, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp, _int,
                             _f32, _int, _i64, _vp, _vp, _f32, _f32, _f32, _f32, _vp, _vp, _vp, _vp,
-                            _vp, _vp, _sz, _int, _f32, _vp]),
+                            _vp, _vp, _sz, _int, _f32, _vp, _vp, _vp]),
     "mm25_sample_projnormal_fwd": (_int, [_vp, _vp, _vp, _u64, _i64, _i64, _i64, _vp, _vp, _vp]),
     "mm25_sample_projnormal_bwd": (_int, [_vp, _vp, _vp, _vp, _u64, _i64, _i64, _i64, _vp, _vp,
                                           _vp]),
@@ -115,7 +116,7 @@ SIGNATURES = {
     "mm25_log_bessel": (_int, [_vp, _i64, _f64, _vp, _vp, _vp]),
     "mm25_sim_bwd_rs": (_int, [_vp, _vp, _int, _i64, _i64, _i64, _vp, _int, _f32, _i64, _vp, _vp,
                                _f32, _f32, _f32, _f32, _vp, _vp, _vp, _i64, _vp, _vp, _sz, _f32,
-                               _vp]),
+                               _vp, _vp, _vp]),
     "mm25_topk_rows": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
     "mm25_rowdot": (_int, [_vp, _vp, _vp, _i64, _i64, _vp]),
     "mm25_hopfield_bwd_pass": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _vp,

@@ -49,9 +49,11 @@ extern "C" int mm25_sim_fwd(const void* a, const void* b, int dtype, const float
                             int64_t N, int64_t d, int64_t d2, const float* scale, int scale_kind,
                             float clamp_max, int mode, int64_t diag_offset, float* row_lse,
                             float* col_max, float* col_sum, float* diag, void* workspace,
-                            size_t workspace_bytes, int impl, float dot_bound, void* stream) {
+                            size_t workspace_bytes, int impl, float dot_bound, void* e_keep,
+                            int* e_flag, void* stream) {
   if (B <= 0 || M <= 0 || N <= 0 || d <= 0) return MM25_ERR_SHAPE;
   if (!a || !b || !scale || !row_lse || !diag) return MM25_ERR_ARG;
+  if ((e_keep == nullptr) != (e_flag == nullptr)) return MM25_ERR_ARG;
   if ((col_max == nullptr) != (col_sum == nullptr)) return MM25_ERR_ARG;
   if (mode < 0 || mode > 2) return MM25_ERR_ARG;
   if (mode == MM25_SIM_MODULATED && (!u || !v || d2 <= 0)) return MM25_ERR_ARG;
@@ -63,17 +65,20 @@ extern "C" int mm25_sim_fwd(const void* a, const void* b, int dtype, const float
   cudaStream_t st = (cudaStream_t)stream;
   if (t)
     return tc::launch_fwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
-                          col_max, col_sum, diag, workspace, workspace_bytes, dot_bound, st);
+                          col_max, col_sum, diag, workspace, workspace_bytes, dot_bound, e_keep,
+                          e_flag, st);
+  // the SIMT kernels keep nothing: tell the backward to recompute
+  if (e_flag) MM25_CUDA_CHECK(cudaMemsetAsync(e_flag, 0, sizeof(int), st));
   return simt::launch_fwd(a, b, dtype, u, v, diag_add, B, M, N, d, d2, scale, scale_kind,
                           clamp_max, mode, diag_offset, row_lse, col_max, col_sum, diag,
                           workspace, workspace_bytes, st);
 }
 
 extern "C" size_t mm25_sim_bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d,
-                                               int dtype, int impl) {
+                                               int dtype, int impl, int with_e) {
   int err;
   if (use_tc(true, impl, B, M, N, d, dtype, MM25_SIM_PLAIN, &err))
-    return tc::bwd_workspace_bytes(B, M, N, d);
+    return tc::bwd_workspace_bytes(B, M, N, d, with_e != 0);
   return 16;
 }
 
@@ -95,7 +100,8 @@ static int sim_bwd_impl(const void* a, const void* b, int dtype, const float* u,
                         float w_row, float w_col, float w_diag, float w_all, const float* gout,
                         float* da, float* db, float* dscale_part, float* ddiag, void* workspace,
                         size_t workspace_bytes, int impl, float dot_bound,
-                        float* const* db_peers, int npeers, void* stream) {
+                        float* const* db_peers, int npeers, void* e_keep, const int* e_flag,
+                        void* stream) {
   if (B <= 0 || M <= 0 || N <= 0 || d <= 0) return MM25_ERR_SHAPE;
   if (!a || !b || !scale || !row_lse) return MM25_ERR_ARG;
   if (!col_lse && w_col != 0.f) return MM25_ERR_ARG;
@@ -109,7 +115,8 @@ static int sim_bwd_impl(const void* a, const void* b, int dtype, const float* u,
   if (t)
     return tc::launch_bwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
                           col_lse, w_row, w_col, w_diag, w_all, gout, da, db, dscale_part,
-                          workspace, workspace_bytes, dot_bound, db_peers, npeers, st);
+                          workspace, workspace_bytes, dot_bound, db_peers, npeers, e_keep, e_flag,
+                          st);
   if (db_peers) return MM25_ERR_SHAPE;  // the fused reduce-scatter exists on the tcgen05 path only
   int rc = MM25_OK;
   if (da) {
@@ -134,11 +141,12 @@ extern "C" int mm25_sim_bwd(const void* a, const void* b, int dtype, const float
                             const float* col_lse, float w_row, float w_col, float w_diag,
                             float w_all, const float* gout, float* da, float* db,
                             float* dscale_part, float* ddiag, void* workspace,
-                            size_t workspace_bytes, int impl, float dot_bound, void* stream) {
+                            size_t workspace_bytes, int impl, float dot_bound, void* e_keep,
+                            const int* e_flag, void* stream) {
   return sim_bwd_impl(a, b, dtype, u, v, diag_add, B, M, N, d, d2, scale, scale_kind, clamp_max,
                       mode, diag_offset, row_lse, col_lse, w_row, w_col, w_diag, w_all, gout, da,
                       db, dscale_part, ddiag, workspace, workspace_bytes, impl, dot_bound,
-                      nullptr, 0, stream);
+                      nullptr, 0, e_keep, e_flag, stream);
 }
 
 extern "C" int mm25_sim_bwd_rs(const void* a, const void* b, int dtype, int64_t M, int64_t N,
@@ -147,12 +155,14 @@ extern "C" int mm25_sim_bwd_rs(const void* a, const void* b, int dtype, int64_t 
                                float w_row, float w_col, float w_diag, float w_all,
                                const float* gout, float* da, float* const* db_peers,
                                int64_t npeers, float* dscale_part, void* workspace,
-                               size_t workspace_bytes, float dot_bound, void* stream) {
+                               size_t workspace_bytes, float dot_bound, void* e_keep,
+                               const int* e_flag, void* stream) {
   if (!db_peers || npeers < 1 || npeers > 16) return MM25_ERR_ARG;
   for (int64_t i = 0; i < npeers; ++i)
     if (!db_peers[i]) return MM25_ERR_ARG;
   return sim_bwd_impl(a, b, dtype, nullptr, nullptr, nullptr, 1, M, N, d, 0, scale, scale_kind,
                       clamp_max, MM25_SIM_PLAIN, diag_offset, row_lse, col_lse, w_row, w_col,
                       w_diag, w_all, gout, da, nullptr, dscale_part, nullptr, workspace,
-                      workspace_bytes, 2, dot_bound, db_peers, (int)npeers, stream);
+                      workspace_bytes, 2, dot_bound, db_peers, (int)npeers, e_keep, e_flag,
+                      stream);
 }

@@ -30,7 +30,9 @@ __device__ __forceinline__ float butterfly_colsum(float (&e)[32], int lane) {
 
 __global__ void __launch_bounds__(FWD_THREADS, 1)
 sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                  const __grid_constant__ CUtensorMap tmap_b, int64_t M, int64_t N, int d,
+                  const __grid_constant__ CUtensorMap tmap_b,
+                  const __grid_constant__ CUtensorMap tmap_e, int store_e,
+                  int* __restrict__ e_flag, int64_t M, int64_t N, int d,
                   int nrb_per_batch, int total_rb, int nseg, int tps,
                   const float* __restrict__ scale, int scale_kind, float clamp_max,
                   int64_t diag_offset, float* __restrict__ row_pm, float* __restrict__ row_pl,
@@ -61,6 +63,14 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const float c2 = s * LOG2E;
     const float m2s = dot_bound * fabsf(c2);
     const bool fast_static = !force_slow && dot_bound > 0.f && 2.f * m2s <= SPREAD_LIMIT;
+    // E = 2^(z log2e - m2s) in bf16 is kept for the backward (static shift only): it replaces
+    // the S-tile recompute there.  e_flag tells the backward whether E is valid.
+    const bool keep_e = store_e && fast_static;
+    if (store_e && blockIdx.x == 0 && threadIdx.x == 64) *e_flag = keep_e ? 1 : 0;
+    uint8_t* stage = sm.stage[ew];
+    const uint32_t st_row = smem_u32(stage) + lane * 64;
+    const uint32_t st_xor = (lane >> 1) & 3;
+    if (keep_e && lane == 0) tma_prefetch_desc(&tmap_e);
     uint32_t as = 0, accph = 0, buf = 0;
     for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
       const int rbg = item / nseg, seg = item % nseg;
@@ -102,6 +112,31 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
             for (int j = 0; j < 32; ++j) { e[j] = ex2_approx(fmaf(v[j], c2, -m2s)); rs += e[j]; }
             rl += rs;
             cm = m2s;
+            if (keep_e) {
+              uint32_t pk[16];
+#pragma unroll
+              for (int j2 = 0; j2 < 16; ++j2) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(e[2 * j2], e[2 * j2 + 1]);
+                pk[j2] = *reinterpret_cast<uint32_t*>(&h);
+              }
+              if (lane == 0) tma_store_wait_read<0>();
+              __syncwarp();
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                const uint32_t addr = st_row + ((u ^ st_xor) << 4);
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr),
+                             "r"(pk[4 * u]), "r"(pk[4 * u + 1]), "r"(pk[4 * u + 2]),
+                             "r"(pk[4 * u + 3])
+                             : "memory");
+              }
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_2d(&tmap_e, stage, (int32_t)cbase,
+                             (int32_t)((int64_t)bz * M + (int64_t)rb * BM + q * 32));
+                tma_store_commit();
+              }
+            }
           } else {
             float tmx = v[0], tmn = v[0];
 #pragma unroll
@@ -183,6 +218,7 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
       row_pm[o] = rm;
       row_pl[o] = rl;
     }
+    if (keep_e && lane == 0) tma_store_wait_all<0>();
   }
 
   tc_fence_before();
@@ -334,8 +370,9 @@ void set_force_slow(int v) { g_force_slow = v; }
 int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,
                const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
                float* row_lse, float* col_max, float* col_sum, float* diag, void* ws,
-               size_t ws_bytes, float dot_bound, cudaStream_t st) {
+               size_t ws_bytes, float dot_bound, void* e_out, int* e_flag, cudaStream_t st) {
   if (!eligible_fwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)) return MM25_ERR_SHAPE;
+  if ((e_out == nullptr) != (e_flag == nullptr)) return MM25_ERR_ARG;
   if (ws_bytes < fwd_workspace_bytes(B, M, N, d)) return MM25_ERR_WORKSPACE;
   FwdGeom g = fwd_geom(B, M, N);
   CUtensorMap ta, tb;
@@ -343,6 +380,11 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   if (rc) return rc;
   rc = make_tmap_bf16(&tb, b, (uint64_t)(B * N), (uint64_t)d, BN, BK);
   if (rc) return rc;
+  CUtensorMap te = ta;  // placeholder when E is not kept
+  if (e_out) {
+    rc = make_tmap_bf16(&te, e_out, (uint64_t)(B * M), (uint64_t)N, 32, 32, 64);
+    if (rc) return rc;
+  }
   float* row_pm = (float*)ws;
   float* row_pl = row_pm + (size_t)B * g.nseg * 2 * M;
   float* col_pm = row_pl + (size_t)B * g.nseg * 2 * M;
@@ -351,7 +393,7 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_fwd_tc_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   sim_fwd_tc_kernel<<<g.grid, FWD_THREADS, smem, st>>>(
-      ta, tb, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind, clamp_max,
+      ta, tb, te, e_out ? 1 : 0, e_flag, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind, clamp_max,
       diag_offset, row_pm, row_pl, col_pm, col_pl, diag, g_force_slow, dot_bound);
   MM25_LAUNCH_CHECK();
   const int64_t mx = M > N ? M : N;

@@ -49,7 +49,10 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                    const float* __restrict__ row_lse, const float* __restrict__ col_lse,
                    float w_row, float w_col, float w_diag, float w_all,
                    const float* __restrict__ gout, float* __restrict__ dscale_part,
-                   const float* __restrict__ Cc, float dot_bound) {
+                   const float* __restrict__ Cc, float dot_bound,
+                   const int* __restrict__ skip_flag) {
+  // the forward kept E (grad_from_e_kernel already formed G' from it): nothing to recompute
+  if (skip_flag && *skip_flag) return;
   extern __shared__ uint8_t smem_raw[];
   GradSmem& sm = *reinterpret_cast<GradSmem*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -221,6 +224,99 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
 }
 
 // ------------------------------------------------------------------------------------------
+// Kept-E path.  When the forward ran its static-shift epilogue it stored E = 2^(z log2e - m2) as
+// bf16 [M, N] (sim_tc.cu) and raised *e_flag.  The backward then needs no S-tile recompute:
+//   G'_ij = E_ij (R_i + C_j) - K  (- k_diag on the positives),   in place over E.
+// HBM-bound: 2 B read + 2 B written per logit.  One CTA owns a 32-row x 2048-column block; each
+// thread keeps its 8 column factors C_j in registers and walks the rows four at a time.
+constexpr int GE_ROWS = 32, GE_COLS = 2048;
+
+__global__ void __launch_bounds__(256)
+grad_from_e_kernel(__nv_bfloat16* __restrict__ EG, const int* __restrict__ e_flag, int64_t M,
+                   int64_t N, const float* __restrict__ scale, int scale_kind, float clamp_max,
+                   int64_t diag_offset, const float* __restrict__ row_lse,
+                   const float* __restrict__ Cc, float w_row, float w_diag, float w_all,
+                   const float* __restrict__ gout, float dot_bound) {
+  if (*e_flag == 0) return;
+  const int64_t c0 = (int64_t)blockIdx.x * GE_COLS + threadIdx.x * 8;
+  if (c0 >= N) return;
+  const int64_t r0 = (int64_t)blockIdx.y * GE_ROWS;
+  const float s = load_scale(scale, scale_kind, clamp_max);
+  const float gs = (gout ? __ldg(gout) : 1.f) * s;
+  const float m2 = dot_bound * fabsf(s) * LOG2E;
+  const float k_all = gs * w_all, k_diag = gs * w_diag, gr = gs * w_row;
+  float cj[8];
+  {
+    const float4 x = __ldg(reinterpret_cast<const float4*>(Cc + c0));
+    const float4 y = __ldg(reinterpret_cast<const float4*>(Cc + c0 + 4));
+    cj[0] = x.x; cj[1] = x.y; cj[2] = x.z; cj[3] = x.w;
+    cj[4] = y.x; cj[5] = y.y; cj[6] = y.z; cj[7] = y.w;
+  }
+  const int64_t rend = (r0 + GE_ROWS < M) ? r0 + GE_ROWS : M;
+  for (int64_t r = r0; r < rend; r += 4) {
+    uint4 v[4];
+    float Ri[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (r + u < rend) {
+        v[u] = __ldcs(reinterpret_cast<const uint4*>(EG + (r + u) * N + c0));
+        Ri[u] = gr * exp2f(m2 - __ldg(row_lse + r + u) * LOG2E);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (r + u >= rend) break;
+      const int64_t rel = r + u + diag_offset - c0;  // position of the positive in this thread
+      uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float e0 = __uint_as_float(w[k] << 16);
+        const float e1 = __uint_as_float(w[k] & 0xffff0000u);
+        float g0 = fmaf(e0, Ri[u] + cj[2 * k], -k_all);
+        float g1 = fmaf(e1, Ri[u] + cj[2 * k + 1], -k_all);
+        if (rel == 2 * k) g0 -= k_diag;
+        if (rel == 2 * k + 1) g1 -= k_diag;
+        __nv_bfloat162 h = __floats2bfloat162_rn(g0, g1);
+        w[k] = *reinterpret_cast<uint32_t*>(&h);
+      }
+      __stcs(reinterpret_cast<uint4*>(EG + (r + u) * N + c0), make_uint4(w[0], w[1], w[2], w[3]));
+    }
+  }
+}
+
+// d(loss)/d(scale) of the kept-E path:  gout sum_ij G_ij v_ij = (1/s) sum_i a_i . dA_i  (dA = G' B
+// already holds gout s G B), so the logits are not needed again.  `x` is the bf16 operand whose
+// gradient `g` (fp32, same shape) the grouped GEMM just wrote; one partial per CTA.
+__global__ void __launch_bounds__(256)
+dscale_from_grad_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ g,
+                        int64_t n, const int* __restrict__ e_flag,
+                        const float* __restrict__ scale, int scale_kind, float clamp_max,
+                        float* __restrict__ part) {
+  if (*e_flag == 0) return;
+  float acc = 0.f;
+  for (int64_t i = ((int64_t)blockIdx.x * 256 + threadIdx.x) * 4; i < n;
+       i += (int64_t)gridDim.x * 256 * 4) {
+    const uint2 xv = __ldg(reinterpret_cast<const uint2*>(x + i));
+    const float4 gv = __ldg(reinterpret_cast<const float4*>(g + i));
+    acc = fmaf(__uint_as_float(xv.x << 16), gv.x, acc);
+    acc = fmaf(__uint_as_float(xv.x & 0xffff0000u), gv.y, acc);
+    acc = fmaf(__uint_as_float(xv.y << 16), gv.z, acc);
+    acc = fmaf(__uint_as_float(xv.y & 0xffff0000u), gv.w, acc);
+  }
+  __shared__ float red[8];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float tot = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) tot += red[k];
+    const float s = load_scale(scale, scale_kind, clamp_max);
+    part[blockIdx.x] = s != 0.f ? tot / s : 0.f;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 static size_t g_workspace_cap = (size_t)1 << 30;   // bytes of the bf16 G panel
 void set_g_cap(size_t bytes) { g_workspace_cap = bytes ? bytes : ((size_t)1 << 30); }
 
@@ -235,14 +331,17 @@ static int64_t panel_rows(int64_t M, int64_t N) {
   return r;
 }
 
-size_t bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d) {
-  // bf16 G panel + the [N] column factors of the static-shift epilogue
-  return (size_t)panel_rows(M, N) * (size_t)N * 2 + 256 + (size_t)N * sizeof(float) + 256;
+size_t bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, bool with_e) {
+  // bf16 G panel (not needed when the forward kept E: G' is formed in place there) + the [N]
+  // column factors of the static-shift epilogue
+  const size_t panel = with_e ? 0 : (size_t)panel_rows(M, N) * (size_t)N * 2;
+  return panel + 256 + (size_t)N * sizeof(float) + 256;
 }
 
 int64_t bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d) {
+  // one slot per CTA of every panel's G kernel + one set for the kept-E scale gradient
   const int64_t R = panel_rows(M, N);
-  return B * ceil_div(M, R) * tc_sm_count();
+  return B * (ceil_div(M, R) + 1) * tc_sm_count();
 }
 
 int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,
@@ -250,18 +349,21 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                const float* row_lse, const float* col_lse, float w_row, float w_col,
                float w_diag, float w_all, const float* gout, float* da, float* db,
                float* dscale_part, void* ws, size_t ws_bytes, float dot_bound,
-               float* const* db_peers, int npeers, cudaStream_t st) {
+               float* const* db_peers, int npeers, void* e_buf, const int* e_flag,
+               cudaStream_t st) {
   if (!eligible_bwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)) return MM25_ERR_SHAPE;
   if (db_peers && (B != 1 || npeers < 1 || N % npeers != 0)) return MM25_ERR_SHAPE;
   if (!col_lse) return MM25_ERR_ARG;
-  if (ws_bytes < bwd_workspace_bytes(B, M, N, d)) return MM25_ERR_WORKSPACE;
-  __nv_bfloat16* G = reinterpret_cast<__nv_bfloat16*>(
-      (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255));
-  const int64_t R = panel_rows(M, N);
+  if ((e_buf == nullptr) != (e_flag == nullptr)) return MM25_ERR_ARG;
+  // kept-E path: the scale gradient comes from a . dA (or b . dB), so one of them must exist
+  const bool use_e = e_buf && dot_bound > 0.f && (!dscale_part || da || (db && !db_peers));
+  if (ws_bytes < bwd_workspace_bytes(B, M, N, d, use_e)) return MM25_ERR_WORKSPACE;
+  const uintptr_t ws0 = (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255);
+  const int64_t R = use_e ? M : panel_rows(M, N);
   float* Cc = nullptr;
   if (dot_bound > 0.f) {
     Cc = reinterpret_cast<float*>(
-        (reinterpret_cast<uintptr_t>(G) + (size_t)R * (size_t)N * 2 + 255) & ~uintptr_t(255));
+        use_e ? ws0 : ((ws0 + (size_t)R * (size_t)N * 2 + 255) & ~uintptr_t(255)));
   }
   const int sms = tc_sm_count();
   const size_t smem = sizeof(GradSmem) + 1024;
@@ -273,6 +375,8 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   for (int64_t bz = 0; bz < B; ++bz) {
     const __nv_bfloat16* a_b = ab + bz * M * d;
     const __nv_bfloat16* b_b = bb + bz * N * d;
+    __nv_bfloat16* G = use_e ? reinterpret_cast<__nv_bfloat16*>(e_buf) + bz * M * N
+                             : reinterpret_cast<__nv_bfloat16*>(ws0);
     CUtensorMap ta, tb;
     int rc = make_tmap_bf16(&ta, a_b, (uint64_t)M, (uint64_t)d, BM, BK);
     if (rc) return rc;
@@ -282,6 +386,15 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
       grad_col_coef_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(
           col_lse + bz * N, N, scale, scale_kind, clamp_max, gout ? gout + bz : nullptr, w_col,
           dot_bound, Cc);
+      MM25_LAUNCH_CHECK();
+    }
+    if (use_e) {
+      // E -> G' in place (no-op when the forward did not raise the flag; the recompute kernel
+      // below then fills the same buffer)
+      dim3 grid((unsigned)ceil_div(N, GE_COLS), (unsigned)ceil_div(M, GE_ROWS));
+      grad_from_e_kernel<<<grid, 256, 0, st>>>(
+          G, e_flag, M, N, scale, scale_kind, clamp_max, diag_offset, row_lse + bz * M, Cc, w_row,
+          w_diag, w_all, gout ? gout + bz : nullptr, dot_bound);
       MM25_LAUNCH_CHECK();
     }
     for (int64_t p0 = 0; p0 < M; p0 += R) {
@@ -314,7 +427,7 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
           ta, tb, tg, M, N, (int)d, (int)(p0 / BM), num_rb, nseg, tps, scale, scale_kind, clamp_max,
           diag_offset, row_lse + bz * M, col_lse + bz * N, w_row, w_col, w_diag, w_all,
           gout ? gout + bz : nullptr, dscale_part ? dscale_part + part : nullptr, Cc,
-          dot_bound);
+          dot_bound, use_e ? e_flag : nullptr);
       MM25_LAUNCH_CHECK();
       part += sms;
       {
@@ -334,6 +447,19 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
         }
         if (rc) return rc;
       }
+    }
+    if (dscale_part) {
+      MM25_CUDA_CHECK(cudaMemsetAsync(dscale_part + part, 0, sizeof(float) * sms, st));
+      if (use_e) {
+        if (da)
+          dscale_from_grad_kernel<<<sms, 256, 0, st>>>(a_b, da + bz * M * d, M * d, e_flag, scale,
+                                                       scale_kind, clamp_max, dscale_part + part);
+        else
+          dscale_from_grad_kernel<<<sms, 256, 0, st>>>(b_b, db + bz * N * d, N * d, e_flag, scale,
+                                                       scale_kind, clamp_max, dscale_part + part);
+        MM25_LAUNCH_CHECK();
+      }
+      part += sms;
     }
   }
   return MM25_OK;

@@ -28,6 +28,7 @@ struct FwdSmem {
   uint8_t b[NST][B_BYTES];
   float colm[2][4][BN];
   float cols[2][4][BN];
+  uint8_t stage[NEPI][2048];  // per-warp staging of the bf16 E chunk (TMA store, 64B swizzle)
   uint64_t full[NST], empty[NST];
   uint64_t acc_full[NACC], acc_empty[NACC];
   uint32_t tmem_base;

@@ -104,9 +104,18 @@ class _ShardedClipFn(torch.autograd.Function):
         # (2) all-gather the other modality
         yall = _all_gather_cat(yhat[0], group).unsqueeze(0)
         # (3) local block
-        row_lse, cmax, csum, diag = B.sim_fwd(xhat, yall, None, None, None, scale32,
-                                              B.SCALE_LOG, clamp_max, B.SIM_PLAIN, rank * n,
-                                              True, impl, 1.01 if normalize else 0.0)
+        bound = 1.01 if normalize else 0.0
+        keep = (hasattr(B, "sim_fwd_keep") and xhat.is_cuda and torch.is_grad_enabled()
+                and any(ctx.needs_input_grad[:3]) and bound > 0.0 and impl != 1
+                and B.tc_eligible_bwd(xhat, yall) and 2 * n * N <= B.keep_e_bytes_limit())
+        e_keep = e_flag = None
+        if keep:  # E = exp(z - shift) of the local [n, N] block is kept for the backward
+            row_lse, cmax, csum, diag, e_keep, e_flag = B.sim_fwd_keep(
+                xhat, yall, scale32, B.SCALE_LOG, clamp_max, rank * n, True, impl, bound)
+        else:
+            row_lse, cmax, csum, diag = B.sim_fwd(xhat, yall, None, None, None, scale32,
+                                                  B.SCALE_LOG, clamp_max, B.SIM_PLAIN, rank * n,
+                                                  True, impl, bound)
         # (4) ONE all-gather carries the column partials (max, sum)[N] and each rank's scalar
         #     pieces (column sums of xhat / yhat for the smoothing term); everything is then
         #     merged / summed locally in rank order (deterministic, one collective fewer)
@@ -130,6 +139,7 @@ class _ShardedClipFn(torch.autograd.Function):
                               logits_scale)
         ctx.cfg = (eps_ls, normalize, clamp_max, group, backend, grad_scale, impl, in_dtype,
                    rank, n, N)
+        ctx.kept = (e_keep, e_flag)
         return loss
 
     @staticmethod
@@ -141,6 +151,9 @@ class _ShardedClipFn(torch.autograd.Function):
         nn_ = float(N)
         g = (gout.detach().to(torch.float32).reshape(1) * grad_scale).contiguous()
         bound = 1.01 if normalize else 0.0
+        e_keep, e_flag = ctx.kept
+        ctx.kept = (None, None)
+        kept = () if e_keep is None else (e_keep, e_flag)
         weights = (0.5 / nn_, 0.5 / nn_, (1.0 - eps_ls) / nn_, eps_ls / (nn_ * nn_))
         symm = None
         if (hasattr(B, "sim_bwd_rs") and xhat.is_cuda and xhat.dtype == torch.bfloat16 and
@@ -158,14 +171,14 @@ class _ShardedClipFn(torch.autograd.Function):
             hdl.barrier(channel=0)
             da, dscale = B.sim_bwd_rs(xhat, yall, scale32, B.SCALE_LOG, clamp_max, rank * n,
                                       row_lse, col_lse.reshape(1, N), *weights, g,
-                                      [int(p) for p in hdl.buffer_ptrs], bound)
+                                      [int(p) for p in hdl.buffer_ptrs], bound, *kept)
             hdl.barrier(channel=1)
             dy_local = buf.unsqueeze(0)
         else:
             da, db, dscale, _ = B.sim_bwd(xhat, yall, None, None, None, scale32, B.SCALE_LOG,
                                           clamp_max, B.SIM_PLAIN, rank * n, row_lse,
                                           col_lse.reshape(1, N), *weights, g, True, True, False,
-                                          impl, bound)
+                                          impl, bound, *kept)
             dy_local = _reduce_scatter_sum(db[0], group).unsqueeze(0)
         out_dt = B.BF16 if in_dtype == torch.bfloat16 else B.F32
         dimg = B.rownorm_bwd(da, xhat, invx, normalize, out_dt, None)[0].to(in_dtype)

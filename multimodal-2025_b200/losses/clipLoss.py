@@ -40,15 +40,27 @@ class _ClipLossFn(torch.autograd.Function):
         scale32 = logits_scale.detach().reshape(1).to(torch.float32).contiguous()
         B, M, _ = xhat.shape
         bound = ops.DOT_BOUND_NORMALIZED if normalize else 0.0
-        row_lse, cmax, csum, diag = ops.sim_fwd(xhat, yhat, None, None, None, scale32,
-                                                scale_kind, clamp_max, ops.SIM_PLAIN, 0, True,
-                                                impl, bound)
+        # Keep E = exp(z - shift) (bf16, the activation autograd would have saved) so the
+        # backward forms G' from it instead of recomputing the S tiles (include/mm25.h e_keep).
+        N = yhat.shape[1]
+        keep = (torch.is_grad_enabled() and any(ctx.needs_input_grad[:3]) and bound > 0.0
+                and impl != ops.IMPL_SIMT and ops.tc_eligible_bwd(xhat, yhat)
+                and 2 * B * M * N <= ops.keep_e_bytes_limit())
+        e_keep = e_flag = None
+        if keep:
+            row_lse, cmax, csum, diag, e_keep, e_flag = ops.sim_fwd_keep(
+                xhat, yhat, scale32, scale_kind, clamp_max, 0, True, impl, bound)
+        else:
+            row_lse, cmax, csum, diag = ops.sim_fwd(xhat, yhat, None, None, None, scale32,
+                                                    scale_kind, clamp_max, ops.SIM_PLAIN, 0,
+                                                    True, impl, bound)
         col_lse = ops.col_merge(cmax.reshape(1, -1), csum.reshape(1, -1)).reshape(B, -1)
         loss = ops.clip_loss_finalize(row_lse, diag, col_lse, sx if want_cs else None,
                                       sy if want_cs else None, M, scale32, scale_kind,
                                       clamp_max, eps_ls)
         ctx.save_for_backward(xhat, yhat, invx, invy, row_lse, col_lse, scale32, logits_scale)
         ctx.cfg = (eps_ls, normalize, clamp_max, scale_kind, impl, in_dtype)
+        ctx.kept = (e_keep, e_flag)  # consumed by the (single) backward, never an output
         return loss
 
     @staticmethod
@@ -58,11 +70,13 @@ class _ClipLossFn(torch.autograd.Function):
         B, M, _ = xhat.shape
         n = float(M)
         gout = gout.detach().to(torch.float32).reshape(B).contiguous()
+        e_keep, e_flag = ctx.kept
+        ctx.kept = (None, None)  # E is overwritten by G': a second backward recomputes
         da, db, dscale, _ = ops.sim_bwd(
             xhat, yhat, None, None, None, scale32, scale_kind, clamp_max, ops.SIM_PLAIN, 0,
             row_lse, col_lse, 0.5 / n, 0.5 / n, (1.0 - eps_ls) / n, eps_ls / (n * n), gout,
             ctx.needs_input_grad[0] or ctx.needs_input_grad[2], ctx.needs_input_grad[1], False,
-            impl, ops.DOT_BOUND_NORMALIZED if normalize else 0.0)
+            impl, ops.DOT_BOUND_NORMALIZED if normalize else 0.0, e_keep, e_flag)
         out_dt = ops.BF16 if in_dtype == torch.bfloat16 else ops.F32
         dimg = dtxt = dls = None
         if ctx.needs_input_grad[0]:

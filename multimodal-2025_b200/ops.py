@@ -88,13 +88,8 @@ def rownorm_bwd(g: Tensor, xhat: Tensor, inv_norm: Tensor, normalize: bool, out_
     return dx
 
 
-@torch.library.custom_op("mm25::sim_fwd", mutates_args=(), device_types="cuda")
-def sim_fwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
-            diag_add: Optional[Tensor], scale: Tensor, scale_kind: int, clamp_max: float,
-            mode: int, diag_offset: int, want_cols: bool,
-            impl: int, dot_bound: float = 0.0) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
-    """Fused similarity + online row/column LSE; returns (row_lse, col_max, col_sum, diag).
-    `dot_bound`: bound on |a_i.b_j| if the caller knows one (include/mm25.h), else 0."""
+def _sim_fwd_impl(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offset,
+                  want_cols, impl, dot_bound, keep):
     a = _cuda3(a, "a")
     b = _cuda3(b, "b")
     if a.dtype != b.dtype:
@@ -112,23 +107,62 @@ def sim_fwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
         col_sum = torch.empty(cshape, dtype=torch.float32, device=dev)
         wsb = L.mm25_sim_fwd_workspace_bytes(B, M, N, d, _dt(a), impl)
         ws = torch.empty((max(int(wsb), 16),), dtype=torch.uint8, device=dev)
+        e_keep = torch.empty((B * M, N) if keep else (0,), dtype=torch.bfloat16, device=dev)
+        e_flag = torch.zeros((1,), dtype=torch.int32, device=dev)
         rc = L.mm25_sim_fwd(_p(a), _p(b), _dt(a), _p(u), _p(v), _p(diag_add), B, M, N, d, d2,
                             _p(scale), scale_kind, clamp_max, mode, diag_offset, _p(row_lse),
                             _p(col_max) if want_cols else None,
                             _p(col_sum) if want_cols else None, _p(diag), _p(ws), ws.numel(),
-                            impl, dot_bound, _stream(a))
+                            impl, dot_bound, _p(e_keep) if keep else None,
+                            _p(e_flag) if keep else None, _stream(a))
     _lib.check(rc, "mm25_sim_fwd")
-    return row_lse, col_max, col_sum, diag
+    return row_lse, col_max, col_sum, diag, e_keep, e_flag
 
 
+@torch.library.custom_op("mm25::sim_fwd", mutates_args=(), device_types="cuda")
+def sim_fwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
+            diag_add: Optional[Tensor], scale: Tensor, scale_kind: int, clamp_max: float,
+            mode: int, diag_offset: int, want_cols: bool,
+            impl: int, dot_bound: float = 0.0) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """Fused similarity + online row/column LSE; returns (row_lse, col_max, col_sum, diag).
+    `dot_bound`: bound on |a_i.b_j| if the caller knows one (include/mm25.h), else 0."""
+    return _sim_fwd_impl(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offset,
+                         want_cols, impl, dot_bound, False)[:4]
+
+
+@torch.library.custom_op("mm25::sim_fwd_keep", mutates_args=(), device_types="cuda")
+def sim_fwd_keep(a: Tensor, b: Tensor, scale: Tensor, scale_kind: int, clamp_max: float,
+                 diag_offset: int, want_cols: bool, impl: int, dot_bound: float
+                 ) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor, Tensor]:
+    """PLAIN-mode sim_fwd that also keeps E = exp(z - shift) for the backward (include/mm25.h
+    `e_keep`): returns (row_lse, col_max, col_sum, diag, e_keep [B*M, N] bf16, e_flag [1] int32).
+    Pass the last two to sim_bwd / sim_bwd_rs, which consume e_keep."""
+    return _sim_fwd_impl(a, b, None, None, None, scale, scale_kind, clamp_max, SIM_PLAIN,
+                         diag_offset, want_cols, impl, dot_bound, True)
+
+
+def keep_e_bytes_limit() -> int:
+    """Largest E buffer (bytes) the losses keep for the backward (MM25_KEEP_E_GB, default 0 =
+    always recompute).  Measured on one B200 at B = 32768 (profiles/r1_keep_e.md): the E store
+    costs the epilogue-bound forward +0.23 ms and saves the backward 0.32 ms, i.e. 3.86 vs
+    3.89 ms per step, while E's extra bf16 rounding adds ~40 % to the gradient error — so the
+    S-tile recompute stays the default and this is an opt-in memory/time trade."""
+    import os
+    return int(float(os.environ.get("MM25_KEEP_E_GB", "0")) * (1 << 30))
+
+
+# e_keep is scratch owned by the loss's autograd node and consumed here (never an autograd-visible
+# tensor), so it is not declared in mutates_args (torch cannot version-bump a defaulted argument).
 @torch.library.custom_op("mm25::sim_bwd", mutates_args=(), device_types="cuda")
 def sim_bwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
             diag_add: Optional[Tensor], scale: Tensor, scale_kind: int, clamp_max: float,
             mode: int, diag_offset: int, row_lse: Tensor, col_lse: Optional[Tensor],
             w_row: float, w_col: float, w_diag: float, w_all: float, gout: Optional[Tensor],
             need_da: bool, need_db: bool, need_ddiag: bool,
-            impl: int, dot_bound: float = 0.0) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+            impl: int, dot_bound: float = 0.0, e_keep: Optional[Tensor] = None,
+            e_flag: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
     """Fused backward with tile recompute; returns (da, db, dscale[1], ddiag), all fp32.
+    `e_keep`, `e_flag`: the pair sim_fwd_keep returned (consumed), or None to recompute.
 
     dscale is dL/d(multiplicative scale) = sum_ij G_ij z_ij / s (already times gout)."""
     a = _cuda3(a, "a")
@@ -145,14 +179,16 @@ def sim_bwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
         nparts = int(L.mm25_sim_bwd_nparts(B, M, N, d, _dt(a), impl))
         parts = torch.zeros((max(nparts, 1),), dtype=torch.float32, device=dev)
         dscale = torch.empty((1,), dtype=torch.float32, device=dev)
-        wsb = L.mm25_sim_bwd_workspace_bytes(B, M, N, d, _dt(a), impl)
+        with_e = e_keep is not None and e_keep.numel() > 0 and e_flag is not None
+        wsb = L.mm25_sim_bwd_workspace_bytes(B, M, N, d, _dt(a), impl, int(with_e))
         ws = torch.empty((max(int(wsb), 16),), dtype=torch.uint8, device=dev)
         rc = L.mm25_sim_bwd(_p(a), _p(b), _dt(a), _p(u), _p(v), _p(diag_add), B, M, N, d, d2,
                             _p(scale), scale_kind, clamp_max, mode, diag_offset, _p(row_lse),
                             _p(col_lse), w_row, w_col, w_diag, w_all, _p(gout),
                             _p(da) if need_da else None, _p(db) if need_db else None, _p(parts),
                             _p(ddiag) if need_ddiag else None, _p(ws), ws.numel(), impl,
-                            dot_bound, _stream(a))
+                            dot_bound, _p(e_keep) if with_e else None,
+                            _p(e_flag) if with_e else None, _stream(a))
         _lib.check(rc, "mm25_sim_bwd")
         rc = L.mm25_sum_parts(_p(parts), parts.numel(), 1.0, _p(dscale), _stream(a))
     _lib.check(rc, "mm25_sum_parts")
@@ -387,7 +423,8 @@ def topk_rows(scores: Tensor, k: int) -> Tuple[Tensor, Tensor]:
 def sim_bwd_rs(a: Tensor, b: Tensor, scale: Tensor, scale_kind: int, clamp_max: float,
                diag_offset: int, row_lse: Tensor, col_lse: Tensor, w_row: float, w_col: float,
                w_diag: float, w_all: float, gout: Optional[Tensor], peer_ptrs: List[int],
-               dot_bound: float) -> Tuple[Tensor, Tensor]:
+               dot_bound: float, e_keep: Optional[Tensor] = None,
+               e_flag: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
     """Fused backward + reduce-scatter (include/mm25.h mm25_sim_bwd_rs): returns (da, dscale);
     the partial db of this rank is added into the peers' [N/P, d] fp32 buffers `peer_ptrs`."""
     a = _cuda3(a, "a")
@@ -404,12 +441,14 @@ def sim_bwd_rs(a: Tensor, b: Tensor, scale: Tensor, scale_kind: int, clamp_max: 
         nparts = int(L.mm25_sim_bwd_nparts(1, M, N, d, _dt(a), IMPL_TC))
         parts = torch.zeros((max(nparts, 1),), dtype=torch.float32, device=dev)
         dscale = torch.empty((1,), dtype=torch.float32, device=dev)
-        wsb = L.mm25_sim_bwd_workspace_bytes(1, M, N, d, _dt(a), IMPL_TC)
+        with_e = e_keep is not None and e_keep.numel() > 0 and e_flag is not None
+        wsb = L.mm25_sim_bwd_workspace_bytes(1, M, N, d, _dt(a), IMPL_TC, int(with_e))
         ws = torch.empty((max(int(wsb), 16),), dtype=torch.uint8, device=dev)
         rc = L.mm25_sim_bwd_rs(_p(a), _p(b), _dt(a), M, N, d, _p(scale), scale_kind, clamp_max,
                                diag_offset, _p(row_lse), _p(col_lse), w_row, w_col, w_diag, w_all,
                                _p(gout), _p(da), table, P, _p(parts), _p(ws), ws.numel(),
-                               dot_bound, _stream(a))
+                               dot_bound, _p(e_keep) if with_e else None,
+                               _p(e_flag) if with_e else None, _stream(a))
         _lib.check(rc, "mm25_sim_bwd_rs")
         rc = L.mm25_sum_parts(_p(parts), parts.numel(), 1.0, _p(dscale), _stream(a))
     _lib.check(rc, "mm25_sum_parts")

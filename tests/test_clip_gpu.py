@@ -89,6 +89,22 @@ def test_clip_bf16_vs_oracle(lib_built, impl, n, d, ls):
     assert abs(float(gl) - float(rl)) <= 2e-2 * max(abs(float(rl)), 1e-3)
 
 
+@pytest.mark.parametrize("n,d,ls", [(256, 512, 2.6592), (1024, 256, 3.0), (2048, 512, 4.6052)])
+def test_clip_bf16_kept_e_vs_oracle(lib_built, monkeypatch, n, d, ls):
+    """opt-in kept-E backward (MM25_KEEP_E_GB > 0; the last case exceeds the static-shift range,
+    so the flag stays down and the backward recomputes) against the same oracle and contract."""
+    from multimodal_2025_b200.losses import ClipLoss
+    monkeypatch.setenv("MM25_KEEP_E_GB", "1")
+    x, y = O.synth_embeddings(n, d, 5, correlated=True, dtype=torch.bfloat16)
+    lsc = torch.tensor(ls)
+    ref, (rx, ry, rl) = O.loss_and_grads(O.clip_loss, [x.float(), y.float(), lsc], 0.1, True)
+    m = ClipLoss(0.1).cuda()
+    loss, (gx, gy, gl) = run_ours(lambda a, b, c: m(a, b, c), [x, y, lsc], torch.bfloat16)
+    assert rel_err(loss, ref) < 2e-3
+    assert rel_err(gx, rx) < 2e-2 and rel_err(gy, ry) < 2e-2
+    assert abs(float(gl) - float(rl)) <= 2e-2 * max(abs(float(rl)), 1e-3)
+
+
 def test_clip_linearity_in_upstream_grad(lib_built):
     """size-independent property: grads scale linearly with the upstream gradient."""
     from multimodal_2025_b200.losses import ClipLoss

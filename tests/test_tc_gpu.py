@@ -143,3 +143,68 @@ def test_tc_gemm_grouped_pair(lib_built, M0, K0, M1, K1, Ng):
     r1 = G.float().t() @ X.float()
     assert (C0 - r0).abs().max().item() < 1e-2 * max(1.0, r0.abs().max().item() / 10)
     assert (C1 - r1).abs().max().item() < 1e-2 * max(1.0, r1.abs().max().item() / 10)
+
+
+@pytest.mark.parametrize("B,M,N,d,off,ls", [
+    (1, 256, 256, 256, 0, 2.6592),
+    (1, 384, 1024, 512, 256, 2.6592),    # rank-local rectangular block, shifted positives
+    (3, 256, 512, 256, 0, 3.2),          # batched (vCLIP samples)
+    (1, 2176, 2304, 512, 0, 2.0),        # not a multiple of the 2048-column block
+    (1, 256, 256, 256, 0, 4.6052),       # spread too large for the static shift: flag stays 0
+])
+def test_tc_backward_kept_e_matches_recompute(lib_built, B, M, N, d, off, ls):
+    """the kept-E backward (forward stores E, elementwise E -> G', dscale from a . dA) against
+    the S-tile recompute backward on the same inputs, and E itself against its definition."""
+    from multimodal_2025_b200 import ops
+    a, b = make(B, M, N, d, 7)
+    a = torch.nn.functional.normalize(a.float(), dim=-1).bfloat16()
+    b = torch.nn.functional.normalize(b.float(), dim=-1).bfloat16()
+    scale = torch.tensor([ls], device="cuda")
+    bound = ops.DOT_BOUND_NORMALIZED
+    row_lse, cmax, csum, diag, e_keep, e_flag = ops.sim_fwd_keep(
+        a, b, scale, ops.SCALE_LOG, 4.6052, off, True, ops.IMPL_TC, bound)
+    plain = ops.sim_fwd(a, b, None, None, None, scale, ops.SCALE_LOG, 4.6052, ops.SIM_PLAIN, off,
+                        True, ops.IMPL_TC, bound)
+    for got, ref in zip((row_lse, cmax, csum, diag), plain):
+        assert torch.equal(got, ref)  # keeping E does not change the statistics
+    s = float(torch.tensor(ls).clamp(max=4.6052).exp())
+    fast = 2 * bound * s * 1.4426950408889634 <= 96.0
+    assert int(e_flag.item()) == (1 if fast else 0)
+    if fast:
+        z = s * (a.float() @ b.float().transpose(1, 2))
+        e_ref = torch.exp(z - bound * s).reshape(B * M, N)
+        rel = ((e_keep.float() - e_ref).abs() / e_ref.clamp_min(1e-30)).max().item()
+        assert rel < 1.5e-2, rel  # bf16 rounding (2^-8) + ex2.approx
+    col_lse = (cmax + csum.log())
+    nn_ = float(N)
+    w = (0.5 / nn_, 0.5 / nn_, 0.9 / nn_, 0.1 / (nn_ * nn_))
+    gout = torch.linspace(0.5, 1.5, B, device="cuda")
+    ref = ops.sim_bwd(a, b, None, None, None, scale, ops.SCALE_LOG, 4.6052, ops.SIM_PLAIN, off,
+                      row_lse, col_lse, *w, gout, True, True, False, ops.IMPL_TC, bound)
+    got = ops.sim_bwd(a, b, None, None, None, scale, ops.SCALE_LOG, 4.6052, ops.SIM_PLAIN, off,
+                      row_lse, col_lse, *w, gout, True, True, False, ops.IMPL_TC, bound,
+                      e_keep, e_flag)
+    # fp32 closed form (SURVEY App. A.1) on the same bf16 operands: the bf16 contract (2e-2) holds
+    # for both paths; E's second bf16 rounding makes the kept-E path the looser of the two
+    af, bf = a.float(), b.float()
+    z = s * (af @ bf.transpose(1, 2))
+    r = torch.logsumexp(z, dim=2, keepdim=True)
+    c = torch.logsumexp(z, dim=1, keepdim=True)
+    G = w[0] * (z - r).exp() + w[1] * (z - c).exp() - w[3]
+    idx = torch.arange(M, device="cuda")
+    G[:, idx, idx + off] -= w[2]
+    G = G * gout.reshape(B, 1, 1) * s
+    exact = (G @ bf, G.transpose(1, 2) @ af)
+    for k in (0, 1):
+        den = exact[k].norm().item()
+        e_rec = (ref[k] - exact[k]).norm().item() / den
+        e_kept = (got[k] - exact[k]).norm().item() / den
+        assert e_rec <= 2e-2 and e_kept <= 2e-2, (k, e_rec, e_kept)
+    assert abs(got[2].item() - ref[2].item()) <= 2e-2 * abs(ref[2].item()) + 1e-7
+    # only da requested: dscale still comes out (from a . dA); only db: from b . dB
+    e2 = ops.sim_fwd_keep(a, b, scale, ops.SCALE_LOG, 4.6052, off, True, ops.IMPL_TC, bound)
+    only_db = ops.sim_bwd(a, b, None, None, None, scale, ops.SCALE_LOG, 4.6052, ops.SIM_PLAIN,
+                          off, row_lse, col_lse, *w, gout, False, True, False, ops.IMPL_TC, bound,
+                          e2[4], e2[5])
+    assert abs(only_db[2].item() - ref[2].item()) <= 2e-2 * abs(ref[2].item()) + 1e-7
+    assert (only_db[1] - exact[1]).norm().item() <= 2e-2 * exact[1].norm().item()
