@@ -154,6 +154,19 @@ int mm25_sim_fwd(const void* a, const void* b, int dtype, const float* u, const 
 size_t mm25_sim_bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
                                     int impl, int with_e);
 int64_t mm25_sim_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int impl);
+/* MODULATED mode (AlignCLIP semantic term, loss.py:229-242) also has a tcgen05 path: bf16 a/b,
+ * B = 1, M, N % 128 == 0, d, d2 % 64 == 0, row statistics only (col_max = NULL, w_col = 0);
+ * backward additionally d % 256 == 0, d <= 1024, N % 256 == 0.  Each 128 x 128 tile keeps two
+ * TMEM accumulators (a.b over d, u.v over d2).  It is taken when `impl` != 1 and the caller's
+ * workspace is at least the size below (0 = not eligible: the SIMT kernels run); dscale_part
+ * then needs max(mm25_sim_bwd_nparts, mm25_sim_mod_bwd_nparts) entries. */
+/* Kernel family taken by the last mm25_sim_fwd / mm25_sim_bwd call of this process:
+ * 0 = fp32 SIMT, 1 = tcgen05 PLAIN, 2 = tcgen05 MODULATED, -1 = none yet (test hook). */
+int mm25_debug_last_sim_path(void);
+size_t mm25_sim_mod_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, int64_t d2,
+                                    int dtype, int bwd);
+int64_t mm25_sim_mod_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d, int64_t d2,
+                                int dtype);
 int mm25_sim_bwd(const void* a, const void* b, int dtype, const float* u, const float* v,
                  const float* diag_add, int64_t B, int64_t M, int64_t N, int64_t d, int64_t d2,
                  const float* scale, int scale_kind, float clamp_max, int mode,

@@ -16,8 +16,8 @@ LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libmm25.so")
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 
-SOURCES = ["prep.cu", "sim_simt.cu", "sim_tc.cu", "sim_tc_bwd.cu", "gemm_tc.cu", "api_sim.cu",
-           "hopfield.cu", "samplers.cu", "beta_vmf.cu", "bessel.cu", "topk.cu"]
+SOURCES = ["prep.cu", "sim_simt.cu", "sim_tc.cu", "sim_tc_bwd.cu", "sim_tc_mod.cu", "gemm_tc.cu",
+           "api_sim.cu", "hopfield.cu", "samplers.cu", "beta_vmf.cu", "bessel.cu", "topk.cu"]
 
 _lock = threading.Lock()
 _lib = None
@@ -100,6 +100,9 @@ SIGNATURES = {
                             _vp]),
     "mm25_sim_bwd_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64, _int, _int, _int]),
     "mm25_sim_bwd_nparts": (_i64, [_i64, _i64, _i64, _i64, _int, _int]),
+    "mm25_debug_last_sim_path": (_int, []),
+    "mm25_sim_mod_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _int, _int]),
+    "mm25_sim_mod_bwd_nparts": (_i64, [_i64, _i64, _i64, _i64, _i64, _int]),
     "mm25_sim_bwd": (_int, [_vp, _vp, _int, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp, _int,
                             _f32, _int, _i64, _vp, _vp, _f32, _f32, _f32, _f32, _vp, _vp, _vp, _vp,
                             _vp, _vp, _sz, _int, _f32, _vp, _vp, _vp]),

@@ -23,6 +23,11 @@ int launch_bwd_pass(const void* a, const void* b, int dtype, const float* u, con
 
 using namespace mm25;
 
+// which kernel family the last mm25_sim_fwd / mm25_sim_bwd call of this process took
+// (0 = fp32 SIMT, 1 = tcgen05 PLAIN, 2 = tcgen05 MODULATED); tests use it to prove the path.
+static int g_last_path = -1;
+extern "C" int mm25_debug_last_sim_path(void) { return g_last_path; }
+
 static bool use_tc(bool bwd, int impl, int64_t B, int64_t M, int64_t N, int64_t d, int dtype,
                    int mode, int* err) {
   *err = MM25_OK;
@@ -59,10 +64,19 @@ extern "C" int mm25_sim_fwd(const void* a, const void* b, int dtype, const float
   if (mode == MM25_SIM_MODULATED && (!u || !v || d2 <= 0)) return MM25_ERR_ARG;
   if (dtype != MM25_F32 && dtype != MM25_BF16) return MM25_ERR_DTYPE;
   if (!workspace) return MM25_ERR_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == MM25_SIM_MODULATED && impl != 1 && !col_max &&
+      tcm::eligible(B, M, N, d, d2, dtype, false) &&
+      workspace_bytes >= tcm::workspace_bytes(M, N, d, d2, false)) {
+    if (e_flag) MM25_CUDA_CHECK(cudaMemsetAsync(e_flag, 0, sizeof(int), st));
+    g_last_path = 2;
+    return tcm::launch_fwd(a, b, u, v, diag_add, M, N, d, d2, scale, scale_kind, clamp_max,
+                           diag_offset, row_lse, diag, workspace, workspace_bytes, st);
+  }
   int err;
   const bool t = use_tc(false, impl, B, M, N, d, dtype, mode, &err);
   if (err) return err;
-  cudaStream_t st = (cudaStream_t)stream;
+  g_last_path = t ? 1 : 0;
   if (t)
     return tc::launch_fwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
                           col_max, col_sum, diag, workspace, workspace_bytes, dot_bound, e_keep,
@@ -93,6 +107,21 @@ extern "C" int64_t mm25_sim_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t 
   return n;
 }
 
+// MODULATED mode on the tensor cores: workspace (bf16 copies of u, v + partials / G'' panel) and
+// dscale partial count; 0 when the shape is not eligible (the SIMT kernels then run and the
+// PLAIN-mode queries above apply).
+extern "C" size_t mm25_sim_mod_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d,
+                                               int64_t d2, int dtype, int bwd) {
+  if (!tcm::eligible(B, M, N, d, d2, dtype, bwd != 0)) return 0;
+  return tcm::workspace_bytes(M, N, d, d2, bwd != 0);
+}
+
+extern "C" int64_t mm25_sim_mod_bwd_nparts(int64_t B, int64_t M, int64_t N, int64_t d,
+                                           int64_t d2, int dtype) {
+  if (!tcm::eligible(B, M, N, d, d2, dtype, true)) return 0;
+  return tcm::bwd_nparts(M, N);
+}
+
 static int sim_bwd_impl(const void* a, const void* b, int dtype, const float* u, const float* v,
                         const float* diag_add, int64_t B, int64_t M, int64_t N, int64_t d,
                         int64_t d2, const float* scale, int scale_kind, float clamp_max, int mode,
@@ -108,10 +137,19 @@ static int sim_bwd_impl(const void* a, const void* b, int dtype, const float* u,
   if (mode < 0 || mode > 2) return MM25_ERR_ARG;
   if (mode == MM25_SIM_MODULATED && (!u || !v || d2 <= 0)) return MM25_ERR_ARG;
   if (dtype != MM25_F32 && dtype != MM25_BF16) return MM25_ERR_DTYPE;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == MM25_SIM_MODULATED && impl != 1 && w_col == 0.f && !db_peers &&
+      tcm::eligible(B, M, N, d, d2, dtype, true) && workspace &&
+      workspace_bytes >= tcm::workspace_bytes(M, N, d, d2, true)) {
+    g_last_path = 2;
+    return tcm::launch_bwd(a, b, u, v, diag_add, M, N, d, d2, scale, scale_kind, clamp_max,
+                           diag_offset, row_lse, w_row, w_diag, w_all, gout, da, db, dscale_part,
+                           ddiag, workspace, workspace_bytes, st);
+  }
   int err;
   const bool t = use_tc(true, impl, B, M, N, d, dtype, mode, &err);
   if (err) return err;
-  cudaStream_t st = (cudaStream_t)stream;
+  g_last_path = t ? 1 : 0;
   if (t)
     return tc::launch_bwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
                           col_lse, w_row, w_col, w_diag, w_all, gout, da, db, dscale_part,

@@ -33,4 +33,23 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                cudaStream_t st);
 
 }  // namespace tc
+
+// sim_tc_mod.cu — MODULATED mode on the tensor cores (two TMEM accumulators per tile), B = 1,
+// row statistics only.  u, v are the fp32 normalised semantic features of the C-ABI (cast to
+// bf16 into the workspace).
+namespace tcm {
+bool eligible(int64_t B, int64_t M, int64_t N, int64_t d, int64_t d2, int dtype, bool bwd);
+size_t workspace_bytes(int64_t M, int64_t N, int64_t d, int64_t d2, bool bwd);
+int64_t bwd_nparts(int64_t M, int64_t N);
+int launch_fwd(const void* a, const void* b, const float* u, const float* v,
+               const float* diag_add, int64_t M, int64_t N, int64_t d, int64_t d2,
+               const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
+               float* row_lse, float* diag, void* ws, size_t ws_bytes, cudaStream_t st);
+int launch_bwd(const void* a, const void* b, const float* u, const float* v,
+               const float* diag_add, int64_t M, int64_t N, int64_t d, int64_t d2,
+               const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
+               const float* row_lse, float w_row, float w_diag, float w_all, const float* gout,
+               float* da, float* db, float* dscale_part, float* ddiag, void* ws,
+               size_t ws_bytes, cudaStream_t st);
+}  // namespace tcm
 }  // namespace mm25

@@ -36,7 +36,7 @@ class _ModulatedCEFn(torch.autograd.Function):
     """mean_i (LSE_j z_ij - z_ii),  z = s [(f f^T) o (1 - u u^T) + diag(D)]  (loss.py:229-242)."""
 
     @staticmethod
-    def forward(ctx, feats, sem_hat, paired, logit_scale):
+    def forward(ctx, feats, sem_hat, paired, logit_scale, impl=ops.IMPL_AUTO):
         in_dtype = feats.dtype
         f = feats.detach()
         if f.dtype not in (torch.float32, torch.bfloat16):
@@ -46,13 +46,16 @@ class _ModulatedCEFn(torch.autograd.Function):
         D = paired.detach().float().contiguous().reshape(1, -1)
         sc = logit_scale.detach().reshape(1).float().contiguous()
         n = f3.shape[1]
+        # bf16 features of an eligible shape run the two-accumulator tcgen05 kernels
+        # (csrc/sim_tc_mod.cu); everything else the fp32 SIMT kernels (include/mm25.h)
         row_lse, _, _, diag = ops.sim_fwd(f3, f3, u3, u3, D, sc, ops.SCALE_MUL, 0.0,
-                                          ops.SIM_MODULATED, 0, False, ops.IMPL_SIMT)
+                                          ops.SIM_MODULATED, 0, False, impl)
         # (1/n) sum_i (r_i - z_ii): the CLIP finalize with weights 1/(2n) on 2 r_i and 1/n on diag
         loss = ops.clip_loss_finalize(row_lse * 2.0, diag, None, None, None, n, sc,
                                       ops.SCALE_MUL, 0.0, 0.0)
         ctx.save_for_backward(f3, u3, D, sc, row_lse, logit_scale)
         ctx.in_dtype = in_dtype
+        ctx.impl = impl
         return loss.reshape(())
 
     @staticmethod
@@ -62,13 +65,13 @@ class _ModulatedCEFn(torch.autograd.Function):
         g = gout.detach().float().reshape(1).contiguous()
         da, db, dscale, ddiag = ops.sim_bwd(f3, f3, u3, u3, D, sc, ops.SCALE_MUL, 0.0,
                                             ops.SIM_MODULATED, 0, row_lse, None, 1.0 / n, 0.0,
-                                            1.0 / n, 0.0, g, True, True, True, ops.IMPL_SIMT)
+                                            1.0 / n, 0.0, g, True, True, True, ctx.impl)
         dfeats = (da[0] + db[0]).to(ctx.in_dtype) if ctx.needs_input_grad[0] else None
         dpaired = ddiag[0] if ctx.needs_input_grad[2] else None
         dls = None
         if ctx.needs_input_grad[3]:
             dls = ops.scale_param_grad(dscale, logit_scale, ops.SCALE_MUL, 0.0)
-        return dfeats, None, dpaired, dls
+        return dfeats, None, dpaired, dls, None
 
 
 class ClipLoss(nn.Module):

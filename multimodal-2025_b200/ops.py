@@ -106,6 +106,8 @@ def _sim_fwd_impl(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag
         col_max = torch.empty(cshape, dtype=torch.float32, device=dev)
         col_sum = torch.empty(cshape, dtype=torch.float32, device=dev)
         wsb = L.mm25_sim_fwd_workspace_bytes(B, M, N, d, _dt(a), impl)
+        if mode == SIM_MODULATED and impl != IMPL_SIMT and not want_cols:
+            wsb = max(wsb, L.mm25_sim_mod_workspace_bytes(B, M, N, d, d2, _dt(a), 0))
         ws = torch.empty((max(int(wsb), 16),), dtype=torch.uint8, device=dev)
         e_keep = torch.empty((B * M, N) if keep else (0,), dtype=torch.bfloat16, device=dev)
         e_flag = torch.zeros((1,), dtype=torch.int32, device=dev)
@@ -177,10 +179,13 @@ def sim_bwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
         db = torch.empty((B, N, d) if need_db else (0,), dtype=torch.float32, device=dev)
         ddiag = torch.zeros((B, M) if need_ddiag else (0,), dtype=torch.float32, device=dev)
         nparts = int(L.mm25_sim_bwd_nparts(B, M, N, d, _dt(a), impl))
-        parts = torch.zeros((max(nparts, 1),), dtype=torch.float32, device=dev)
-        dscale = torch.empty((1,), dtype=torch.float32, device=dev)
         with_e = e_keep is not None and e_keep.numel() > 0 and e_flag is not None
         wsb = L.mm25_sim_bwd_workspace_bytes(B, M, N, d, _dt(a), impl, int(with_e))
+        if mode == SIM_MODULATED and impl != IMPL_SIMT and w_col == 0.0:
+            wsb = max(wsb, L.mm25_sim_mod_workspace_bytes(B, M, N, d, d2, _dt(a), 1))
+            nparts = max(nparts, int(L.mm25_sim_mod_bwd_nparts(B, M, N, d, d2, _dt(a))))
+        parts = torch.zeros((max(nparts, 1),), dtype=torch.float32, device=dev)
+        dscale = torch.empty((1,), dtype=torch.float32, device=dev)
         ws = torch.empty((max(int(wsb), 16),), dtype=torch.uint8, device=dev)
         rc = L.mm25_sim_bwd(_p(a), _p(b), _dt(a), _p(u), _p(v), _p(diag_add), B, M, N, d, d2,
                             _p(scale), scale_kind, clamp_max, mode, diag_offset, _p(row_lse),

@@ -86,3 +86,63 @@ def test_alignclip_bf16_tensor_core_cross_modal(lib_built):
     assert rel_err(loss, ref) < 2e-3
     assert rel_err(gx, rx) < 2e-2 and rel_err(gy, ry) < 2e-2
     assert rel_err(gs, rs) < 2e-2
+
+
+@pytest.mark.parametrize("n,d,dsem,sep_img", [(256, 256, 128, False), (512, 512, 768, True),
+                                              (1024, 256, 64, False)])
+def test_semantic_branch_bf16_tensor_core(lib_built, n, d, dsem, sep_img):
+    """bf16 features of an eligible shape: the in-modality semantic term runs the two-accumulator
+    tcgen05 kernels (csrc/sim_tc_mod.cu); oracle fed the same bf16-rounded features, bf16
+    contract (2e-3 loss / 2e-2 grads)."""
+    from multimodal_2025_b200.losses.align_clip_loss import ClipInModalityLoss
+    x, y = O.synth_embeddings(n, d, 3, correlated=True, dtype=torch.bfloat16)
+    s = torch.tensor(14.285)
+    sem = torch.randn(n, dsem, generator=torch.Generator().manual_seed(1))
+    ref, (rx, ry, rs) = O.loss_and_grads(
+        lambda a, b, c: O.inmodality_loss(a, b, c, sem, nl_semantic_supervision=True,
+                                          separate_image=sep_img)[0],
+        [x.float(), y.float(), s])
+    crit = ClipInModalityLoss(alpha=1.0, beta=0.5, nl_semantic_supervision=True,
+                              separate_image=sep_img)
+    semc = sem.cuda()
+    loss, (gx, gy, gs) = run_ours(lambda a, b, c: crit(a, b, c, semantic_features=semc),
+                                  [x, y, s], torch.bfloat16)
+    assert rel_err(loss, ref) < 2e-3
+    assert rel_err(gx, rx) < 2e-2 and rel_err(gy, ry) < 2e-2
+    assert rel_err(gs, rs) < 2e-2
+
+
+@pytest.mark.parametrize("M,N,d,d2,off", [(128, 256, 256, 64, 0), (256, 1024, 512, 192, 512),
+                                          (384, 768, 256, 768, 384)])
+def test_modulated_tc_matches_simt(lib_built, M, N, d, d2, off):
+    """C-ABI level: MODULATED forward statistics and backward (da, db, dscale, ddiag) of the
+    tcgen05 path against the fp32 SIMT kernels on the same bf16 operands, rectangular blocks
+    with shifted positives (the row-sharded layout)."""
+    from multimodal_2025_b200 import ops
+    g = torch.Generator().manual_seed(M + N)
+    nrm = torch.nn.functional.normalize
+    a = nrm(torch.randn(1, M, d, generator=g), dim=-1).cuda().bfloat16()
+    b = nrm(torch.randn(1, N, d, generator=g), dim=-1).cuda().bfloat16()
+    v = nrm(torch.randn(1, N, d2, generator=g), dim=-1).cuda()
+    u = v[:, off:off + M].contiguous()
+    # semantic features rounded to bf16 once so that both paths see the same operands
+    u, v = u.bfloat16().float(), v.bfloat16().float()
+    D = torch.rand(1, M, generator=g).cuda()
+    sc = torch.tensor([14.285], device="cuda")
+    outs = {}
+    for impl in (ops.IMPL_SIMT, ops.IMPL_AUTO):
+        row_lse, _, _, diag = ops.sim_fwd(a, b, u, v, D, sc, ops.SCALE_MUL, 0.0,
+                                          ops.SIM_MODULATED, off, False, impl)
+        gout = torch.tensor([0.7], device="cuda")
+        bw = ops.sim_bwd(a, b, u, v, D, sc, ops.SCALE_MUL, 0.0, ops.SIM_MODULATED, off, row_lse,
+                         None, 1.0 / M, 0.0, 1.0 / M, 0.0, gout, True, True, True, impl)
+        outs[impl] = (row_lse, diag) + tuple(bw)
+        from multimodal_2025_b200 import _lib
+        assert _lib.lib().mm25_debug_last_sim_path() == (0 if impl == ops.IMPL_SIMT else 2)
+    ref, got = outs[ops.IMPL_SIMT], outs[ops.IMPL_AUTO]
+    assert (got[0] - ref[0]).abs().max().item() < 2e-4          # row LSE (fp32 accumulate)
+    assert (got[1] - ref[1]).abs().max().item() < 2e-4 * 15      # positives
+    for k in (2, 3):                                             # da, db (bf16 G'' panel)
+        assert (got[k] - ref[k]).norm().item() <= 2e-2 * ref[k].norm().item(), k
+    assert abs(got[4].item() - ref[4].item()) <= 2e-2 * abs(ref[4].item()) + 1e-6
+    assert (got[5] - ref[5]).norm().item() <= 1e-3 * ref[5].norm().item() + 1e-7

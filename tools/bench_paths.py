@@ -155,7 +155,8 @@ def main():
     emit(path="ClipInModalityLoss(semantic) fwd+bwd", ms=ms, pairs_per_s=n / (ms * 1e-3),
          tflops_algorithmic=n * n * (12.0 * da_ + 2 * dsem) / (ms * 1e-3) / 1e12,
          note="N=8192 d=1024 d_sem=768 bf16 (cfg5 is N=65536 over 8 GPUs); cross-modal term on "
-              "tcgen05, in-modality MODULATED term on the fp32 SIMT kernels")
+              "the PLAIN tcgen05 kernels, in-modality MODULATED term on the two-accumulator "
+              "tcgen05 kernels (csrc/sim_tc_mod.cu)")
 
     # ---- top-k ---------------------------------------------------------------------------------
     Q, Nt, k = 1024, 65536, 100
