@@ -85,7 +85,7 @@ def _symm_grad_buffer(n: int, d: int, device, group):
 class _ShardedClipFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, img, txt, logits_scale, eps_ls, normalize, clamp_max, group, backend,
-                grad_scale, impl):
+                grad_scale, impl, scale_kind=1):
         B = backend
         world = dist.get_world_size(group)
         rank = dist.get_rank(group)
@@ -111,10 +111,10 @@ class _ShardedClipFn(torch.autograd.Function):
         e_keep = e_flag = None
         if keep:  # E = exp(z - shift) of the local [n, N] block is kept for the backward
             row_lse, cmax, csum, diag, e_keep, e_flag = B.sim_fwd_keep(
-                xhat, yall, scale32, B.SCALE_LOG, clamp_max, rank * n, True, impl, bound)
+                xhat, yall, scale32, scale_kind, clamp_max, rank * n, True, impl, bound)
         else:
             row_lse, cmax, csum, diag = B.sim_fwd(xhat, yall, None, None, None, scale32,
-                                                  B.SCALE_LOG, clamp_max, B.SIM_PLAIN, rank * n,
+                                                  scale_kind, clamp_max, B.SIM_PLAIN, rank * n,
                                                   True, impl, bound)
         # (4) ONE all-gather carries the column partials (max, sum)[N] and each rank's scalar
         #     pieces (column sums of xhat / yhat for the smoothing term); everything is then
@@ -126,19 +126,20 @@ class _ShardedClipFn(torch.autograd.Function):
         # (5) scalar pieces of the loss: local rows + local columns, then one small all-reduce
         part = B.clip_loss_finalize(row_lse, diag, col_lse[rank * n:(rank + 1) * n]
                                     .reshape(1, n).contiguous(), None, None, N, scale32,
-                                    B.SCALE_LOG, clamp_max, eps_ls)
+                                    scale_kind, clamp_max, eps_ls)
         red = part.reshape(1).clone()
         dist.all_reduce(red, group=group)
         loss = red.reshape(())
         if want_cs:
             sxg = gathered[:, 2 * N:2 * N + d].sum(dim=0)
             syg = gathered[:, 2 * N + d:2 * N + 2 * d].sum(dim=0)
-            s = scale32.clamp(max=clamp_max).exp().reshape(())
+            s = (scale32.clamp(max=clamp_max).exp() if scale_kind == B.SCALE_LOG
+                 else scale32).reshape(())
             loss = loss - (eps_ls / float(N) ** 2) * s * (sxg * syg).sum()
         ctx.save_for_backward(xhat, yhat, yall, invx, invy, row_lse, col_lse, scale32,
                               logits_scale)
         ctx.cfg = (eps_ls, normalize, clamp_max, group, backend, grad_scale, impl, in_dtype,
-                   rank, n, N)
+                   rank, n, N, scale_kind)
         ctx.kept = (e_keep, e_flag)
         return loss
 
@@ -147,7 +148,7 @@ class _ShardedClipFn(torch.autograd.Function):
         (xhat, yhat, yall, invx, invy, row_lse, col_lse, scale32,
          logits_scale) = ctx.saved_tensors
         (eps_ls, normalize, clamp_max, group, B, grad_scale, impl, in_dtype, rank, n,
-         N) = ctx.cfg
+         N, scale_kind) = ctx.cfg
         nn_ = float(N)
         g = (gout.detach().to(torch.float32).reshape(1) * grad_scale).contiguous()
         bound = 1.01 if normalize else 0.0
@@ -169,13 +170,13 @@ class _ShardedClipFn(torch.autograd.Function):
             buf, hdl = symm
             buf.zero_()
             hdl.barrier(channel=0)
-            da, dscale = B.sim_bwd_rs(xhat, yall, scale32, B.SCALE_LOG, clamp_max, rank * n,
+            da, dscale = B.sim_bwd_rs(xhat, yall, scale32, scale_kind, clamp_max, rank * n,
                                       row_lse, col_lse.reshape(1, N), *weights, g,
                                       [int(p) for p in hdl.buffer_ptrs], bound, *kept)
             hdl.barrier(channel=1)
             dy_local = buf.unsqueeze(0)
         else:
-            da, db, dscale, _ = B.sim_bwd(xhat, yall, None, None, None, scale32, B.SCALE_LOG,
+            da, db, dscale, _ = B.sim_bwd(xhat, yall, None, None, None, scale32, scale_kind,
                                           clamp_max, B.SIM_PLAIN, rank * n, row_lse,
                                           col_lse.reshape(1, N), *weights, g, True, True, False,
                                           impl, bound, *kept)
@@ -186,8 +187,8 @@ class _ShardedClipFn(torch.autograd.Function):
         dls = None
         if ctx.needs_input_grad[2]:
             dist.all_reduce(dscale, group=group)
-            dls = B.scale_param_grad(dscale, logits_scale, B.SCALE_LOG, clamp_max)
-        return dimg, dtxt, dls, None, None, None, None, None, None, None
+            dls = B.scale_param_grad(dscale, logits_scale, scale_kind, clamp_max)
+        return dimg, dtxt, dls, None, None, None, None, None, None, None, None
 
 
 class ShardedClipLoss(nn.Module):
@@ -215,3 +216,144 @@ class ShardedClipLoss(nn.Module):
         return _ShardedClipFn.apply(image_features, text_features, logits_scale,
                                     float(self.label_smoothing), bool(normalize), 4.6052, group,
                                     backend, float(self.grad_scale), int(self.impl))
+
+
+# ----------------------------------------------------------------------------------------------
+# AlignCLIP (reference AlignCLIP/align_clip/loss.py) on the row-sharded global batch
+# ----------------------------------------------------------------------------------------------
+def _sharded_ce_pair(a, b, logit_scale, group, backend, grad_scale, impl):
+    """0.5 (CE(s A B^T) + CE(s B A^T)) of the GLOBAL batch from the local [n, d] shards
+    (no smoothing, no normalisation, multiplicative scale: loss.py:103-132)."""
+    return _ShardedClipFn.apply(a, b, logit_scale, 0.0, False, 0.0, group, backend,
+                                float(grad_scale), int(impl), backend.SCALE_MUL)
+
+
+class _ShardedModCEFn(torch.autograd.Function):
+    """mean over the GLOBAL rows of LSE_j z_ij - z_ii with
+    z = s [(F F^T) o (1 - S S^T) + diag(D)] (loss.py:229-242): rank r holds rows
+    [r n, (r+1) n) of F, of the normalised semantic features S and of D; F and S are
+    all-gathered, the local [n, N] block runs the MODULATED kernels with the positives at
+    column offset r n, the partial dF of the gathered operand is reduce-scattered."""
+
+    @staticmethod
+    def forward(ctx, feats, sem_hat, paired, logit_scale, group, backend, grad_scale, impl):
+        B = backend
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        in_dtype = feats.dtype
+        f = feats.detach()
+        if f.dtype not in (torch.float32, torch.bfloat16):
+            f = f.float()
+        f = f.contiguous()
+        n = f.shape[0]
+        N = n * world
+        fall = _all_gather_cat(f, group).unsqueeze(0)
+        u = sem_hat.detach().float().contiguous()
+        uall = _all_gather_cat(u, group).unsqueeze(0)
+        D = paired.detach().float().contiguous().reshape(1, n)
+        sc = logit_scale.detach().reshape(1).float().contiguous()
+        row_lse, _, _, diag = B.sim_fwd(f.unsqueeze(0), fall, u.unsqueeze(0), uall, D, sc,
+                                        B.SCALE_MUL, 0.0, B.SIM_MODULATED, rank * n, False, impl)
+        # (1/N) sum_i (r_i - z_ii) over the local rows, then one scalar all-reduce
+        part = B.clip_loss_finalize(row_lse * 2.0, diag, None, None, None, N, sc, B.SCALE_MUL,
+                                    0.0, 0.0)
+        red = part.reshape(1).clone()
+        dist.all_reduce(red, group=group)
+        ctx.save_for_backward(f, fall, u, uall, D, sc, row_lse, logit_scale)
+        ctx.cfg = (group, B, grad_scale, impl, in_dtype, rank, n, N)
+        return red.reshape(())
+
+    @staticmethod
+    def backward(ctx, gout):
+        f, fall, u, uall, D, sc, row_lse, logit_scale = ctx.saved_tensors
+        group, B, grad_scale, impl, in_dtype, rank, n, N = ctx.cfg
+        g = (gout.detach().float().reshape(1) * grad_scale).contiguous()
+        nn_ = float(N)
+        da, db, dscale, ddiag = B.sim_bwd(f.unsqueeze(0), fall, u.unsqueeze(0), uall, D, sc,
+                                          B.SCALE_MUL, 0.0, B.SIM_MODULATED, rank * n, row_lse,
+                                          None, 1.0 / nn_, 0.0, 1.0 / nn_, 0.0, g, True, True,
+                                          True, impl)
+        dfeats = dpaired = dls = None
+        if ctx.needs_input_grad[0]:
+            dfeats = (da[0] + _reduce_scatter_sum(db[0], group)).to(in_dtype)
+        if ctx.needs_input_grad[2]:
+            dpaired = ddiag[0]
+        if ctx.needs_input_grad[3]:
+            dist.all_reduce(dscale, group=group)
+            dls = B.scale_param_grad(dscale, logit_scale, B.SCALE_MUL, 0.0)
+        return dfeats, None, dpaired, dls, None, None, None, None
+
+
+class ShardedAlignClipLoss(nn.Module):
+    """open_clip-style ClipLoss (loss.py:67-132) of the GLOBAL batch from local shards: what
+    `world_size > 1, gather_with_grad=True, local_loss=False` computes, without gathering the
+    gradients through autograd and without materialising [N, N] logits."""
+
+    def __init__(self, group=None, grad_scale: float = 1.0, backend=None):
+        super().__init__()
+        self.group, self.grad_scale, self.backend, self.impl = group, grad_scale, backend, 0
+
+    def _ctx(self, ref):
+        backend = self.backend
+        if backend is None:
+            from . import ops as backend
+        group = self.group if self.group is not None else dist.group.WORLD
+        return backend, group
+
+    def forward(self, image_features, text_features, logit_scale, output_dict=False,
+                semantic_features=None):
+        backend, group = self._ctx(image_features)
+        if not torch.is_tensor(logit_scale):
+            logit_scale = torch.tensor(float(logit_scale), device=image_features.device)
+        loss = _sharded_ce_pair(image_features, text_features, logit_scale, group, backend,
+                                self.grad_scale, self.impl)
+        return {"contrastive_loss": loss} if output_dict else loss
+
+
+class ShardedClipInModalityLoss(ShardedAlignClipLoss):
+    """ClipInModalityLoss (loss.py:135-273; AlignCLIPLoss = alpha 1, beta 0.5, semantic) of the
+    GLOBAL batch from local [n, d] feature shards and local [n, d_sem] semantic features (cfg5:
+    N = 65536 over 8 GPUs).  The reference's own world_size > 1 branch never gathers the
+    semantic features; this is the single-process formula on the concatenated
+    batch, which is what the tests check it against."""
+
+    def __init__(self, alpha=1.0, beta=0.5, nl_semantic_supervision=False, separate_text=True,
+                 separate_image=False, group=None, grad_scale: float = 1.0, backend=None):
+        super().__init__(group, grad_scale, backend)
+        self.alpha, self.beta = alpha, beta
+        self.nl_semantic_supervision = nl_semantic_supervision
+        self.separate_text, self.separate_image = separate_text, separate_image
+
+    def forward(self, image_features, text_features, logit_scale, output_dict=False,
+                semantic_features=None):
+        backend, group = self._ctx(image_features)
+        if not torch.is_tensor(logit_scale):
+            logit_scale = torch.tensor(float(logit_scale), device=image_features.device)
+        args = (group, backend, self.grad_scale, self.impl)
+        if self.nl_semantic_supervision:
+            if semantic_features is None:
+                raise TypeError("nl_semantic_supervision=True needs semantic_features")
+            sem = semantic_features.detach().float().unsqueeze(0)
+            sem_hat, _, _ = backend.rownorm_fwd(sem, True, 0.0, backend.F32, False)
+            paired = (image_features.float() * text_features.float()).sum(dim=-1)
+            terms = []
+            if self.separate_text:
+                terms.append(_ShardedModCEFn.apply(text_features, sem_hat[0], paired,
+                                                   logit_scale, *args))
+            if self.separate_image:
+                terms.append(_ShardedModCEFn.apply(image_features, sem_hat[0], paired,
+                                                   logit_scale, *args))
+            if not terms:
+                raise UnboundLocalError("inModality_loss: neither separate_text nor "
+                                        "separate_image is set (reference loss.py:249-255)")
+            inModality_loss = self.beta * sum(terms[1:], terms[0])
+        else:
+            inModality_loss = self.beta * (
+                _sharded_ce_pair(image_features, image_features, logit_scale, *args) +
+                _sharded_ce_pair(text_features, text_features, logit_scale, *args))
+        clip_loss = self.alpha * (2.0 * _sharded_ce_pair(image_features, text_features,
+                                                         logit_scale, *args))
+        total_loss = inModality_loss + clip_loss
+        if output_dict:
+            return {"total_loss": total_loss, "clip_loss": clip_loss,
+                    "inModality_loss": inModality_loss}
+        return total_loss

@@ -22,9 +22,13 @@ def rownorm_fwd(x, normalize, eps, out_dtype, want_colsum):
 
 def sim_fwd(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offset, want_cols,
             impl, dot_bound=0.0):
-    z = _s(scale, scale_kind, clamp_max) * (a.float() @ b.float().transpose(1, 2))
     M = a.shape[1]
     idx = torch.arange(M)
+    base = a.float() @ b.float().transpose(1, 2)
+    if mode == SIM_MODULATED:
+        base = base * (1.0 - u.float() @ v.float().transpose(1, 2))
+        base[:, idx, idx + diag_offset] += diag_add
+    z = _s(scale, scale_kind, clamp_max) * base
     diag = z[:, idx, idx + diag_offset]
     cmax = z.max(dim=1).values
     csum = (z - cmax.unsqueeze(1)).exp().sum(dim=1)
@@ -52,18 +56,26 @@ def sim_bwd(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offse
             col_lse, w_row, w_col, w_diag, w_all, gout, need_da, need_db, need_ddiag, impl,
             dot_bound=0.0):
     s = _s(scale, scale_kind, clamp_max)
-    dot = a.float() @ b.float().transpose(1, 2)
-    z = s * dot
-    G = w_row * (z - row_lse.unsqueeze(2)).exp() + w_col * (z - col_lse.unsqueeze(1)).exp() - w_all
     M = a.shape[1]
     idx = torch.arange(M)
+    dot = a.float() @ b.float().transpose(1, 2)
+    chain = 1.0
+    if mode == SIM_MODULATED:
+        chain = 1.0 - u.float() @ v.float().transpose(1, 2)
+        dot = dot * chain
+        dot[:, idx, idx + diag_offset] += diag_add
+    z = s * dot
+    G = w_row * (z - row_lse.unsqueeze(2)).exp() - w_all
+    if col_lse is not None:
+        G = G + w_col * (z - col_lse.unsqueeze(1)).exp()
     G[:, idx, idx + diag_offset] -= w_diag
     go = gout.reshape(-1, 1, 1) if gout is not None else 1.0
     G = G * go
-    da = s * (G @ b.float())
-    db = s * (G.transpose(1, 2) @ a.float())
+    da = s * ((G * chain) @ b.float())
+    db = s * ((G * chain).transpose(1, 2) @ a.float())
     dscale = (G * dot).sum().reshape(1)
-    return da, db, dscale, torch.empty(0)
+    ddiag = s * G[:, idx, idx + diag_offset] if need_ddiag else torch.empty(0)
+    return da, db, dscale, ddiag
 
 
 def rownorm_bwd(g, xhat, inv_norm, normalize, out_dtype, gscale):

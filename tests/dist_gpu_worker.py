@@ -40,6 +40,34 @@ def main():
         print("rank %d %s N=%d loss_rel=%.2e gx=%.2e gy=%.2e gl=%.2e %s" %
               (rank, dtype, N, el, egx, egy, egl, "OK" if good else "FAIL"), flush=True)
         ok = ok and good
+    # sharded AlignCLIP (semantic, separate_image) on the global batch vs the oracle: fp32 SIMT
+    # kernels and bf16 two-accumulator tcgen05 kernels
+    from multimodal_2025_b200.dist import ShardedClipInModalityLoss
+    for dtype, n, d, dsem, tl, tg in ((torch.float32, 64, 32, 16, 1e-5, 1e-4),
+                                      (torch.bfloat16, 256, 256, 128, 2e-3, 2e-2)):
+        N = n * world
+        x, y = O.synth_embeddings(N, d, 13, correlated=True, dtype=dtype)
+        sem = torch.randn(N, dsem, generator=torch.Generator().manual_seed(5))
+        s = torch.tensor(14.285)
+        fn = lambda a, b, c: O.inmodality_loss(a, b, c, sem, nl_semantic_supervision=True,  # noqa
+                                               separate_image=True)[0]
+        ref, (rx, ry, rs) = O.loss_and_grads(fn, [x.float(), y.float(), s])
+        sl = slice(rank * n, (rank + 1) * n)
+        xl = x[sl].to(dev).requires_grad_(True)
+        yl = y[sl].to(dev).requires_grad_(True)
+        sp = s.to(dev).requires_grad_(True)
+        crit = ShardedClipInModalityLoss(nl_semantic_supervision=True, separate_image=True)
+        loss = crit(xl, yl, sp, semantic_features=sem[sl].to(dev))
+        loss.backward()
+        torch.cuda.synchronize()
+        el = abs(float(loss) - float(ref)) / abs(float(ref))
+        egx = float((xl.grad.float().cpu() - rx[sl]).norm() / rx[sl].norm())
+        egy = float((yl.grad.float().cpu() - ry[sl]).norm() / ry[sl].norm())
+        egl = abs(float(sp.grad) - float(rs)) / abs(float(rs))
+        good = el < tl and egx < tg and egy < tg and egl < tg
+        print("rank %d alignclip %s N=%d loss_rel=%.2e gx=%.2e gy=%.2e gs=%.2e %s" %
+              (rank, dtype, N, el, egx, egy, egl, "OK" if good else "FAIL"), flush=True)
+        ok = ok and good
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()

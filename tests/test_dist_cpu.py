@@ -70,3 +70,70 @@ def test_sharded_clip_world2_gloo(eps, ls):
         assert (gx - rx[sl]).norm() < 1e-4 * rx[sl].norm()
         assert (gy - ry[sl]).norm() < 1e-4 * ry[sl].norm()
         assert abs(gl - float(rl)) <= 1e-4 * max(abs(float(rl)), 1e-6)
+
+
+def _worker_align(rank, world, port, q, semantic, n, d, dsem):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import cpu_backend
+        from multimodal_2025_b200.dist import ShardedAlignClipLoss, ShardedClipInModalityLoss
+        from oracle import losses_oracle as O
+        x, y = O.synth_embeddings(n * world, d, 11, correlated=True)
+        sem = torch.randn(n * world, dsem, generator=torch.Generator().manual_seed(4))
+        sl = slice(rank * n, (rank + 1) * n)
+        xl = x[sl].clone().requires_grad_(True)
+        yl = y[sl].clone().requires_grad_(True)
+        sc = torch.tensor(14.285, requires_grad=True)
+        crit = ShardedClipInModalityLoss(alpha=1.0, beta=0.5, nl_semantic_supervision=semantic,
+                                         separate_image=semantic, backend=cpu_backend)
+        out = crit(xl, yl, sc, output_dict=True, semantic_features=sem[sl] if semantic else None)
+        out["total_loss"].backward()
+        plain = ShardedAlignClipLoss(backend=cpu_backend)(xl.detach(), yl.detach(), sc.detach())
+        q.put((rank, float(out["total_loss"].detach()), float(out["clip_loss"].detach()),
+               float(out["inModality_loss"].detach()), xl.grad.clone(), yl.grad.clone(),
+               float(sc.grad), float(plain)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("semantic", [True, False])
+def test_sharded_alignclip_world2_gloo(semantic):
+    """ShardedClipInModalityLoss / ShardedAlignClipLoss on 2 ranks against the single-process
+    oracle on the concatenated batch (reference loss.py:221-273 restated in oracle/)."""
+    from oracle import losses_oracle as O
+    world, n, d, dsem = 2, 40, 24, 12
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_align, args=(r, world, port, q, semantic, n, d, dsem))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    x, y = O.synth_embeddings(n * world, d, 11, correlated=True)
+    sem = torch.randn(n * world, dsem, generator=torch.Generator().manual_seed(4))
+    s = torch.tensor(14.285)
+    fn = lambda a, b, c: O.inmodality_loss(a, b, c, sem if semantic else None,  # noqa: E731
+                                           nl_semantic_supervision=semantic,
+                                           separate_image=semantic)
+    tot, clip, inm = fn(x, y, s)
+    ref, (rx, ry, rs) = O.loss_and_grads(lambda a, b, c: fn(a, b, c)[0], [x, y, s])
+    oc = O.openclip_loss(x, y, s)
+    for rank, ltot, lclip, linm, gx, gy, gs, lplain in res:
+        assert abs(ltot - float(tot)) < 1e-5 * abs(float(tot))
+        assert abs(lclip - float(clip)) < 1e-5 * abs(float(clip))
+        # CE(s I I^T) ~ 3e-3 is a difference of O(10) fp32 terms: absolute floor 1e-6
+        assert abs(linm - float(inm)) < 1e-5 * abs(float(inm)) + 1e-6
+        assert abs(lplain - float(oc)) < 1e-5 * abs(float(oc))
+        sl = slice(rank * n, (rank + 1) * n)
+        assert (gx - rx[sl]).norm() < 1e-4 * rx[sl].norm()
+        assert (gy - ry[sl]).norm() < 1e-4 * ry[sl].norm()
+        assert abs(gs - float(rs)) <= 1e-4 * max(abs(float(rs)), 1e-6)
