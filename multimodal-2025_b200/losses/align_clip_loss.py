@@ -75,7 +75,8 @@ class _ModulatedCEFn(torch.autograd.Function):
 
 
 class ClipLoss(nn.Module):
-    """open_clip-style CLIP loss (reference AlignCLIP/align_clip/loss.py:67-132), world_size 1."""
+    """open_clip-style CLIP loss (reference AlignCLIP/align_clip/loss.py:67-132); world_size > 1
+    delegates to dist.ShardedAlignClipLoss (needs an initialised process group)."""
 
     def __init__(self, local_loss=False, gather_with_grad=False, cache_labels=False, rank=0,
                  world_size=1, use_horovod=False):
@@ -90,16 +91,19 @@ class ClipLoss(nn.Module):
     def forward(self, image_features, text_features, logit_scale, output_dict=False,
                 semantic_features=None):
         if self.world_size > 1:
-            raise NotImplementedError(
-                "world_size > 1: use multimodal_2025_b200.dist.ShardedClipLoss (the reference's "
-                "gather path is not wired, SURVEY §0.3)")
+            # global-batch loss from the local shards (what gather_with_grad=True,
+            # local_loss=False computes, loss.py:103-114) on the default process group
+            from ..dist import ShardedAlignClipLoss
+            return ShardedAlignClipLoss()(image_features, text_features, logit_scale,
+                                          output_dict=output_dict)
         logit_scale = _as_scale(logit_scale, image_features)
         clip_loss = _ce_pair(image_features, text_features, logit_scale)
         return {"contrastive_loss": clip_loss} if output_dict else clip_loss
 
 
 class ClipInModalityLoss(nn.Module):
-    """reference AlignCLIP/align_clip/loss.py:135-273 (single-process branch)."""
+    """reference AlignCLIP/align_clip/loss.py:135-273; world_size > 1 delegates to
+    dist.ShardedClipInModalityLoss."""
 
     def __init__(self, local_loss=False, gather_with_grad=False, cache_labels=False, rank=0,
                  world_size=1, use_horovod=False, alpha=1.0, beta=0.5, n_epoch=30,
@@ -120,8 +124,13 @@ class ClipInModalityLoss(nn.Module):
     def forward(self, image_features, text_features, logit_scale, output_dict=False,
                 semantic_features=None):
         if self.world_size > 1:
-            raise NotImplementedError("world_size > 1 is not wired in the reference either "
-                                      "(SURVEY §0.3)")
+            # the reference's own branch never gathers the semantic features; the
+            # sharded module evaluates the single-process formula on the concatenated batch
+            from ..dist import ShardedClipInModalityLoss
+            crit = ShardedClipInModalityLoss(self.alpha, self.beta, self.nl_semantic_supervision,
+                                             self.separate_text, self.separate_image)
+            return crit(image_features, text_features, logit_scale, output_dict=output_dict,
+                        semantic_features=semantic_features)
         logit_scale = _as_scale(logit_scale, image_features)
         if self.nl_semantic_supervision:
             if semantic_features is None:
