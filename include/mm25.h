@@ -192,6 +192,19 @@ int mm25_sim_bwd_rs(const void* a, const void* b, int dtype, int64_t M, int64_t 
                     size_t workspace_bytes, float dot_bound, void* e_keep, const int* e_flag,
                     void* stream);
 
+/* Hopfield-retrieval backward on the tensor cores (cloobLoss.py:43-47; O = softmax(beta Q K^T) K):
+ * q [M,d], k [N,d] bf16; d_o [M,d] fp32 = dL/dO; lse [M] = LSE_j beta q_i.k_j (mm25_sim_fwd row
+ * LSE); delta [M] = d_o_i . O_i (mm25_rowdot); beta: device scalar.  Writes dq [M,d] and/or
+ * dk [N,d] fp32 (NULL to skip).  One sweep with two TMEM accumulators (Q K^T and dO K^T) emits
+ * the bf16 panels dZ = beta P (dP - delta) and P; dQ = dZ K, dK = dZ^T Q + P^T dO follow on the
+ * grouped GEMM.  Eligible: M % 128 == 0, N % 256 == 0, d % 256 == 0, d <= 1024 (workspace query
+ * returns 0 otherwise; use mm25_hopfield_bwd_pass then). */
+size_t mm25_hopfield_bwd_tc_workspace_bytes(int64_t M, int64_t N, int64_t d);
+int mm25_hopfield_bwd_tc(const void* q, const void* k, const float* d_o, int64_t M, int64_t N,
+                         int64_t d, const float* beta, const float* lse, const float* delta,
+                         float* dq, float* dk, void* workspace, size_t workspace_bytes,
+                         void* stream);
+
 /* Deterministic fixed-order sum of n fp32 values into out[0] (one CTA). out = alpha * sum. */
 int mm25_sum_parts(const float* parts, int64_t n, float alpha, float* out, void* stream);
 

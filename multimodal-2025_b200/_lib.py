@@ -124,6 +124,9 @@ SIGNATURES = {
     "mm25_rowdot": (_int, [_vp, _vp, _vp, _i64, _i64, _vp]),
     "mm25_hopfield_bwd_pass": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _vp,
                                       _vp, _int, _vp, _vp]),
+    "mm25_hopfield_bwd_tc_workspace_bytes": (_sz, [_i64, _i64, _i64]),
+    "mm25_hopfield_bwd_tc": (_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp,
+                                    _sz, _vp]),
     "mm25_sum_parts": (_int, [_vp, _i64, _f32, _vp, _vp]),
     "mm25_col_merge": (_int, [_vp, _vp, _i64, _i64, _vp, _vp]),
     "mm25_clip_loss_finalize": (_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp,

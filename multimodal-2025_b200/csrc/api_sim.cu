@@ -79,8 +79,10 @@ extern "C" int mm25_sim_fwd(const void* a, const void* b, int dtype, const float
   g_last_path = t ? 1 : 0;
   if (t)
     return tc::launch_fwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
-                          col_max, col_sum, diag, workspace, workspace_bytes, dot_bound, e_keep,
-                          e_flag, st);
+                          col_max, col_sum, diag, workspace, workspace_bytes, dot_bound,
+                          mode == MM25_SIM_MASKDIAG ? nullptr : e_keep,
+                          mode == MM25_SIM_MASKDIAG ? nullptr : e_flag, st,
+                          mode == MM25_SIM_MASKDIAG);
   // the SIMT kernels keep nothing: tell the backward to recompute
   if (e_flag) MM25_CUDA_CHECK(cudaMemsetAsync(e_flag, 0, sizeof(int), st));
   return simt::launch_fwd(a, b, dtype, u, v, diag_add, B, M, N, d, d2, scale, scale_kind,
@@ -153,8 +155,10 @@ static int sim_bwd_impl(const void* a, const void* b, int dtype, const float* u,
   if (t)
     return tc::launch_bwd(a, b, B, M, N, d, scale, scale_kind, clamp_max, diag_offset, row_lse,
                           col_lse, w_row, w_col, w_diag, w_all, gout, da, db, dscale_part,
-                          workspace, workspace_bytes, dot_bound, db_peers, npeers, e_keep, e_flag,
-                          st);
+                          workspace, workspace_bytes, dot_bound, db_peers, npeers,
+                          mode == MM25_SIM_MASKDIAG ? nullptr : e_keep,
+                          mode == MM25_SIM_MASKDIAG ? nullptr : e_flag, st,
+                          mode == MM25_SIM_MASKDIAG);
   if (db_peers) return MM25_ERR_SHAPE;  // the fused reduce-scatter exists on the tcgen05 path only
   int rc = MM25_OK;
   if (da) {

@@ -62,6 +62,11 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const float s = load_scale(scale, scale_kind, clamp_max);
     const float c2 = s * LOG2E;
     const float m2s = dot_bound * fabsf(c2);
+    // force_slow carries two flags: bit 0 = test hook (robust epilogue), bit 1 = MASKDIAG mode
+    // (InfoLOOB, cloobLoss.py:28-31: the positive enters the LSE as the constant -10000)
+    const bool mask_diag = (force_slow & 2) != 0;
+    force_slow &= 1;
+    const float vmask = s != 0.f ? -10000.f / s : 0.f;
     const bool fast_static = !force_slow && dot_bound > 0.f && 2.f * m2s <= SPREAD_LIMIT;
     // E = 2^(z log2e - m2s) in bf16 is kept for the backward (static shift only): it replaces
     // the S-tile recompute there.  e_flag tells the backward whether E is valid.
@@ -101,6 +106,10 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll
               for (int j = 0; j < 32; ++j) dv = (j == rel) ? v[j] : dv;
               if (rel >= 0 && rel < 32) diag[(int64_t)bz * M + row] = s * dv;
+              if (mask_diag) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = (j == rel) ? vmask : v[j];
+              }
             }
           }
           float e[32];
@@ -327,7 +336,7 @@ static int sm_count() {
 }
 
 bool eligible_fwd(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode) {
-  return dtype == MM25_BF16 && mode == MM25_SIM_PLAIN && d % BK == 0 && d >= BK &&
+  return dtype == MM25_BF16 && (mode == MM25_SIM_PLAIN || mode == MM25_SIM_MASKDIAG) && d % BK == 0 && d >= BK &&
          d <= MAX_KC * BK && M % BM == 0 && N % BN == 0 && NEPI * 32 == BN && B * M < (1ll << 31) &&
          B * N < (1ll << 31);
 }
@@ -370,7 +379,9 @@ void set_force_slow(int v) { g_force_slow = v; }
 int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,
                const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
                float* row_lse, float* col_max, float* col_sum, float* diag, void* ws,
-               size_t ws_bytes, float dot_bound, void* e_out, int* e_flag, cudaStream_t st) {
+               size_t ws_bytes, float dot_bound, void* e_out, int* e_flag, cudaStream_t st,
+               int mask_diag) {
+  if (mask_diag && e_out) return MM25_ERR_ARG;
   if (!eligible_fwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)) return MM25_ERR_SHAPE;
   if ((e_out == nullptr) != (e_flag == nullptr)) return MM25_ERR_ARG;
   if (ws_bytes < fwd_workspace_bytes(B, M, N, d)) return MM25_ERR_WORKSPACE;
@@ -394,7 +405,8 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   sim_fwd_tc_kernel<<<g.grid, FWD_THREADS, smem, st>>>(
       ta, tb, te, e_out ? 1 : 0, e_flag, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind, clamp_max,
-      diag_offset, row_pm, row_pl, col_pm, col_pl, diag, g_force_slow, dot_bound);
+      diag_offset, row_pm, row_pl, col_pm, col_pl, diag, g_force_slow | (mask_diag ? 2 : 0),
+      dot_bound);
   MM25_LAUNCH_CHECK();
   const int64_t mx = M > N ? M : N;
   fwd_tc_merge_kernel<<<dim3((unsigned)ceil_div(mx, 32), (unsigned)B), 1024, 0, st>>>(

@@ -17,7 +17,8 @@ size_t fwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d);
 int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, int64_t d,
                const float* scale, int scale_kind, float clamp_max, int64_t diag_offset,
                float* row_lse, float* col_max, float* col_sum, float* diag, void* ws,
-               size_t ws_bytes, float dot_bound, void* e_out, int* e_flag, cudaStream_t st);
+               size_t ws_bytes, float dot_bound, void* e_out, int* e_flag, cudaStream_t st,
+               int mask_diag = 0);
 
 // `e_buf` (optional, [B, M, N] bf16 + flag written by launch_fwd): E = 2^(z log2e - m) kept by
 // the forward; the backward then forms G' from it in place (no S-tile recompute) and needs no
@@ -30,7 +31,7 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                float w_diag, float w_all, const float* gout, float* da, float* db,
                float* dscale_part, void* ws, size_t ws_bytes, float dot_bound,
                float* const* db_peers, int npeers, void* e_buf, const int* e_flag,
-               cudaStream_t st);
+               cudaStream_t st, int mask_diag = 0);
 
 }  // namespace tc
 

@@ -50,7 +50,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                    float w_row, float w_col, float w_diag, float w_all,
                    const float* __restrict__ gout, float* __restrict__ dscale_part,
                    const float* __restrict__ Cc, float dot_bound,
-                   const int* __restrict__ skip_flag) {
+                   const int* __restrict__ skip_flag, int mask_diag) {
   // the forward kept E (grad_from_e_kernel already formed G' from it): nothing to recompute
   if (skip_flag && *skip_flag) return;
   extern __shared__ uint8_t smem_raw[];
@@ -79,6 +79,8 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const float m2 = dot_bound * fabsf(c2);
     const bool fast = Cc != nullptr && dot_bound > 0.f && 2.f * m2 <= SPREAD_LIMIT;
     const float k_all = gs * w_all, k_diag = gs * w_diag;
+    const float vmask = s != 0.f ? -10000.f / s : 0.f;  // MASKDIAG: z_ii = -10000 in the LSE
+    const bool use_col = w_col != 0.f;  // row-only losses pass a placeholder col_lse
     // per-column operand of the epilogue: C_j (static shift) or c_j (general), staged per warp
     const float* colv = fast ? Cc : col_lse;
     float* ccw = sm.ccw[ew];
@@ -118,10 +120,19 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
           const int rel = (int)min((int64_t)64, max((int64_t)-1, dcol - cbase));
           const float4* cc4 = reinterpret_cast<const float4*>(ccw + chl * 32);
           uint32_t packed[16];
+          // warp-uniform: does this chunk cross the warp's positives?
+          const int64_t d0 = (int64_t)rb * BM + q * 32 + diag_offset;
+          const bool has_diag = (d0 + 31 >= cbase) && (d0 < cbase + 32);
+          if (mask_diag && has_diag) {
+            // the masked positive contributes no softmax mass; d/ds keeps the true logit
+            // (sim_simt.cu: glse = 0, base unchanged), so correct `ds` for the substitution
+            float vo = vmask;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j == rel) { vo = __uint_as_float(r[j]); r[j] = __float_as_uint(vmask); }
+            ds = fmaf(fast ? -(k_all + k_diag) : -(w_all + w_diag), vo - vmask, ds);
+          }
           if (fast) {
-            // warp-uniform: does this chunk cross the warp's positives?
-            const int64_t d0 = (int64_t)rb * BM + q * 32 + diag_offset;
-            const bool has_diag = (d0 + 31 >= cbase) && (d0 < cbase + 32);
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4) {
               const float4 cc = cc4[j4];
@@ -153,8 +164,8 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const int j = j4 * 4 + u;
                 const float vj = __uint_as_float(r[j]);
                 const float zl = vj * c2;
-                float gg = w_row * ex2_approx(zl - r2) +
-                           w_col * ex2_approx(fmaf(-cj[u], LOG2E, zl));
+                float gg = w_row * ex2_approx(zl - r2);
+                if (use_col) gg += w_col * ex2_approx(fmaf(-cj[u], LOG2E, zl));
                 gg -= w_all;
                 gg -= (j == rel) ? w_diag : 0.f;
                 ds = fmaf(gg, vj, ds);
@@ -350,21 +361,23 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                float w_diag, float w_all, const float* gout, float* da, float* db,
                float* dscale_part, void* ws, size_t ws_bytes, float dot_bound,
                float* const* db_peers, int npeers, void* e_buf, const int* e_flag,
-               cudaStream_t st) {
+               cudaStream_t st, int mask_diag) {
   if (!eligible_bwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)) return MM25_ERR_SHAPE;
+  if (mask_diag && e_buf) return MM25_ERR_ARG;
   if (db_peers && (B != 1 || npeers < 1 || N % npeers != 0)) return MM25_ERR_SHAPE;
-  if (!col_lse) return MM25_ERR_ARG;
+  if (!col_lse && w_col != 0.f) return MM25_ERR_ARG;
   if ((e_buf == nullptr) != (e_flag == nullptr)) return MM25_ERR_ARG;
   // kept-E path: the scale gradient comes from a . dA (or b . dB), so one of them must exist
   const bool use_e = e_buf && dot_bound > 0.f && (!dscale_part || da || (db && !db_peers));
   if (ws_bytes < bwd_workspace_bytes(B, M, N, d, use_e)) return MM25_ERR_WORKSPACE;
   const uintptr_t ws0 = (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255);
   const int64_t R = use_e ? M : panel_rows(M, N);
-  float* Cc = nullptr;
-  if (dot_bound > 0.f) {
-    Cc = reinterpret_cast<float*>(
-        use_e ? ws0 : ((ws0 + (size_t)R * (size_t)N * 2 + 255) & ~uintptr_t(255)));
-  }
+  // [N] floats after the panel: the column factors C_j of the static-shift path; for row-only
+  // losses (col_lse = NULL, w_col = 0) also the placeholder the kernel's column loads read
+  float* cbuf = reinterpret_cast<float*>(
+      use_e ? ws0 : ((ws0 + (size_t)R * (size_t)N * 2 + 255) & ~uintptr_t(255)));
+  float* Cc = dot_bound > 0.f ? cbuf : nullptr;
+  if (!col_lse) MM25_CUDA_CHECK(cudaMemsetAsync(cbuf, 0, sizeof(float) * N, st));
   const int sms = tc_sm_count();
   const size_t smem = sizeof(GradSmem) + 1024;
   MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_grad_tc_kernel,
@@ -382,7 +395,7 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
     if (rc) return rc;
     rc = make_tmap_bf16(&tb, b_b, (uint64_t)N, (uint64_t)d, BN, BK);
     if (rc) return rc;
-    if (Cc) {
+    if (Cc && col_lse) {
       grad_col_coef_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(
           col_lse + bz * N, N, scale, scale_kind, clamp_max, gout ? gout + bz : nullptr, w_col,
           dot_bound, Cc);
@@ -425,9 +438,10 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
       if (rc) return rc;
       sim_grad_tc_kernel<<<grid, FWD_THREADS, smem, st>>>(
           ta, tb, tg, M, N, (int)d, (int)(p0 / BM), num_rb, nseg, tps, scale, scale_kind, clamp_max,
-          diag_offset, row_lse + bz * M, col_lse + bz * N, w_row, w_col, w_diag, w_all,
+          diag_offset, row_lse + bz * M, col_lse ? col_lse + bz * N : cbuf, w_row, w_col, w_diag,
+          w_all,
           gout ? gout + bz : nullptr, dscale_part ? dscale_part + part : nullptr, Cc,
-          dot_bound, use_e ? e_flag : nullptr);
+          dot_bound, use_e ? e_flag : nullptr, mask_diag);
       MM25_LAUNCH_CHECK();
       part += sms;
       {

@@ -36,6 +36,7 @@ struct ModSmem {
   uint8_t a[MNST][MT_BYTES];
   uint8_t b[MNST][MT_BYTES];
   uint8_t stage[MNEPI][2048];  // bf16 G'' chunk of each warp (32 rows x 64 B, 64B swizzle)
+  uint8_t stage2[MNEPI][2048];  // second panel (Hopfield: P)
   float red[MNEPI];
   uint64_t full[MNST], empty[MNST];
   uint64_t acc_full[MNACC], acc_empty[MNACC];
@@ -46,13 +47,20 @@ struct ModGeom {
   int KC1, KC2, ntiles, nseg, tps, first_rb, num_rb;
 };
 
-template <bool GRAD>
+// EPI 0: MODULATED forward; 1: MODULATED gradient panel; 2: Hopfield-retrieval gradient panels
+// (cloobLoss.py:43-47 backward: a = Q, b = K, u = dO, v = K, so the second accumulator is
+// dP = dO K^T; row_lse = LSE_j beta q.k_j, diag_add = delta_i = dO_i . O_i;
+// panel 1 = dZ = beta P (dP - delta), panel 2 = P).
+constexpr int EPI_FWD = 0, EPI_GRAD = 1, EPI_HOPF = 2;
+
+template <int EPI>
 __global__ void __launch_bounds__(MTHREADS, 1)
 sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                   const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_u,
                   const __grid_constant__ CUtensorMap tmap_v,
-                  const __grid_constant__ CUtensorMap tmap_g, ModGeom g, int64_t M, int64_t N,
+                  const __grid_constant__ CUtensorMap tmap_g,
+                  const __grid_constant__ CUtensorMap tmap_p, ModGeom g, int64_t M, int64_t N,
                   const float* __restrict__ scale, int scale_kind, float clamp_max,
                   int64_t diag_offset, const float* __restrict__ diag_add,
                   // forward outputs: partial (max, sum) per (segment, half) and the positives
@@ -62,6 +70,7 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                   const float* __restrict__ row_lse, float w_row, float w_diag, float w_all,
                   const float* __restrict__ gout, float* __restrict__ dscale_part,
                   float* __restrict__ ddiag) {
+  constexpr bool GRAD = EPI != EPI_FWD;
   extern __shared__ uint8_t smem_raw[];
   ModSmem& sm = *reinterpret_cast<ModSmem*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -155,6 +164,8 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const uint32_t st_row = smem_u32(stage) + lane * 64;
     const uint32_t st_xor = (lane >> 1) & 3;
     if (GRAD && lane == 0) tma_prefetch_desc(&tmap_g);
+    if (EPI == EPI_HOPF && lane == 0) tma_prefetch_desc(&tmap_p);
+    const uint32_t st2_row = smem_u32(sm.stage2[ew]) + lane * 64;
     float ds = 0.f;
     uint32_t as = 0, accph = 0;
     for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
@@ -179,6 +190,46 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
           tmem_ld_wait(rv);
           tmem_ld_wait(rw);
           const int64_t cbase = col0 + half * 64 + c * 32;
+          if (EPI == EPI_HOPF) {
+            uint32_t pz[16], pp[16];
+#pragma unroll
+            for (int j2 = 0; j2 < 16; ++j2) {
+              float zq[2], pq[2];
+#pragma unroll
+              for (int u = 0; u < 2; ++u) {
+                const int j = 2 * j2 + u;
+                const float p = ex2_approx(fmaf(__uint_as_float(rv[j]), c2, -r2));
+                pq[u] = p;
+                zq[u] = s * p * (__uint_as_float(rw[j]) - Di);
+              }
+              __nv_bfloat162 hz = __floats2bfloat162_rn(zq[0], zq[1]);
+              __nv_bfloat162 hp = __floats2bfloat162_rn(pq[0], pq[1]);
+              pz[j2] = *reinterpret_cast<uint32_t*>(&hz);
+              pp[j2] = *reinterpret_cast<uint32_t*>(&hp);
+            }
+            if (lane == 0) tma_store_wait_read<0>();
+            __syncwarp();
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const uint32_t off = (u ^ st_xor) << 4;
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(st_row + off),
+                           "r"(pz[4 * u]), "r"(pz[4 * u + 1]), "r"(pz[4 * u + 2]),
+                           "r"(pz[4 * u + 3])
+                           : "memory");
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(st2_row + off),
+                           "r"(pp[4 * u]), "r"(pp[4 * u + 1]), "r"(pp[4 * u + 2]),
+                           "r"(pp[4 * u + 3])
+                           : "memory");
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmap_g, stage, (int32_t)cbase, grow0);
+              tma_store_2d(&tmap_p, sm.stage2[ew], (int32_t)cbase, grow0);
+              tma_store_commit();
+            }
+            continue;
+          }
           const int rel = (int)min((int64_t)64, max((int64_t)-1, dcol - cbase));
           float base[32];
 #pragma unroll
@@ -187,7 +238,7 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
             base[j] = __uint_as_float(rv[j]) * (1.f - wv);
             if (j == rel) base[j] += Di;
           }
-          if (!GRAD) {
+          if (EPI == EPI_FWD) {
             if (rel >= 0 && rel < 32) {
               float dv = 0.f;
 #pragma unroll
@@ -246,7 +297,7 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         if (lane == 0) mbar_arrive(&sm.acc_empty[as]);
         if (++as == MNACC) { as = 0; accph ^= 1; }
       }
-      if (!GRAD) {
+      if (EPI == EPI_FWD) {
         const int64_t o = ((int64_t)seg * 2 + half) * M + row;
         row_pm[o] = rm;
         row_pl[o] = rl;
@@ -254,6 +305,8 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     if (GRAD) {
       if (lane == 0) tma_store_wait_all<0>();
+    }
+    if (EPI == EPI_GRAD) {
       ds = warp_sum(ds) * go;
       if (lane == 0) sm.red[ew] = ds;
       named_bar_sync(1, 32 * MNEPI);
@@ -395,14 +448,14 @@ int launch_fwd(const void* a, const void* b, const float* u, const float* v,
   if ((rc = make_tmap_bf16(&tu, p.ub, (uint64_t)M, (uint64_t)d2, MBM, MBK))) return rc;
   if ((rc = make_tmap_bf16(&tv, p.vb, (uint64_t)N, (uint64_t)d2, MBN, MBK))) return rc;
   const size_t smem = sizeof(ModSmem) + 1024;
-  MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_mod_tc_kernel<false>,
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_mod_tc_kernel<EPI_FWD>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long items = (long)g.num_rb * g.nseg;
   const int grid = (int)(items < sms ? items : sms);
   // rows whose positive lies outside [0, N) keep diag = 0
   MM25_CUDA_CHECK(cudaMemsetAsync(diag, 0, sizeof(float) * M, st));
-  sim_mod_tc_kernel<false><<<grid, MTHREADS, smem, st>>>(
-      ta, tb, tu, tv, ta, g, M, N, scale, scale_kind, clamp_max, diag_offset, diag_add, row_pm,
+  sim_mod_tc_kernel<EPI_FWD><<<grid, MTHREADS, smem, st>>>(
+      ta, tb, tu, tv, ta, ta, g, M, N, scale, scale_kind, clamp_max, diag_offset, diag_add, row_pm,
       row_pl, diag, nullptr, 0.f, 0.f, 0.f, nullptr, nullptr, nullptr);
   MM25_LAUNCH_CHECK();
   mod_row_merge_kernel<<<(unsigned)ceil_div(M, 256), 256, 0, st>>>(row_pm, row_pl, 2 * g.nseg, M,
@@ -431,7 +484,7 @@ int launch_bwd(const void* a, const void* b, const float* u, const float* v,
   if ((rc = make_tmap_bf16(&tu, p.ub, (uint64_t)M, (uint64_t)d2, MBM, MBK))) return rc;
   if ((rc = make_tmap_bf16(&tv, p.vb, (uint64_t)N, (uint64_t)d2, MBN, MBK))) return rc;
   const size_t smem = sizeof(ModSmem) + 1024;
-  MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_mod_tc_kernel<true>,
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_mod_tc_kernel<EPI_GRAD>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (ddiag) MM25_CUDA_CHECK(cudaMemsetAsync(ddiag, 0, sizeof(float) * M, st));
   const __nv_bfloat16* ab = (const __nv_bfloat16*)a;
@@ -448,8 +501,8 @@ int launch_bwd(const void* a, const void* b, const float* u, const float* v,
     if (dscale_part) MM25_CUDA_CHECK(cudaMemsetAsync(dscale_part + part, 0, sizeof(float) * sms, st));
     CUtensorMap tg;
     if ((rc = make_tmap_bf16(&tg, G, (uint64_t)rows, (uint64_t)N, 32, 32, 64))) return rc;
-    sim_mod_tc_kernel<true><<<grid, MTHREADS, smem, st>>>(
-        ta, tb, tu, tv, tg, g, M, N, scale, scale_kind, clamp_max, diag_offset, diag_add, nullptr,
+    sim_mod_tc_kernel<EPI_GRAD><<<grid, MTHREADS, smem, st>>>(
+        ta, tb, tu, tv, tg, tg, g, M, N, scale, scale_kind, clamp_max, diag_offset, diag_add, nullptr,
         nullptr, nullptr, row_lse, w_row, w_diag, w_all, gout,
         dscale_part ? dscale_part + part : nullptr, ddiag);
     MM25_LAUNCH_CHECK();
@@ -462,5 +515,93 @@ int launch_bwd(const void* a, const void* b, const float* u, const float* v,
   return MM25_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// Hopfield retrieval backward on the tensor cores (cloobLoss.py:43-47, O = softmax(beta Q K^T) K):
+//   dP = dO K^T,  dZ = beta P o (dP - delta_i),  dQ = dZ K,  dK = dZ^T Q + P^T dO.
+// One dual-accumulator sweep writes the bf16 panels dZ and P; three GEMMs follow (two grouped).
+// ------------------------------------------------------------------------------------------
+static int64_t hopf_panel_rows(int64_t M, int64_t N) {
+  int64_t r = (int64_t)(g_panel_cap / ((size_t)N * 4)) / MBM * MBM;  // two bf16 panels
+  if (r < MBM) r = MBM;
+  return r > M ? M : r;
+}
+
+bool hopfield_eligible(int64_t M, int64_t N, int64_t d) {
+  return eligible(1, M, N, d, d, MM25_BF16, true);
+}
+
+size_t hopfield_workspace_bytes(int64_t M, int64_t N, int64_t d) {
+  return 256 + align256((size_t)M * d * 2) +
+         2 * align256((size_t)hopf_panel_rows(M, N) * (size_t)N * 2);
+}
+
+int launch_hopfield_bwd(const void* q, const void* k, const float* d_o, int64_t M, int64_t N,
+                        int64_t d, const float* beta, const float* lse, const float* delta,
+                        float* dq, float* dk, void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (!hopfield_eligible(M, N, d)) return MM25_ERR_SHAPE;
+  if (ws_bytes < hopfield_workspace_bytes(M, N, d)) return MM25_ERR_WORKSPACE;
+  uintptr_t w0 = (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255);
+  __nv_bfloat16* dob = reinterpret_cast<__nv_bfloat16*>(w0);
+  w0 += align256((size_t)M * d * 2);
+  const int64_t R = hopf_panel_rows(M, N);
+  __nv_bfloat16* GZ = reinterpret_cast<__nv_bfloat16*>(w0);
+  __nv_bfloat16* GP = reinterpret_cast<__nv_bfloat16*>(w0 + align256((size_t)R * (size_t)N * 2));
+  cast_bf16_kernel<<<(unsigned)ceil_div(M * d, 1024), 256, 0, st>>>(d_o, dob, M * d);
+  MM25_LAUNCH_CHECK();
+  const int sms = tc::tc_sm_count();
+  CUtensorMap ta, tb, tu;
+  int rc;
+  if ((rc = make_tmap_bf16(&ta, q, (uint64_t)M, (uint64_t)d, MBM, MBK))) return rc;
+  if ((rc = make_tmap_bf16(&tb, k, (uint64_t)N, (uint64_t)d, MBN, MBK))) return rc;
+  if ((rc = make_tmap_bf16(&tu, dob, (uint64_t)M, (uint64_t)d, MBM, MBK))) return rc;
+  const size_t smem = sizeof(ModSmem) + 1024;
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_mod_tc_kernel<EPI_HOPF>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const __nv_bfloat16* qb = (const __nv_bfloat16*)q;
+  const __nv_bfloat16* kb = (const __nv_bfloat16*)k;
+  for (int64_t p0 = 0; p0 < M; p0 += R) {
+    const int64_t rows = (M - p0 < R) ? (M - p0) : R;
+    ModGeom g;
+    g.KC1 = g.KC2 = (int)(d / MBK); g.ntiles = (int)(N / MBN);
+    g.first_rb = (int)(p0 / MBM); g.num_rb = (int)(rows / MBM);
+    pick_segments(g.num_rb, g.ntiles, sms, &g.nseg, &g.tps);
+    const long items = (long)g.num_rb * g.nseg;
+    const int grid = (int)(items < sms ? items : sms);
+    CUtensorMap tg, tp;
+    if ((rc = make_tmap_bf16(&tg, GZ, (uint64_t)rows, (uint64_t)N, 32, 32, 64))) return rc;
+    if ((rc = make_tmap_bf16(&tp, GP, (uint64_t)rows, (uint64_t)N, 32, 32, 64))) return rc;
+    sim_mod_tc_kernel<EPI_HOPF><<<grid, MTHREADS, smem, st>>>(
+        ta, tb, tu, tb, tg, tp, g, M, N, beta, MM25_SCALE_MUL, 0.f, 0, delta, nullptr, nullptr,
+        nullptr, lse, 0.f, 0.f, 0.f, nullptr, nullptr, nullptr);
+    MM25_LAUNCH_CHECK();
+    // dQ[panel] = dZ K  and  dK (+)= dZ^T Q[panel]  in one grouped launch, then dK += P^T dO
+    GemmDesc ga{GZ, kb, dq ? dq + p0 * d : nullptr, d, rows, N, 0, 1, 0, 1.f, nullptr, 0, 0};
+    GemmDesc gb{GZ, qb + p0 * d, dk, d, N, rows, 1, 1, p0 > 0 ? 1 : 0, 1.f, nullptr, 0, 0};
+    rc = gemm_grouped(dq ? &ga : nullptr, dk ? &gb : nullptr, d, nullptr, st);
+    if (rc) return rc;
+    if (dk) {
+      GemmDesc gc{GP, dob + p0 * d, dk, d, N, rows, 1, 1, 1, 1.f, nullptr, 0, 0};
+      rc = gemm_grouped(nullptr, &gc, d, nullptr, st);
+      if (rc) return rc;
+    }
+  }
+  return MM25_OK;
+}
+
 }  // namespace tcm
 }  // namespace mm25
+
+extern "C" size_t mm25_hopfield_bwd_tc_workspace_bytes(int64_t M, int64_t N, int64_t d) {
+  if (!mm25::tcm::hopfield_eligible(M, N, d)) return 0;
+  return mm25::tcm::hopfield_workspace_bytes(M, N, d);
+}
+
+extern "C" int mm25_hopfield_bwd_tc(const void* q, const void* k, const float* d_o, int64_t M,
+                                    int64_t N, int64_t d, const float* beta, const float* lse,
+                                    const float* delta, float* dq, float* dk, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  if (!q || !k || !d_o || !beta || !lse || !delta || !workspace) return MM25_ERR_ARG;
+  if (!dq && !dk) return MM25_OK;
+  return mm25::tcm::launch_hopfield_bwd(q, k, d_o, M, N, d, beta, lse, delta, dq, dk, workspace,
+                                        workspace_bytes, (cudaStream_t)stream);
+}

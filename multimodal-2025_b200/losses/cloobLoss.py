@@ -18,12 +18,49 @@ def _scalar(v, dev):
     return torch.tensor([float(v)], dtype=torch.float32, device=dev)
 
 
+def _tc_operands(x, y):
+    """bf16 copies for the tensor-core kernels when the inputs are bf16 (or COMPUTE_DTYPE asks
+    for it) and the shape is eligible; else None (fp32 SIMT kernels, the reference's dtype)."""
+    want = (x.dtype == torch.bfloat16 and y.dtype == torch.bfloat16) or \
+        COMPUTE_DTYPE == torch.bfloat16
+    if not (want and x.is_cuda):
+        return None
+    xb = x.detach().to(torch.bfloat16).contiguous()
+    yb = y.detach().to(torch.bfloat16).contiguous()
+    return (xb, yb) if ops.hopfield_tc_eligible(xb, yb) and ops.hopfield_tc_eligible(yb, xb) \
+        else None
+
+
+# None: compute in fp32 on the SIMT kernels unless the inputs are bf16 (reference semantics, rel
+# 1e-5 / 1e-4).  torch.bfloat16: fp32 inputs are rounded to bf16 once per GEMM operand and run the
+# tcgen05 kernels (bf16 contract 2e-3 / 2e-2), as under torch.autocast(dtype=bfloat16).
+COMPUTE_DTYPE = None
+
+
 class _HopfieldFn(torch.autograd.Function):
     """U[Nq, d] = rownorm(softmax(beta Q K^T) K)."""
 
     @staticmethod
     def forward(ctx, q, k, beta):
         in_dtype = q.dtype
+        tc = _tc_operands(q, k)
+        if tc is not None:
+            # tensor cores: row LSE from the PLAIN sweep; O = P K from the gradient-panel kernel
+            # with w_row = 1 (bf16 P panel) and the grouped GEMM
+            qb, kb = tc
+            sc = _scalar(beta, q.device)
+            q3, k3 = qb.unsqueeze(0), kb.unsqueeze(0)
+            lse, _, _, _ = ops.sim_fwd(q3, k3, None, None, None, sc, ops.SCALE_MUL, 0.0,
+                                       ops.SIM_PLAIN, 0, False, ops.IMPL_TC)
+            o, _, _, _ = ops.sim_bwd(q3, k3, None, None, None, sc, ops.SCALE_MUL, 0.0,
+                                     ops.SIM_PLAIN, 0, lse, None, 1.0, 0.0, 0.0, 0.0, None, True,
+                                     False, False, ops.IMPL_TC)
+            o = o / float(beta)
+            u, inv, _ = ops.rownorm_fwd(o, True, 1e-30, ops.F32, False)
+            ctx.save_for_backward(qb, kb, o[0], u[0], inv, lse[0], sc)
+            ctx.beta, ctx.in_dtype, ctx.tc = float(beta), in_dtype, True
+            return u[0].to(in_dtype)
+        ctx.tc = False
         qf = q.detach().float().contiguous()
         kf = k.detach().float().contiguous()
         sc = _scalar(beta, q.device)
@@ -43,6 +80,15 @@ class _HopfieldFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, du):
+        if ctx.tc:
+            qb, kb, o, u, inv, lse, sc = ctx.saved_tensors
+            du = du.detach().float().contiguous()
+            do = ops.rownorm_bwd(du.unsqueeze(0), u.unsqueeze(0), inv, True, ops.F32, None)[0]
+            delta = ops.rowdot(do, o)
+            dq, dk = ops.hopfield_bwd_tc(qb, kb, do, sc, lse, delta, ctx.needs_input_grad[0],
+                                         ctx.needs_input_grad[1])
+            return (dq.to(ctx.in_dtype) if ctx.needs_input_grad[0] else None,
+                    dk.to(ctx.in_dtype) if ctx.needs_input_grad[1] else None, None)
         qf, kf, o, u, inv, lse = ctx.saved_tensors
         beta = ctx.beta
         du = du.detach().float().contiguous()
@@ -62,17 +108,23 @@ class _InfoLoobFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, y, inv_tau):
         in_dtype = x.dtype
-        xf = x.detach().float().contiguous().unsqueeze(0)
-        yf = y.detach().float().contiguous().unsqueeze(0)
+        tc = _tc_operands(x, y)
+        impl = ops.IMPL_SIMT if tc is None else ops.IMPL_TC
+        if tc is None:
+            xf = x.detach().float().contiguous().unsqueeze(0)
+            yf = y.detach().float().contiguous().unsqueeze(0)
+        else:
+            xf, yf = tc[0].unsqueeze(0), tc[1].unsqueeze(0)
         sc = _scalar(inv_tau, x.device)
         lse, _, _, diag = ops.sim_fwd(xf, yf, None, None, None, sc, ops.SCALE_MUL, 0.0,
-                                      ops.SIM_MASKDIAG, 0, False, ops.IMPL_SIMT)
+                                      ops.SIM_MASKDIAG, 0, False, impl)
         n = xf.shape[1]
         # -mean(diag) + mean(lse): one deterministic reduction kernel (weights 1/2n * 2)
         loss = ops.clip_loss_finalize(lse * 2.0, diag, None, None, None, n, sc, ops.SCALE_MUL,
                                       0.0, 0.0)
         ctx.save_for_backward(xf, yf, lse, sc)
         ctx.in_dtype = in_dtype
+        ctx.impl = impl
         return loss.reshape(())
 
     @staticmethod
@@ -83,7 +135,7 @@ class _InfoLoobFn(torch.autograd.Function):
         da, db, _, _ = ops.sim_bwd(xf, yf, None, None, None, sc, ops.SCALE_MUL, 0.0,
                                    ops.SIM_MASKDIAG, 0, lse, None, 1.0 / n, 0.0, 1.0 / n, 0.0,
                                    g, ctx.needs_input_grad[0], ctx.needs_input_grad[1], False,
-                                   ops.IMPL_SIMT)
+                                   ctx.impl)
         dx = da[0].to(ctx.in_dtype) if ctx.needs_input_grad[0] else None
         dy = db[0].to(ctx.in_dtype) if ctx.needs_input_grad[1] else None
         return dx, dy, None

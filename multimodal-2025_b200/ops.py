@@ -264,6 +264,40 @@ def hopfield_bwd_pass(a: Tensor, b: Tensor, a2: Tensor, b2: Tensor, bm1: Tensor,
     return out
 
 
+def hopfield_tc_eligible(q: Tensor, k: Tensor) -> bool:
+    """bf16 retrieval shapes the tensor-core Hopfield kernels take (include/mm25.h)."""
+    if q.dtype != torch.bfloat16 or k.dtype != torch.bfloat16 or not q.is_cuda:
+        return False
+    M, d = q.shape[-2], q.shape[-1]
+    N = k.shape[-2]
+    return int(_lib.lib().mm25_hopfield_bwd_tc_workspace_bytes(M, N, d)) > 0
+
+
+@torch.library.custom_op("mm25::hopfield_bwd_tc", mutates_args=(), device_types="cuda")
+def hopfield_bwd_tc(q: Tensor, k: Tensor, d_o: Tensor, beta: Tensor, lse: Tensor, delta: Tensor,
+                    need_dq: bool, need_dk: bool) -> Tuple[Tensor, Tensor]:
+    """Hopfield-retrieval backward on the tensor cores: (dq [M,d], dk [N,d]) fp32 from bf16 q, k,
+    fp32 dL/dO, the forward's row LSE and delta_i = dO_i . O_i (include/mm25.h)."""
+    q, k, d_o = q.contiguous(), k.contiguous(), d_o.contiguous()
+    M, d = q.shape
+    N = k.shape[0]
+    dev = q.device
+    L = _lib.lib()
+    with torch.cuda.device(dev):
+        dq = torch.empty((M, d) if need_dq else (0,), dtype=torch.float32, device=dev)
+        dk = torch.empty((N, d) if need_dk else (0,), dtype=torch.float32, device=dev)
+        wsb = int(L.mm25_hopfield_bwd_tc_workspace_bytes(M, N, d))
+        if wsb == 0:
+            raise _lib.MM25Error("mm25_hopfield_bwd_tc: shape not eligible (M %% 128, N %% 256, "
+                                 "d %% 256, d <= 1024): M=%d N=%d d=%d" % (M, N, d))
+        ws = torch.empty((wsb,), dtype=torch.uint8, device=dev)
+        rc = L.mm25_hopfield_bwd_tc(_p(q), _p(k), _p(d_o), M, N, d, _p(beta), _p(lse), _p(delta),
+                                    _p(dq) if need_dq else None, _p(dk) if need_dk else None,
+                                    _p(ws), ws.numel(), _stream(q))
+    _lib.check(rc, "mm25_hopfield_bwd_tc")
+    return dq, dk
+
+
 def scale_param_grad(dscale: Tensor, scale: Tensor, scale_kind: int, clamp_max: float) -> Tensor:
     """Chain dL/ds to the raw scale parameter (clamp passes gradient at equality)."""
     if scale_kind == SCALE_MUL:

@@ -53,3 +53,52 @@ def test_infoloob_rows_sum_property(lib_built):
     y = torch.ones(n, d, device="cuda") * 0.1
     infoloob_loss(x, y, None, 30.0).backward()
     assert x.grad.abs().max() < 1e-6
+
+
+@pytest.mark.parametrize("n,d", [(256, 256), (1024, 512), (768, 256)])
+def test_cloob_bf16_tensor_core_vs_oracle(lib_built, n, d):
+    """bf16 inputs of an eligible shape: Hopfield retrievals (forward via the P-panel GEMM,
+    backward via the dual-accumulator sweep) and InfoLOOB (MASKDIAG on tcgen05) against the fp32
+    oracle on the same bf16-rounded inputs; bf16 contract 2e-3 loss / 2e-2 grads."""
+    from multimodal_2025_b200 import _lib
+    from multimodal_2025_b200.losses import cloob_loss
+    x, y = O.synth_embeddings(n, d, 8, correlated=True, dtype=torch.bfloat16)
+    ref, (rx, ry) = O.loss_and_grads(lambda a, b: O.cloob_loss(a, b, 30.0, 15.0),
+                                     [x.float(), y.float()])
+    xc = x.cuda().requires_grad_(True)
+    yc = y.cuda().requires_grad_(True)
+    loss = cloob_loss(xc, yc, 30.0, 15.0, "cuda")
+    assert _lib.lib().mm25_debug_last_sim_path() == 1   # InfoLOOB forward ran on tcgen05
+    loss.backward()
+    assert rel_err(loss.detach().float().cpu(), ref) < 2e-3
+    assert rel_err(xc.grad.float().cpu(), rx) < 2e-2
+    assert rel_err(yc.grad.float().cpu(), ry) < 2e-2
+
+
+@pytest.mark.parametrize("M,N,d", [(128, 256, 256), (384, 1024, 512)])
+def test_hopfield_tc_pieces_vs_dense(lib_built, M, N, d):
+    """retrieval forward O = softmax(beta Q K^T) K and backward (dQ, dK) of the tensor-core path
+    against dense fp32 autograd on the same bf16 operands (rectangular Q / K)."""
+    from multimodal_2025_b200 import ops
+    g = torch.Generator().manual_seed(M + N)
+    nrm = torch.nn.functional.normalize
+    q = nrm(torch.randn(M, d, generator=g), dim=-1).cuda().bfloat16()
+    k = nrm(torch.randn(N, d, generator=g), dim=-1).cuda().bfloat16()
+    beta = 15.0
+    qf = q.float().requires_grad_(True)
+    kf = k.float().requires_grad_(True)
+    o_ref = torch.softmax(beta * qf @ kf.T, dim=-1) @ kf
+    d_o = torch.randn(M, d, generator=g).cuda()
+    o_ref.backward(d_o)
+    sc = torch.tensor([beta], device="cuda")
+    lse, _, _, _ = ops.sim_fwd(q.unsqueeze(0), k.unsqueeze(0), None, None, None, sc,
+                               ops.SCALE_MUL, 0.0, ops.SIM_PLAIN, 0, False, ops.IMPL_TC)
+    o, _, _, _ = ops.sim_bwd(q.unsqueeze(0), k.unsqueeze(0), None, None, None, sc, ops.SCALE_MUL,
+                             0.0, ops.SIM_PLAIN, 0, lse, None, 1.0, 0.0, 0.0, 0.0, None, True,
+                             False, False, ops.IMPL_TC)
+    o = o[0] / beta
+    assert rel_err(o.cpu(), o_ref.detach().cpu()) < 1e-2
+    delta = ops.rowdot(d_o, o)
+    dq, dk = ops.hopfield_bwd_tc(q, k, d_o, sc, lse[0], delta, True, True)
+    assert rel_err(dq.cpu(), qf.grad.cpu()) < 2e-2
+    assert rel_err(dk.cpu(), kf.grad.cpu()) < 2e-2

@@ -139,6 +139,16 @@ def main():
     emit(path="CLOOBLoss fwd+bwd", ms=ms, pairs_per_s=n / (ms * 1e-3),
          tflops_algorithmic=60.0 * n * n * d / (ms * 1e-3) / 1e12,
          note="cfg3 N=4096 d=512 fp32 SIMT path (60 N^2 d algorithmic FLOP)")
+    xb, yb = x.bfloat16(), yv.bfloat16()
+
+    def fb():
+        a_, b_ = xb.clone().requires_grad_(True), yb.clone().requires_grad_(True)
+        crit(a_, b_).backward()
+    ms = timeit(fb, reps=5, warm=2)
+    emit(path="CLOOBLoss fwd+bwd", ms=ms, pairs_per_s=n / (ms * 1e-3),
+         tflops_algorithmic=60.0 * n * n * d / (ms * 1e-3) / 1e12,
+         note="cfg3 N=4096 d=512 bf16: Hopfield retrievals + InfoLOOB on the tcgen05 kernels "
+              "(P-panel GEMM forward, dual-accumulator sweep backward, MASKDIAG)")
 
     # ---- AlignCLIP semantic (reduced N: fp32 SIMT MODULATED kernels) ---------------------------
     n, da_, dsem = 8192, 1024, 768
