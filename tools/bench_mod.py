@@ -61,5 +61,6 @@ def run(M, N, d, d2, impl):
 
 if __name__ == "__main__":
     run(8192, 65536, 1024, 768, ops.IMPL_AUTO)      # cfg5 per-GPU block at P = 8
-    run(8192, 8192, 1024, 768, ops.IMPL_AUTO)       # single-GPU square (profiles/r1_paths.jsonl)
-    run(8192, 8192, 1024, 768, ops.IMPL_SIMT)       # the fp32 SIMT kernels on the same input
+    if "--only-cfg5" not in sys.argv:
+        run(8192, 8192, 1024, 768, ops.IMPL_AUTO)   # single-GPU square (profiles/r1_paths.jsonl)
+        run(8192, 8192, 1024, 768, ops.IMPL_SIMT)   # the fp32 SIMT kernels on the same input
