@@ -43,6 +43,9 @@ struct ModSmem {
   uint32_t tmem_base;
 };
 
+// items are ordered segment-major (item = seg * num_rb + row block): the CTAs of one wave then
+// sweep the same few column segments, whose B tiles (N (d + d2) 2 B in total, more than L2 at
+// cfg5) stay L2-resident while every row block passes over them.
 struct ModGeom {
   int KC1, KC2, ntiles, nseg, tps, first_rb, num_rb;
 };
@@ -100,7 +103,7 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (lane == 0) {
       uint32_t st = 0, ph = 0;
       for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-        const int rb = g.first_rb + item / g.nseg, seg = item % g.nseg;
+        const int rb = g.first_rb + item % g.num_rb, seg = item / g.num_rb;
         const int32_t arow = rb * MBM;
         const int t0 = seg * g.tps, t1 = min(g.ntiles, t0 + g.tps);
         for (int t = t0; t < t1; ++t) {
@@ -125,7 +128,7 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
       constexpr uint32_t idesc = make_idesc_bf16(MBM, MBN, 0, 0);
       uint32_t st = 0, ph = 0, as = 0, accph = 0;
       for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-        const int seg = item % g.nseg;
+        const int seg = item / g.num_rb;
         const int t0 = seg * g.tps, t1 = min(g.ntiles, t0 + g.tps);
         for (int t = t0; t < t1; ++t) {
           mbar_wait(&sm.acc_empty[as], accph ^ 1);
@@ -169,7 +172,7 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     float ds = 0.f;
     uint32_t as = 0, accph = 0;
     for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-      const int rb = g.first_rb + item / g.nseg, seg = item % g.nseg;
+      const int rb = g.first_rb + item % g.num_rb, seg = item / g.num_rb;
       const int64_t row = (int64_t)rb * MBM + q * 32 + lane;
       const int64_t dcol = row + diag_offset;
       const float Di = diag_add ? __ldg(diag_add + row) : 0.f;
