@@ -212,6 +212,19 @@ int mm25_sum_parts(const float* parts, int64_t n, float alpha, float* out, void*
  * (single GPU: P = 1).  Used after the cross-rank all-gather of column partials. */
 int mm25_col_merge(const float* col_max, const float* col_sum, int64_t P, int64_t N,
                    float* col_lse, void* stream);
+/* The same with a leading dimension: the partials are rows of a gathered [P, ld] payload. */
+int mm25_col_merge_ld(const float* col_max, const float* col_sum, int64_t P, int64_t N,
+                      int64_t ld, float* col_lse, void* stream);
+/* Label-smoothing term of the row-sharded loss (clipLoss.py:111-117 in closed form):
+ * loss[0] -= coef * s * (sum_p sx_p) . (sum_p sy_p), sx_p / sy_p = the [d] column sums of
+ * xhat / yhat of rank p at column offsets ox / oy of a gathered [P, ld] payload.  One CTA. */
+int mm25_smooth_term(const float* payload, int64_t P, int64_t ld, int64_t ox, int64_t oy,
+                     int64_t d, const float* scale, int scale_kind, float clamp_max, float coef,
+                     float* loss, void* stream);
+/* dL/d(raw scale parameter) from dL/ds (device scalars): MM25_SCALE_LOG: dscale * exp(l) when
+ * l <= clamp_max else 0 (clipLoss.py:106 `clamp(max=4.6052).exp()`); MM25_SCALE_MUL: dscale. */
+int mm25_scale_param_grad(const float* dscale, const float* scale, int scale_kind,
+                          float clamp_max, float* out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * CLIP loss value from statistics (clipLoss.py:116-119 in closed form):

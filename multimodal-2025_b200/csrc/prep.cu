@@ -256,13 +256,52 @@ __global__ void __launch_bounds__(256) sum_parts_kernel(const float* __restrict_
 
 __global__ void __launch_bounds__(256) col_merge_kernel(const float* __restrict__ cmax,
                                                         const float* __restrict__ csum,
-                                                        int64_t P, int64_t N,
+                                                        int64_t P, int64_t N, int64_t ld,
                                                         float* __restrict__ col_lse) {
   int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (j >= N) return;
   float m = -INFINITY, l = 0.f;
-  for (int64_t p = 0; p < P; ++p) lse_merge(m, l, cmax[p * N + j], csum[p * N + j]);
+  for (int64_t p = 0; p < P; ++p) lse_merge(m, l, cmax[p * ld + j], csum[p * ld + j]);
   col_lse[j] = m + logf(l);
+}
+
+// label-smoothing term of the row-sharded loss: the column sums of xhat / yhat of every rank
+// sit in a gathered [P, ld] payload at column offsets ox / oy;
+//   loss -= coef * s * (sum_p sx_p) . (sum_p sy_p)        (clipLoss.py:111-117 in closed form)
+__global__ void __launch_bounds__(256) smooth_term_kernel(
+    const float* __restrict__ payload, int64_t P, int64_t ld, int64_t ox, int64_t oy, int d,
+    const float* __restrict__ scale, int scale_kind, float clamp_max, float coef,
+    float* __restrict__ loss) {
+  __shared__ double red[256];
+  double acc = 0.0;
+  for (int k = threadIdx.x; k < d; k += 256) {
+    float sx = 0.f, sy = 0.f;
+    for (int64_t p = 0; p < P; ++p) {
+      sx += payload[p * ld + ox + k];
+      sy += payload[p * ld + oy + k];
+    }
+    acc += (double)sx * (double)sy;
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const float s = load_scale(scale, scale_kind, clamp_max);
+    loss[0] = (float)((double)loss[0] - (double)coef * (double)s * red[0]);
+  }
+}
+
+// dL/d(raw scale parameter) from dL/ds: s = exp(min(l, clamp)) passes gradient at equality
+// (torch.clamp semantics), multiplicative scales pass it through
+__global__ void scale_param_grad_kernel(const float* __restrict__ dscale,
+                                        const float* __restrict__ scale, int scale_kind,
+                                        float clamp_max, float* __restrict__ out) {
+  const float l = scale[0];
+  out[0] = scale_kind == MM25_SCALE_LOG ? (l <= clamp_max ? dscale[0] * expf(l) : 0.f)
+                                        : dscale[0];
 }
 
 // one CTA (1024 threads) per batch entry; fixed-order tree reduction -> deterministic
@@ -427,7 +466,36 @@ extern "C" int mm25_col_merge(const float* col_max, const float* col_sum, int64_
                               float* col_lse, void* stream) {
   if (!col_max || !col_sum || !col_lse || P <= 0 || N <= 0) return MM25_ERR_ARG;
   col_merge_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, (cudaStream_t)stream>>>(
-      col_max, col_sum, P, N, col_lse);
+      col_max, col_sum, P, N, N, col_lse);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
+extern "C" int mm25_col_merge_ld(const float* col_max, const float* col_sum, int64_t P,
+                                 int64_t N, int64_t ld, float* col_lse, void* stream) {
+  if (!col_max || !col_sum || !col_lse || P <= 0 || N <= 0 || ld < N) return MM25_ERR_ARG;
+  col_merge_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, (cudaStream_t)stream>>>(
+      col_max, col_sum, P, N, ld, col_lse);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
+extern "C" int mm25_smooth_term(const float* payload, int64_t P, int64_t ld, int64_t ox,
+                                int64_t oy, int64_t d, const float* scale, int scale_kind,
+                                float clamp_max, float coef, float* loss, void* stream) {
+  if (!payload || !scale || !loss || P <= 0 || d <= 0 || ox + d > ld || oy + d > ld)
+    return MM25_ERR_ARG;
+  smooth_term_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(payload, P, ld, ox, oy, (int)d, scale,
+                                                          scale_kind, clamp_max, coef, loss);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
+extern "C" int mm25_scale_param_grad(const float* dscale, const float* scale, int scale_kind,
+                                     float clamp_max, float* out, void* stream) {
+  if (!dscale || !scale || !out) return MM25_ERR_ARG;
+  scale_param_grad_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(dscale, scale, scale_kind,
+                                                             clamp_max, out);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

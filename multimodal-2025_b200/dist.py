@@ -122,20 +122,28 @@ class _ShardedClipFn(torch.autograd.Function):
         extra = torch.cat([sx.reshape(-1), sy.reshape(-1)]) if want_cs else cmax.new_zeros(0)
         payload = torch.cat([cmax[0], csum[0], extra]).unsqueeze(0)
         gathered = _all_gather_cat(payload, group)                      # [P, 2N (+ 2d)]
-        col_lse = B.col_merge(gathered[:, :N].contiguous(), gathered[:, N:2 * N].contiguous())
+        if hasattr(B, "col_merge_ld"):
+            col_lse = B.col_merge_ld(gathered, N)
+        else:
+            col_lse = B.col_merge(gathered[:, :N].contiguous(), gathered[:, N:2 * N].contiguous())
         # (5) scalar pieces of the loss: local rows + local columns, then one small all-reduce
         part = B.clip_loss_finalize(row_lse, diag, col_lse[rank * n:(rank + 1) * n]
                                     .reshape(1, n).contiguous(), None, None, N, scale32,
                                     scale_kind, clamp_max, eps_ls)
-        red = part.reshape(1).clone()
+        red = part.reshape(1)
         dist.all_reduce(red, group=group)
-        loss = red.reshape(())
         if want_cs:
-            sxg = gathered[:, 2 * N:2 * N + d].sum(dim=0)
-            syg = gathered[:, 2 * N + d:2 * N + 2 * d].sum(dim=0)
-            s = (scale32.clamp(max=clamp_max).exp() if scale_kind == B.SCALE_LOG
-                 else scale32).reshape(())
-            loss = loss - (eps_ls / float(N) ** 2) * s * (sxg * syg).sum()
+            coef = eps_ls / float(N) ** 2
+            if hasattr(B, "smooth_term_"):
+                red = B.smooth_term_(red, gathered, 2 * N, 2 * N + d, d, scale32, scale_kind,
+                                     clamp_max, coef)
+            else:
+                sxg = gathered[:, 2 * N:2 * N + d].sum(dim=0)
+                syg = gathered[:, 2 * N + d:2 * N + 2 * d].sum(dim=0)
+                s = (scale32.clamp(max=clamp_max).exp() if scale_kind == B.SCALE_LOG
+                     else scale32).reshape(())
+                red = red - coef * s * (sxg * syg).sum()
+        loss = red.reshape(())
         ctx.save_for_backward(xhat, yhat, yall, invx, invy, row_lse, col_lse, scale32,
                               logits_scale)
         ctx.cfg = (eps_ls, normalize, clamp_max, group, backend, grad_scale, impl, in_dtype,
@@ -150,7 +158,10 @@ class _ShardedClipFn(torch.autograd.Function):
         (eps_ls, normalize, clamp_max, group, B, grad_scale, impl, in_dtype, rank, n,
          N, scale_kind) = ctx.cfg
         nn_ = float(N)
-        g = (gout.detach().to(torch.float32).reshape(1) * grad_scale).contiguous()
+        g = gout.detach().to(torch.float32).reshape(1)
+        if grad_scale != 1.0:
+            g = g * grad_scale
+        g = g.contiguous()
         bound = 1.01 if normalize else 0.0
         e_keep, e_flag = ctx.kept
         ctx.kept = (None, None)

@@ -299,12 +299,37 @@ def hopfield_bwd_tc(q: Tensor, k: Tensor, d_o: Tensor, beta: Tensor, lse: Tensor
 
 
 def scale_param_grad(dscale: Tensor, scale: Tensor, scale_kind: int, clamp_max: float) -> Tensor:
-    """Chain dL/ds to the raw scale parameter (clamp passes gradient at equality)."""
-    if scale_kind == SCALE_MUL:
-        return dscale.reshape(scale.shape).to(scale.dtype)
-    l = scale.detach().float()
-    chain = torch.where(l <= clamp_max, l.exp(), torch.zeros_like(l))
-    return (dscale.reshape(()) * chain).reshape(scale.shape).to(scale.dtype)
+    """Chain dL/ds to the raw scale parameter (clamp passes gradient at equality); one kernel."""
+    s32 = scale.detach().reshape(1).to(torch.float32).contiguous()
+    with torch.cuda.device(dscale.device):
+        out = torch.empty((1,), dtype=torch.float32, device=dscale.device)
+        rc = _lib.lib().mm25_scale_param_grad(_p(dscale), _p(s32), scale_kind, clamp_max, _p(out),
+                                              _stream(dscale))
+    _lib.check(rc, "mm25_scale_param_grad")
+    return out.reshape(scale.shape).to(scale.dtype)
+
+
+def col_merge_ld(payload: Tensor, N: int) -> Tensor:
+    """col_merge on a gathered [P, ld] payload whose rows start with (col_max[N], col_sum[N])."""
+    P, ld = payload.shape
+    with torch.cuda.device(payload.device):
+        out = torch.empty((N,), dtype=torch.float32, device=payload.device)
+        rc = _lib.lib().mm25_col_merge_ld(_p(payload), payload.data_ptr() + 4 * N, P, N, ld,
+                                          _p(out), _stream(payload))
+    _lib.check(rc, "mm25_col_merge_ld")
+    return out
+
+
+def smooth_term_(loss: Tensor, payload: Tensor, ox: int, oy: int, d: int, scale: Tensor,
+                 scale_kind: int, clamp_max: float, coef: float) -> Tensor:
+    """loss[0] -= coef * s * (sum_p payload[p, ox:ox+d]) . (sum_p payload[p, oy:oy+d]) in place
+    (label-smoothing term of the sharded loss, include/mm25.h mm25_smooth_term)."""
+    P, ld = payload.shape
+    with torch.cuda.device(loss.device):
+        rc = _lib.lib().mm25_smooth_term(_p(payload), P, ld, ox, oy, d, _p(scale), scale_kind,
+                                         clamp_max, coef, _p(loss), _stream(loss))
+    _lib.check(rc, "mm25_smooth_term")
+    return loss
 
 
 # ------------------------------------------------------------------------------------------------
