@@ -61,6 +61,27 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x,
   }
 }
 
+// stage 2 over the [P, d] partials of the fused kernels: 32 columns x 32 row lanes
+__global__ void __launch_bounds__(1024) colsum_wide_kernel(const float* __restrict__ x,
+                                                           float* __restrict__ out, int64_t M,
+                                                           int d) {
+  __shared__ float red[32][33];
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int rl = threadIdx.x >> 5;
+  const float* xb = x + (int64_t)blockIdx.y * M * d;
+  float acc = 0.f;
+  if (c < d)
+    for (int64_t r = rl; r < M; r += 32) acc += xb[r * d + c];
+  red[rl][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (rl == 0 && c < d) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) s += red[k][threadIdx.x];
+    out[(int64_t)blockIdx.y * d + c] = s;
+  }
+}
+
 // stage 1 of the fast column sum: each CTA owns a strided set of rows, warps accumulate 16-byte
 // vectors in registers, fixed-order cross-warp sum -> partial [B][P][d]; stage 2 = colsum_kernel
 template <typename T>
@@ -141,7 +162,10 @@ template <> struct Vec4<__nv_bfloat16> {
 
 constexpr int RN_MAXIT = 16;  // d <= 16 * 128
 
-template <typename TI, typename TO, bool CS>
+// NIT = 128-element chunks per row held in registers (instantiated for 2, 4, 8, 16): the
+// register footprint sets how many CTAs stay resident, i.e. how many bytes are in flight per SM —
+// with the d = 2048 footprint a d = 512 launch ran one CTA per SM at ~1.5 TB/s.
+template <typename TI, typename TO, bool CS, int NIT>
 __global__ void __launch_bounds__(256)
 rownorm_fused_kernel(const TI* __restrict__ x, TO* __restrict__ xhat,
                      float* __restrict__ inv_norm, float* __restrict__ part, int64_t M, int d,
@@ -151,20 +175,20 @@ rownorm_fused_kernel(const TI* __restrict__ x, TO* __restrict__ xhat,
   const int P = gridDim.x;
   const int niter = d >> 7;
   const int64_t base = (int64_t)blockIdx.y * M;
-  float acc[CS ? RN_MAXIT : 1][4];
+  float acc[CS ? NIT : 1][4];
   if (CS) {
 #pragma unroll
-    for (int it = 0; it < RN_MAXIT; ++it)
+    for (int it = 0; it < NIT; ++it)
 #pragma unroll
       for (int u = 0; u < 4; ++u) acc[it][u] = 0.f;
   }
   for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < M; r += (int64_t)P * 8) {
     const TI* xr = x + (base + r) * d;
     TO* o = xhat + (base + r) * d;
-    float v[RN_MAXIT][4];
+    float v[NIT][4];
     float ss = 0.f;
 #pragma unroll
-    for (int it = 0; it < RN_MAXIT; ++it)
+    for (int it = 0; it < NIT; ++it)
       if (it < niter) {
         Vec4<TI>::load(xr + (it * 32 + lane) * 4, v[it]);
 #pragma unroll
@@ -176,7 +200,7 @@ rownorm_fused_kernel(const TI* __restrict__ x, TO* __restrict__ xhat,
       inv = 1.f / fmaxf(sqrtf(ss), eps);
     }
 #pragma unroll
-    for (int it = 0; it < RN_MAXIT; ++it)
+    for (int it = 0; it < NIT; ++it)
       if (it < niter) {
         float w[4];
 #pragma unroll
@@ -192,7 +216,7 @@ rownorm_fused_kernel(const TI* __restrict__ x, TO* __restrict__ xhat,
   }
   if (CS) {
 #pragma unroll
-    for (int it = 0; it < RN_MAXIT; ++it)
+    for (int it = 0; it < NIT; ++it)
       if (it < niter)
 #pragma unroll
         for (int u = 0; u < 4; ++u) red[warp * d + (it * 32 + lane) * 4 + u] = acc[it][u];
@@ -208,7 +232,7 @@ rownorm_fused_kernel(const TI* __restrict__ x, TO* __restrict__ xhat,
 
 static int colsum_parts(int64_t M) {
   int64_t p = (M + 7) / 8;
-  return (int)(p > 592 ? 592 : (p < 1 ? 1 : p));  // up to 4 CTAs per SM
+  return (int)(p > 740 ? 740 : (p < 1 ? 1 : p));  // up to 5 CTAs per SM
 }
 
 // dx = inv * (g - xhat (xhat . g))   (backward of F.normalize away from the eps clamp)
@@ -384,28 +408,37 @@ extern "C" int mm25_rownorm_fwd(const void* x, int dtype, void* xhat, int out_dt
     float* part = colsum ? colsum + B * d : nullptr;
     dim3 g1((unsigned)P, (unsigned)B);
     const size_t sh = colsum ? sizeof(float) * 8 * (size_t)d : 0;
-#define RF(TI, TO)                                                                            \
+#define RF2(TI, TO, NIT)                                                                       \
   do {                                                                                        \
     if (colsum) {                                                                             \
-      MM25_CUDA_CHECK(cudaFuncSetAttribute(rownorm_fused_kernel<TI, TO, true>,                \
+      MM25_CUDA_CHECK(cudaFuncSetAttribute(rownorm_fused_kernel<TI, TO, true, NIT>,           \
                                            cudaFuncAttributeMaxDynamicSharedMemorySize,       \
                                            (int)sh));                                         \
-      rownorm_fused_kernel<TI, TO, true><<<g1, 256, sh, st>>>(                                \
+      rownorm_fused_kernel<TI, TO, true, NIT><<<g1, 256, sh, st>>>(                           \
           (const TI*)x, (TO*)xhat, inv_norm, part, M, (int)d, normalize, eps);                \
     } else {                                                                                  \
-      rownorm_fused_kernel<TI, TO, false><<<g1, 256, 0, st>>>(                                \
+      rownorm_fused_kernel<TI, TO, false, NIT><<<g1, 256, 0, st>>>(                           \
           (const TI*)x, (TO*)xhat, inv_norm, nullptr, M, (int)d, normalize, eps);             \
     }                                                                                         \
+  } while (0)
+#define RF(TI, TO)                                                                            \
+  do {                                                                                        \
+    const int nit_ = (int)(d >> 7);                                                           \
+    if (nit_ <= 2) RF2(TI, TO, 2);                                                            \
+    else if (nit_ <= 4) RF2(TI, TO, 4);                                                       \
+    else if (nit_ <= 8) RF2(TI, TO, 8);                                                       \
+    else RF2(TI, TO, 16);                                                                     \
   } while (0)
     if (dtype == MM25_F32 && out_dtype == MM25_F32) RF(float, float);
     else if (dtype == MM25_F32 && out_dtype == MM25_BF16) RF(float, __nv_bfloat16);
     else if (dtype == MM25_BF16 && out_dtype == MM25_BF16) RF(__nv_bfloat16, __nv_bfloat16);
     else RF(__nv_bfloat16, float);
 #undef RF
+#undef RF2
     MM25_LAUNCH_CHECK();
     if (colsum) {
       dim3 g2((unsigned)ceil_div(d, 32), (unsigned)B);
-      colsum_kernel<float><<<g2, 256, 0, st>>>(part, colsum, P, (int)d);
+      colsum_wide_kernel<<<g2, 1024, 0, st>>>(part, colsum, P, (int)d);
       MM25_LAUNCH_CHECK();
     }
     return MM25_OK;

@@ -8,6 +8,7 @@
 #include "sim_tc_sweep.cuh"
 #include "sim_tc.h"
 
+#include <cstdlib>
 #include <mutex>
 
 namespace mm25 {
@@ -65,6 +66,7 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // force_slow carries two flags: bit 0 = test hook (robust epilogue), bit 1 = MASKDIAG mode
     // (InfoLOOB, cloobLoss.py:28-31: the positive enters the LSE as the constant -10000)
     const bool mask_diag = (force_slow & 2) != 0;
+    const bool sums_only_ok = (force_slow & 4) == 0;  // A/B switch MM25_COL_PARTIAL_MAX
     force_slow &= 1;
     const float vmask = s != 0.f ? -10000.f / s : 0.f;
     const bool fast_static = !force_slow && dot_bound > 0.f && 2.f * m2s <= SPREAD_LIMIT;
@@ -209,17 +211,24 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         named_bar_sync(1, 32 * NEPI);
         {
           const int c = ew * 32 + lane;   // 8 warps x 32 lanes = the tile's 256 columns
-          float m = sm.colm[buf][0][c], l = sm.cols[buf][0][c];
-#pragma unroll
-          for (int g = 1; g < 4; ++g) {
-            const float m2 = sm.colm[buf][g][c], l2 = sm.cols[buf][g][c];
-            const float mn = fmaxf(m, m2);
-            l = l * ex2_approx(m - mn) + l2 * ex2_approx(m2 - mn);
-            m = mn;
-          }
           const int64_t o = ((int64_t)bz * nrb_per_batch + rb) * N + col0 + c;
-          col_pm[o] = m;
-          col_pl[o] = l;
+          if (fast_static && sums_only_ok) {
+            // every partial shares the shift m2s: plain sums, and the merge kernel knows the
+            // maximum without reading it (half the partial traffic)
+            col_pl[o] = (sm.cols[buf][0][c] + sm.cols[buf][1][c]) +
+                        (sm.cols[buf][2][c] + sm.cols[buf][3][c]);
+          } else {
+            float m = sm.colm[buf][0][c], l = sm.cols[buf][0][c];
+#pragma unroll
+            for (int g = 1; g < 4; ++g) {
+              const float m2 = sm.colm[buf][g][c], l2 = sm.cols[buf][g][c];
+              const float mn = fmaxf(m, m2);
+              l = l * ex2_approx(m - mn) + l2 * ex2_approx(m2 - mn);
+              m = mn;
+            }
+            col_pm[o] = m;
+            col_pl[o] = l;
+          }
         }
         buf ^= 1;
       }
@@ -251,7 +260,13 @@ __global__ void __launch_bounds__(1024) fwd_tc_merge_kernel(
     const float* __restrict__ row_pm, const float* __restrict__ row_pl, int nseg, int64_t M,
     float* __restrict__ row_lse, const float* __restrict__ col_pm,
     const float* __restrict__ col_pl, int nrb, int64_t N, float* __restrict__ col_max,
-    float* __restrict__ col_sum) {
+    float* __restrict__ col_sum, const float* __restrict__ scale, int scale_kind,
+    float clamp_max, float dot_bound, int force_slow) {
+  // same predicate as the forward kernel: on the static-shift path the column partials carry no
+  // maxima (all equal m2s)
+  const float m2s = dot_bound * fabsf(load_scale(scale, scale_kind, clamp_max) * LOG2E);
+  const bool fast_static = !(force_slow & 1) && !(force_slow & 4) && dot_bound > 0.f &&
+                           2.f * m2s <= SPREAD_LIMIT;
   __shared__ float sm_m[32][33], sm_l[32][33];
   const int bz = blockIdx.y;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -274,7 +289,7 @@ __global__ void __launch_bounds__(1024) fwd_tc_merge_kernel(
     float m = -INFINITY, l = 0.f;
     if (t < N)
       for (int p = ty; p < nrb; p += 32)
-        lse2_merge(m, l, col_pm[((int64_t)bz * nrb + p) * N + t],
+        lse2_merge(m, l, fast_static ? m2s : col_pm[((int64_t)bz * nrb + p) * N + t],
                    col_pl[((int64_t)bz * nrb + p) * N + t]);
     sm_m[ty][tx] = m; sm_l[ty][tx] = l;
     __syncthreads();
@@ -386,6 +401,8 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   if ((e_out == nullptr) != (e_flag == nullptr)) return MM25_ERR_ARG;
   if (ws_bytes < fwd_workspace_bytes(B, M, N, d)) return MM25_ERR_WORKSPACE;
   FwdGeom g = fwd_geom(B, M, N);
+  static const int legacy_partials = getenv("MM25_COL_PARTIAL_MAX") ? 4 : 0;  // A/B switch
+  const int flags = g_force_slow | (mask_diag ? 2 : 0) | legacy_partials;
   CUtensorMap ta, tb;
   int rc = make_tmap_bf16(&ta, a, (uint64_t)(B * M), (uint64_t)d, BM, BK);
   if (rc) return rc;
@@ -405,12 +422,12 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   sim_fwd_tc_kernel<<<g.grid, FWD_THREADS, smem, st>>>(
       ta, tb, te, e_out ? 1 : 0, e_flag, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind, clamp_max,
-      diag_offset, row_pm, row_pl, col_pm, col_pl, diag, g_force_slow | (mask_diag ? 2 : 0),
-      dot_bound);
+      diag_offset, row_pm, row_pl, col_pm, col_pl, diag, flags, dot_bound);
   MM25_LAUNCH_CHECK();
   const int64_t mx = M > N ? M : N;
   fwd_tc_merge_kernel<<<dim3((unsigned)ceil_div(mx, 32), (unsigned)B), 1024, 0, st>>>(
-      row_pm, row_pl, g.nseg * 2, M, row_lse, col_pm, col_pl, g.nrb, N, col_max, col_sum);
+      row_pm, row_pl, g.nseg * 2, M, row_lse, col_pm, col_pl, g.nrb, N, col_max, col_sum, scale,
+      scale_kind, clamp_max, dot_bound, flags);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

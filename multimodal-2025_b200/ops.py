@@ -110,7 +110,7 @@ def _sim_fwd_impl(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag
             wsb = max(wsb, L.mm25_sim_mod_workspace_bytes(B, M, N, d, d2, _dt(a), 0))
         ws = torch.empty((max(int(wsb), 16),), dtype=torch.uint8, device=dev)
         e_keep = torch.empty((B * M, N) if keep else (0,), dtype=torch.bfloat16, device=dev)
-        e_flag = torch.zeros((1,), dtype=torch.int32, device=dev)
+        e_flag = torch.zeros((1,) if keep else (0,), dtype=torch.int32, device=dev)
         rc = L.mm25_sim_fwd(_p(a), _p(b), _dt(a), _p(u), _p(v), _p(diag_add), B, M, N, d, d2,
                             _p(scale), scale_kind, clamp_max, mode, diag_offset, _p(row_lse),
                             _p(col_max) if want_cols else None,
