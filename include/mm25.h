@@ -215,6 +215,13 @@ int mm25_col_merge(const float* col_max, const float* col_sum, int64_t P, int64_
 /* The same with a leading dimension: the partials are rows of a gathered [P, ld] payload. */
 int mm25_col_merge_ld(const float* col_max, const float* col_sum, int64_t P, int64_t N,
                       int64_t ld, float* col_lse, void* stream);
+/* One-shot all-gather over NVLink peer memory: copies `bytes` from `src` to byte offset
+ * `dst_offset_bytes` of each of the `npeers` peer-mapped buffers (HOST array of device pointers,
+ * symmetric memory, the caller's own buffer included).  Everything 16-byte aligned.  A
+ * cross-rank barrier must follow before any rank reads its gathered buffer.  Replaces
+ * `torch.distributed.nn.all_gather` of the reference's gather_features (loss.py:49-51). */
+int mm25_peer_bcast(const void* src, int64_t bytes, void* const* peer_ptrs, int64_t npeers,
+                    int64_t dst_offset_bytes, void* stream);
 /* Label-smoothing term of the row-sharded loss (clipLoss.py:111-117 in closed form):
  * loss[0] -= coef * s * (sum_p sx_p) . (sum_p sy_p), sx_p / sy_p = the [d] column sums of
  * xhat / yhat of rank p at column offsets ox / oy of a gathered [P, ld] payload.  One CTA. */

@@ -504,6 +504,40 @@ extern "C" int mm25_col_merge(const float* col_max, const float* col_sum, int64_
   return MM25_OK;
 }
 
+// One-shot all-gather over NVLink peer memory: every rank stores its contiguous shard into the
+// same offset of all P peer-mapped buffers (symmetric memory; one of them is its own).  16-byte
+// vectors, one load and P stores per thread; a cross-rank barrier must follow before the
+// gathered buffer is read.
+struct PeerTable { void* p[16]; };
+__global__ void __launch_bounds__(256) peer_bcast_kernel(const uint4* __restrict__ src,
+                                                         int64_t nvec, PeerTable peers,
+                                                         int npeers, int64_t dst_off_vec) {
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * 256) {
+    const uint4 v = __ldg(src + i);
+    for (int q = 0; q < npeers; ++q) reinterpret_cast<uint4*>(peers.p[q])[dst_off_vec + i] = v;
+  }
+}
+
+extern "C" int mm25_peer_bcast(const void* src, int64_t bytes, void* const* peer_ptrs,
+                               int64_t npeers, int64_t dst_offset_bytes, void* stream) {
+  if (!src || !peer_ptrs || npeers < 1 || npeers > 16 || bytes <= 0) return MM25_ERR_ARG;
+  if ((bytes & 15) || (dst_offset_bytes & 15) || (reinterpret_cast<uintptr_t>(src) & 15))
+    return MM25_ERR_ALIGN;
+  PeerTable t;
+  for (int64_t i = 0; i < npeers; ++i) {
+    if (!peer_ptrs[i] || (reinterpret_cast<uintptr_t>(peer_ptrs[i]) & 15)) return MM25_ERR_ALIGN;
+    t.p[i] = peer_ptrs[i];
+  }
+  const int64_t nvec = bytes / 16;
+  int64_t blocks = ceil_div(nvec, 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  peer_bcast_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)src, nvec, t, (int)npeers, dst_offset_bytes / 16);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
 extern "C" int mm25_col_merge_ld(const float* col_max, const float* col_sum, int64_t P,
                                  int64_t N, int64_t ld, float* col_lse, void* stream) {
   if (!col_max || !col_sum || !col_lse || P <= 0 || N <= 0 || ld < N) return MM25_ERR_ARG;

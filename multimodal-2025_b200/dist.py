@@ -25,6 +25,8 @@ inject a CPU stand-in to exercise the collective logic under gloo.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 from torch import nn
@@ -82,6 +84,49 @@ def _symm_grad_buffer(n: int, d: int, device, group):
     return out
 
 
+_SYMM_GEN = {}
+
+
+def _symm_buffer(tag, shape, dtype, device, group):
+    """Cached symmetric-memory tensor + handle (peer-mapped on every rank), or None."""
+    key = (tag, tuple(shape), dtype, device.index, id(group))
+    if key in _SYMM_CACHE:
+        return key, _SYMM_CACHE[key]
+    out = None
+    try:
+        import torch.distributed._symmetric_memory as symm_mem
+        buf = symm_mem.empty(tuple(shape), dtype=dtype, device=device)
+        hdl = symm_mem.rendezvous(buf, group)
+        out = (buf, hdl)
+    except Exception:  # no peer access / unsupported allocator: callers keep the NCCL path
+        out = None
+    _SYMM_CACHE[key] = out
+    return key, out
+
+
+def _peer_all_gather(B, t, tag, group):
+    """[n, ...] per rank -> [P n, ...]: every rank stores its shard straight into all peers'
+    symmetric buffers over NVLink (one kernel) and one symmetric-memory barrier follows — no NCCL
+    ring, no staging.  Returns (gathered buffer, key) or None when the fast path does not apply.
+    The buffer is reused by the next call with the same shape: consume it (or check
+    `_SYMM_GEN[key]`) before gathering again."""
+    if not (hasattr(B, "peer_bcast") and t.is_cuda and dist.get_backend(group) == "nccl"):
+        return None
+    nbytes = t.numel() * t.element_size()
+    if nbytes % 16 or os.environ.get("MM25_NCCL_GATHER"):
+        return None
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    key, sb = _symm_buffer(tag, (world * t.shape[0],) + tuple(t.shape[1:]), t.dtype, t.device,
+                           group)
+    if sb is None:
+        return None
+    buf, hdl = sb
+    B.peer_bcast(t, [int(p) for p in hdl.buffer_ptrs], rank * nbytes)
+    hdl.barrier(channel=0)
+    _SYMM_GEN[key] = _SYMM_GEN.get(key, 0) + 1
+    return buf, key
+
+
 class _ShardedClipFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, img, txt, logits_scale, eps_ls, normalize, clamp_max, group, backend,
@@ -102,7 +147,12 @@ class _ShardedClipFn(torch.autograd.Function):
         yhat, invy, sy = B.rownorm_fwd(txt.unsqueeze(0), normalize, _EPS_NORM, cdt, want_cs)
         scale32 = logits_scale.detach().reshape(1).to(torch.float32).contiguous()
         # (2) all-gather the other modality
-        yall = _all_gather_cat(yhat[0], group).unsqueeze(0)
+        pg = _peer_all_gather(B, yhat[0], "yall", group)
+        if pg is not None:
+            yall, ykey = pg[0].unsqueeze(0), pg[1]
+            ygen = _SYMM_GEN[ykey]
+        else:
+            yall, ykey, ygen = _all_gather_cat(yhat[0], group).unsqueeze(0), None, 0
         # (3) local block
         bound = 1.01 if normalize else 0.0
         keep = (hasattr(B, "sim_fwd_keep") and xhat.is_cuda and torch.is_grad_enabled()
@@ -121,7 +171,8 @@ class _ShardedClipFn(torch.autograd.Function):
         #     merged / summed locally in rank order (deterministic, one collective fewer)
         extra = torch.cat([sx.reshape(-1), sy.reshape(-1)]) if want_cs else cmax.new_zeros(0)
         payload = torch.cat([cmax[0], csum[0], extra]).unsqueeze(0)
-        gathered = _all_gather_cat(payload, group)                      # [P, 2N (+ 2d)]
+        pg = _peer_all_gather(B, payload, "colstats", group)            # [P, 2N (+ 2d)]
+        gathered = pg[0] if pg is not None else _all_gather_cat(payload, group)
         if hasattr(B, "col_merge_ld"):
             col_lse = B.col_merge_ld(gathered, N)
         else:
@@ -149,12 +200,17 @@ class _ShardedClipFn(torch.autograd.Function):
         ctx.cfg = (eps_ls, normalize, clamp_max, group, backend, grad_scale, impl, in_dtype,
                    rank, n, N, scale_kind)
         ctx.kept = (e_keep, e_flag)
+        ctx.ygen = (ykey, ygen)
         return loss
 
     @staticmethod
     def backward(ctx, gout):
         (xhat, yhat, yall, invx, invy, row_lse, col_lse, scale32,
          logits_scale) = ctx.saved_tensors
+        ykey, ygen = ctx.ygen
+        if ykey is not None and _SYMM_GEN.get(ykey) != ygen:
+            # another forward reused the symmetric gather buffer since: gather Yhat again
+            yall = _all_gather_cat(yhat[0], ctx.cfg[3]).unsqueeze(0)
         (eps_ls, normalize, clamp_max, group, B, grad_scale, impl, in_dtype, rank, n,
          N, scale_kind) = ctx.cfg
         nn_ = float(N)

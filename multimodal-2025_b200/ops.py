@@ -309,6 +309,19 @@ def scale_param_grad(dscale: Tensor, scale: Tensor, scale_kind: int, clamp_max: 
     return out.reshape(scale.shape).to(scale.dtype)
 
 
+def peer_bcast(src: Tensor, peer_ptrs: List[int], dst_offset_bytes: int) -> None:
+    """One-shot all-gather piece: store the contiguous `src` at `dst_offset_bytes` of every
+    peer-mapped buffer in `peer_ptrs` (include/mm25.h mm25_peer_bcast).  Barrier afterwards."""
+    import ctypes
+    src = src.contiguous()
+    P = len(peer_ptrs)
+    table = (ctypes.c_void_p * P)(*peer_ptrs)
+    with torch.cuda.device(src.device):
+        rc = _lib.lib().mm25_peer_bcast(_p(src), src.numel() * src.element_size(), table, P,
+                                        dst_offset_bytes, _stream(src))
+    _lib.check(rc, "mm25_peer_bcast")
+
+
 def col_merge_ld(payload: Tensor, N: int) -> Tensor:
     """col_merge on a gathered [P, ld] payload whose rows start with (col_max[N], col_sum[N])."""
     P, ld = payload.shape

@@ -46,4 +46,6 @@ if rank == 0:
         print("%8.1f %8.1f  %s" % (e.time_range.start - t0, e.time_range.end - e.time_range.start, e.name[:70]))
         busy += e.time_range.end - e.time_range.start
     print("span_us", last[-1].time_range.end - t0, "busy_us", busy)
-dist.destroy_process_group()
+sys.stdout.flush()
+torch.cuda.synchronize()
+os._exit(0)  # skip the process-group teardown: it hung after graph capture at 8 ranks
