@@ -308,9 +308,10 @@ def run_ours(args):
         import multimodal_2025_b200.dist as mdist
         peer = any(k[0] == "yall" and v is not None for k, v in mdist._SYMM_CACHE.items()
                    if isinstance(k[0], str))
-        coll_note = (("one-shot all-gather over NVLink peer memory (Yhat, col stats)" if peer
-                      else "nccl all-gather(Yhat) + all-gather(col stats)")
-                     + " + nccl all-reduce(scalars); dY: " + str(mdist.LAST_BACKWARD_PATH))
+        coll_note = (("one-shot all-gather over NVLink peer memory (Yhat, col stats, scalar "
+                      "partials) + symmetric-memory barriers, no NCCL in the step" if peer
+                      else "nccl all-gather(Yhat) + all-gather(col stats) + all-reduce(scalars)")
+                     + "; dY: " + str(mdist.LAST_BACKWARD_PATH))
     tm = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)

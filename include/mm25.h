@@ -217,7 +217,8 @@ int mm25_col_merge_ld(const float* col_max, const float* col_sum, int64_t P, int
                       int64_t ld, float* col_lse, void* stream);
 /* One-shot all-gather over NVLink peer memory: copies `bytes` from `src` to byte offset
  * `dst_offset_bytes` of each of the `npeers` peer-mapped buffers (HOST array of device pointers,
- * symmetric memory, the caller's own buffer included).  Everything 16-byte aligned.  A
+ * symmetric memory, the caller's own buffer included).  16-byte aligned sizes / offsets take the
+ * vector kernel; 4-byte aligned payloads up to 1 MiB (scalars) a word kernel.  A
  * cross-rank barrier must follow before any rank reads its gathered buffer.  Replaces
  * `torch.distributed.nn.all_gather` of the reference's gather_features (loss.py:49-51). */
 int mm25_peer_bcast(const void* src, int64_t bytes, void* const* peer_ptrs, int64_t npeers,

@@ -519,15 +519,32 @@ __global__ void __launch_bounds__(256) peer_bcast_kernel(const uint4* __restrict
   }
 }
 
+// small / unaligned payloads (scalars): 4-byte words, one CTA
+__global__ void __launch_bounds__(256) peer_bcast_words_kernel(const uint32_t* __restrict__ src,
+                                                               int64_t nw, PeerTable peers,
+                                                               int npeers, int64_t dst_off_w) {
+  for (int64_t i = threadIdx.x; i < nw; i += 256) {
+    const uint32_t v = src[i];
+    for (int q = 0; q < npeers; ++q) reinterpret_cast<uint32_t*>(peers.p[q])[dst_off_w + i] = v;
+  }
+}
+
 extern "C" int mm25_peer_bcast(const void* src, int64_t bytes, void* const* peer_ptrs,
                                int64_t npeers, int64_t dst_offset_bytes, void* stream) {
   if (!src || !peer_ptrs || npeers < 1 || npeers > 16 || bytes <= 0) return MM25_ERR_ARG;
-  if ((bytes & 15) || (dst_offset_bytes & 15) || (reinterpret_cast<uintptr_t>(src) & 15))
-    return MM25_ERR_ALIGN;
   PeerTable t;
   for (int64_t i = 0; i < npeers; ++i) {
     if (!peer_ptrs[i] || (reinterpret_cast<uintptr_t>(peer_ptrs[i]) & 15)) return MM25_ERR_ALIGN;
     t.p[i] = peer_ptrs[i];
+  }
+  if ((bytes & 15) || (dst_offset_bytes & 15) || (reinterpret_cast<uintptr_t>(src) & 15)) {
+    if ((bytes & 3) || (dst_offset_bytes & 3) || (reinterpret_cast<uintptr_t>(src) & 3) ||
+        bytes > (1 << 20))
+      return MM25_ERR_ALIGN;
+    peer_bcast_words_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(
+        (const uint32_t*)src, bytes / 4, t, (int)npeers, dst_offset_bytes / 4);
+    MM25_LAUNCH_CHECK();
+    return MM25_OK;
   }
   const int64_t nvec = bytes / 16;
   int64_t blocks = ceil_div(nvec, 256);

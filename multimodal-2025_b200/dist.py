@@ -113,7 +113,7 @@ def _peer_all_gather(B, t, tag, group):
     if not (hasattr(B, "peer_bcast") and t.is_cuda and dist.get_backend(group) == "nccl"):
         return None
     nbytes = t.numel() * t.element_size()
-    if nbytes % 16 or os.environ.get("MM25_NCCL_GATHER"):
+    if nbytes % 4 or os.environ.get("MM25_NCCL_GATHER"):
         return None
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     key, sb = _symm_buffer(tag, (world * t.shape[0],) + tuple(t.shape[1:]), t.dtype, t.device,
@@ -125,6 +125,16 @@ def _peer_all_gather(B, t, tag, group):
     hdl.barrier(channel=0)
     _SYMM_GEN[key] = _SYMM_GEN.get(key, 0) + 1
     return buf, key
+
+
+def _all_reduce_scalar(B, t, tag, group):
+    """Sum of a [1] fp32 tensor over the ranks: peer stores into a [P, 1] symmetric buffer, one
+    barrier and a local fixed-order sum (same bits on every rank); NCCL all-reduce otherwise."""
+    pg = _peer_all_gather(B, t.reshape(1, 1), tag, group)
+    if pg is None:
+        dist.all_reduce(t, group=group)
+        return t
+    return pg[0].sum(dim=0)
 
 
 class _ShardedClipFn(torch.autograd.Function):
@@ -181,8 +191,7 @@ class _ShardedClipFn(torch.autograd.Function):
         part = B.clip_loss_finalize(row_lse, diag, col_lse[rank * n:(rank + 1) * n]
                                     .reshape(1, n).contiguous(), None, None, N, scale32,
                                     scale_kind, clamp_max, eps_ls)
-        red = part.reshape(1)
-        dist.all_reduce(red, group=group)
+        red = _all_reduce_scalar(B, part.reshape(1), "loss", group)
         if want_cs:
             coef = eps_ls / float(N) ** 2
             if hasattr(B, "smooth_term_"):
@@ -253,7 +262,7 @@ class _ShardedClipFn(torch.autograd.Function):
         dtxt = B.rownorm_bwd(dy_local, yhat, invy, normalize, out_dt, None)[0].to(in_dtype)
         dls = None
         if ctx.needs_input_grad[2]:
-            dist.all_reduce(dscale, group=group)
+            dscale = _all_reduce_scalar(B, dscale.reshape(1), "dscale", group)
             dls = B.scale_param_grad(dscale, logits_scale, scale_kind, clamp_max)
         return dimg, dtxt, dls, None, None, None, None, None, None, None, None
 
