@@ -18,6 +18,8 @@
 #include "tc_common.cuh"
 #include "gemm_tc.h"
 
+#include <cstdlib>
+
 namespace mm25 {
 namespace tc {
 
@@ -52,6 +54,7 @@ struct Problem {
   // peer[q] + (row - q R) * ldc — peer-mapped fp32 buffers of the other ranks over NVLink
   int scatter;
   int rows_per_rank;
+  int rot;         // scatter: m-block rotation (ring order over the owners, see GemmDesc)
   float* peer[GEMM_MAX_PEERS];
 };
 
@@ -63,6 +66,8 @@ struct Schedule {
   int r;
   int nbA, nbB;
   int nsA, nsB;
+  int p1_first;    // walk problem 1 before problem 0 (problem 1 scatters over NVLink: its
+                   // fire-and-forget adds then drain under problem 0's tiles)
 };
 
 struct Params {
@@ -77,21 +82,34 @@ __device__ __forceinline__ bool job_at(const Params& P, int grp, int k, int* pro
   const Schedule& s = P.s;
   const bool A = grp < s.r;
   const int nb = A ? s.nbA : s.nbB;
+  const int ns = A ? s.nsA : s.nsB;
+  const int base = A ? grp * s.nsA : s.r * s.nsA + (grp - s.r) * s.nsB;
   int job;
-  if (k < nb) {
+  if (s.p1_first) {
+    // this group's run of problem 1 may be cut short by the end of the problem
+    const int tot1 = P.p[1].mblocks * P.p[1].ksplit;
+    const int n1 = min(ns, max(0, tot1 - base));
+    if (k < n1) {
+      *prob = 1;
+      job = base + k;
+    } else {
+      if (k - n1 >= nb) return false;
+      *prob = 0;
+      job = grp + (k - n1) * s.ngroups;
+    }
+  } else if (k < nb) {
     *prob = 0;
     job = grp + k * s.ngroups;
   } else {
     const int ks = k - nb;
-    const int ns = A ? s.nsA : s.nsB;
     if (ks >= ns) return false;
-    const int base = A ? grp * s.nsA : s.r * s.nsA + (grp - s.r) * s.nsB;
     *prob = 1;
     job = base + ks;
   }
   const Problem& pr = P.p[*prob];
   if (job >= pr.mblocks * pr.ksplit) return false;
   *mb = job % pr.mblocks;
+  if (pr.scatter) *mb = (*mb + pr.rot) % pr.mblocks;
   *kb0 = (job / pr.mblocks) * pr.nk;
   return true;
 }
@@ -279,6 +297,7 @@ static int fill_problem(g::Problem* p, const GemmDesc& d, int64_t Ng) {
       return MM25_ERR_SHAPE;
     p->scatter = 1;
     p->rows_per_rank = (int)d.rows_per_rank;
+    p->rot = (int)(((d.self_rank + 1) % d.npeers) * (d.rows_per_rank / g::BM));
     for (int i = 0; i < d.npeers; ++i) p->peer[i] = d.peers[i];
   }
   return MM25_OK;
@@ -353,6 +372,10 @@ int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float
   gemm_schedule((int64_t)P.p[0].mblocks * P.p[0].ksplit, P.p[0].nk,
                 (int64_t)P.p[1].mblocks * P.p[1].ksplit, P.p[1].nk, ngroups, &P.s.r, &P.s.nbA,
                 &P.s.nbB, &P.s.nsA, &P.s.nsB);
+  // A/B switch: walking the scatter problem first measured no better at 8 GPUs (0.871 vs
+  // 0.860 ms per step), so the default keeps problem 0 first
+  static const bool p1_first = getenv("MM25_GEMM_P1_FIRST") != nullptr;
+  P.s.p1_first = (P.p[1].mblocks > 0 && P.p[1].scatter && p1_first) ? 1 : 0;
   const size_t smem = sizeof(g::Smem) + 1024;
   MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_grouped_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -23,6 +23,10 @@ struct GemmDesc {
   float* const* peers;
   int npeers;
   int64_t rows_per_rank;
+  // scatter mode only: this rank's index.  The m-blocks are walked starting with the rows owned
+  // by rank self + 1 and ending with the local ones, so at any moment the P ranks add into P
+  // different owners (a ring order) instead of all hitting owner 0 first.
+  int self_rank;
 };
 constexpr int GEMM_MAX_PEERS = 16;
 

@@ -449,7 +449,9 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
         GemmDesc ga{G, b_b, da ? da + (bz * M + p0) * d : nullptr, d, rows, N, 0, 1, 0, 1.f,
                     nullptr, 0, 0};
         GemmDesc gb{G, a_b + p0 * d, db ? db + bz * N * d : nullptr, d, N, rows, 1, 1,
-                    p0 > 0 ? 1 : 0, 1.f, db_peers, npeers, db_peers ? N / npeers : 0};
+                    p0 > 0 ? 1 : 0, 1.f, db_peers, npeers, db_peers ? N / npeers : 0,
+                    // row-sharded layout: diag_offset = rank * M (loss.py:94-95)
+                    db_peers ? (int)((diag_offset / M) % npeers) : 0};
         const bool have_db = db != nullptr || db_peers != nullptr;
         static const bool split = getenv("MM25_GEMM_SPLIT") != nullptr;  // A/B switch
         if (split) {
