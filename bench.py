@@ -36,6 +36,8 @@ def parse_args():
     p.add_argument("--d", type=int, default=512)
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="eager launches instead of a CUDA graph")
+    p.add_argument("--serial-e2e", action="store_true",
+                   help="e2e without the double-buffered input pipeline (H2D, step, D2H in series)")
     p.add_argument("--slab-rows", type=int, default=1024, help="rows of the CPU sample slab")
     return p.parse_args()
 
@@ -297,10 +299,39 @@ def run_ours(args):
         loss = step(xi, yi)
         loss_host.copy_(loss.detach(), non_blocking=True)
 
+    def e2e_pipelined(k):
+        """k steps through GraphedLossStep's double-buffered input pipeline: the H2D of step
+        t+1 runs on a copy stream under step t.  ONE event pair brackets all k steps (every
+        H2D, L2 flush, replay and D2H is inside it); returns total ms."""
+        cur = torch.cuda.current_stream()
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        flush.zero_()
+        e0.record(cur)
+        graphed.prefetch(x_host, y_host, after=e0)
+        for t in range(k):
+            if t + 1 < k:
+                graphed.prefetch(x_host, y_host)
+            if t > 0:
+                flush.zero_()
+            loss, _, _, _ = graphed.run_prefetched()
+            loss_host.copy_(loss, non_blocking=True)
+        e1.record(cur)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1)
+
+    e2e_note = "serial: H2D -> step -> D2H per step"
     for _ in range(2):
         e2e_step()
     barrier()
-    ms_e2e = timed(e2e_step, args.steps)
+    if graphed is not None and not args.serial_e2e:
+        e2e_pipelined(2)
+        barrier()
+        ms_e2e = e2e_pipelined(args.steps)
+        e2e_note = ("double-buffered: H2D of step t+1 on a copy stream under step t "
+                    "(graphs.GraphedLossStep.prefetch); all copies inside the timed region")
+    else:
+        ms_e2e = timed(e2e_step, args.steps)
     barrier()
 
     coll_note = "none (single GPU)"
@@ -323,7 +354,7 @@ def run_ours(args):
                 ms_step=ms_step, value=value, e2e_value=e2e_value, launches=int(launches),
                 clocks=clocks, loss=loss_val, wall_ms=wall_ms, flush=flush, ops=ops,
                 h2d=int(x_host.numel() * 2 * 2), dist=dist, graph_note=graph_note,
-                coll_note=coll_note)
+                coll_note=coll_note, e2e_note=e2e_note)
 
 
 def kernel_roofline(r, args, peaks):
@@ -386,9 +417,19 @@ def kernel_roofline(r, args, peaks):
     tf_f, tf_b = fl_f / (ms_f * 1e-3) / 1e12, fl_b / (ms_b * 1e-3) / 1e12
     peak = peaks["bf16_tflops"]
     dom = ("sim_bwd", tf_b, ms_b, fl_b) if ms_b >= ms_f else ("sim_fwd", tf_f, ms_f, fl_f)
+    # DRAM bytes per launch of the dominant op from the committed ncu --set full capture
+    # (profiles/r1_v5_ncu_summary.md: dram read + write of each kernel; sim_bwd = 2 panels x
+    # (grad 0.252 + 1.022 GB, grouped GEMM 2.342 + 0.087 GB), sim_fwd 0.067 + 0.059 GB).  Only for
+    # the shape that capture was taken on.
+    traffic = None
+    if M == 32768 and N == 32768 and d == 512 and not keep:
+        traffic = {"sim_bwd": 2 * (0.252 + 1.022 + 2.342 + 0.087) * 1e9,
+                   "sim_fwd": (0.067 + 0.059) * 1e9}[dom[0]]
     return {
         "bound": "tensor", "kernel": dom[0], "achieved": dom[1], "peak": peak,
-        "unit": "TFLOP/s", "frac": dom[1] / peak, "traffic": None,
+        "unit": "TFLOP/s", "frac": dom[1] / peak, "traffic": traffic,
+        "traffic_source": "profiles/r1_v5_ncu_summary.md (ncu --set full, bytes per launch)"
+        if traffic else None,
         "peak_source": peaks["source"] + " bf16_tflops (burst: kernel timed alone)",
         "ms_per_launch": dom[2], "algorithmic_flops_per_launch": dom[3],
         "kernels": {"sim_fwd": {"ms": ms_f, "tflops": tf_f, "frac": tf_f / peak,
@@ -439,7 +480,8 @@ def main():
             "loss": r["loss"],
             "clocks": r["clocks"],
             "e2e": {"value": r["e2e_value"], "unit": "pairs/s",
-                    "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": 4},
+                    "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": 4,
+                    "pipeline": r["e2e_note"]},
             "gpu_launches": r["launches"],
             "roofline": roof,
         }

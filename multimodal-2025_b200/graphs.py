@@ -9,6 +9,15 @@ host at capture time, so the captured launches stay valid) and replays it with o
 
     step = GraphedLossStep(ClipLoss(0.1).cuda(), x, y, logit_scale)
     loss, dx, dy, dscale = step(x_new, y_new)      # copies into the static inputs, replays
+
+Host-resident batches (a pinned-memory loader) can be double-buffered so that the host->device
+copy of batch t+1 runs on a copy stream while batch t computes:
+
+    step.prefetch(x_host_0, y_host_0)
+    for t in range(T):
+        if t + 1 < T:
+            step.prefetch(x_host[t + 1], y_host[t + 1])   # overlaps with the replay below
+        loss, dx, dy, dscale = step.run_prefetched()
 """
 from __future__ import annotations
 
@@ -38,6 +47,51 @@ class GraphedLossStep:
             loss.backward()
             self.loss = loss.detach()
         torch.cuda.synchronize()
+
+    # ---- double-buffered host -> device input pipeline ---------------------------------------
+    def _ensure_pipeline(self):
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream()
+            self._stage = [(torch.empty_like(self.x), torch.empty_like(self.y)) for _ in range(2)]
+            self._ready = [torch.cuda.Event(), torch.cuda.Event()]
+            self._free = [None, None]
+            self._slot = 0
+            self._queue = []
+
+    def prefetch(self, x_host, y_host, after=None):
+        """Enqueue the H2D copy of the next batch (pinned host tensors) on the copy stream into
+        the idle staging slot; at most two batches may be in flight.  `after`: optional event the
+        copy must not start before (benchmarks: the start-of-timing event)."""
+        self._ensure_pipeline()
+        if len(self._queue) >= 2:
+            raise RuntimeError("prefetch: both staging slots are in flight; call run_prefetched()")
+        s, cs = self._slot, self._copy_stream
+        if after is not None:
+            cs.wait_event(after)
+        if self._free[s] is not None:      # the previous consumer of this slot has copied it out
+            cs.wait_event(self._free[s])
+        with torch.cuda.stream(cs), torch.no_grad():
+            self._stage[s][0].copy_(x_host, non_blocking=True)
+            self._stage[s][1].copy_(y_host, non_blocking=True)
+            self._ready[s].record(cs)
+        self._queue.append(s)
+        self._slot ^= 1
+
+    def run_prefetched(self):
+        """Replay on the oldest prefetched batch; returns what __call__ returns."""
+        if not getattr(self, "_queue", None):
+            raise RuntimeError("run_prefetched: nothing was prefetched")
+        s = self._queue.pop(0)
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self._ready[s])
+        with torch.no_grad():
+            self.x.copy_(self._stage[s][0], non_blocking=True)
+            self.y.copy_(self._stage[s][1], non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self._free[s] = ev
+        self.graph.replay()
+        return self.loss, self.x.grad, self.y.grad, self.scale.grad
 
     def _eager(self):
         self.x.grad = self.y.grad = self.scale.grad = None

@@ -166,3 +166,40 @@ def test_clip_fp32_inputs_bf16_compute(lib_built):
     ls_, (gxs, gys, gls) = run_ours(lambda a, b, c: m.forward_sampled(a, b, c), [xs, ys, lsc])
     assert rel_err(ls_, refs) < 2e-3
     assert rel_err(gxs, rxs) < 2e-2 and rel_err(gys, rys) < 2e-2
+
+
+def test_graphed_step_and_input_pipeline(lib_built):
+    """graphs.GraphedLossStep: replay equals the eager step on new inputs, and the double-buffered
+    host->device pipeline (prefetch / run_prefetched) returns the batches in order."""
+    from multimodal_2025_b200.graphs import GraphedLossStep
+    from multimodal_2025_b200.losses import ClipLoss
+    n, d = 512, 256
+    crit = ClipLoss(0.1).cuda()
+    batches = [O.synth_embeddings(n, d, 20 + i, correlated=True, dtype=torch.bfloat16)
+               for i in range(4)]
+    ls = torch.tensor(2.6592, device="cuda")
+    x0, y0 = batches[0]
+    step = GraphedLossStep(crit, x0.cuda(), y0.cuda(), ls)
+    eager = []
+    for x, y in batches:
+        xc, yc = x.cuda().requires_grad_(True), y.cuda().requires_grad_(True)
+        lc = ls.clone().requires_grad_(True)
+        loss = crit(xc, yc, lc)
+        loss.backward()
+        eager.append((loss.detach().clone(), xc.grad.clone(), yc.grad.clone(), lc.grad.clone()))
+    for (x, y), ref in zip(batches, eager):          # plain replay
+        got = step(x.cuda(), y.cuda())
+        torch.cuda.synchronize()
+        for g, r in zip(got, ref):
+            assert torch.equal(g, r)
+    host = [(x.pin_memory(), y.pin_memory()) for x, y in batches]
+    step.prefetch(*host[0])
+    for t, ref in enumerate(eager):                  # pipelined replay
+        if t + 1 < len(host):
+            step.prefetch(*host[t + 1])
+        got = [g.clone() for g in step.run_prefetched()]
+        torch.cuda.synchronize()
+        for g, r in zip(got, ref):
+            assert torch.equal(g, r)
+    with pytest.raises(RuntimeError):
+        step.run_prefetched()
