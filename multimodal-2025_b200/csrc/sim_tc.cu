@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(1024) fwd_tc_merge_kernel(
     }
     __syncthreads();
   }
-  if (col_max) {
+  if (col_max && !fast_static) {  // the static-shift case runs fwd_tc_colsum_static_kernel
     float m = -INFINITY, l = 0.f;
     if (t < N)
       for (int p = ty; p < nrb; p += 32)
@@ -298,6 +298,50 @@ __global__ void __launch_bounds__(1024) fwd_tc_merge_kernel(
       col_max[(int64_t)bz * N + t] = m * LN2;
       col_sum[(int64_t)bz * N + t] = l;
     }
+  }
+}
+
+// Column sums of the static-shift path: the partials are plain sums under the common maximum
+// m2s, so they are added with independent 16-byte loads (512 B contiguous per warp and partial
+// row) in a fixed order.  Returns at once on the other paths (same predicate as the forward).
+__global__ void __launch_bounds__(1024) fwd_tc_colsum_static_kernel(
+    const float* __restrict__ col_pl, int nrb, int64_t N, float* __restrict__ col_max,
+    float* __restrict__ col_sum, const float* __restrict__ scale, int scale_kind,
+    float clamp_max, float dot_bound, int force_slow) {
+  const float m2s = dot_bound * fabsf(load_scale(scale, scale_kind, clamp_max) * LOG2E);
+  const bool fast_static = !(force_slow & 1) && !(force_slow & 4) && dot_bound > 0.f &&
+                           2.f * m2s <= SPREAD_LIMIT;
+  if (!fast_static) return;
+  __shared__ float4 sm[32][33];
+  const int bz = blockIdx.y;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t c4 = (int64_t)blockIdx.x * 32 + tx, n4 = N >> 2;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (c4 < n4) {
+    const float4* src = reinterpret_cast<const float4*>(col_pl + (int64_t)bz * nrb * N) + c4;
+    int p = ty;
+    for (; p + 96 < nrb; p += 128) {
+      const float4 v0 = src[(int64_t)p * n4], v1 = src[(int64_t)(p + 32) * n4];
+      const float4 v2 = src[(int64_t)(p + 64) * n4], v3 = src[(int64_t)(p + 96) * n4];
+      acc.x += (v0.x + v1.x) + (v2.x + v3.x); acc.y += (v0.y + v1.y) + (v2.y + v3.y);
+      acc.z += (v0.z + v1.z) + (v2.z + v3.z); acc.w += (v0.w + v1.w) + (v2.w + v3.w);
+    }
+    for (; p < nrb; p += 32) {
+      const float4 v = src[(int64_t)p * n4];
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+  }
+  sm[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && c4 < n4) {
+    float4 t = sm[0][tx];
+    for (int k = 1; k < 32; ++k) {
+      const float4 v = sm[k][tx];
+      t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+    }
+    const float m = m2s * LN2;
+    reinterpret_cast<float4*>(col_max + (int64_t)bz * N)[c4] = make_float4(m, m, m, m);
+    reinterpret_cast<float4*>(col_sum + (int64_t)bz * N)[c4] = t;
   }
 }
 
@@ -429,6 +473,11 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
       row_pm, row_pl, g.nseg * 2, M, row_lse, col_pm, col_pl, g.nrb, N, col_max, col_sum, scale,
       scale_kind, clamp_max, dot_bound, flags);
   MM25_LAUNCH_CHECK();
+  if (col_max && dot_bound > 0.f) {
+    fwd_tc_colsum_static_kernel<<<dim3((unsigned)ceil_div(N, 128), (unsigned)B), 1024, 0, st>>>(
+        col_pl, g.nrb, N, col_max, col_sum, scale, scale_kind, clamp_max, dot_bound, flags);
+    MM25_LAUNCH_CHECK();
+  }
   return MM25_OK;
 }
 
