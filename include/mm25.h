@@ -266,7 +266,7 @@ int mm25_hopfield_bwd_pass(const float* a, const float* b, const float* a2, cons
  * vCLIP sampling path (losses/vclipLoss.py:98-121, losses/distributions/*.py, power_spherical).
  * All tensors fp32.  Sample layout is sample-major [S, B, d] as the reference returns
  * (VonMisesFisher.py:238-239).  Noise: pass the draws the reference would make (parity mode)
- * or NULL to generate them in-kernel with Philox4x32-10 keyed by `seed` (the backward
+ * or NULL to generate them in-kernel with Philox4x32-7 keyed by `seed` (the backward
  * regenerates the same noise from the same seed).
  * ------------------------------------------------------------------------------------------ */
 /* ProjectedNormal.rsample (ProjectedNormal.py:41-49): out = (mu + sigma*eps)/||.||;

@@ -7,7 +7,7 @@
 // Rows are processed in groups of 4 consecutive elements per lane: 16-byte loads / stores when
 // d % 4 == 0, scalar otherwise.  Noise is either injected by the caller (parity mode: the
 // deterministic transform is compared with the reference given identical draws) or generated
-// in-kernel with Philox4x32-10 keyed by (seed, row, element) and regenerated in the backward.
+// in-kernel with Philox4x32-7 keyed by (seed, row, element) and regenerated in the backward.
 #include "common.cuh"
 #include "philox.cuh"
 
