@@ -130,29 +130,46 @@ projnormal_bwd_kernel(const float* __restrict__ gout, const float* __restrict__ 
   float* as = am + dpad;
   for (int k = lane; k < dpad; k += 32) { am[k] = 0.f; as[k] = 0.f; }
   __syncwarp();
-  for (int64_t s = 0; s < S; ++s) {
-    const int64_t row = s * B + b;
-    const float* gr = gout + row * d;
-    const float* yr = y + row * d;
-    float dot = 0.f;
+  // two samples per iteration: twice the bytes in flight per warp (the loop is latency-bound:
+  // each sample needs a warp reduction between its two passes)
+  for (int64_t s = 0; s < S; s += 2) {
+    const bool two = s + 1 < S;
+    const int64_t row0 = s * B + b, row1 = two ? row0 + B : row0;
+    const float* g0 = gout + row0 * d;
+    const float* y0 = y + row0 * d;
+    const float* g1 = gout + row1 * d;
+    const float* y1 = y + row1 * d;
+    float dot0 = 0.f, dot1 = 0.f;
     for (int g = lane; g < ngroups; g += 32) {
-      const F4 gg = load4(gr, g * 4, d, vec), yy = load4(yr, g * 4, d, vec);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) dot = fmaf(gg.v[i], yy.v[i], dot);
-    }
-    dot = warp_sum(dot);
-    const float inv = inv_norm[row];
-    for (int g = lane; g < ngroups; g += 32) {
-      const int k0 = g * 4;
-      const F4 gg = load4(gr, k0, d, vec), yy = load4(yr, k0, d, vec);
-      F4 e;
-      if (eps_in) e = load4(eps_in + row * d, k0, d, vec);
-      else rng::normal4(seed, (uint64_t)row * 0x100000ull + (uint64_t)g, STREAM_PN, e.v);
+      const F4 ga = load4(g0, g * 4, d, vec), ya = load4(y0, g * 4, d, vec);
+      const F4 gb = load4(g1, g * 4, d, vec), yb = load4(y1, g * 4, d, vec);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const float dv = (gg.v[i] - yy.v[i] * dot) * inv;
-        am[k0 + i] += dv;
-        as[k0 + i] = fmaf(dv, e.v[i], as[k0 + i]);
+        dot0 = fmaf(ga.v[i], ya.v[i], dot0);
+        dot1 = fmaf(gb.v[i], yb.v[i], dot1);
+      }
+    }
+    dot0 = warp_sum(dot0);
+    dot1 = warp_sum(dot1);
+    const float inv0 = inv_norm[row0], inv1 = two ? inv_norm[row1] : 0.f;
+    for (int g = lane; g < ngroups; g += 32) {
+      const int k0 = g * 4;
+      const F4 ga = load4(g0, k0, d, vec), ya = load4(y0, k0, d, vec);
+      const F4 gb = load4(g1, k0, d, vec), yb = load4(y1, k0, d, vec);
+      F4 e0, e1;
+      if (eps_in) {
+        e0 = load4(eps_in + row0 * d, k0, d, vec);
+        e1 = load4(eps_in + row1 * d, k0, d, vec);
+      } else {
+        rng::normal4(seed, (uint64_t)row0 * 0x100000ull + (uint64_t)g, STREAM_PN, e0.v);
+        rng::normal4(seed, (uint64_t)row1 * 0x100000ull + (uint64_t)g, STREAM_PN, e1.v);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float dv0 = (ga.v[i] - ya.v[i] * dot0) * inv0;
+        const float dv1 = (gb.v[i] - yb.v[i] * dot1) * inv1;   // inv1 = 0 on the odd tail
+        am[k0 + i] += dv0 + dv1;
+        as[k0 + i] = fmaf(dv1, e1.v[i], fmaf(dv0, e0.v[i], as[k0 + i]));
       }
     }
   }
@@ -296,46 +313,66 @@ sphere_bwd_kernel(const float* __restrict__ gout, const float* __restrict__ y,
   const float iden = 1.f / den;
   const float uu = (nw * iden) * (nw * iden);
   __syncwarp();
-  for (int64_t s = 0; s < S; ++s) {
-    const int64_t row = s * B + b;
-    const float* gr = gout + row * d;
-    const float* yr = y + row * d;
-    float yu = 0.f, gu = 0.f;
+  // two samples per iteration (latency-bound loop: two warp reductions per sample)
+  for (int64_t s = 0; s < S; s += 2) {
+    const bool two = s + 1 < S;
+    const int64_t row0 = s * B + b, row1 = two ? row0 + B : row0;
+    const float* g0 = gout + row0 * d;
+    const float* y0 = y + row0 * d;
+    const float* g1 = gout + row1 * d;
+    const float* y1 = y + row1 * d;
+    float yu0 = 0.f, gu0 = 0.f, yu1 = 0.f, gu1 = 0.f;
     for (int g = lane; g < ngroups; g += 32) {
       const int k0 = g * 4;
-      const F4 gg = load4(gr, k0, d, vec), yy = load4(yr, k0, d, vec), m = load4(mr, k0, d, vec);
+      const F4 ga = load4(g0, k0, d, vec), ya = load4(y0, k0, d, vec);
+      const F4 gb = load4(g1, k0, d, vec), yb = load4(y1, k0, d, vec);
+      const F4 m = load4(mr, k0, d, vec);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const float u = ((k0 + i == 0) ? w0 : -m.v[i]) * iden;
-        yu = fmaf(yy.v[i], u, yu);
-        gu = fmaf(gg.v[i], u, gu);
+        yu0 = fmaf(ya.v[i], u, yu0); gu0 = fmaf(ga.v[i], u, gu0);
+        yu1 = fmaf(yb.v[i], u, yu1); gu1 = fmaf(gb.v[i], u, gu1);
       }
     }
-    yu = warp_sum(yu); gu = warp_sum(gu);
-    const float xu = yu * (1.f - 2.f * uu);
-    float sgx = 0.f, gx0 = 0.f;
+    yu0 = warp_sum(yu0); gu0 = warp_sum(gu0);
+    yu1 = warp_sum(yu1); gu1 = warp_sum(gu1);
+    const float keep1 = two ? 1.f : 0.f;  // the odd tail contributes nothing to A
+    const float xu0 = yu0 * (1.f - 2.f * uu), xu1 = yu1 * (1.f - 2.f * uu);
+    float sgx0 = 0.f, gx00 = 0.f, sgx1 = 0.f, gx01 = 0.f;
     for (int g = lane; g < ngroups; g += 32) {
       const int k0 = g * 4;
-      const F4 gg = load4(gr, k0, d, vec), yy = load4(yr, k0, d, vec), m = load4(mr, k0, d, vec);
+      const F4 ga = load4(g0, k0, d, vec), ya = load4(y0, k0, d, vec);
+      const F4 gb = load4(g1, k0, d, vec), yb = load4(y1, k0, d, vec);
+      const F4 m = load4(mr, k0, d, vec);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int k = k0 + i;
         if (k < d) {
           const float u = ((k == 0) ? w0 : -m.v[i]) * iden;
-          const float x = fmaf(-2.f * yu, u, yy.v[i]);
-          const float gx = fmaf(-2.f * gu, u, gg.v[i]);
-          A[k] += -2.f * (xu * gg.v[i] + gu * x);
-          if (k == 0) gx0 = gx; else sgx = fmaf(gx, x, sgx);
+          const float xa = fmaf(-2.f * yu0, u, ya.v[i]);
+          const float gxa = fmaf(-2.f * gu0, u, ga.v[i]);
+          const float xb = fmaf(-2.f * yu1, u, yb.v[i]);
+          const float gxb = fmaf(-2.f * gu1, u, gb.v[i]);
+          A[k] += -2.f * (xu0 * ga.v[i] + gu0 * xa) - 2.f * keep1 * (xu1 * gb.v[i] + gu1 * xb);
+          if (k == 0) { gx00 = gxa; gx01 = gxb; }
+          else { sgx0 = fmaf(gxa, xa, sgx0); sgx1 = fmaf(gxb, xb, sgx1); }
         }
       }
     }
-    sgx = warp_sum(sgx);
-    gx0 = __shfl_sync(0xffffffffu, gx0, 0);
+    sgx0 = warp_sum(sgx0); sgx1 = warp_sum(sgx1);
+    gx00 = __shfl_sync(0xffffffffu, gx00, 0);
+    gx01 = __shfl_sync(0xffffffffu, gx01, 0);
     if (lane == 0 && dt) {
-      const float t = t_in[row];
-      const float omt2 = 1.f - t * t;
-      const bool clamped = cfg.omt2_min >= 0.f && !(omt2 > cfg.omt2_min);
-      dt[row] = clamped ? gx0 : gx0 - t / omt2 * sgx;
+      const float t0 = t_in[row0];
+      const float o0 = 1.f - t0 * t0;
+      const bool c0 = cfg.omt2_min >= 0.f && !(o0 > cfg.omt2_min);
+      dt[row0] = c0 ? gx00 : gx00 - t0 / o0 * sgx0;
+      if (two) {
+        const float t1 = t_in[row1];
+        const float o1 = 1.f - t1 * t1;
+        const bool c1 = cfg.omt2_min >= 0.f && !(o1 > cfg.omt2_min);
+        dt[row1] = c1 ? gx01 : gx01 - t1 / o1 * sgx1;
+      }
     }
   }
   __syncwarp();
