@@ -111,3 +111,55 @@ class GraphedLossStep:
                 self.scale.copy_(logit_scale, non_blocking=True)
         self.graph.replay()
         return self.loss, self.x.grad, self.y.grad, self.scale.grad
+
+
+class GraphedStep:
+    """CUDA-graph capture of `loss = fn(*inputs); loss.backward()` for any of the loss modules
+    whose forward takes only tensors (CLOOBLoss, ClipInModalityLoss with semantic features, ...).
+    Losses that draw fresh noise per call (VClipLoss: the Philox seed is a host value) must not be
+    captured — the replay would reuse the captured seed.
+
+        step = GraphedStep(lambda a, b: crit(a, b), [img, txt])
+        loss, (dimg, dtxt) = step(img_new, txt_new)
+
+    Inputs with `requires_grad=False` are treated as constants-with-storage (copied into, no grad).
+    """
+
+    def __init__(self, fn, inputs, warmup: int = 3):
+        if not all(t.is_cuda for t in inputs):
+            raise RuntimeError("GraphedStep needs CUDA tensors (no CPU fallback)")
+        self.fn = fn
+        self.inputs = [t.detach().clone().requires_grad_(t.requires_grad) for t in inputs]
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._eager()
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        for t in self.inputs:
+            t.grad = None
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            loss = fn(*self.inputs)
+            loss.backward()
+            self.loss = loss.detach()
+        torch.cuda.synchronize()
+
+    def _eager(self):
+        for t in self.inputs:
+            t.grad = None
+        loss = self.fn(*self.inputs)
+        loss.backward()
+        return loss
+
+    def __call__(self, *new_inputs):
+        """Replay on new inputs (None / omitted = keep).  Returns (loss, [grad or None, ...]) —
+        static tensors overwritten by the next call."""
+        with torch.no_grad():
+            for dst, src in zip(self.inputs, new_inputs):
+                if src is not None:
+                    dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        return self.loss, [t.grad for t in self.inputs]

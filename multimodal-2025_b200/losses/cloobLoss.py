@@ -15,7 +15,8 @@ from .. import ops
 
 
 def _scalar(v, dev):
-    return torch.tensor([float(v)], dtype=torch.float32, device=dev)
+    # a fill kernel, not a host->device copy: stays legal under CUDA-graph capture
+    return torch.full((1,), float(v), dtype=torch.float32, device=dev)
 
 
 def _tc_operands(x, y):

@@ -102,3 +102,23 @@ def test_hopfield_tc_pieces_vs_dense(lib_built, M, N, d):
     dq, dk = ops.hopfield_bwd_tc(q, k, d_o, sc, lse[0], delta, True, True)
     assert rel_err(dq.cpu(), qf.grad.cpu()) < 2e-2
     assert rel_err(dk.cpu(), kf.grad.cpu()) < 2e-2
+
+
+def test_cloob_graphed_step_matches_eager(lib_built):
+    """graphs.GraphedStep (generic capture of loss + backward) on the bf16 CLOOB path."""
+    from multimodal_2025_b200.graphs import GraphedStep
+    from multimodal_2025_b200.losses import CLOOBLoss
+    crit = CLOOBLoss(30.0, 15.0, "cuda")
+    xs = [O.synth_embeddings(512, 256, 30 + i, correlated=True, dtype=torch.bfloat16)
+          for i in range(3)]
+    x0, y0 = xs[0]
+    step = GraphedStep(lambda a, b: crit(a, b), [x0.cuda().requires_grad_(True),
+                                                 y0.cuda().requires_grad_(True)])
+    for x, y in xs:
+        xc, yc = x.cuda().requires_grad_(True), y.cuda().requires_grad_(True)
+        ref = crit(xc, yc)
+        ref.backward()
+        loss, (gx, gy) = step(x.cuda(), y.cuda())
+        torch.cuda.synchronize()
+        assert torch.equal(loss, ref.detach())
+        assert torch.equal(gx, xc.grad) and torch.equal(gy, yc.grad)

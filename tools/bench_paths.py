@@ -150,6 +150,14 @@ def main():
          note="cfg3 N=4096 d=512 bf16: Hopfield retrievals + InfoLOOB on the tcgen05 kernels "
               "(P-panel GEMM forward, dual-accumulator sweep backward, MASKDIAG)")
 
+    from multimodal_2025_b200.graphs import GraphedStep  # noqa: E402
+    gs = GraphedStep(lambda a_, b_: crit(a_, b_), [xb.clone().requires_grad_(True),
+                                                    yb.clone().requires_grad_(True)])
+    ms = timeit(lambda: gs(xb, yb), reps=5, warm=2)
+    emit(path="CLOOBLoss fwd+bwd (CUDA-graph replay)", ms=ms, pairs_per_s=n / (ms * 1e-3),
+         tflops_algorithmic=60.0 * n * n * d / (ms * 1e-3) / 1e12,
+         note="cfg3 N=4096 d=512 bf16, graphs.GraphedStep")
+
     # ---- AlignCLIP semantic (reduced N: fp32 SIMT MODULATED kernels) ---------------------------
     n, da_, dsem = 8192, 1024, 768
     xi = torch.nn.functional.normalize(torch.randn(n, da_, generator=g), dim=-1).to(dev)
@@ -167,6 +175,15 @@ def main():
          note="N=8192 d=1024 d_sem=768 bf16 (cfg5 is N=65536 over 8 GPUs); cross-modal term on "
               "the PLAIN tcgen05 kernels, in-modality MODULATED term on the two-accumulator "
               "tcgen05 kernels (csrc/sim_tc_mod.cu)")
+
+    xa, xtb = xi.bfloat16(), xt.bfloat16()
+    gs = GraphedStep(lambda a_, b_: crit(a_, b_, sc, semantic_features=sem),
+                     [xa.clone().requires_grad_(True), xtb.clone().requires_grad_(True)])
+    ms = timeit(lambda: gs(xa, xtb), reps=5, warm=2)
+    emit(path="ClipInModalityLoss(semantic) fwd+bwd (CUDA-graph replay)", ms=ms,
+         pairs_per_s=n / (ms * 1e-3),
+         tflops_algorithmic=n * n * (12.0 * da_ + 2 * dsem) / (ms * 1e-3) / 1e12,
+         note="N=8192 d=1024 d_sem=768 bf16, graphs.GraphedStep")
 
     # ---- top-k ---------------------------------------------------------------------------------
     Q, Nt, k = 1024, 65536, 100
