@@ -55,6 +55,8 @@ struct Problem {
   int scatter;
   int rows_per_rank;
   int rot;         // scatter: m-block rotation (ring order over the owners, see GemmDesc)
+  int mb_per_batch;     // batched: m-blocks per batch entry (0 = not batched)
+  int a_k_rows, b_k_rows;  // batched: K-coordinate shift per entry of A (MN-major) and B
   float* peer[GEMM_MAX_PEERS];
 };
 
@@ -148,7 +150,10 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
       int prob, mb, kb0;
       for (int k = 0; job_at(P, grp, k, &prob, &mb, &kb0); ++k) {
         const Problem& pr = P.p[prob];
-        const int m0 = mb * BM;
+        const int bz = pr.mb_per_batch ? mb / pr.mb_per_batch : 0;
+        // MN-major A of a batched problem: M coordinate local to the entry, K shifted
+        const int m0 = ((pr.mb_per_batch && pr.a_mn) ? mb % pr.mb_per_batch : mb) * BM;
+        const int ka_off = pr.a_mn ? bz * pr.a_k_rows : 0, kb_off = bz * pr.b_k_rows;
         for (int kb = 0; kb < pr.nk; ++kb) {
           const int k0 = (kb0 + kb) * BK;
           mbar_wait(&sm.empty[st], ph ^ 1);
@@ -156,16 +161,16 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
           if (pr.a_mn) {
 #pragma unroll
             for (int at = 0; at < BM / 64; ++at)
-              tma_load_2d(sm.a[st] + at * 8192, &pr.ta, &sm.full[st], m0 + at * 64, k0);
+              tma_load_2d(sm.a[st] + at * 8192, &pr.ta, &sm.full[st], m0 + at * 64, k0 + ka_off);
           } else {
             tma_load_2d(sm.a[st], &pr.ta, &sm.full[st], k0, m0);
           }
           if (pr.b_mn) {
 #pragma unroll
             for (int at = 0; at < BN / 64; ++at)
-              tma_load_2d(sm.b[st] + at * 8192, &pr.tb, &sm.full[st], n0 + at * 64, k0);
+              tma_load_2d(sm.b[st] + at * 8192, &pr.tb, &sm.full[st], n0 + at * 64, k0 + kb_off);
           } else {
-            tma_load_2d(sm.b[st], &pr.tb, &sm.full[st], k0, n0);
+            tma_load_2d(sm.b[st], &pr.tb, &sm.full[st], k0 + kb_off, n0);
           }
           if (++st == NST) { st = 0; ph ^= 1; }
         }
@@ -275,16 +280,21 @@ bool gemm_eligible(int64_t Mg, int64_t Ng, int64_t K) {
 
 static int fill_problem(g::Problem* p, const GemmDesc& d, int64_t Ng) {
   int rc;
-  if (d.a_mn) rc = make_tmap_bf16(&p->ta, d.A, (uint64_t)d.K, (uint64_t)d.Mg, 64, 64);
-  else rc = make_tmap_bf16(&p->ta, d.A, (uint64_t)d.Mg, (uint64_t)d.K, g::BM, 64);
+  const int64_t nb = d.batch > 1 ? d.batch : 1;
+  if (nb > 1 && (!d.b_mn || d.peers)) return MM25_ERR_SHAPE;
+  if (nb * d.Mg >= (1ll << 31) || nb * d.K >= (1ll << 31)) return MM25_ERR_SHAPE;
+  if (d.a_mn) rc = make_tmap_bf16(&p->ta, d.A, (uint64_t)(nb * d.K), (uint64_t)d.Mg, 64, 64);
+  else rc = make_tmap_bf16(&p->ta, d.A, (uint64_t)(nb * d.Mg), (uint64_t)d.K, g::BM, 64);
   if (rc) return rc;
-  if (d.b_mn) rc = make_tmap_bf16(&p->tb, d.B, (uint64_t)d.K, (uint64_t)Ng, 64, 64);
+  if (d.b_mn) rc = make_tmap_bf16(&p->tb, d.B, (uint64_t)(nb * d.K), (uint64_t)Ng, 64, 64);
   else rc = make_tmap_bf16(&p->tb, d.B, (uint64_t)Ng, (uint64_t)d.K, g::BN, 64);
   if (rc) return rc;
   p->C = d.C;
   p->ldc = d.ldc;
   p->nk = (int)(d.K / g::BK);
-  p->mblocks = (int)(d.Mg / g::BM);
+  p->mblocks = (int)(nb * d.Mg / g::BM);
+  p->mb_per_batch = nb > 1 ? (int)(d.Mg / g::BM) : 0;
+  p->a_k_rows = p->b_k_rows = nb > 1 ? (int)d.K : 0;
   p->ksplit = 1;
   p->a_mn = d.a_mn;
   p->b_mn = d.b_mn;
@@ -366,7 +376,8 @@ int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float
       P.p[0].nk /= ks;
       if (!P.p[0].accumulate)
         MM25_CUDA_CHECK(cudaMemsetAsync(P.p[0].C, 0,
-                                        sizeof(float) * (size_t)d0->Mg * (size_t)P.p[0].ldc, st));
+                                        sizeof(float) * (size_t)P.p[0].mblocks * g::BM *
+                                            (size_t)P.p[0].ldc, st));
     }
   }
   gemm_schedule((int64_t)P.p[0].mblocks * P.p[0].ksplit, P.p[0].nk,

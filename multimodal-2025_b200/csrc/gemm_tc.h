@@ -27,6 +27,11 @@ struct GemmDesc {
   // by rank self + 1 and ending with the local ones, so at any moment the P ranks add into P
   // different owners (a ring order) instead of all hitting owner 0 first.
   int self_rank;
+  // batched problems (B entries of identical shape stacked along the rows of every operand and
+  // of C): the m-blocks run over batch * Mg / 128 (Mg, K = sizes of ONE entry).  For entry z the
+  // K coordinate of an MN-major operand (its rows are K) is shifted by z * K, and the M coordinate
+  // of an MN-major A stays local to the entry.  Needs b_mn = 1.  batch <= 1: plain problem.
+  int batch;
 };
 constexpr int GEMM_MAX_PEERS = 16;
 

@@ -28,10 +28,11 @@ grad_col_coef_kernel(const float* __restrict__ col_lse, int64_t N, const float* 
                      float dot_bound, float* __restrict__ Cc) {
   const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (j >= N) return;
+  const int64_t bz = blockIdx.y;  // batch entry (grid.y = 1 for a single problem)
   const float s = load_scale(scale, scale_kind, clamp_max);
   const float m2 = dot_bound * fabsf(s) * LOG2E;
-  const float go = gout ? __ldg(gout) : 1.f;
-  Cc[j] = go * s * w_col * exp2f(m2 - col_lse[j] * LOG2E);
+  const float go = gout ? __ldg(gout + bz) : 1.f;
+  Cc[bz * N + j] = go * s * w_col * exp2f(m2 - col_lse[bz * N + j] * LOG2E);
 }
 
 // Epilogue paths:
@@ -74,11 +75,12 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int half = ew >> 2;
     const float s = load_scale(scale, scale_kind, clamp_max);
     const float c2 = s * LOG2E;
-    const float go = gout ? __ldg(gout) : 1.f;
-    const float gs = go * s;
     const float m2 = dot_bound * fabsf(c2);
     const bool fast = Cc != nullptr && dot_bound > 0.f && 2.f * m2 <= SPREAD_LIMIT;
-    const float k_all = gs * w_all, k_diag = gs * w_diag;
+    // per batch entry (a launch may cover several: row blocks are numbered over [B * M / 128)
+    // and every per-row / per-column array is indexed with the batch offset)
+    float go = 1.f, gs = s, k_all = s * w_all, k_diag = s * w_diag;
+    const int nrb_b = (int)(M / BM);
     const float vmask = s != 0.f ? -10000.f / s : 0.f;  // MASKDIAG: z_ii = -10000 in the LSE
     const bool use_col = w_col != 0.f;  // row-only losses pass a placeholder col_lse
     // per-column operand of the epilogue: C_j (static shift) or c_j (general), staged per warp
@@ -92,15 +94,19 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     float ds = 0.f;  // fast: sum G' v (= gout s sum G v); general: sum G v
     uint32_t as = 0, accph = 0;
     for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-      const int rb = first_rb + item / nseg, seg = item % nseg;
-      const int64_t row = (int64_t)rb * BM + q * 32 + lane;
+      const int rbg = first_rb + item / nseg, seg = item % nseg;
+      const int bz = rbg / nrb_b, rb = rbg % nrb_b;
+      go = gout ? __ldg(gout + bz) : 1.f;
+      gs = go * s; k_all = gs * w_all; k_diag = gs * w_diag;
+      const float* colb = colv + (int64_t)bz * N;
+      const int64_t row = (int64_t)rb * BM + q * 32 + lane;   // row inside its batch entry
       const int64_t dcol = row + diag_offset;
-      const float r2 = __ldg(row_lse + row) * LOG2E;
+      const float r2 = __ldg(row_lse + (int64_t)bz * M + row) * LOG2E;
       const float Ri = gs * w_row * exp2f(m2 - r2);
-      const int32_t grow0 = (int32_t)((int64_t)(rb - first_rb) * BM + q * 32);  // panel row
+      const int32_t grow0 = (int32_t)((int64_t)(rbg - first_rb) * BM + q * 32);  // panel row
       const int t0 = seg * tps, t1 = min(w.ntiles, t0 + tps);
       float4 cnext = __ldg(reinterpret_cast<const float4*>(
-          colv + (int64_t)t0 * BN + half * (BN / 2) + lane * 4));
+          colb + (int64_t)t0 * BN + half * (BN / 2) + lane * 4));
       for (int t = t0; t < t1; ++t) {
         const int64_t col0 = (int64_t)t * BN;
         // stage this tile's column operands (all lanes are past the previous tile's reads)
@@ -109,7 +115,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         __syncwarp();
         if (t + 1 < t1)
           cnext = __ldg(reinterpret_cast<const float4*>(
-              colv + (int64_t)(t + 1) * BN + half * (BN / 2) + lane * 4));
+              colb + (int64_t)(t + 1) * BN + half * (BN / 2) + lane * 4));
         mbar_wait(&sm.acc_full[as], accph);
         tc_fence_after();
         const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + as * BN +
@@ -130,7 +136,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll
             for (int j = 0; j < 32; ++j)
               if (j == rel) { vo = __uint_as_float(r[j]); r[j] = __float_as_uint(vmask); }
-            ds = fmaf(fast ? -(k_all + k_diag) : -(w_all + w_diag), vo - vmask, ds);
+            ds = fmaf(fast ? -(k_all + k_diag) : -(w_all + w_diag) * go, vo - vmask, ds);
           }
           if (fast) {
 #pragma unroll
@@ -168,7 +174,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 if (use_col) gg += w_col * ex2_approx(fmaf(-cj[u], LOG2E, zl));
                 gg -= w_all;
                 gg -= (j == rel) ? w_diag : 0.f;
-                ds = fmaf(gg, vj, ds);
+                ds = fmaf(gg * go, vj, ds);
                 gq[u] = gg * gs;
               }
               __nv_bfloat162 lo = __floats2bfloat162_rn(gq[0], gq[1]);
@@ -219,7 +225,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     if (lane == 0) tma_store_wait_all<0>();
     // d(loss)/d(scale) partial of this CTA: gout * sum G.z/s = gout * sum G.v
-    ds = warp_sum(ds) * (fast ? (s != 0.f ? 1.f / s : 0.f) : go);
+    ds = warp_sum(ds) * (fast ? (s != 0.f ? 1.f / s : 0.f) : 1.f);
     if (lane == 0) sm.red[ew] = ds;
     named_bar_sync(1, 32 * NEPI);
     if (warp == 2 && lane == 0 && dscale_part) {
@@ -329,7 +335,12 @@ dscale_from_grad_kernel(const __nv_bfloat16* __restrict__ x, const float* __rest
 
 // ------------------------------------------------------------------------------------------
 static size_t g_workspace_cap = (size_t)1 << 30;   // bytes of the bf16 G panel
-void set_g_cap(size_t bytes) { g_workspace_cap = bytes ? bytes : ((size_t)1 << 30); }
+static size_t g_batched_cap = (size_t)6 << 30;   // bytes of all B panels of a batched launch
+// test hook: a small cap forces the multi-panel (and per-entry) code paths
+void set_g_cap(size_t bytes) {
+  g_workspace_cap = bytes ? bytes : ((size_t)1 << 30);
+  g_batched_cap = bytes ? bytes : ((size_t)6 << 30);
+}
 
 bool eligible_bwd(int64_t B, int64_t M, int64_t N, int64_t d, int dtype, int mode) {
   return eligible_fwd(B, M, N, d, dtype, mode) && d % 256 == 0 && gemm_eligible(M >= 128 ? 128 : M, d, N);
@@ -342,9 +353,19 @@ static int64_t panel_rows(int64_t M, int64_t N) {
   return r;
 }
 
+// B > 1 (forward_sampled: S sample slices): when all B panels fit, ONE gradient-panel launch and
+// ONE batched grouped GEMM cover every entry instead of 2 B launches of quarter-filled waves
+static bool batched_fits(int64_t B, int64_t M, int64_t N) {
+  return B > 1 && (size_t)B * (size_t)M * (size_t)N * 2 <= g_batched_cap &&
+         B * M < (1ll << 31) && B * N < (1ll << 31);
+}
+
 size_t bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, bool with_e) {
   // bf16 G panel (not needed when the forward kept E: G' is formed in place there) + the [N]
   // column factors of the static-shift epilogue
+  if (!with_e && batched_fits(B, M, N))
+    return (((size_t)B * M * N * 2 + 255) & ~(size_t)255) + 256 + (size_t)B * N * sizeof(float) +
+           256;
   const size_t panel = with_e ? 0 : (size_t)panel_rows(M, N) * (size_t)N * 2;
   return panel + 256 + (size_t)N * sizeof(float) + 256;
 }
@@ -371,6 +392,54 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   const bool use_e = e_buf && dot_bound > 0.f && (!dscale_part || da || (db && !db_peers));
   if (ws_bytes < bwd_workspace_bytes(B, M, N, d, use_e)) return MM25_ERR_WORKSPACE;
   const uintptr_t ws0 = (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255);
+  if (!use_e && !db_peers && batched_fits(B, M, N)) {
+    __nv_bfloat16* G = reinterpret_cast<__nv_bfloat16*>(ws0);
+    float* cbuf = reinterpret_cast<float*>(
+        (ws0 + (size_t)B * M * N * 2 + 255) & ~uintptr_t(255));
+    float* Cc = dot_bound > 0.f ? cbuf : nullptr;
+    const int sms = tc_sm_count();
+    const size_t smem = sizeof(GradSmem) + 1024;
+    MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_grad_tc_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (!col_lse) MM25_CUDA_CHECK(cudaMemsetAsync(cbuf, 0, sizeof(float) * B * N, st));
+    if (Cc && col_lse) {
+      grad_col_coef_kernel<<<dim3((unsigned)ceil_div(N, 256), (unsigned)B), 256, 0, st>>>(
+          col_lse, N, scale, scale_kind, clamp_max, gout, w_col, dot_bound, Cc);
+      MM25_LAUNCH_CHECK();
+    }
+    CUtensorMap ta, tb, tg;
+    int rc = make_tmap_bf16(&ta, a, (uint64_t)(B * M), (uint64_t)d, BM, BK);
+    if (rc) return rc;
+    if ((rc = make_tmap_bf16(&tb, b, (uint64_t)(B * N), (uint64_t)d, BN, BK))) return rc;
+    if ((rc = make_tmap_bf16(&tg, G, (uint64_t)(B * M), (uint64_t)N, 32, 32, 64))) return rc;
+    const int num_rb = (int)(B * M / BM), ntiles = (int)(N / BN);
+    int nseg = 1;
+    {
+      double best = 0.0;
+      const int max_seg = ntiles >= 8 ? ntiles / 4 : 1;
+      for (int ns = 1; ns <= max_seg && ns <= 64; ++ns) {
+        const int tps = (ntiles + ns - 1) / ns;
+        const int sg = (ntiles + tps - 1) / tps;
+        const long items = (long)num_rb * sg;
+        const double eff = (double)items / ((double)((items + sms - 1) / sms) * sms);
+        if (eff > best + 0.01) { best = eff; nseg = sg; }
+      }
+    }
+    const int tps = (ntiles + nseg - 1) / nseg;
+    nseg = (ntiles + tps - 1) / tps;
+    const long items = (long)num_rb * nseg;
+    const int grid = (int)(items < sms ? items : sms);
+    if (dscale_part)
+      MM25_CUDA_CHECK(cudaMemsetAsync(dscale_part, 0, sizeof(float) * bwd_nparts(B, M, N, d), st));
+    sim_grad_tc_kernel<<<grid, FWD_THREADS, smem, st>>>(
+        ta, tb, tg, M, N, (int)d, 0, num_rb, nseg, tps, scale, scale_kind, clamp_max, diag_offset,
+        row_lse, col_lse ? col_lse : cbuf, w_row, w_col, w_diag, w_all, gout, dscale_part, Cc,
+        dot_bound, nullptr, mask_diag);
+    MM25_LAUNCH_CHECK();
+    GemmDesc ga{G, b, da, d, M, N, 0, 1, 0, 1.f, nullptr, 0, 0, 0, (int)B};
+    GemmDesc gb{G, a, db, d, N, M, 1, 1, 0, 1.f, nullptr, 0, 0, 0, (int)B};
+    return gemm_grouped(da ? &ga : nullptr, db ? &gb : nullptr, d, nullptr, st);
+  }
   const int64_t R = use_e ? M : panel_rows(M, N);
   // [N] floats after the panel: the column factors C_j of the static-shift path; for row-only
   // losses (col_lse = NULL, w_col = 0) also the placeholder the kernel's column loads read

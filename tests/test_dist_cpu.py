@@ -20,6 +20,34 @@ def _free_port():
     return p
 
 
+def _run_world(target, world, args, attempts=2):
+    """Spawn `world` gloo ranks and collect one result per rank; a failed rendezvous (port taken
+    between the probe and the bind, slow start-up on a loaded box) is retried on a fresh port."""
+    import queue as _queue
+    last = None
+    for _ in range(attempts):
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        port = _free_port()
+        procs = [ctx.Process(target=target, args=(r, world, port, q) + tuple(args))
+                 for r in range(world)]
+        for p in procs:
+            p.start()
+        try:
+            res = sorted([q.get(timeout=180) for _ in range(world)], key=lambda t: t[0])
+            ok = True
+        except _queue.Empty as e:
+            res, ok, last = None, False, e
+        for p in procs:
+            p.join(timeout=60)
+            if p.is_alive():
+                p.terminate()
+            ok = ok and p.exitcode == 0
+        if ok:
+            return res
+    raise AssertionError("gloo world failed after %d attempts: %r" % (attempts, last))
+
+
 def _worker(rank, world, port, q, eps, n, d, ls):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -49,17 +77,7 @@ def _worker(rank, world, port, q, eps, n, d, ls):
 def test_sharded_clip_world2_gloo(eps, ls):
     from oracle import losses_oracle as O
     world, n, d = 2, 48, 32
-    ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q, eps, n, d, ls))
-             for r in range(world)]
-    for p in procs:
-        p.start()
-    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
-    for p in procs:
-        p.join(timeout=60)
-        assert p.exitcode == 0
+    res = _run_world(_worker, world, (eps, n, d, ls))
     x, y = O.synth_embeddings(n * world, d, 7, correlated=True)
     x = x * 1.7
     ref, (rx, ry, rl) = O.loss_and_grads(lambda a, b, c: 2.0 * O.clip_loss(a, b, c, eps, True),
@@ -107,17 +125,7 @@ def test_sharded_alignclip_world2_gloo(semantic):
     oracle on the concatenated batch (reference loss.py:221-273 restated in oracle/)."""
     from oracle import losses_oracle as O
     world, n, d, dsem = 2, 40, 24, 12
-    ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    port = _free_port()
-    procs = [ctx.Process(target=_worker_align, args=(r, world, port, q, semantic, n, d, dsem))
-             for r in range(world)]
-    for p in procs:
-        p.start()
-    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
-    for p in procs:
-        p.join(timeout=60)
-        assert p.exitcode == 0
+    res = _run_world(_worker_align, world, (semantic, n, d, dsem))
     x, y = O.synth_embeddings(n * world, d, 11, correlated=True)
     sem = torch.randn(n * world, dsem, generator=torch.Generator().manual_seed(4))
     s = torch.tensor(14.285)
