@@ -14,6 +14,7 @@
 #include "gemm_tc.h"
 
 #include <cstdlib>
+#include <type_traits>
 
 namespace mm25 {
 namespace tc {
@@ -121,15 +122,17 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + as * BN +
                                half * CH_PER_WARP * 32;
 
-        auto process = [&](uint32_t (&r)[32], int chl) {
+        // DIAG is a compile-time tag: only the one chunk in 128 that crosses the warp's positives
+        // carries the per-element (j == rel) compare / select; ptxas otherwise if-converts a
+        // runtime `if (has_diag)` and every logit pays 4 extra instructions (a third of this
+        // epilogue, profiles/r1_final_ncu_summary.md)
+        auto process_t = [&](auto diag_tag, uint32_t (&r)[32], int chl) {
+          constexpr bool has_diag = decltype(diag_tag)::value;
           const int64_t cbase = col0 + (half * CH_PER_WARP + chl) * 32;
           const int rel = (int)min((int64_t)64, max((int64_t)-1, dcol - cbase));
           const float4* cc4 = reinterpret_cast<const float4*>(ccw + chl * 32);
           uint32_t packed[16];
-          // warp-uniform: does this chunk cross the warp's positives?
-          const int64_t d0 = (int64_t)rb * BM + q * 32 + diag_offset;
-          const bool has_diag = (d0 + 31 >= cbase) && (d0 < cbase + 32);
-          if (mask_diag && has_diag) {
+          if (has_diag && mask_diag) {
             // the masked positive contributes no softmax mass; d/ds keeps the true logit
             // (sim_simt.cu: glse = 0, base unchanged), so correct `ds` for the substitution
             float vo = vmask;
@@ -150,7 +153,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const float vj = __uint_as_float(r[j]);
                 const float E = ex2_approx(fmaf(vj, c2, -m2));
                 float gg = fmaf(E, Ri + cj[u], -k_all);
-                if (has_diag) gg -= (j == rel) ? k_diag : 0.f;
+                if constexpr (has_diag) gg -= (j == rel) ? k_diag : 0.f;
                 ds = fmaf(gg, vj, ds);
                 gq[u] = gg;
               }
@@ -173,7 +176,7 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 float gg = w_row * ex2_approx(zl - r2);
                 if (use_col) gg += w_col * ex2_approx(fmaf(-cj[u], LOG2E, zl));
                 gg -= w_all;
-                gg -= (j == rel) ? w_diag : 0.f;
+                if constexpr (has_diag) gg -= (j == rel) ? w_diag : 0.f;
                 ds = fmaf(gg * go, vj, ds);
                 gq[u] = gg * gs;
               }
@@ -200,6 +203,14 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
             tma_store_2d(&tmap_g, stage, (int32_t)cbase, grow0);
             tma_store_commit();
           }
+        };
+
+        // warp-uniform: does chunk `chl` cross the warp's positives?
+        const int64_t d0 = (int64_t)rb * BM + q * 32 + diag_offset;
+        auto process = [&](uint32_t (&r)[32], int chl) {
+          const int64_t cbase = col0 + (half * CH_PER_WARP + chl) * 32;
+          if ((d0 + 31 >= cbase) && (d0 < cbase + 32)) process_t(std::true_type{}, r, chl);
+          else process_t(std::false_type{}, r, chl);
         };
 
         // software pipeline over the warp's chunks: the TMEM load of chunk c+1 is in flight
