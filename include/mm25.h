@@ -317,6 +317,25 @@ int mm25_log_bessel(const double* kappa, int64_t n, double nu, double* log_i_nu,
 int mm25_topk_rows(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_t k,
                    int64_t* out_idx, float* out_val, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Retrieval ranks without the sort (AlignCLIP/main/train.py:338-356 `get_clip_metrics`:
+ * `ranking = argsort(logit, descending=True); preds = where(ranking == ground_truth)[1]`, once
+ * per direction on the CPU copy of the N x N logits; main/retrieval.py:69-71,88-90 the same
+ * argsort for recall@k).
+ * scores [Q, N] fp32 slab (row stride ld) holding global rows row0 .. row0+Q-1.  One pass reads
+ * each score once and ACCUMULATES (atomic integer adds; the caller zeroes the outputs)
+ *   row_rank[q] += #{j : s[q,j] sorts ahead of the row target (value row_tval[q], column
+ *                     row_tcol[q])},
+ *   col_rank[j] += #{q : s[q,j] sorts ahead of the column target (value col_tval[j], global row
+ *                     col_trow[j])},
+ * where "ahead" is the stable descending order: larger value, or equal value and smaller
+ * position (NaN largest, as torch sorts).  Either direction may be skipped by passing NULL for
+ * its rank pointer.  Integer result: bit-exact and independent of the slab split.
+ * ------------------------------------------------------------------------------------------ */
+int mm25_rank_both(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_t row0,
+                   const float* row_tval, const int64_t* row_tcol, const float* col_tval,
+                   const int64_t* col_trow, int* row_rank, int* col_rank, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

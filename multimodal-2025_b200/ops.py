@@ -496,6 +496,36 @@ def topk_rows(scores: Tensor, k: int) -> Tuple[Tensor, Tensor]:
     return idx, val
 
 
+@torch.library.custom_op("mm25::rank_both", mutates_args=("row_rank", "col_rank"),
+                         device_types="cuda")
+def rank_both(scores: Tensor, row0: int, row_tval: Optional[Tensor], row_tcol: Optional[Tensor],
+              col_tval: Optional[Tensor], col_trow: Optional[Tensor],
+              row_rank: Optional[Tensor], col_rank: Optional[Tensor]) -> None:
+    """One pass over the fp32 slab `scores` [Q, N] (global rows row0..) that ADDS into
+    row_rank[q] / col_rank[j] (int32) how many entries sort ahead of the row / column target in
+    the stable descending order (include/mm25.h mm25_rank_both; train.py:338-356)."""
+    if not scores.is_cuda:
+        raise _lib.MM25Error("scores must be a CUDA tensor: this path has no CPU fallback")
+    if scores.dtype != torch.float32 or scores.dim() != 2 or scores.stride(1) != 1:
+        raise ValueError("scores must be a row-major fp32 [Q, N] slab")
+    Q, N = scores.shape
+    for name, t, n, dt in (("row_tval", row_tval, Q, torch.float32),
+                           ("row_tcol", row_tcol, Q, torch.int64),
+                           ("row_rank", row_rank, Q, torch.int32),
+                           ("col_tval", col_tval, N, torch.float32),
+                           ("col_trow", col_trow, N, torch.int64),
+                           ("col_rank", col_rank, N, torch.int32)):
+        if t is not None and (t.dtype != dt or t.numel() != n or not t.is_contiguous()
+                              or t.device != scores.device):
+            raise ValueError("%s must be a contiguous %s tensor of %d elements on %s"
+                             % (name, dt, n, scores.device))
+    with torch.cuda.device(scores.device):
+        rc = _lib.lib().mm25_rank_both(_p(scores), Q, N, scores.stride(0), row0, _p(row_tval),
+                                       _p(row_tcol), _p(col_tval), _p(col_trow), _p(row_rank),
+                                       _p(col_rank), _stream(scores))
+    _lib.check(rc, "mm25_rank_both")
+
+
 @torch.library.custom_op("mm25::sim_bwd_rs", mutates_args=(), device_types="cuda")
 def sim_bwd_rs(a: Tensor, b: Tensor, scale: Tensor, scale_kind: int, clamp_max: float,
                diag_offset: int, row_lse: Tensor, col_lse: Tensor, w_row: float, w_col: float,

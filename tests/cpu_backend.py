@@ -93,3 +93,38 @@ def scale_param_grad(dscale, scale, scale_kind, clamp_max):
     l = scale.detach().float()
     return (dscale.reshape(()) * torch.where(l <= clamp_max, l.exp(), torch.zeros_like(l))
             ).reshape(scale.shape)
+
+
+def _order_key(v):
+    """int64 keys whose order is torch's sort order of fp32 (NaN largest, -0.0 < +0.0 as the
+    kernels' bit-pattern keys have it)."""
+    u = v.contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+    key = torch.where(u >= 0x80000000, 0xFFFFFFFF - u, u | 0x80000000)
+    return torch.where(torch.isnan(v), torch.full_like(key, 0xFFFFFFFF), key)
+
+
+def rank_both(scores, row0, row_tval, row_tcol, col_tval, col_trow, row_rank, col_rank):
+    """include/mm25.h mm25_rank_both, dense: counts of entries ahead of the row / column target
+    in the stable descending order, ADDED into the int32 outputs."""
+    Q, N = scores.shape
+    key = _order_key(scores.float())
+    if row_rank is not None:
+        tk = _order_key(row_tval).view(-1, 1)
+        pos = torch.arange(N).view(1, -1)
+        ahead = (key > tk) | ((key == tk) & (pos < row_tcol.view(-1, 1)))
+        row_rank += ahead.sum(dim=1).to(torch.int32)
+    if col_rank is not None:
+        tk = _order_key(col_tval).view(1, -1)
+        pos = (row0 + torch.arange(Q)).view(-1, 1)
+        ahead = (key > tk) | ((key == tk) & (pos < col_trow.view(1, -1)))
+        col_rank += ahead.sum(dim=0).to(torch.int32)
+
+
+def topk_rows(scores, k):
+    """include/mm25.h mm25_topk_rows, dense: stable descending sort, first k."""
+    s = scores.float()
+    if s.dim() == 1:
+        s = s.unsqueeze(0)
+    key = _order_key(s)
+    idx = torch.argsort(key, dim=1, descending=True, stable=True)[:, :k]
+    return idx, s.gather(1, idx)
