@@ -70,6 +70,15 @@ int mm25_debug_gemm_grouped(const void* A0, int a0_mn, const void* B0, int b0_mn
                             int64_t M0, int64_t K0, const void* A1, int a1_mn, const void* B1,
                             int b1_mn, float* C1, int64_t M1, int64_t K1, int64_t Ng,
                             void* stream);
+/* test hook: the scatter-mode GEMM of the fused reduce-scatter (mm25_sim_bwd_rs) with the owner
+ * buffers as a HOST array of `nowners` device pointers to [rows_per_rank, Ng] fp32: rows
+ * [q R, (q+1) R) of op(A) op(B) are ADDED into owners[q].  On one GPU the owners are local
+ * buffers, so the epilogue variants selected by the environment variable MM25_RS_MODE
+ * (0 = per-lane red.global, 1 = 128-byte TMA reductions, 2 = staged row-contiguous red.global)
+ * can be checked without NVLink. */
+int mm25_debug_gemm_scatter(const void* A, int a_mn, const void* B, int b_mn,
+                            float* const* owners, int nowners, int64_t rows_per_rank,
+                            int self_rank, int64_t Mg, int64_t Ng, int64_t K, void* stream);
 /* 1 if the current device is compute capability 10.x, else 0. */
 int mm25_device_ok(void);
 

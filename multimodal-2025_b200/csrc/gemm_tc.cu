@@ -39,6 +39,18 @@ struct Smem {
   uint32_t tmem_base;
 };
 
+// Opt-in staged scatter (MM25_RS_MODE, default 0 = per-lane 16-byte red.global): the plain
+// scatter epilogue has every lane add 16 bytes of its own row, i.e. 32 separate 16-byte remote
+// atomics per warp instruction over NVLink (measured: the 56 MB a rank pushes at P = 8 take
+// ~180 us on top of the math, ~0.3 TB/s of a 0.9 TB/s link).  The staged modes pass each
+// 32 x 32 chunk through a padded per-warp shared-memory buffer (row stride 144 B: 16-byte
+// stores of a quarter-warp land in distinct banks) and send whole 128-byte row segments:
+//   mode 1: one `cp.reduce.async.bulk ... add.f32` (TMA reduce) of 128 B per lane and chunk;
+//   mode 2: `red.global.add.v4.f32` re-read row-contiguously (8 lanes cover one 128-byte row).
+// The buffer lives after Smem and is only allocated when a staged mode is selected.
+constexpr int STG_LD = 36;                         // floats per staged row (128 B + 16 B pad)
+constexpr int STG_BYTES = 4 * 32 * STG_LD * 4;     // 4 epilogue warps x 32 rows
+
 struct Problem {
   CUtensorMap ta, tb;
   float* C;
@@ -117,6 +129,7 @@ __device__ __forceinline__ bool job_at(const Params& P, int grp, int k, int* pro
 }
 }  // namespace g
 
+template <int RS>
 __global__ void __launch_bounds__(g::THREADS, 1)
 gemm_grouped_kernel(const __grid_constant__ g::Params P) {
   using namespace g;
@@ -229,6 +242,50 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
       const int scatter = pr.scatter | (pr.ksplit > 1);  // both add with red.global
       mbar_wait(&sm.acc_full[as], accph);
       tc_fence_after();
+      if (RS != 0 && pr.scatter) {
+        // staged scatter: 128-byte row segments instead of per-lane 16-byte atomics
+        float* stg = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(&sm) +
+                                              ((sizeof(Smem) + 127) & ~size_t(127))) +
+                     q * 32 * STG_LD;
+        float* mine = stg + lane * STG_LD;
+        // row 0 of this warp's 32 rows in the owner's buffer (all 32 rows share the owner)
+        float* crow0 = crow - (int64_t)lane * pr.ldc;
+#pragma unroll 1
+        for (int ch = 0; ch < BN / 32; ++ch) {
+          float v[32];
+          tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + as * BN + ch * 32, v);
+          if (RS == 1) tma_store_wait_read<0>();  // my previous bulk op has read my row
+          else __syncwarp();                      // everyone has re-read the previous chunk
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(mine + 4 * j) = make_float4(
+                v[4 * j] * al, v[4 * j + 1] * al, v[4 * j + 2] * al, v[4 * j + 3] * al);
+          if (RS == 1) {
+            fence_proxy_async_smem();
+            asm volatile(
+                "cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], 128;" ::
+                    "l"(crow + ch * 32), "r"(smem_u32(mine))
+                : "memory");
+            tma_store_commit();
+          } else {
+            __syncwarp();
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int r = it * 4 + (lane >> 3), u = lane & 7;
+              const float4 o = *reinterpret_cast<const float4*>(stg + r * STG_LD + 4 * u);
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(
+                               crow0 + (int64_t)r * pr.ldc + ch * 32 + 4 * u),
+                           "f"(o.x), "f"(o.y), "f"(o.z), "f"(o.w)
+                           : "memory");
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.acc_empty[as]);
+        if (++as == NACC) { as = 0; accph ^= 1; }
+        continue;
+      }
 #pragma unroll 1
       for (int ch = 0; ch < BN / 32; ++ch) {
         float v[32];
@@ -255,6 +312,10 @@ gemm_grouped_kernel(const __grid_constant__ g::Params P) {
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.acc_empty[as]);
       if (++as == NACC) { as = 0; accph ^= 1; }
+    }
+    if (RS == 1) {  // every bulk reduction of this thread has completed before the CTA exits
+      tma_store_wait_all<0>();
+      __threadfence_system();
     }
   }
   tc_fence_before();
@@ -387,10 +448,22 @@ int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float
   // 0.860 ms per step), so the default keeps problem 0 first
   static const bool p1_first = getenv("MM25_GEMM_P1_FIRST") != nullptr;
   P.s.p1_first = (P.p[1].mblocks > 0 && P.p[1].scatter && p1_first) ? 1 : 0;
+  // staged scatter modes: opt-in A/B switch (see g::STG_LD); only when a problem scatters
+  static const int rs_env = getenv("MM25_RS_MODE") ? atoi(getenv("MM25_RS_MODE")) : 0;
+  const int rs = (P.p[0].scatter || (P.p[1].mblocks > 0 && P.p[1].scatter)) ? rs_env : 0;
+  if (rs == 1 || rs == 2) {
+    const size_t smem = ((sizeof(g::Smem) + 127) & ~size_t(127)) + g::STG_BYTES + 1024;
+    auto kern = rs == 1 ? gemm_grouped_kernel<1> : gemm_grouped_kernel<2>;
+    MM25_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem));
+    kern<<<ngroups * group, g::THREADS, smem, st>>>(P);
+    MM25_LAUNCH_CHECK();
+    return MM25_OK;
+  }
   const size_t smem = sizeof(g::Smem) + 1024;
-  MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_grouped_kernel,
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_grouped_kernel<0>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  gemm_grouped_kernel<<<ngroups * group, g::THREADS, smem, st>>>(P);
+  gemm_grouped_kernel<0><<<ngroups * group, g::THREADS, smem, st>>>(P);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }
@@ -421,4 +494,18 @@ extern "C" int mm25_debug_gemm_grouped(const void* A0, int a0_mn, const void* B0
   mm25::tc::GemmDesc d0{A0, B0, C0, Ng, M0, K0, a0_mn, b0_mn, 0, 1.f, nullptr, 0, 0};
   mm25::tc::GemmDesc d1{A1, B1, C1, Ng, M1, K1, a1_mn, b1_mn, 0, 1.f, nullptr, 0, 0};
   return mm25::tc::gemm_grouped(&d0, &d1, Ng, nullptr, (cudaStream_t)stream);
+}
+
+// debug / test entry: the scatter-mode problem (fused reduce-scatter epilogue) with the P owner
+// buffers given as a HOST array of device pointers — on one GPU they are P local [R, Ng] fp32
+// buffers, which exercises the same epilogue code (plain, TMA-reduce or staged per
+// MM25_RS_MODE) without NVLink.  Adds op(A) op(B) rows [q R, (q+1) R) into owners[q].
+extern "C" int mm25_debug_gemm_scatter(const void* A, int a_mn, const void* B, int b_mn,
+                                       float* const* owners, int nowners, int64_t rows_per_rank,
+                                       int self_rank, int64_t Mg, int64_t Ng, int64_t K,
+                                       void* stream) {
+  if (!owners || nowners < 1 || nowners > mm25::tc::GEMM_MAX_PEERS) return MM25_ERR_ARG;
+  mm25::tc::GemmDesc d{A, B, nullptr, Ng, Mg, K, a_mn, b_mn, 0, 1.f, owners, nowners,
+                       rows_per_rank, self_rank, 0};
+  return mm25::tc::gemm_grouped(&d, nullptr, Ng, nullptr, (cudaStream_t)stream);
 }

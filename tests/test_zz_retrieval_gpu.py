@@ -226,3 +226,46 @@ def test_full_size_rank_properties(lib_built):
     order = torch.argsort(st[rows], dim=1, descending=True, stable=True)
     want = torch.where(order == rows.view(-1, 1))[1]
     assert torch.equal(c.index_select(0, rows).long(), want)
+
+
+# ---------------------------------------------------------------------------------------------
+# Opt-in experiments (not part of the default suite): epilogue variants of the fused
+# GEMM -> reduce-scatter selected by MM25_RS_MODE.  Run with MM25_TEST_EXPERIMENTAL=1.
+# ---------------------------------------------------------------------------------------------
+_SCATTER_SNIPPET = r"""
+import ctypes, sys, torch
+sys.path.insert(0, {root!r})
+from multimodal_2025_b200 import _lib
+L = _lib.lib()
+torch.manual_seed(0)
+P, R, K, Ng = 4, 256, 1024, 512           # dB = G^T X of a 4-rank job: Mg = P R rows, owners of R
+G = torch.randn(K, P * R, device="cuda").bfloat16()      # A, MN-major: stored [K, Mg]
+X = torch.randn(K, Ng, device="cuda").bfloat16()         # B, MN-major: stored [K, Ng]
+own = [torch.full((R, Ng), float(q), device="cuda") for q in range(P)]
+table = (ctypes.c_void_p * P)(*[t.data_ptr() for t in own])
+for self_rank in (0, 3):
+    rc = L.mm25_debug_gemm_scatter(G.data_ptr(), 1, X.data_ptr(), 1, table, P, R, self_rank,
+                                   P * R, Ng, K, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, rc
+torch.cuda.synchronize()
+ref = G.float().t() @ X.float()
+for q in range(P):
+    want = 2 * ref[q * R:(q + 1) * R] + q
+    err = (own[q] - want).abs().max().item()
+    assert err < 2e-2 * max(1.0, want.abs().max().item() / 10), (q, err)
+print("scatter ok")
+"""
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_experimental_scatter_epilogue_modes(lib_built, mode):
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    if mode != 0 and os.environ.get("MM25_TEST_EXPERIMENTAL") != "1":
+        pytest.skip("opt-in: MM25_TEST_EXPERIMENTAL=1 (staged scatter epilogues, unmeasured)")
+    env = dict(os.environ, MM25_RS_MODE=str(mode))
+    r = subprocess.run([sys.executable, "-c", _SCATTER_SNIPPET.format(root=ROOT)], env=env,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "scatter ok" in r.stdout, r.stdout + r.stderr
