@@ -433,3 +433,125 @@ class ShardedClipInModalityLoss(ShardedAlignClipLoss):
             return {"total_loss": total_loss, "clip_loss": clip_loss,
                     "inModality_loss": inModality_loss}
         return total_loss
+
+
+# ----------------------------------------------------------------------------------------------
+# Retrieval over a gallery sharded across the ranks (SURVEY §8e, last row)
+# ----------------------------------------------------------------------------------------------
+def _gather_ragged_counts(n_local: int, device, group):
+    """[P] int64 shard sizes in rank order (shards may differ in length)."""
+    world = dist.get_world_size(group)
+    mine = torch.tensor([n_local], dtype=torch.int64, device=device)
+    parts = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine, group=group)
+    return torch.cat(parts)
+
+
+def sharded_topk(scores_local: torch.Tensor, k: int, group=None, backend=None):
+    """Exact top-k over a gallery whose columns are sharded across the ranks.
+
+    scores_local [Q, n_r] fp32: the scores of the SAME Q queries (replicated) against this
+    rank's gallery shard (rank r holds global columns [off_r, off_r + n_r), off_r = sum of the
+    earlier shards).  Returns (indices int64 [Q, k] GLOBAL, values [Q, k]) sorted descending,
+    identical on every rank and identical to `topk_rows` on the concatenated [Q, sum n_r] matrix
+    (metrics/topk.py:43-48 on the full gallery): per-shard top-min(k, n_r), one all-gather of the
+    [Q, k] candidates, then a k-way merge by the same exact kernel.  Ties: lowest global index
+    first — candidates are laid out in rank order and each shard's list is already in
+    (value desc, index asc) order, so candidate position order equals global-index order among
+    equal values, which is the kernel's tie rule."""
+    B = backend
+    if B is None:
+        from . import ops as B
+    group = group if group is not None else dist.group.WORLD
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    s = scores_local.detach().float()
+    if s.dim() == 1:
+        s = s.unsqueeze(0)
+    Q, n_r = s.shape
+    counts = _gather_ragged_counts(n_r, s.device, group)
+    total = int(counts.sum())
+    if not 1 <= k <= total:
+        raise RuntimeError("selected index k out of range")  # what torch.topk raises
+    offset = int(counts[:rank].sum())
+    kl = min(k, n_r)
+    # fixed-size candidate slots so one all_gather serves ragged shards: unused slots hold
+    # (-inf, sentinel index); a sentinel can only be selected when k exceeds the real entries,
+    # which the range check above excludes (ties at -inf resolve to the lower position = real)
+    cand_v = torch.full((Q, k), float("-inf"), dtype=torch.float32, device=s.device)
+    cand_i = torch.full((Q, k), total, dtype=torch.int64, device=s.device)
+    if kl > 0:
+        idx, val = B.topk_rows(s.contiguous(), kl)
+        cand_v[:, :kl] = val
+        cand_i[:, :kl] = idx + offset
+    all_v = _all_gather_cat(cand_v.unsqueeze(0), group)       # [P, Q, k]
+    all_i = _all_gather_cat(cand_i.unsqueeze(0), group)
+    # real entries of shard r first, its padding last: put every padding slot behind every real
+    # one so that a real -inf score still wins the position tie-break against padding
+    flat_v = all_v.permute(1, 0, 2).reshape(Q, world * k)
+    flat_i = all_i.permute(1, 0, 2).reshape(Q, world * k)
+    pad = flat_i == total
+    order = torch.argsort(pad.to(torch.int8), dim=1, stable=True)
+    flat_v = flat_v.gather(1, order).contiguous()
+    flat_i = flat_i.gather(1, order)
+    pos, val = B.topk_rows(flat_v, k)
+    return flat_i.gather(1, pos), val
+
+
+def sharded_top_k_score(text_local, owner_image_local, images_all, k=5, group=None,
+                        backend=None):
+    """top_k_score (metrics/topk.py:54-82) with the TEXT gallery sharded: every rank holds a
+    slice `text_local` [n_r, d] of the stacked text embeddings with `owner_image_local` [n_r]
+    (index of the image each text belongs to) and ALL image embeddings `images_all` [Q, d]
+    (replicated).  An image is correct when one of its own texts is in its global top-k.
+    Returns (accuracy, {"correct", "total"}) on every rank."""
+    t = text_local.float()
+    q = images_all.float()
+    t = t / t.norm(dim=1, keepdim=True).clamp_min(1e-8)  # cosine_similarity eps (topk.py:44)
+    q = q / q.norm(dim=1, keepdim=True).clamp_min(1e-8)
+    group = group if group is not None else dist.group.WORLD
+    idx, _ = sharded_topk(q @ t.T, k, group, backend)
+    owners = _all_gather_ragged(owner_image_local.to(torch.int64), group)
+    hit = (owners[idx] == torch.arange(q.shape[0], device=q.device).view(-1, 1)).any(dim=1)
+    correct = int(hit.sum().item())
+    total = q.shape[0]
+    return (correct / total if total > 0 else 0.0), {"correct": correct, "total": total}
+
+
+def _all_gather_ragged(t: torch.Tensor, group):
+    """concatenate 1-D shards of different lengths in rank order."""
+    counts = _gather_ragged_counts(t.shape[0], t.device, group)
+    m = int(counts.max())
+    padded = torch.zeros((1, m), dtype=t.dtype, device=t.device)
+    padded[0, :t.shape[0]] = t
+    allp = _all_gather_cat(padded, group)                     # [P, m]
+    return torch.cat([allp[r, :int(counts[r])] for r in range(allp.shape[0])])
+
+
+def sharded_paired_ranks(image_local, text_local, logit_scale=None, group=None, backend=None):
+    """get_clip_metrics' ranks (AlignCLIP/main/train.py:338-356) on a row-sharded batch: rank r
+    holds rows [r n, (r+1) n) of both modalities.  The text shard is all-gathered, the local
+    [n, N] block of `logit_scale * image @ text.T` feeds `mm25_rank_both` once: the row counts
+    (image -> text) are complete locally, the column counts (text -> image) are partial sums
+    over the local rows and are all-reduced (integers: exact, order-free).  The column targets
+    (the diagonal) are all-gathered first.  Returns (i2t_local [n], t2i_local [n]) int32: the
+    ranks of the LOCAL pairs."""
+    B = backend
+    if B is None:
+        from . import ops as B
+    group = group if group is not None else dist.group.WORLD
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    x, y = image_local.detach(), text_local.detach()
+    n = x.shape[0]
+    N = n * world
+    yall = _all_gather_cat(y.contiguous(), group)
+    s = (logit_scale * x @ yall.t()) if logit_scale is not None else x @ yall.t()
+    s = s.float().contiguous()
+    cols = torch.arange(rank * n, (rank + 1) * n, device=s.device, dtype=torch.int64)
+    diag_local = s.gather(1, cols.view(-1, 1)).view(-1).contiguous()
+    diag_all = _all_gather_cat(diag_local, group)
+    rows_all = torch.arange(N, device=s.device, dtype=torch.int64)
+    i2t = torch.zeros((n,), dtype=torch.int32, device=s.device)
+    t2i = torch.zeros((N,), dtype=torch.int32, device=s.device)
+    B.rank_both(s, rank * n, diag_local, cols, diag_all, rows_all, i2t, t2i)
+    dist.all_reduce(t2i, group=group)
+    return i2t, t2i[rank * n:(rank + 1) * n].clone()

@@ -68,6 +68,36 @@ def main():
         print("rank %d alignclip %s N=%d loss_rel=%.2e gx=%.2e gy=%.2e gs=%.2e %s" %
               (rank, dtype, N, el, egx, egy, egl, "OK" if good else "FAIL"), flush=True)
         ok = ok and good
+    # sharded retrieval (SURVEY §8e last row): exact top-k over a ragged sharded gallery and the
+    # paired ranks of a row-sharded batch, against single-device results on the same scores
+    from multimodal_2025_b200 import dist as mdist, ops
+    from oracle import metrics_oracle as MO
+    g = torch.Generator().manual_seed(23)
+    sizes = [300 + 17 * r for r in range(world)]
+    scores = torch.randn(12, sum(sizes), generator=g)
+    scores[:6] = torch.round(scores[:6] * 4) / 4               # ties across shards
+    off = sum(sizes[:rank])
+    local = scores[:, off:off + sizes[rank]].contiguous().to(dev)
+    good = True
+    for k in (1, 10, 350):
+        idx, val = mdist.sharded_topk(local, k)
+        widx, wval = ops.topk_rows(scores.to(dev), k)
+        good = good and torch.equal(idx, widx) and torch.equal(val, wval)
+    n, d = 192, 64
+    N = n * world
+    x, y = O.synth_embeddings(N, d, 29, correlated=True)
+    sl = slice(rank * n, (rank + 1) * n)
+    i2t, t2i = mdist.sharded_paired_ranks(x[sl].to(dev), y[sl].to(dev), 14.0)
+    yall = y.to(dev)
+    s_loc = (14.0 * x[sl].to(dev) @ yall.t()).float().cpu()    # the block this rank ranked
+    parts = [None] * world
+    dist.all_gather_object(parts, s_loc)
+    s_all = torch.cat(parts)
+    ar = torch.arange(N)
+    good = good and torch.equal(i2t.cpu().long(), MO.ranks_by_sort(s_all, ar)[sl])
+    good = good and torch.equal(t2i.cpu().long(), MO.ranks_by_sort(s_all.t().contiguous(), ar)[sl])
+    print("rank %d sharded retrieval %s" % (rank, "OK" if good else "FAIL"), flush=True)
+    ok = ok and good
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()

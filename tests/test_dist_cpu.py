@@ -145,3 +145,79 @@ def test_sharded_alignclip_world2_gloo(semantic):
         assert (gx - rx[sl]).norm() < 1e-4 * rx[sl].norm()
         assert (gy - ry[sl]).norm() < 1e-4 * ry[sl].norm()
         assert abs(gs - float(rs)) <= 1e-4 * max(abs(float(rs)), 1e-6)
+
+
+def _worker_retrieval(rank, world, port, q, seed):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import cpu_backend
+        from conftest import load_golden
+        from multimodal_2025_b200 import dist as mdist
+        g = torch.Generator().manual_seed(seed)
+        sizes = [37, 23]                       # ragged gallery shards
+        off = sum(sizes[:rank])
+        scores = torch.randn(9, sum(sizes), generator=g)
+        scores[:5] = torch.round(scores[:5] * 2) / 2          # heavy ties in the first rows
+        scores[8, 40:] = float("-inf")
+        local = scores[:, off:off + sizes[rank]].contiguous()
+        out = {}
+        for k in (1, 4, 30, 60):               # 30 > the smaller shard, 60 = the whole gallery
+            idx, val = mdist.sharded_topk(local, k, backend=cpu_backend)
+            out[k] = (idx, val)
+        # top_k_score on the reference's golden embeddings, texts sharded 170 / 130
+        G = load_golden("topk.npz")[""]
+        texts, images = torch.from_numpy(G["texts"]), torch.from_numpy(G["images"])
+        cut = [0, 170, 300]
+        tl = texts[cut[rank]:cut[rank + 1]]
+        owner = torch.arange(300)[cut[rank]:cut[rank + 1]] // 3
+        score = {k: mdist.sharded_top_k_score(tl, owner, images, k, backend=cpu_backend)
+                 for k in (1, 5, 10, 100)}
+        # paired ranks of a row-sharded batch
+        n, d = 21, 16
+        x = torch.randn(n * world, d, generator=torch.Generator().manual_seed(3))
+        y = x + 0.7 * torch.randn(n * world, d, generator=torch.Generator().manual_seed(4))
+        sl = slice(rank * n, (rank + 1) * n)
+        i2t, t2i = mdist.sharded_paired_ranks(x[sl], y[sl], 7.5, backend=cpu_backend)
+        q.put((rank, out, score, i2t, t2i))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_retrieval_world2_gloo():
+    """sharded_topk == exact top-k of the concatenated gallery (stable ties, ragged shards,
+    k larger than a shard), sharded_top_k_score == the reference's golden counts, and
+    sharded_paired_ranks == the sort-based oracle on the concatenated batch."""
+    import cpu_backend
+    from conftest import load_golden
+    from oracle import metrics_oracle as MO
+    world, seed = 2, 17
+    res = _run_world(_worker_retrieval, world, (seed,))
+    g = torch.Generator().manual_seed(seed)
+    scores = torch.randn(9, 60, generator=g)
+    scores[:5] = torch.round(scores[:5] * 2) / 2
+    scores[8, 40:] = float("-inf")
+    G = load_golden("topk.npz")
+    n, d = 21, 16
+    x = torch.randn(n * world, d, generator=torch.Generator().manual_seed(3))
+    y = x + 0.7 * torch.randn(n * world, d, generator=torch.Generator().manual_seed(4))
+    s = torch.cat([7.5 * x[r * n:(r + 1) * n] @ y.t() for r in range(world)])
+    ar = torch.arange(n * world)
+    want_i2t = MO.ranks_by_sort(s, ar)
+    want_t2i = MO.ranks_by_sort(s.t().contiguous(), ar)
+    for rank, out, score, i2t, t2i in res:
+        for k, (idx, val) in out.items():
+            widx, wval = cpu_backend.topk_rows(scores, k)
+            assert torch.equal(idx, widx), k
+            assert torch.equal(val, wval), k
+            assert torch.equal(val[5:8], torch.topk(scores[5:8], k, dim=1).values)
+        for k, (acc, info) in score.items():
+            assert info["correct"] == int(G["k%d" % k]["correct"]) and info["total"] == 100
+            assert acc == float(G["k%d" % k]["acc"])
+        sl = slice(rank * n, (rank + 1) * n)
+        assert torch.equal(i2t.long(), want_i2t[sl])
+        assert torch.equal(t2i.long(), want_t2i[sl])
