@@ -555,3 +555,84 @@ def sharded_paired_ranks(image_local, text_local, logit_scale=None, group=None, 
     B.rank_both(s, rank * n, diag_local, cols, diag_all, rows_all, i2t, t2i)
     dist.all_reduce(t2i, group=group)
     return i2t, t2i[rank * n:(rank + 1) * n].clone()
+
+
+# ----------------------------------------------------------------------------------------------
+# CLOOB (reference losses/cloobLoss.py) on the row-sharded global batch (SURVEY §8e)
+# ----------------------------------------------------------------------------------------------
+class _AllGatherRowsFn(torch.autograd.Function):
+    """[n, d] per rank -> [P n, d]; backward reduce-scatters (sums) the gradient of the gathered
+    tensor so every rank receives the gradient of ITS rows from all ranks' partial losses — what
+    `torch.distributed.nn.all_gather` + cat does in loss.py:49-51, in one collective."""
+
+    @staticmethod
+    def forward(ctx, t, group):
+        ctx.group = group
+        return _all_gather_cat(t.detach(), group)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _reduce_scatter_sum(g.detach().contiguous(), ctx.group), None
+
+
+class _AllReduceSumFn(torch.autograd.Function):
+    """sum of a scalar part over the ranks; d(sum)/d(part) = 1 on every rank."""
+
+    @staticmethod
+    def forward(ctx, t, group):
+        out = t.detach().clone()
+        dist.all_reduce(out, group=group)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, None
+
+
+def sharded_cloob_loss(image_local, text_local, inv_tau, scale_hopfield, group=None,
+                       backend=None, grad_scale: float = 1.0):
+    """cloob_loss (cloobLoss.py:10-21) of the GLOBAL batch from the local [n, d] shards.
+
+    The Hopfield softmax runs over the STORED set, so both modalities are gathered (as
+    cloob-training/train.py:241-242 does); each rank then retrieves for its own n state
+    patterns against all N stored ones (rectangular [n, N] retrievals, complete per row), the
+    retrieved text-side patterns are gathered once more as the columns of InfoLOOB, and the
+    rank's rows contribute `sum_local (LSE'_i - k_ii) / N` with the positives at column offset
+    r n.  The scalar parts are summed over the ranks.  Every gather is differentiable
+    (reduce-scatter of the gradient), so the gradients are those of the global loss w.r.t. the
+    local shards, times `grad_scale` (cf. ShardedClipLoss)."""
+    from .losses.cloobLoss import _HopfieldFn, _InfoLoobFn
+    group = group if group is not None else dist.group.WORLD
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    n = image_local.shape[0]
+    N, off = n * world, rank * n
+    beta = float(scale_hopfield)
+    x_all = _AllGatherRowsFn.apply(image_local, group)
+    y_all = _AllGatherRowsFn.apply(text_local, group)
+    # rows = local state patterns, softmax over all stored patterns (cloobLoss.py:35-40)
+    u_xx = _HopfieldFn.apply(image_local, x_all, beta, backend)   # state image, stored image
+    u_yy = _HopfieldFn.apply(text_local, y_all, beta, backend)    # state text,  stored text
+    u_xy = _HopfieldFn.apply(text_local, x_all, beta, backend)    # state text,  stored image
+    u_yx = _HopfieldFn.apply(image_local, y_all, beta, backend)   # state image, stored text
+    u_xy_all = _AllGatherRowsFn.apply(u_xy, group)
+    u_yx_all = _AllGatherRowsFn.apply(u_yx, group)
+    part_img = _InfoLoobFn.apply(u_xx, u_xy_all, float(inv_tau), off, N, backend)  # :18
+    part_txt = _InfoLoobFn.apply(u_yy, u_yx_all, float(inv_tau), off, N, backend)  # :19
+    part = (part_img + part_txt) / 2                                               # :20
+    if grad_scale != 1.0:  # forward value unchanged, gradients scaled
+        part = part * grad_scale + (part * (1.0 - grad_scale)).detach()
+    return _AllReduceSumFn.apply(part, group)
+
+
+class ShardedCLOOBLoss(nn.Module):
+    """CLOOBLoss(inv_tau, scale_hopfield, device) of the GLOBAL batch from local shards."""
+
+    def __init__(self, inv_tau, scale_hopfield, device=None, group=None, grad_scale: float = 1.0,
+                 backend=None):
+        super().__init__()
+        self.inv_tau, self.scale_hopfield, self.device = inv_tau, scale_hopfield, device
+        self.group, self.grad_scale, self.backend = group, grad_scale, backend
+
+    def forward(self, image_features, text_features):
+        return sharded_cloob_loss(image_features, text_features, self.inv_tau,
+                                  self.scale_hopfield, self.group, self.backend, self.grad_scale)

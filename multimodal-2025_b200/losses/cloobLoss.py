@@ -13,6 +13,8 @@ from torch import nn
 
 from .. import ops
 
+_OPS = ops  # default backend of the autograd functions below (they accept a stand-in)
+
 
 def _scalar(v, dev):
     # a fill kernel, not a host->device copy: stays legal under CUDA-graph capture
@@ -42,7 +44,11 @@ class _HopfieldFn(torch.autograd.Function):
     """U[Nq, d] = rownorm(softmax(beta Q K^T) K)."""
 
     @staticmethod
-    def forward(ctx, q, k, beta):
+    def forward(ctx, q, k, beta, backend=None):
+        # `backend`: the ops module (default) or a stand-in with the same functions — the gloo
+        # tests of dist.ShardedCLOOBLoss exercise this host logic on CPU through it
+        ops = backend if backend is not None else _OPS
+        ctx.ops = ops
         in_dtype = q.dtype
         tc = _tc_operands(q, k)
         if tc is not None:
@@ -81,6 +87,7 @@ class _HopfieldFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, du):
+        ops = ctx.ops
         if ctx.tc:
             qb, kb, o, u, inv, lse, sc = ctx.saved_tensors
             du = du.detach().float().contiguous()
@@ -89,7 +96,7 @@ class _HopfieldFn(torch.autograd.Function):
             dq, dk = ops.hopfield_bwd_tc(qb, kb, do, sc, lse, delta, ctx.needs_input_grad[0],
                                          ctx.needs_input_grad[1])
             return (dq.to(ctx.in_dtype) if ctx.needs_input_grad[0] else None,
-                    dk.to(ctx.in_dtype) if ctx.needs_input_grad[1] else None, None)
+                    dk.to(ctx.in_dtype) if ctx.needs_input_grad[1] else None, None, None)
         qf, kf, o, u, inv, lse = ctx.saved_tensors
         beta = ctx.beta
         du = du.detach().float().contiguous()
@@ -102,12 +109,19 @@ class _HopfieldFn(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             dk = ops.hopfield_bwd_pass(kf, qf, kf, do, qf, do, beta, lse, D, True)
             dk = dk.to(ctx.in_dtype)
-        return dq, dk, None
+        return dq, dk, None, None
 
 
 class _InfoLoobFn(torch.autograd.Function):
+    """InfoLOOB of the rows `x` [M, d] against the columns `y` [N, d]; the positive of row i is
+    column i + diag_offset and the means run over n_norm rows (defaults: square problem, M).
+    A row shard of a larger problem passes its offset and the global row count and gets its
+    additive part of the loss (dist.ShardedCLOOBLoss)."""
+
     @staticmethod
-    def forward(ctx, x, y, inv_tau):
+    def forward(ctx, x, y, inv_tau, diag_offset=0, n_norm=None, backend=None):
+        ops = backend if backend is not None else _OPS
+        ctx.ops = ops
         in_dtype = x.dtype
         tc = _tc_operands(x, y)
         impl = ops.IMPL_SIMT if tc is None else ops.IMPL_TC
@@ -118,8 +132,9 @@ class _InfoLoobFn(torch.autograd.Function):
             xf, yf = tc[0].unsqueeze(0), tc[1].unsqueeze(0)
         sc = _scalar(inv_tau, x.device)
         lse, _, _, diag = ops.sim_fwd(xf, yf, None, None, None, sc, ops.SCALE_MUL, 0.0,
-                                      ops.SIM_MASKDIAG, 0, False, impl)
-        n = xf.shape[1]
+                                      ops.SIM_MASKDIAG, int(diag_offset), False, impl)
+        n = xf.shape[1] if n_norm is None else int(n_norm)
+        ctx.off, ctx.n_norm = int(diag_offset), n
         # -mean(diag) + mean(lse): one deterministic reduction kernel (weights 1/2n * 2)
         loss = ops.clip_loss_finalize(lse * 2.0, diag, None, None, None, n, sc, ops.SCALE_MUL,
                                       0.0, 0.0)
@@ -130,21 +145,22 @@ class _InfoLoobFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, gout):
+        ops = ctx.ops
         xf, yf, lse, sc = ctx.saved_tensors
-        n = float(xf.shape[1])
+        n = float(ctx.n_norm)
         g = gout.detach().float().reshape(1).contiguous()
         da, db, _, _ = ops.sim_bwd(xf, yf, None, None, None, sc, ops.SCALE_MUL, 0.0,
-                                   ops.SIM_MASKDIAG, 0, lse, None, 1.0 / n, 0.0, 1.0 / n, 0.0,
-                                   g, ctx.needs_input_grad[0], ctx.needs_input_grad[1], False,
-                                   ctx.impl)
+                                   ops.SIM_MASKDIAG, ctx.off, lse, None, 1.0 / n, 0.0, 1.0 / n,
+                                   0.0, g, ctx.needs_input_grad[0], ctx.needs_input_grad[1],
+                                   False, ctx.impl)
         dx = da[0].to(ctx.in_dtype) if ctx.needs_input_grad[0] else None
         dy = db[0].to(ctx.in_dtype) if ctx.needs_input_grad[1] else None
-        return dx, dy, None
+        return dx, dy, None, None, None, None
 
 
 def hopfield(state_patterns, stored_patterns, scale_hopfield):
     """Retrieved, column-normalised patterns [d, N_state] (reference cloobLoss.py:43-47)."""
-    return _HopfieldFn.apply(state_patterns, stored_patterns, float(scale_hopfield)).T
+    return _HopfieldFn.apply(state_patterns, stored_patterns, float(scale_hopfield), None).T
 
 
 def hopfield_retrieval(image_features, text_features, scale_hopfield):
@@ -164,7 +180,7 @@ def infoloob_loss(x, y, i, inv_tau, device=None):
     """InfoLOOB (reference cloobLoss.py:24-32).  `i` is the positives mask of the reference
     signature; the fused kernel assumes it is the identity (as cloob_loss passes it) and never
     reads it, so no N x N mask has to exist (pass None)."""
-    return _InfoLoobFn.apply(x, y, float(inv_tau))
+    return _InfoLoobFn.apply(x, y, float(inv_tau), 0, None, None)
 
 
 def cloob_loss(image_features, text_features, inv_tau, scale_hopfield, device=None):

@@ -29,7 +29,10 @@ def sim_fwd(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offse
         base = base * (1.0 - u.float() @ v.float().transpose(1, 2))
         base[:, idx, idx + diag_offset] += diag_add
     z = _s(scale, scale_kind, clamp_max) * base
-    diag = z[:, idx, idx + diag_offset]
+    diag = z[:, idx, idx + diag_offset].clone()
+    if mode == SIM_MASKDIAG:  # InfoLOOB: the positive is replaced by -10000 inside the LSE
+        z = z.clone()
+        z[:, idx, idx + diag_offset] = -10000.0
     cmax = z.max(dim=1).values
     csum = (z - cmax.unsqueeze(1)).exp().sum(dim=1)
     return torch.logsumexp(z, dim=2), cmax, csum, diag
@@ -65,6 +68,9 @@ def sim_bwd(a, b, u, v, diag_add, scale, scale_kind, clamp_max, mode, diag_offse
         dot = dot * chain
         dot[:, idx, idx + diag_offset] += diag_add
     z = s * dot
+    if mode == SIM_MASKDIAG:
+        z = z.clone()
+        z[:, idx, idx + diag_offset] = -10000.0
     G = w_row * (z - row_lse.unsqueeze(2)).exp() - w_all
     if col_lse is not None:
         G = G + w_col * (z - col_lse.unsqueeze(1)).exp()
@@ -128,3 +134,23 @@ def topk_rows(scores, k):
     key = _order_key(s)
     idx = torch.argsort(key, dim=1, descending=True, stable=True)[:, :k]
     return idx, s.gather(1, idx)
+
+
+IMPL_AUTO, IMPL_SIMT, IMPL_TC = 0, 1, 2
+
+
+def rowdot(x, y):
+    return (x * y).sum(dim=-1)
+
+
+def hopfield_bwd_pass(a, b, a2, b2, bm1, bm2, beta, lse, D, stat_by_col):
+    """include/mm25.h mm25_hopfield_bwd_pass, dense."""
+    S = a @ b.T
+    dP = a2 @ b2.T
+    l = lse.reshape(1, -1) if stat_by_col else lse.reshape(-1, 1)
+    Dq = D.reshape(1, -1) if stat_by_col else D.reshape(-1, 1)
+    p = (beta * S - l).exp()
+    out = (beta * p * (dP - Dq)) @ bm1
+    if bm2 is not None:
+        out = out + p @ bm2
+    return out

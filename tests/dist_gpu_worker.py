@@ -98,6 +98,27 @@ def main():
     good = good and torch.equal(t2i.cpu().long(), MO.ranks_by_sort(s_all.t().contiguous(), ar)[sl])
     print("rank %d sharded retrieval %s" % (rank, "OK" if good else "FAIL"), flush=True)
     ok = ok and good
+    # sharded CLOOB (rectangular Hopfield retrievals + InfoLOOB with shifted positives)
+    from multimodal_2025_b200.dist import ShardedCLOOBLoss
+    for dtype, n, d, tl, tg in ((torch.float32, 48, 32, 1e-5, 1e-4),
+                                (torch.bfloat16, 256, 256, 2e-3, 2e-2)):
+        N = n * world
+        x, y = O.synth_embeddings(N, d, 17, correlated=True, dtype=dtype)
+        ref, (rx, ry) = O.loss_and_grads(lambda a, b: O.cloob_loss(a, b, 30.0, 15.0),
+                                         [x.float(), y.float()])
+        sl = slice(rank * n, (rank + 1) * n)
+        xl = x[sl].to(dev).requires_grad_(True)
+        yl = y[sl].to(dev).requires_grad_(True)
+        loss = ShardedCLOOBLoss(30.0, 15.0, dev)(xl, yl)
+        loss.backward()
+        torch.cuda.synchronize()
+        el = abs(float(loss) - float(ref)) / abs(float(ref))
+        egx = float((xl.grad.float().cpu() - rx[sl]).norm() / rx[sl].norm())
+        egy = float((yl.grad.float().cpu() - ry[sl]).norm() / ry[sl].norm())
+        good = el < tl and egx < tg and egy < tg
+        print("rank %d cloob %s N=%d loss_rel=%.2e gx=%.2e gy=%.2e %s" %
+              (rank, dtype, N, el, egx, egy, "OK" if good else "FAIL"), flush=True)
+        ok = ok and good
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()

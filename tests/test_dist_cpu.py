@@ -221,3 +221,61 @@ def test_sharded_retrieval_world2_gloo():
         sl = slice(rank * n, (rank + 1) * n)
         assert torch.equal(i2t.long(), want_i2t[sl])
         assert torch.equal(t2i.long(), want_t2i[sl])
+
+
+def test_cloob_host_logic_with_standin_vs_oracle():
+    """single process: the CLOOB autograd functions (losses/cloobLoss.py) driven through the
+    dense stand-in ops reproduce the oracle's loss and gradients — covers the plumbing the
+    sharded loss relies on (rectangular retrievals, diag offset, n_norm)."""
+    import cpu_backend
+    from multimodal_2025_b200.losses.cloobLoss import _HopfieldFn, _InfoLoobFn
+    from oracle import losses_oracle as O
+    x, y = O.synth_embeddings(40, 24, 5, correlated=True)
+    ref, (rx, ry) = O.loss_and_grads(lambda a, b: O.cloob_loss(a, b, 30.0, 15.0), [x, y])
+    xl, yl = x.clone().requires_grad_(True), y.clone().requires_grad_(True)
+    H = lambda q, k: _HopfieldFn.apply(q, k, 15.0, cpu_backend)  # noqa: E731
+    li = _InfoLoobFn.apply(H(xl, xl), H(yl, xl), 30.0, 0, None, cpu_backend)
+    lt = _InfoLoobFn.apply(H(yl, yl), H(xl, yl), 30.0, 0, None, cpu_backend)
+    loss = (li + lt) / 2
+    loss.backward()
+    assert abs(float(loss.detach()) - float(ref)) < 1e-5 * abs(float(ref))
+    assert (xl.grad - rx).norm() < 1e-4 * rx.norm()
+    assert (yl.grad - ry).norm() < 1e-4 * ry.norm()
+
+
+def _worker_cloob(rank, world, port, q, n, d):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import cpu_backend
+        from multimodal_2025_b200.dist import ShardedCLOOBLoss
+        from oracle import losses_oracle as O
+        x, y = O.synth_embeddings(n * world, d, 9, correlated=True)
+        sl = slice(rank * n, (rank + 1) * n)
+        xl = x[sl].clone().requires_grad_(True)
+        yl = y[sl].clone().requires_grad_(True)
+        loss = ShardedCLOOBLoss(30.0, 15.0, "cpu", backend=cpu_backend)(xl, yl)
+        (3.0 * loss).backward()
+        q.put((rank, float(loss.detach()), xl.grad.clone(), yl.grad.clone()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_cloob_world2_gloo():
+    """ShardedCLOOBLoss on 2 ranks against the single-process oracle (cloobLoss.py:10-47
+    restated in oracle/) on the concatenated batch: same loss on every rank, gradients of the
+    global loss w.r.t. the local shards."""
+    from oracle import losses_oracle as O
+    world, n, d = 2, 28, 24
+    res = _run_world(_worker_cloob, world, (n, d))
+    x, y = O.synth_embeddings(n * world, d, 9, correlated=True)
+    ref, (rx, ry) = O.loss_and_grads(lambda a, b: 3.0 * O.cloob_loss(a, b, 30.0, 15.0), [x, y])
+    for rank, loss, gx, gy in res:
+        assert abs(3.0 * loss - float(ref)) < 1e-5 * abs(float(ref))
+        sl = slice(rank * n, (rank + 1) * n)
+        assert (gx - rx[sl]).norm() < 1e-4 * rx[sl].norm()
+        assert (gy - ry[sl]).norm() < 1e-4 * ry[sl].norm()
