@@ -636,3 +636,133 @@ class ShardedCLOOBLoss(nn.Module):
     def forward(self, image_features, text_features):
         return sharded_cloob_loss(image_features, text_features, self.inv_tau,
                                   self.scale_hopfield, self.group, self.backend, self.grad_scale)
+
+
+# ----------------------------------------------------------------------------------------------
+# vCLIP on the row-sharded batch: the sample-batched CLIP term (clipLoss.py:24-79) shards like
+# cfg2 per sample slice; the samplers are row-parallel (replicas only, no collective)
+# ----------------------------------------------------------------------------------------------
+def _gather_dim1(t: torch.Tensor, group) -> torch.Tensor:
+    """[S, n, d] per rank -> [S, P n, d] (rows in rank order)."""
+    return _all_gather_cat(t.transpose(0, 1).contiguous(), group).transpose(0, 1).contiguous()
+
+
+def _reduce_scatter_dim1(t: torch.Tensor, group) -> torch.Tensor:
+    """[S, P n, d] partial per rank -> sum over ranks of the local [S, n, d] rows."""
+    return _reduce_scatter_sum(t.transpose(0, 1).contiguous(), group).transpose(0, 1).contiguous()
+
+
+class _ShardedClipSampledFn(torch.autograd.Function):
+    """loss [S] of S independent GLOBAL CLIP problems from local [S, n, d] sample shards: the
+    algorithm of _ShardedClipFn with the batch dimension of the fused kernels = S (one gather,
+    one statistics exchange, one reduce-scatter for all slices)."""
+
+    @staticmethod
+    def forward(ctx, img, txt, logits_scale, eps_ls, clamp_max, group, backend, grad_scale, impl):
+        B = backend
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        in_dtype = img.dtype
+        if in_dtype not in (torch.float32, torch.bfloat16):
+            img, txt = img.float(), txt.float()
+        if txt.dtype != img.dtype:
+            txt = txt.to(img.dtype)
+        cdt = B.BF16 if img.dtype == torch.bfloat16 else B.F32
+        S, n, d = img.shape
+        N = n * world
+        want_cs = eps_ls != 0.0
+        xhat, invx, sx = B.rownorm_fwd(img.contiguous(), True, _EPS_NORM, cdt, want_cs)
+        yhat, invy, sy = B.rownorm_fwd(txt.contiguous(), True, _EPS_NORM, cdt, want_cs)
+        scale32 = logits_scale.detach().reshape(1).to(torch.float32).contiguous()
+        yall = _gather_dim1(yhat, group)
+        row_lse, cmax, csum, diag = B.sim_fwd(xhat, yall, None, None, None, scale32,
+                                              B.SCALE_LOG, clamp_max, B.SIM_PLAIN, rank * n,
+                                              True, impl, 1.01)
+        extra = [sx.reshape(S, d), sy.reshape(S, d)] if want_cs else []
+        payload = torch.cat([cmax.reshape(S, N), csum.reshape(S, N)] + extra, dim=1)
+        gathered = _all_gather_cat(payload.unsqueeze(0), group)          # [P, S, 2N (+ 2d)]
+        col_lse = B.col_merge(gathered[:, :, :N].reshape(world, S * N).contiguous(),
+                              gathered[:, :, N:2 * N].reshape(world, S * N).contiguous()
+                              ).reshape(S, N)
+        part = B.clip_loss_finalize(row_lse, diag,
+                                    col_lse[:, rank * n:(rank + 1) * n].contiguous(), None, None,
+                                    N, scale32, B.SCALE_LOG, clamp_max, eps_ls)
+        red = part.reshape(S).clone()
+        dist.all_reduce(red, group=group)
+        if want_cs:
+            sxg = gathered[:, :, 2 * N:2 * N + d].sum(dim=0)
+            syg = gathered[:, :, 2 * N + d:2 * N + 2 * d].sum(dim=0)
+            s = scale32.clamp(max=clamp_max).exp().reshape(())
+            red = red - (eps_ls / float(N) ** 2) * s * (sxg * syg).sum(dim=1)
+        ctx.save_for_backward(xhat, yhat, yall, invx, invy, row_lse, col_lse, scale32,
+                              logits_scale)
+        ctx.cfg = (eps_ls, clamp_max, group, B, grad_scale, impl, in_dtype, rank, n, N)
+        return red
+
+    @staticmethod
+    def backward(ctx, gout):
+        (xhat, yhat, yall, invx, invy, row_lse, col_lse, scale32,
+         logits_scale) = ctx.saved_tensors
+        eps_ls, clamp_max, group, B, grad_scale, impl, in_dtype, rank, n, N = ctx.cfg
+        nn_ = float(N)
+        g = (gout.detach().to(torch.float32).reshape(-1) * grad_scale).contiguous()
+        da, db, dscale, _ = B.sim_bwd(xhat, yall, None, None, None, scale32, B.SCALE_LOG,
+                                      clamp_max, B.SIM_PLAIN, rank * n, row_lse, col_lse,
+                                      0.5 / nn_, 0.5 / nn_, (1.0 - eps_ls) / nn_,
+                                      eps_ls / (nn_ * nn_), g, True, True, False, impl, 1.01)
+        dy_local = _reduce_scatter_dim1(db, group)
+        out_dt = B.BF16 if in_dtype == torch.bfloat16 else B.F32
+        dimg = B.rownorm_bwd(da, xhat, invx, True, out_dt, None).to(in_dtype)
+        dtxt = B.rownorm_bwd(dy_local, yhat, invy, True, out_dt, None).to(in_dtype)
+        dls = None
+        if ctx.needs_input_grad[2]:
+            dscale = dscale.reshape(1).clone()
+            dist.all_reduce(dscale, group=group)
+            dls = B.scale_param_grad(dscale, logits_scale, B.SCALE_LOG, clamp_max)
+        return dimg, dtxt, dls, None, None, None, None, None, None
+
+
+def _sharded_forward_sampled(self, image_features, text_features, logits_scale):
+    """ClipLoss.forward_sampled (clipLoss.py:24-79) of the GLOBAL batch: local [S, n, E] sample
+    shards -> [S] losses; always normalises, clamp 3.912."""
+    backend = self.backend
+    if backend is None:
+        from . import ops as backend
+    group = self.group if self.group is not None else dist.group.WORLD
+    if not torch.is_tensor(logits_scale):
+        logits_scale = torch.tensor(float(logits_scale), device=image_features.device)
+    return _ShardedClipSampledFn.apply(image_features, text_features, logits_scale,
+                                       float(self.label_smoothing), 3.912, group, backend,
+                                       float(self.grad_scale), int(self.impl))
+
+
+ShardedClipLoss.forward_sampled = _sharded_forward_sampled
+
+
+def make_sharded_vclip_loss(group=None, backend=None, grad_scale: float = 1.0, **vclip_kwargs):
+    """VClipLoss (losses/vclipLoss.py:43-162) of the GLOBAL batch from local distribution
+    shards: sampling stays local (row-parallel), the CLIP term runs on the sharded batch
+    (`ShardedClipLoss.forward` / `.forward_sampled`), and the KL / variance-regulariser means
+    over the batch become global means (differentiable all-reduce / P).  Returns the module."""
+    from .losses.vclipLoss import VClipLoss
+
+    class ShardedVClipLoss(VClipLoss):
+        def __init__(self):
+            super().__init__(**vclip_kwargs)
+            self.clip_loss = ShardedClipLoss(self.clip_loss.label_smoothing, group, grad_scale,
+                                             backend)
+            self._group = group
+
+        def forward(self, image_distribution, text_distribution, image_vars, text_vars,
+                    logits_scale, is_train, kl_weight_override=None):
+            out = super().forward(image_distribution, text_distribution, image_vars, text_vars,
+                                  logits_scale, is_train, kl_weight_override)
+            grp = self._group if self._group is not None else dist.group.WORLD
+            world = dist.get_world_size(grp)
+            for key in ("image_kl_loss", "text_kl_loss", "var_reg"):  # local mean -> global mean
+                out[key] = _AllReduceSumFn.apply(out[key], grp) / world
+            kl_weight = kl_weight_override if kl_weight_override is not None else self.kl_weight
+            out["total_loss"] = (self.clip_weight * out["clip_loss"] + 0.5 * kl_weight * (
+                out["image_kl_loss"] + out["text_kl_loss"]) + self.var_reg_weight * out["var_reg"])
+            return out
+
+    return ShardedVClipLoss()

@@ -98,6 +98,34 @@ def main():
     good = good and torch.equal(t2i.cpu().long(), MO.ranks_by_sort(s_all.t().contiguous(), ar)[sl])
     print("rank %d sharded retrieval %s" % (rank, "OK" if good else "FAIL"), flush=True)
     ok = ok and good
+    # sample-batched CLIP term of vCLIP on the sharded batch (clipLoss.py:24-79)
+    for dtype, S, n, d, tl, tg in ((torch.float32, 3, 64, 32, 1e-5, 1e-4),
+                                   (torch.bfloat16, 4, 256, 256, 2e-3, 2e-2)):
+        N = n * world
+        g = torch.Generator().manual_seed(37)
+        x = torch.randn(S, N, d, generator=g).to(dtype)
+        y = (x.float() + 2.5 * torch.randn(S, N, d, generator=g)).to(dtype)
+        ls = torch.tensor(2.6592)
+        w = torch.arange(1, S + 1, dtype=torch.float32)
+        ref = O.clip_loss_sampled(x.float(), y.float(), ls, 0.1)
+        _, (rx, ry, rl) = O.loss_and_grads(
+            lambda a, b, c: (O.clip_loss_sampled(a, b, c, 0.1) * w).sum(),
+            [x.float(), y.float(), ls])
+        sl = slice(rank * n, (rank + 1) * n)
+        xl = x[:, sl].contiguous().to(dev).requires_grad_(True)
+        yl = y[:, sl].contiguous().to(dev).requires_grad_(True)
+        lp = ls.to(dev).requires_grad_(True)
+        loss = ShardedClipLoss(0.1).to(dev).forward_sampled(xl, yl, lp)
+        (loss * w.to(dev)).sum().backward()
+        torch.cuda.synchronize()
+        el = float((loss.float().cpu() - ref).abs().max() / ref.abs().max())
+        egx = float((xl.grad.float().cpu() - rx[:, sl]).norm() / rx[:, sl].norm())
+        egy = float((yl.grad.float().cpu() - ry[:, sl]).norm() / ry[:, sl].norm())
+        egl = abs(float(lp.grad) - float(rl)) / abs(float(rl))
+        good = el < tl and egx < tg and egy < tg and egl < tg
+        print("rank %d forward_sampled %s N=%d loss_rel=%.2e gx=%.2e gy=%.2e gl=%.2e %s" %
+              (rank, dtype, N, el, egx, egy, egl, "OK" if good else "FAIL"), flush=True)
+        ok = ok and good
     # sharded CLOOB (rectangular Hopfield retrievals + InfoLOOB with shifted positives)
     from multimodal_2025_b200.dist import ShardedCLOOBLoss
     for dtype, n, d, tl, tg in ((torch.float32, 48, 32, 1e-5, 1e-4),

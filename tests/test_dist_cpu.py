@@ -279,3 +279,115 @@ def test_sharded_cloob_world2_gloo():
         sl = slice(rank * n, (rank + 1) * n)
         assert (gx - rx[sl]).norm() < 1e-4 * rx[sl].norm()
         assert (gy - ry[sl]).norm() < 1e-4 * ry[sl].norm()
+
+
+def _worker_sampled(rank, world, port, q, eps, S, n, d, ls):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import cpu_backend
+        from multimodal_2025_b200.dist import ShardedClipLoss
+        g = torch.Generator().manual_seed(31)
+        x = torch.randn(S, n * world, d, generator=g) * 1.3
+        y = x + 2.5 * torch.randn(S, n * world, d, generator=g)
+        sl = slice(rank * n, (rank + 1) * n)
+        xl = x[:, sl].clone().requires_grad_(True)
+        yl = y[:, sl].clone().requires_grad_(True)
+        lsp = torch.tensor(ls, requires_grad=True)
+        crit = ShardedClipLoss(eps, backend=cpu_backend)
+        loss = crit.forward_sampled(xl, yl, lsp)
+        w = torch.arange(1, S + 1, dtype=torch.float32)      # distinct upstream gradients
+        (loss * w).sum().backward()
+        q.put((rank, loss.detach().clone(), xl.grad.clone(), yl.grad.clone(), float(lsp.grad)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("eps,ls", [(0.1, 2.6592), (0.0, 4.5)])
+def test_sharded_clip_forward_sampled_world2_gloo(eps, ls):
+    """ShardedClipLoss.forward_sampled on 2 ranks against the oracle's forward_sampled
+    (clipLoss.py:24-79 restated) on the concatenated [S, N, E] samples."""
+    from oracle import losses_oracle as O
+    world, S, n, d = 2, 3, 20, 16
+    res = _run_world(_worker_sampled, world, (eps, S, n, d, ls))
+    g = torch.Generator().manual_seed(31)
+    x = torch.randn(S, n * world, d, generator=g) * 1.3
+    y = x + 2.5 * torch.randn(S, n * world, d, generator=g)
+    w = torch.arange(1, S + 1, dtype=torch.float32)
+    ref = O.clip_loss_sampled(x, y, torch.tensor(ls), eps)
+    _, (rx, ry, rl) = O.loss_and_grads(
+        lambda a, b, c: (O.clip_loss_sampled(a, b, c, eps) * w).sum(), [x, y, torch.tensor(ls)])
+    for rank, loss, gx, gy, gl in res:
+        assert (loss - ref).abs().max() < 1e-5 * ref.abs().max()
+        sl = slice(rank * n, (rank + 1) * n)
+        assert (gx - rx[:, sl]).norm() < 1e-4 * rx[:, sl].norm()
+        assert (gy - ry[:, sl]).norm() < 1e-4 * ry[:, sl].norm()
+        assert abs(gl - float(rl)) <= 1e-4 * max(abs(float(rl)), 1e-6)
+
+
+def _vclip_inputs(N, d):
+    g = torch.Generator().manual_seed(41)
+    loc_i = torch.nn.functional.normalize(torch.randn(N, d, generator=g), dim=-1)
+    loc_t = torch.nn.functional.normalize(loc_i + 0.8 * torch.randn(N, d, generator=g), dim=-1)
+    k_i = torch.rand(N, generator=g) * 90 + 10
+    k_t = torch.rand(N, generator=g) * 90 + 10
+    return loc_i, loc_t, k_i, k_t
+
+
+def _worker_vclip(rank, world, port, q, n, d):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import cpu_backend
+        from multimodal_2025_b200.dist import make_sharded_vclip_loss
+        from multimodal_2025_b200.losses.distributions.power_spherical import PowerSpherical
+        loc_i, loc_t, k_i, k_t = _vclip_inputs(n * world, d)
+        sl = slice(rank * n, (rank + 1) * n)
+        li = loc_i[sl].clone().requires_grad_(True)
+        lt = loc_t[sl].clone().requires_grad_(True)
+        ki = k_i[sl].clone().requires_grad_(True)
+        kt = k_t[sl].clone().requires_grad_(True)
+        crit = make_sharded_vclip_loss(backend=cpu_backend, kl_weight=0.7, var_reg_weight=0.2)
+        out = crit(PowerSpherical(li, ki), PowerSpherical(lt, kt), 1.0 / ki, 1.0 / kt,
+                   torch.tensor(2.6592), is_train=False)
+        out["total_loss"].backward()
+        q.put((rank, {k: float(v.detach()) for k, v in out.items()}, li.grad.clone(),
+               ki.grad.clone(), kt.grad.clone()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_vclip_eval_path_world2_gloo():
+    """make_sharded_vclip_loss on the no-sampling branch (vclipLoss.py:104-108: distribution
+    means -> ClipLoss.forward) + global KL / var-reg means, against the same formula evaluated
+    on the concatenated batch with the oracle's CLIP loss (the sampling branch needs the CUDA
+    sampler kernels; its sharded CLIP term is covered by the forward_sampled test above)."""
+    from multimodal_2025_b200.losses.distributions.power_spherical import (HypersphericalUniform,
+                                                                           PowerSpherical)
+    from oracle import losses_oracle as O
+    world, n, d = 2, 18, 16
+    res = _run_world(_worker_vclip, world, (n, d))
+    loc_i, loc_t, k_i, k_t = [t.clone().requires_grad_(True) for t in _vclip_inputs(n * world, d)]
+    clip = O.clip_loss(loc_i, loc_t, torch.tensor(2.6592), 0.1, True)
+    kl = lambda loc, k: torch.distributions.kl_divergence(  # noqa: E731
+        PowerSpherical(loc, k), HypersphericalUniform(dim=d)).mean()
+    kli, klt = kl(loc_i, k_i), kl(loc_t, k_t)
+    var = torch.mean((torch.log(1.0 / k_i + 1e-8) - torch.log(1.0 / k_t + 1e-8)) ** 2)
+    total = 1.0 * clip + 0.5 * 0.7 * (kli + klt) + 0.2 * var
+    total.backward()
+    for rank, out, gli, gki, gkt in res:
+        sl = slice(rank * n, (rank + 1) * n)
+        for key, want in (("total_loss", total), ("clip_loss", clip), ("image_kl_loss", kli),
+                          ("text_kl_loss", klt), ("var_reg", var)):
+            assert abs(out[key] - float(want.detach())) < 2e-5 * abs(float(want.detach())), key
+        assert (gli - loc_i.grad[sl]).norm() < 1e-4 * loc_i.grad[sl].norm()
+        assert (gki - k_i.grad[sl]).norm() < 1e-4 * k_i.grad[sl].norm()
+        assert (gkt - k_t.grad[sl]).norm() < 1e-4 * k_t.grad[sl].norm()
