@@ -193,6 +193,26 @@ def main():
     ms_t = timeit(lambda: torch.topk(scores, k, dim=1))
     emit(path="torch.topk same input (library baseline)", ms=ms_t)
 
+    # ---- retrieval ranks without the sort (rank.cu) ----------------------------------------------
+    del scores
+    from multimodal_2025_b200.metrics import get_clip_metrics, retrieval_ranks
+    for n in (8192, 32768):
+        sc = torch.randn(n, n, generator=g).to(dev)
+        ar = torch.arange(n, device=dev)
+        ms = timeit(lambda: retrieval_ranks(sc, ar, ar), reps=5, warm=2)
+        hbm_line("rank_both (rows + columns) N=%d" % n, ms, n * n * 4,
+                 "fp32 scores read once; includes the two target gathers and two memsets")
+        if n == 8192:  # what the reference does with the same matrix (train.py:348-350), on GPU
+            ms_s = timeit(lambda: (torch.argsort(sc, descending=True),
+                                   torch.argsort(sc.t(), descending=True)), reps=3, warm=1)
+            emit(path="2 x torch.argsort of the same N=8192 matrix (library baseline)", ms=ms_s)
+        del sc
+    n, dd = 32768, 512
+    xi = torch.nn.functional.normalize(torch.randn(n, dd, generator=g), dim=-1).to(dev)
+    xt = torch.nn.functional.normalize(xi + 0.05 * torch.randn(n, dd, device=dev), dim=-1)
+    ms = timeit(lambda: get_clip_metrics(xi, xt, 14.2857), reps=3, warm=1)
+    emit(path="get_clip_metrics N=32768 d=512 fp32 (GEMM + rank_both + 2 x D2H of N ints)", ms=ms)
+
 
 if __name__ == "__main__":
     main()
