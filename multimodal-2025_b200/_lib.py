@@ -16,7 +16,7 @@ LIB_DIR = os.path.join(_HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libmm25.so")
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 
-SOURCES = ["prep.cu", "sim_simt.cu", "sim_tc.cu", "sim_tc_bwd.cu", "sim_tc_mod.cu", "gemm_tc.cu",
+SOURCES = ["prep.cu", "sim_simt.cu", "sim_tc.cu", "sim_tc_bwd.cu", "sim_tc_mod.cu", "gemm_tc.cu", "gemm_tc2.cu",
            "api_sim.cu", "hopfield.cu", "samplers.cu", "beta_vmf.cu", "bessel.cu", "topk.cu", "rank.cu"]
 
 _lock = threading.Lock()

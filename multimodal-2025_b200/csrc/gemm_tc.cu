@@ -401,6 +401,12 @@ void gemm_schedule(int64_t mb0, int64_t nk0, int64_t mb1, int64_t nk1, int ngrou
 int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float* alpha_dev,
                  cudaStream_t st) {
   if (!d0 && !d1) return MM25_OK;
+  // opt-in experiment: CTA-pair kernel (gemm_tc2.cu) for the problems it covers
+  static const bool two_cta = getenv("MM25_GEMM_2CTA") != nullptr;
+  if (two_cta) {
+    const int rc2 = gemm_grouped2(d0, d1, Ng, alpha_dev, st);
+    if (rc2 != MM25_ERR_SHAPE) return rc2;
+  }
   if (!d0) { d0 = d1; d1 = nullptr; }
   if (d1 && d1->K > d0->K) { const GemmDesc* t = d0; d0 = d1; d1 = t; }
   if (!gemm_eligible(d0->Mg, Ng, d0->K)) return MM25_ERR_SHAPE;

@@ -40,6 +40,13 @@ constexpr int GEMM_MAX_PEERS = 16;
 int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float* alpha_dev,
                  cudaStream_t st);
 
+// EXPERIMENTAL CTA-pair (cta_group::2) variant of gemm_grouped (gemm_tc2.cu), taken only when
+// the environment variable MM25_GEMM_2CTA is set.  Returns MM25_ERR_SHAPE for problems it does
+// not cover (scatter, split-K, batched, odd 128-row block counts): gemm_grouped then runs the
+// 1-CTA kernel.
+int gemm_grouped2(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float* alpha_dev,
+                  cudaStream_t st);
+
 // single problem (wrapper over gemm_grouped)
 int gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, float* C, int64_t ldc,
               int64_t Mg, int64_t Ng, int64_t K, float alpha, const float* alpha_dev,

@@ -269,3 +269,52 @@ def test_experimental_scatter_epilogue_modes(lib_built, mode):
     r = subprocess.run([sys.executable, "-c", _SCATTER_SNIPPET.format(root=ROOT)], env=env,
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "scatter ok" in r.stdout, r.stdout + r.stderr
+
+
+_TWO_CTA_SNIPPET = r"""
+import sys, torch
+sys.path.insert(0, {root!r})
+from multimodal_2025_b200 import _lib
+L = _lib.lib()
+st = torch.cuda.current_stream().cuda_stream
+g = torch.Generator().manual_seed(1)
+for (M0, K0, M1, K1, Ng) in ((256, 2048, 2048, 256, 512), (1024, 4096, 4096, 1024, 512),
+                             (512, 1024, 1024, 512, 256), (16384, 32768, 32768, 16384, 512)):
+    G = (torch.randn(M0, K0, generator=g) * 0.1).cuda().bfloat16()
+    Y = torch.randn(K0, Ng, generator=g).cuda().bfloat16()
+    X = torch.randn(K1, Ng, generator=g).cuda().bfloat16()
+    C0 = torch.zeros(M0, Ng, device="cuda"); C1 = torch.zeros(M1, Ng, device="cuda")
+    rc = L.mm25_debug_gemm_grouped(G.data_ptr(), 0, Y.data_ptr(), 1, C0.data_ptr(), M0, K0,
+                                   G.data_ptr(), 1, X.data_ptr(), 1, C1.data_ptr(), M1, K1, Ng, st)
+    assert rc == 0, rc
+    torch.cuda.synchronize()
+    r0 = G.float() @ Y.float(); r1 = G.float().t() @ X.float()
+    for C, r in ((C0, r0), (C1, r1)):
+        err = (C - r).abs().max().item()
+        assert err < 1e-2 * max(1.0, r.abs().max().item() / 10), (M0, K0, err)
+# single problem, K-major B, accumulate + alpha
+A = torch.randn(512, 256, generator=g).cuda().bfloat16()
+B = torch.randn(768, 256, generator=g).cuda().bfloat16()
+C = torch.ones(512, 768, device="cuda")
+rc = L.mm25_debug_gemm_bf16(A.data_ptr(), 0, B.data_ptr(), 0, C.data_ptr(), 512, 768, 256, 0.5, 1, st)
+assert rc == 0, rc
+torch.cuda.synchronize()
+ref = 1.0 + 0.5 * (A.float() @ B.float().t())
+assert (C - ref).abs().max().item() < 1e-2 * max(1.0, ref.abs().max().item() / 10)
+print("two-cta ok")
+"""
+
+
+def test_experimental_two_cta_grouped_gemm(lib_built):
+    """MM25_GEMM_2CTA=1: the cta_group::2 variant of the grouped GEMM (gemm_tc2.cu) against
+    dense matmul through the same debug entries as the 1-CTA kernel.  Opt-in."""
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    if os.environ.get("MM25_TEST_EXPERIMENTAL") != "1":
+        pytest.skip("opt-in: MM25_TEST_EXPERIMENTAL=1 (cta_group::2 GEMM, not yet run on a GPU)")
+    env = dict(os.environ, MM25_GEMM_2CTA="1")
+    r = subprocess.run([sys.executable, "-c", _TWO_CTA_SNIPPET.format(root=ROOT)], env=env,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "two-cta ok" in r.stdout, r.stdout + r.stderr
