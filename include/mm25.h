@@ -79,6 +79,12 @@ int mm25_debug_gemm_grouped(const void* A0, int a0_mn, const void* B0, int b0_mn
 int mm25_debug_gemm_scatter(const void* A, int a_mn, const void* B, int b_mn,
                             float* const* owners, int nowners, int64_t rows_per_rank,
                             int self_rank, int64_t Mg, int64_t Ng, int64_t K, void* stream);
+/* host-only test hook (no device work): the static balanced schedule of the grouped GEMM for
+ * mb0 blocks of nk0 k-blocks (problem 0, walked round-robin over the groups) and mb1 blocks of
+ * nk1 (problem 1, contiguous runs sized by water-filling) on `ngroups` CTA groups.
+ * out[5] = {r, nbA, nbB, nsA, nsB}: groups [0, r) take nbA + nsA blocks, the others nbB + nsB. */
+int mm25_debug_gemm_schedule(int64_t mb0, int64_t nk0, int64_t mb1, int64_t nk1, int ngroups,
+                             int* out);
 /* 1 if the current device is compute capability 10.x, else 0. */
 int mm25_device_ok(void);
 

@@ -515,3 +515,15 @@ extern "C" int mm25_debug_gemm_scatter(const void* A, int a_mn, const void* B, i
                        rows_per_rank, self_rank, 0};
   return mm25::tc::gemm_grouped(&d, nullptr, Ng, nullptr, (cudaStream_t)stream);
 }
+
+// host-only test hook: the static schedule of the grouped GEMM (no device work).
+// out = {r, nbA, nbB, nsA, nsB}: groups [0, r) are class A (nbA round-robin blocks of problem 0,
+// then a run of nsA blocks of problem 1), the others class B.
+extern "C" int mm25_debug_gemm_schedule(int64_t mb0, int64_t nk0, int64_t mb1, int64_t nk1,
+                                        int ngroups, int* out) {
+  if (!out || ngroups < 1 || mb0 < 0 || mb1 < 0 || nk0 < 1 || (mb1 > 0 && nk1 < 1))
+    return MM25_ERR_ARG;
+  mm25::tc::gemm_schedule(mb0, nk0, mb1, nk1, ngroups, &out[0], &out[1], &out[2], &out[3],
+                          &out[4]);
+  return MM25_OK;
+}
