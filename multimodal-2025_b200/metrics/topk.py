@@ -28,14 +28,26 @@ def top_k_similarities(embeddings, query_embedding, k=5):
     return list(zip(idx[0].tolist(), val[0].tolist()))
 
 
-def top_k_indices_batched(text_emb: torch.Tensor, image_emb: torch.Tensor, k: int):
-    """indices [Q, k] of the top-k texts for every image (cosine similarity, eps 1e-8)."""
+# score slab held at once by top_k_indices_batched (fp32 bytes); 180 GB of HBM allow large slabs
+MAX_SCORE_BYTES = 16 << 30
+
+
+def top_k_indices_batched(text_emb: torch.Tensor, image_emb: torch.Tensor, k: int,
+                          max_score_bytes: int = None):
+    """indices [Q, k] of the top-k texts for every image (cosine similarity, eps 1e-8).  The
+    [Q, N_t] scores are produced in query slabs of at most `max_score_bytes` (rows are
+    independent, so the split does not change the result)."""
     t = text_emb.float()
     q = image_emb.float()
     t = t / t.norm(dim=1, keepdim=True).clamp_min(1e-8)
     q = q / q.norm(dim=1, keepdim=True).clamp_min(1e-8)
-    idx, _ = ops.topk_rows(q @ t.T, k)
-    return idx
+    budget = MAX_SCORE_BYTES if max_score_bytes is None else int(max_score_bytes)
+    rows = max(1, min(q.shape[0], budget // max(4 * t.shape[0], 1)))
+    if rows >= q.shape[0]:
+        idx, _ = ops.topk_rows(q @ t.T, k)
+        return idx
+    return torch.cat([ops.topk_rows(q[a:a + rows] @ t.T, k)[0]
+                      for a in range(0, q.shape[0], rows)])
 
 
 def top_k_score(embedding_pairs, k=5):
