@@ -293,6 +293,19 @@ class ShardedClipLoss(nn.Module):
                                     float(self.label_smoothing), bool(normalize), 4.6052, group,
                                     backend, float(self.grad_scale), int(self.impl))
 
+    def forward_sampled(self, image_features, text_features, logits_scale):
+        """ClipLoss.forward_sampled (clipLoss.py:24-79) of the GLOBAL batch: local [S, n, E]
+        sample shards -> [S] losses; always normalises, clamp 3.912."""
+        backend = self.backend
+        if backend is None:
+            from . import ops as backend
+        group = self.group if self.group is not None else dist.group.WORLD
+        if not torch.is_tensor(logits_scale):
+            logits_scale = torch.tensor(float(logits_scale), device=image_features.device)
+        return _ShardedClipSampledFn.apply(image_features, text_features, logits_scale,
+                                           float(self.label_smoothing), 3.912, group, backend,
+                                           float(self.grad_scale), int(self.impl))
+
 
 # ----------------------------------------------------------------------------------------------
 # AlignCLIP (reference AlignCLIP/align_clip/loss.py) on the row-sharded global batch
@@ -719,23 +732,6 @@ class _ShardedClipSampledFn(torch.autograd.Function):
             dist.all_reduce(dscale, group=group)
             dls = B.scale_param_grad(dscale, logits_scale, B.SCALE_LOG, clamp_max)
         return dimg, dtxt, dls, None, None, None, None, None, None
-
-
-def _sharded_forward_sampled(self, image_features, text_features, logits_scale):
-    """ClipLoss.forward_sampled (clipLoss.py:24-79) of the GLOBAL batch: local [S, n, E] sample
-    shards -> [S] losses; always normalises, clamp 3.912."""
-    backend = self.backend
-    if backend is None:
-        from . import ops as backend
-    group = self.group if self.group is not None else dist.group.WORLD
-    if not torch.is_tensor(logits_scale):
-        logits_scale = torch.tensor(float(logits_scale), device=image_features.device)
-    return _ShardedClipSampledFn.apply(image_features, text_features, logits_scale,
-                                       float(self.label_smoothing), 3.912, group, backend,
-                                       float(self.grad_scale), int(self.impl))
-
-
-ShardedClipLoss.forward_sampled = _sharded_forward_sampled
 
 
 def make_sharded_vclip_loss(group=None, backend=None, grad_scale: float = 1.0, **vclip_kwargs):
