@@ -129,3 +129,40 @@ def test_standin_rank_ties_and_specials():
         rr = torch.zeros(3, dtype=torch.int32)
         cpu_backend.rank_both(s, 0, s.gather(1, t.view(-1, 1)).view(-1), t, None, None, rr, None)
         assert rr.tolist() == want
+
+
+@pytest.mark.parametrize("n,d,budget,seed", [(67, 8, None, 0), (130, 4, 4096, 1), (33, 3, 2048, 2),
+                                             (257, 6, 40000, 3)])
+def test_host_paired_ranks_with_ties_any_slab_split(host_metrics, n, d, budget, seed):
+    """coarsely quantised features (many exactly tied scores, some tied with the target): the
+    one-shot and the two-pass slab route give the stable-sort ranks of the scores they saw."""
+    retrieval, _ = host_metrics
+    g = torch.Generator().manual_seed(seed)
+    x = torch.round(torch.randn(n, d, generator=g))
+    y = torch.round(x + 0.8 * torch.randn(n, d, generator=g))
+    i2t, t2i = retrieval.paired_ranks(x, y, 2.0, max_score_bytes=budget)
+    s = 2.0 * x @ y.t()                      # small integers: every GEMM split gives the same bits
+    ar = torch.arange(n)
+    assert (s == s.diagonal().view(-1, 1)).sum() > n      # ties with targets really occur
+    assert torch.equal(i2t.long(), MO.ranks_by_sort(s, ar))
+    assert torch.equal(t2i.long(), MO.ranks_by_sort(s.t().contiguous(), ar))
+    m = retrieval.get_clip_metrics(x, y, 2.0, max_score_bytes=budget)
+    want = MO.get_clip_metrics(x, y, 2.0)
+    for k in METRIC_KEYS:
+        assert float(m[k]) == float(want[k]), k
+
+
+def test_host_recall_at_k_with_ties_and_uneven_maps(host_metrics):
+    """tied scores and a caption map that is not the regular i*c+j layout."""
+    retrieval, _ = host_metrics
+    g = torch.Generator().manual_seed(9)
+    num_im, cpi, d = 40, 3, 4
+    im = torch.round(torch.randn(num_im, d, generator=g))
+    perm = torch.randperm(num_im * cpi, generator=g)
+    t2i = (torch.arange(num_im * cpi) // cpi)[perm]          # text q belongs to image t2i[q]
+    tx = torch.round(im[t2i] + 0.7 * torch.randn(num_im * cpi, d, generator=g))
+    i2t = torch.stack([torch.nonzero(t2i == i).view(-1) for i in range(num_im)])
+    k_vals = [1, 2, 5, 17, 120]
+    got = retrieval.recall_at_k_from_encodings(im, tx, t2i, i2t, k_vals)
+    want = MO.recall_at_k(im, tx, t2i, i2t, k_vals)
+    assert got == want
