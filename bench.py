@@ -536,7 +536,10 @@ def main():
         return
     peaks = load_peaks()
     r = run_ours(args)
-    roof = kernel_roofline(r, args, peaks)
+    try:
+        roof = kernel_roofline(r, args, peaks)
+    except Exception as e:  # noqa: BLE001 - the step timing above must still be reported
+        roof = {"bound": "tensor", "error": repr(e)[:300]}
     world, rank = r["world"], r["rank"]
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
