@@ -134,3 +134,44 @@ def _same_default(a, b):
         return float(a) == float(b)
     except ValueError:
         return False
+
+
+def _header_prototypes():
+    """name -> (return C type, [parameter C types]) parsed from include/mm25.h."""
+    src = open(os.path.join(ROOT, "include", "mm25.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    src = re.sub(r"//[^\n]*", "", src)
+    out = {}
+    for m in re.finditer(r"([A-Za-z_][\w\s\*]*?)\b(mm25_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", src, re.S):
+        ret, name, params = m.group(1).strip(), m.group(2), m.group(3).strip()
+        ptypes = []
+        if params and params != "void":
+            for p in params.split(","):
+                p = " ".join(p.split())
+                if "*" in p:
+                    ptypes.append("ptr")
+                else:
+                    ptypes.append(" ".join(p.split(" ")[:-1]))     # drop the parameter name
+        out[name] = (ret, ptypes)
+    return out
+
+
+def test_ctypes_signatures_agree_with_the_header(lib_built):
+    """every binding in _lib.SIGNATURES has the header's arity and, per position, a ctypes type of
+    the header's C type (pointer / int64_t / int / float / double / size_t / uint64_t) — a
+    mismatch here would corrupt arguments silently on the GPU box."""
+    from multimodal_2025_b200 import _lib
+    cmap = {"int64_t": ctypes.c_int64, "int": ctypes.c_int, "float": ctypes.c_float,
+            "double": ctypes.c_double, "size_t": ctypes.c_size_t, "uint64_t": ctypes.c_uint64,
+            "ptr": ctypes.c_void_p, "long long": ctypes.c_longlong}
+    rmap = {"int": ctypes.c_int, "size_t": ctypes.c_size_t, "int64_t": ctypes.c_int64,
+            "void": None, "const char*": ctypes.c_char_p, "const char *": ctypes.c_char_p,
+            "long long": ctypes.c_longlong}
+    protos = _header_prototypes()
+    assert set(protos) == set(_lib.SIGNATURES)
+    for name, (ret, ptypes) in protos.items():
+        res, args = _lib.SIGNATURES[name]
+        assert rmap[ret] == res, (name, ret, res)
+        assert len(args) == len(ptypes), (name, len(args), len(ptypes))
+        for i, (a, p) in enumerate(zip(args, ptypes)):
+            assert cmap[p] == a, (name, i, p, a)
