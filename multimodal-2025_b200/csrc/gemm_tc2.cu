@@ -20,6 +20,12 @@
 //     before the first remote arrive and before the free.
 // Not supported here (the caller falls back to the 1-CTA kernel): scatter (fused
 // reduce-scatter), split-K, batched problems, an odd number of 128-row blocks.
+// The instruction forms and who-executes-what were cross-checked against the CUTLASS headers
+// vendored under site-packages/flashinfer/data/cutlass/include (behaviour only, no code taken):
+// `SM100_TMA_2SM_LOAD_2D` (both CTAs issue, bytes complete on CTA 0's barrier),
+// `Allocator2Sm` (the same warp of BOTH CTAs allocates / frees, same smem slot),
+// `umma_arrive_multicast_2x1SM`, and the 2-SM pipeline of sm100_gemm_tma_warpspecialized.hpp
+// (leader expects the bytes of both CTAs; both epilogues release the leader's accumulator).
 // Written without GPU time left in the round: compiled (ptxas) but NOT yet run; every mbarrier
 // wait is the bounded spin of tc_common.cuh, so a protocol error traps instead of hanging.
 #include "tc_common.cuh"
