@@ -36,7 +36,7 @@ def _stale() -> bool:
         return True
     t = os.path.getmtime(LIB_PATH)
     deps = _sources() + [os.path.join(CSRC, f) for f in os.listdir(CSRC)
-                         if f.endswith((".cuh", ".h"))] + [os.path.join(INCLUDE, "mm25.h")]
+                         if f.endswith((".cuh", ".h", ".inc"))] + [os.path.join(INCLUDE, "mm25.h")]
     return any(os.path.getmtime(p) > t for p in deps)
 
 

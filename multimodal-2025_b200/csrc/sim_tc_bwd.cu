@@ -53,202 +53,27 @@ sim_grad_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                    const float* __restrict__ gout, float* __restrict__ dscale_part,
                    const float* __restrict__ Cc, float dot_bound,
                    const int* __restrict__ skip_flag, int mask_diag) {
-  // the forward kept E (grad_from_e_kernel already formed G' from it): nothing to recompute
-  if (skip_flag && *skip_flag) return;
-  extern __shared__ uint8_t smem_raw[];
-  GradSmem& sm = *reinterpret_cast<GradSmem*>(
-      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  Sweep w;
-  w.KC = d / BK; w.ntiles = (int)(N / BN); w.nseg = nseg; w.tps = tps;
-  w.nrb_per_batch = (int)(M / BM); w.first_rbg = first_rb; w.num_rbg = num_rb; w.N = N;
-  sweep_setup(sm, &tmap_a, &tmap_b);
-  const uint32_t tmem = sm.tmem_base;
-  const int nitems = num_rb * nseg;
+#define MM25_PAIR 0
+#include "sim_tc_bwd_body.inc"
+#undef MM25_PAIR
+}
 
-  if (warp == 0) {
-    if (lane == 0) sweep_producer(sm, &tmap_a, &tmap_b, w);
-  } else if (warp == 1) {
-    if (lane == 0) sweep_mma(sm, tmem, w);
-  } else {
-    const int q = warp & 3;
-    const int ew = warp - 2;
-    const int half = ew >> 2;
-    const float s = load_scale(scale, scale_kind, clamp_max);
-    const float c2 = s * LOG2E;
-    const float m2 = dot_bound * fabsf(c2);
-    const bool fast = Cc != nullptr && dot_bound > 0.f && 2.f * m2 <= SPREAD_LIMIT;
-    // per batch entry (a launch may cover several: row blocks are numbered over [B * M / 128)
-    // and every per-row / per-column array is indexed with the batch offset)
-    float go = 1.f, gs = s, k_all = s * w_all, k_diag = s * w_diag;
-    const int nrb_b = (int)(M / BM);
-    const float vmask = s != 0.f ? -10000.f / s : 0.f;  // MASKDIAG: z_ii = -10000 in the LSE
-    const bool use_col = w_col != 0.f;  // row-only losses pass a placeholder col_lse
-    // per-column operand of the epilogue: C_j (static shift) or c_j (general), staged per warp
-    const float* colv = fast ? Cc : col_lse;
-    float* ccw = sm.ccw[ew];
-    uint8_t* stage = sm.stage[ew];
-    // 64B swizzle of the staging rows: 16-byte chunk c of row r lives at chunk c ^ ((r >> 1) & 3)
-    const uint32_t st_row = smem_u32(stage) + lane * 64;
-    const uint32_t st_xor = (lane >> 1) & 3;
-    if (lane == 0) tma_prefetch_desc(&tmap_g);
-    float ds = 0.f;  // fast: sum G' v (= gout s sum G v); general: sum G v
-    uint32_t as = 0, accph = 0;
-    for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-      const int rbg = first_rb + item / nseg, seg = item % nseg;
-      const int bz = rbg / nrb_b, rb = rbg % nrb_b;
-      go = gout ? __ldg(gout + bz) : 1.f;
-      gs = go * s; k_all = gs * w_all; k_diag = gs * w_diag;
-      const float* colb = colv + (int64_t)bz * N;
-      const int64_t row = (int64_t)rb * BM + q * 32 + lane;   // row inside its batch entry
-      const int64_t dcol = row + diag_offset;
-      const float r2 = __ldg(row_lse + (int64_t)bz * M + row) * LOG2E;
-      const float Ri = gs * w_row * exp2f(m2 - r2);
-      const int32_t grow0 = (int32_t)((int64_t)(rbg - first_rb) * BM + q * 32);  // panel row
-      const int t0 = seg * tps, t1 = min(w.ntiles, t0 + tps);
-      float4 cnext = __ldg(reinterpret_cast<const float4*>(
-          colb + (int64_t)t0 * BN + half * (BN / 2) + lane * 4));
-      for (int t = t0; t < t1; ++t) {
-        const int64_t col0 = (int64_t)t * BN;
-        // stage this tile's column operands (all lanes are past the previous tile's reads)
-        __syncwarp();
-        *reinterpret_cast<float4*>(ccw + lane * 4) = cnext;
-        __syncwarp();
-        if (t + 1 < t1)
-          cnext = __ldg(reinterpret_cast<const float4*>(
-              colb + (int64_t)(t + 1) * BN + half * (BN / 2) + lane * 4));
-        mbar_wait(&sm.acc_full[as], accph);
-        tc_fence_after();
-        const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + as * BN +
-                               half * CH_PER_WARP * 32;
-
-        // DIAG is a compile-time tag: only the one chunk in 128 that crosses the warp's positives
-        // carries the per-element (j == rel) compare / select; ptxas otherwise if-converts a
-        // runtime `if (has_diag)` and every logit pays 4 extra instructions (a third of this
-        // epilogue, profiles/r1_final_ncu_summary.md)
-        auto process_t = [&](auto diag_tag, uint32_t (&r)[32], int chl) {
-          constexpr bool has_diag = decltype(diag_tag)::value;
-          const int64_t cbase = col0 + (half * CH_PER_WARP + chl) * 32;
-          const int rel = (int)min((int64_t)64, max((int64_t)-1, dcol - cbase));
-          const float4* cc4 = reinterpret_cast<const float4*>(ccw + chl * 32);
-          uint32_t packed[16];
-          if (has_diag && mask_diag) {
-            // the masked positive contributes no softmax mass; d/ds keeps the true logit
-            // (sim_simt.cu: glse = 0, base unchanged), so correct `ds` for the substitution
-            float vo = vmask;
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j == rel) { vo = __uint_as_float(r[j]); r[j] = __float_as_uint(vmask); }
-            ds = fmaf(fast ? -(k_all + k_diag) : -(w_all + w_diag) * go, vo - vmask, ds);
-          }
-          if (fast) {
-#pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
-              const float4 cc = cc4[j4];
-              const float cj[4] = {cc.x, cc.y, cc.z, cc.w};
-              float gq[4];
-#pragma unroll
-              for (int u = 0; u < 4; ++u) {
-                const int j = j4 * 4 + u;
-                const float vj = __uint_as_float(r[j]);
-                const float E = ex2_approx(fmaf(vj, c2, -m2));
-                float gg = fmaf(E, Ri + cj[u], -k_all);
-                if constexpr (has_diag) gg -= (j == rel) ? k_diag : 0.f;
-                ds = fmaf(gg, vj, ds);
-                gq[u] = gg;
-              }
-              __nv_bfloat162 lo = __floats2bfloat162_rn(gq[0], gq[1]);
-              __nv_bfloat162 hi = __floats2bfloat162_rn(gq[2], gq[3]);
-              packed[j4 * 2] = *reinterpret_cast<uint32_t*>(&lo);
-              packed[j4 * 2 + 1] = *reinterpret_cast<uint32_t*>(&hi);
-            }
-          } else {
-#pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
-              const float4 cc = cc4[j4];
-              const float cj[4] = {cc.x, cc.y, cc.z, cc.w};
-              float gq[4];
-#pragma unroll
-              for (int u = 0; u < 4; ++u) {
-                const int j = j4 * 4 + u;
-                const float vj = __uint_as_float(r[j]);
-                const float zl = vj * c2;
-                float gg = w_row * ex2_approx(zl - r2);
-                if (use_col) gg += w_col * ex2_approx(fmaf(-cj[u], LOG2E, zl));
-                gg -= w_all;
-                if constexpr (has_diag) gg -= (j == rel) ? w_diag : 0.f;
-                ds = fmaf(gg * go, vj, ds);
-                gq[u] = gg * gs;
-              }
-              __nv_bfloat162 lo = __floats2bfloat162_rn(gq[0], gq[1]);
-              __nv_bfloat162 hi = __floats2bfloat162_rn(gq[2], gq[3]);
-              packed[j4 * 2] = *reinterpret_cast<uint32_t*>(&lo);
-              packed[j4 * 2 + 1] = *reinterpret_cast<uint32_t*>(&hi);
-            }
-          }
-          // the previous TMA store of this warp must be done reading the staging buffer
-          if (lane == 0) tma_store_wait_read<0>();
-          __syncwarp();
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const uint32_t addr = st_row + ((u ^ st_xor) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr),
-                         "r"(packed[4 * u]), "r"(packed[4 * u + 1]), "r"(packed[4 * u + 2]),
-                         "r"(packed[4 * u + 3])
-                         : "memory");
-          }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_2d(&tmap_g, stage, (int32_t)cbase, grow0);
-            tma_store_commit();
-          }
-        };
-
-        // warp-uniform: does chunk `chl` cross the warp's positives?
-        const int64_t d0 = (int64_t)rb * BM + q * 32 + diag_offset;
-        auto process = [&](uint32_t (&r)[32], int chl) {
-          const int64_t cbase = col0 + (half * CH_PER_WARP + chl) * 32;
-          if ((d0 + 31 >= cbase) && (d0 < cbase + 32)) process_t(std::true_type{}, r, chl);
-          else process_t(std::false_type{}, r, chl);
-        };
-
-        // software pipeline over the warp's chunks: the TMEM load of chunk c+1 is in flight
-        // while chunk c is processed
-        static_assert(CH_PER_WARP % 2 == 0, "pipeline is unrolled by two");
-        uint32_t ra[32], rb_[32];
-        tmem_ld_32x32_issue(tbase, ra);
-        tmem_ld_wait(ra);
-#pragma unroll
-        for (int c = 0; c < CH_PER_WARP; c += 2) {
-          tmem_ld_32x32_issue(tbase + (c + 1) * 32, rb_);
-          process(ra, c);
-          tmem_ld_wait(rb_);
-          if (c + 2 < CH_PER_WARP) tmem_ld_32x32_issue(tbase + (c + 2) * 32, ra);
-          process(rb_, c + 1);
-          if (c + 2 < CH_PER_WARP) tmem_ld_wait(ra);
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.acc_empty[as]);
-        if (++as == NACC) { as = 0; accph ^= 1; }
-      }
-    }
-    if (lane == 0) tma_store_wait_all<0>();
-    // d(loss)/d(scale) partial of this CTA: gout * sum G.z/s = gout * sum G.v
-    ds = warp_sum(ds) * (fast ? (s != 0.f ? 1.f / s : 0.f) : 1.f);
-    if (lane == 0) sm.red[ew] = ds;
-    named_bar_sync(1, 32 * NEPI);
-    if (warp == 2 && lane == 0 && dscale_part) {
-      float tot = 0.f;
-#pragma unroll
-      for (int k = 0; k < NEPI; ++k) tot += sm.red[k];
-      dscale_part[blockIdx.x] = tot;
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 512);
+// EXPERIMENTAL (MM25_SWEEP_2CTA=1): clusters of two CTAs; `tmap_b` must have 128-row boxes;
+// num_rb, first_rb and M / 128 even, grid even.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FWD_THREADS, 1)
+sim_grad_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                   const __grid_constant__ CUtensorMap tmap_b,
+                   const __grid_constant__ CUtensorMap tmap_g, int64_t M, int64_t N, int d,
+                   int first_rb, int num_rb, int nseg, int tps, const float* __restrict__ scale,
+                   int scale_kind, float clamp_max, int64_t diag_offset,
+                   const float* __restrict__ row_lse, const float* __restrict__ col_lse,
+                   float w_row, float w_col, float w_diag, float w_all,
+                   const float* __restrict__ gout, float* __restrict__ dscale_part,
+                   const float* __restrict__ Cc, float dot_bound,
+                   const int* __restrict__ skip_flag, int mask_diag) {
+#define MM25_PAIR 1
+#include "sim_tc_bwd_body.inc"
+#undef MM25_PAIR
 }
 
 // ------------------------------------------------------------------------------------------
@@ -516,6 +341,24 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
       CUtensorMap tg;  // the [rows, N] bf16 panel, stored in 32 x 32 boxes (64B swizzle)
       rc = make_tmap_bf16(&tg, G, (uint64_t)rows, (uint64_t)N, 32, 32, 64);
       if (rc) return rc;
+      // opt-in experiment (MM25_SWEEP_2CTA=1): CTA pairs sweep 256-row super-blocks with
+      // `cta_group::2` MMAs (sim_tc_sweep.cuh); needs whole pairs of row blocks
+      static const bool sweep2 = getenv("MM25_SWEEP_2CTA") != nullptr;
+      if (sweep2 && !use_e && num_rb % 2 == 0 && (p0 / BM) % 2 == 0 && sms >= 2) {
+        CUtensorMap tb2;  // B in 128-row boxes: each CTA of a pair stages half of the 256 columns
+        rc = make_tmap_bf16(&tb2, b_b, (uint64_t)N, (uint64_t)d, BN / 2, BK);
+        if (rc) return rc;
+        const long items2 = (long)(num_rb / 2) * nseg;
+        const int pairs = (int)(items2 < sms / 2 ? items2 : sms / 2);
+        MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_grad_tc2_kernel,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem));
+        sim_grad_tc2_kernel<<<2 * pairs, FWD_THREADS, smem, st>>>(
+            ta, tb2, tg, M, N, (int)d, (int)(p0 / BM), num_rb, nseg, tps, scale, scale_kind,
+            clamp_max, diag_offset, row_lse + bz * M, col_lse ? col_lse + bz * N : cbuf, w_row,
+            w_col, w_diag, w_all, gout ? gout + bz : nullptr,
+            dscale_part ? dscale_part + part : nullptr, Cc, dot_bound, nullptr, mask_diag);
+      } else
       sim_grad_tc_kernel<<<grid, FWD_THREADS, smem, st>>>(
           ta, tb, tg, M, N, (int)d, (int)(p0 / BM), num_rb, nseg, tps, scale, scale_kind, clamp_max,
           diag_offset, row_lse + bz * M, col_lse ? col_lse + bz * N : cbuf, w_row, w_col, w_diag,

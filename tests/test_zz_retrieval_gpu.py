@@ -318,3 +318,24 @@ def test_experimental_two_cta_grouped_gemm(lib_built):
     r = subprocess.run([sys.executable, "-c", _TWO_CTA_SNIPPET.format(root=ROOT)], env=env,
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "two-cta ok" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("switch", ["MM25_SWEEP_2CTA", "MM25_GEMM_2CTA"])
+def test_experimental_pair_kernels_pass_the_tensor_core_suites(lib_built, switch):
+    """the existing tcgen05 parity suites (tests/test_tc_gpu.py, tests/test_clip_gpu.py,
+    tests/test_full_size_gpu.py) re-run with a CTA-pair experiment switched on.  Opt-in."""
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    if os.environ.get("MM25_TEST_EXPERIMENTAL") != "1":
+        pytest.skip("opt-in: MM25_TEST_EXPERIMENTAL=1 (cta_group::2 kernels, not yet run on a GPU)")
+    env = dict(os.environ)
+    env[switch] = "1"
+    env.pop("MM25_TEST_EXPERIMENTAL")      # the child must not recurse into this test
+    r = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu",
+                        os.path.join(ROOT, "tests", "test_tc_gpu.py"),
+                        os.path.join(ROOT, "tests", "test_clip_gpu.py"),
+                        os.path.join(ROOT, "tests", "test_full_size_gpu.py")],
+                       env=env, capture_output=True, text=True, timeout=1500, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
