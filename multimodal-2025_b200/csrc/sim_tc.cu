@@ -39,209 +39,26 @@ sim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                   int64_t diag_offset, float* __restrict__ row_pm, float* __restrict__ row_pl,
                   float* __restrict__ col_pm, float* __restrict__ col_pl,
                   float* __restrict__ diag, int force_slow, float dot_bound) {
-  extern __shared__ uint8_t smem_raw[];
-  FwdSmem& sm = *reinterpret_cast<FwdSmem*>(
-      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ntiles = (int)(N / BN);
-  const int nitems = total_rb * nseg;
-  Sweep w;
-  w.KC = d / BK; w.ntiles = ntiles; w.nseg = nseg; w.tps = tps;
-  w.nrb_per_batch = nrb_per_batch; w.first_rbg = 0; w.num_rbg = total_rb; w.N = N;
-  sweep_setup(sm, &tmap_a, &tmap_b);
-  const uint32_t tmem = sm.tmem_base;
+#define MM25_PAIR 0
+#include "sim_tc_fwd_body.inc"
+#undef MM25_PAIR
+}
 
-  if (warp == 0) {
-    if (lane == 0) sweep_producer(sm, &tmap_a, &tmap_b, w);
-  } else if (warp == 1) {
-    if (lane == 0) sweep_mma(sm, tmem, w);
-  } else {
-    // ===================================================================== epilogue warps
-    const int q = warp & 3;        // TMEM lane quadrant this warp may read
-    const int ew = warp - 2;       // 0..7
-    const int half = ew >> 2;      // which half of the tile's columns this warp handles
-    const float s = load_scale(scale, scale_kind, clamp_max);
-    const float c2 = s * LOG2E;
-    const float m2s = dot_bound * fabsf(c2);
-    // force_slow carries two flags: bit 0 = test hook (robust epilogue), bit 1 = MASKDIAG mode
-    // (InfoLOOB, cloobLoss.py:28-31: the positive enters the LSE as the constant -10000)
-    const bool mask_diag = (force_slow & 2) != 0;
-    const bool sums_only_ok = (force_slow & 4) == 0;  // A/B switch MM25_COL_PARTIAL_MAX
-    force_slow &= 1;
-    const float vmask = s != 0.f ? -10000.f / s : 0.f;
-    const bool fast_static = !force_slow && dot_bound > 0.f && 2.f * m2s <= SPREAD_LIMIT;
-    // E = 2^(z log2e - m2s) in bf16 is kept for the backward (static shift only): it replaces
-    // the S-tile recompute there.  e_flag tells the backward whether E is valid.
-    const bool keep_e = store_e && fast_static;
-    if (store_e && blockIdx.x == 0 && threadIdx.x == 64) *e_flag = keep_e ? 1 : 0;
-    uint8_t* stage = sm.stage[ew];
-    const uint32_t st_row = smem_u32(stage) + lane * 64;
-    const uint32_t st_xor = (lane >> 1) & 3;
-    if (keep_e && lane == 0) tma_prefetch_desc(&tmap_e);
-    uint32_t as = 0, accph = 0, buf = 0;
-    for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-      const int rbg = item / nseg, seg = item % nseg;
-      const int bz = rbg / nrb_per_batch, rb = rbg % nrb_per_batch;
-      const int64_t row = (int64_t)rb * BM + q * 32 + lane;  // row inside this batch entry
-      const int64_t dcol = row + diag_offset;                // its positive column
-      float rm = fast_static ? m2s : -INFINITY, rl = 0.f;
-      const int t0 = seg * tps, t1 = min(ntiles, t0 + tps);
-      for (int t = t0; t < t1; ++t) {
-        const int64_t col0 = (int64_t)t * BN;
-        mbar_wait(&sm.acc_full[as], accph);
-        tc_fence_after();
-        const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + as * BN +
-                               half * CH_PER_WARP * 32;
-
-        auto process = [&](uint32_t (&r)[32], int chl) {
-          const int ch = half * CH_PER_WARP + chl;
-          float v[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          const int64_t cbase = col0 + ch * 32;
-          // positive logit (warp-uniform test: this chunk crosses the warp's diagonal range)
-          {
-            const int64_t d0 = (int64_t)rb * BM + q * 32 + diag_offset;
-            if (d0 + 31 >= cbase && d0 < cbase + 32) {
-              const int rel = (int)(dcol - cbase);
-              float dv = 0.f;
-#pragma unroll
-              for (int j = 0; j < 32; ++j) dv = (j == rel) ? v[j] : dv;
-              if (rel >= 0 && rel < 32) diag[(int64_t)bz * M + row] = s * dv;
-              if (mask_diag) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = (j == rel) ? vmask : v[j];
-              }
-            }
-          }
-          float e[32];
-          float cm;
-          if (fast_static) {
-            // static shift m2s >= every z log2e: one exp per logit, no running maximum
-            float rs = 0.f;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) { e[j] = ex2_approx(fmaf(v[j], c2, -m2s)); rs += e[j]; }
-            rl += rs;
-            cm = m2s;
-            if (keep_e) {
-              uint32_t pk[16];
-#pragma unroll
-              for (int j2 = 0; j2 < 16; ++j2) {
-                __nv_bfloat162 h = __floats2bfloat162_rn(e[2 * j2], e[2 * j2 + 1]);
-                pk[j2] = *reinterpret_cast<uint32_t*>(&h);
-              }
-              if (lane == 0) tma_store_wait_read<0>();
-              __syncwarp();
-#pragma unroll
-              for (int u = 0; u < 4; ++u) {
-                const uint32_t addr = st_row + ((u ^ st_xor) << 4);
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr),
-                             "r"(pk[4 * u]), "r"(pk[4 * u + 1]), "r"(pk[4 * u + 2]),
-                             "r"(pk[4 * u + 3])
-                             : "memory");
-              }
-              fence_proxy_async_smem();
-              __syncwarp();
-              if (lane == 0) {
-                tma_store_2d(&tmap_e, stage, (int32_t)cbase,
-                             (int32_t)((int64_t)bz * M + (int64_t)rb * BM + q * 32));
-                tma_store_commit();
-              }
-            }
-          } else {
-            float tmx = v[0], tmn = v[0];
-#pragma unroll
-            for (int j = 1; j < 32; ++j) { tmx = fmaxf(tmx, v[j]); tmn = fminf(tmn, v[j]); }
-            const float bmx = warp_max(tmx), bmn = -warp_max(-tmn);
-            const float hi2 = fmaxf(bmx * c2, bmn * c2), lo2 = fminf(bmx * c2, bmn * c2);
-            if (!force_slow && hi2 - lo2 <= SPREAD_LIMIT) {
-              // fast path: one exp per logit, shared block shift
-              const float m2 = hi2;
-              float rs = 0.f;
-#pragma unroll
-              for (int j = 0; j < 32; ++j) { e[j] = ex2_approx(fmaf(v[j], c2, -m2)); rs += e[j]; }
-              const float mn = fmaxf(rm, m2);
-              rl = rl * ex2_approx(rm - mn) + rs * ex2_approx(m2 - mn);
-              rm = mn;
-              cm = m2;
-            } else {
-              // robust path: per-row and per-column shifts (two exps per logit)
-              float tz = v[0] * c2;
-#pragma unroll
-              for (int j = 1; j < 32; ++j) tz = fmaxf(tz, v[j] * c2);
-              const float mn = fmaxf(rm, tz);
-              float rs = 0.f;
-#pragma unroll
-              for (int j = 0; j < 32; ++j) rs += ex2_approx(fmaf(v[j], c2, -mn));
-              rl = rl * ex2_approx(rm - mn) + rs;
-              rm = mn;
-              cm = 0.f;
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                const float cj = warp_max(v[j] * c2);
-                e[j] = ex2_approx(fmaf(v[j], c2, -cj));
-                cm = (j == lane) ? cj : cm;
-              }
-            }
-          }
-          const float cs = butterfly_colsum(e, lane);
-          sm.colm[buf][q][ch * 32 + lane] = cm;
-          sm.cols[buf][q][ch * 32 + lane] = cs;
-        };
-
-        static_assert(CH_PER_WARP % 2 == 0, "pipeline is unrolled by two");
-        uint32_t ra[32], rb_[32];
-        tmem_ld_32x32_issue(tbase, ra);
-        tmem_ld_wait(ra);
-#pragma unroll
-        for (int c = 0; c < CH_PER_WARP; c += 2) {
-          tmem_ld_32x32_issue(tbase + (c + 1) * 32, rb_);
-          process(ra, c);
-          tmem_ld_wait(rb_);
-          if (c + 2 < CH_PER_WARP) tmem_ld_32x32_issue(tbase + (c + 2) * 32, ra);
-          process(rb_, c + 1);
-          if (c + 2 < CH_PER_WARP) tmem_ld_wait(ra);
-        }
-        // all TMEM reads of this stage are complete (wait::ld inside the load helper)
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.acc_empty[as]);
-        if (++as == NACC) { as = 0; accph ^= 1; }
-        // merge the four 32-row groups of this tile; warp ew owns columns [32 ew, 32 ew + 32)
-        named_bar_sync(1, 32 * NEPI);
-        {
-          const int c = ew * 32 + lane;   // 8 warps x 32 lanes = the tile's 256 columns
-          const int64_t o = ((int64_t)bz * nrb_per_batch + rb) * N + col0 + c;
-          if (fast_static && sums_only_ok) {
-            // every partial shares the shift m2s: plain sums, and the merge kernel knows the
-            // maximum without reading it (half the partial traffic)
-            col_pl[o] = (sm.cols[buf][0][c] + sm.cols[buf][1][c]) +
-                        (sm.cols[buf][2][c] + sm.cols[buf][3][c]);
-          } else {
-            float m = sm.colm[buf][0][c], l = sm.cols[buf][0][c];
-#pragma unroll
-            for (int g = 1; g < 4; ++g) {
-              const float m2 = sm.colm[buf][g][c], l2 = sm.cols[buf][g][c];
-              const float mn = fmaxf(m, m2);
-              l = l * ex2_approx(m - mn) + l2 * ex2_approx(m2 - mn);
-              m = mn;
-            }
-            col_pm[o] = m;
-            col_pl[o] = l;
-          }
-        }
-        buf ^= 1;
-      }
-      const int64_t o = ((int64_t)bz * nseg * 2 + seg * 2 + half) * M + row;
-      row_pm[o] = rm;
-      row_pl[o] = rl;
-    }
-    if (keep_e && lane == 0) tma_store_wait_all<0>();
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 512);
+// EXPERIMENTAL (MM25_SWEEP_2CTA=1): clusters of two CTAs; `tmap_b` must have 128-row boxes;
+// total_rb and nrb_per_batch even, grid even.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FWD_THREADS, 1)
+sim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                  const __grid_constant__ CUtensorMap tmap_b,
+                  const __grid_constant__ CUtensorMap tmap_e, int store_e,
+                  int* __restrict__ e_flag, int64_t M, int64_t N, int d,
+                  int nrb_per_batch, int total_rb, int nseg, int tps,
+                  const float* __restrict__ scale, int scale_kind, float clamp_max,
+                  int64_t diag_offset, float* __restrict__ row_pm, float* __restrict__ row_pl,
+                  float* __restrict__ col_pm, float* __restrict__ col_pl,
+                  float* __restrict__ diag, int force_slow, float dot_bound) {
+#define MM25_PAIR 1
+#include "sim_tc_fwd_body.inc"
+#undef MM25_PAIR
 }
 
 // partials are in log2-scaled units: value = 2^m * l.  Block = 32 elements x 8 partial lanes;
@@ -464,6 +281,22 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   const size_t smem = sizeof(FwdSmem) + 1024;
   MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_fwd_tc_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // opt-in experiment (MM25_SWEEP_2CTA=1): CTA pairs sweep 256-row super-blocks with
+  // `cta_group::2` MMAs (sim_tc_sweep.cuh); needs whole pairs of row blocks per batch entry
+  static const bool sweep2 = getenv("MM25_SWEEP_2CTA") != nullptr;
+  if (sweep2 && !e_out && g.nrb % 2 == 0 && sm_count() >= 2) {
+    CUtensorMap tb2;  // B in 128-row boxes: each CTA of a pair stages half of the 256 columns
+    rc = make_tmap_bf16(&tb2, b, (uint64_t)(B * N), (uint64_t)d, BN / 2, BK);
+    if (rc) return rc;
+    const long items2 = (long)(g.total_rb / 2) * g.nseg;
+    const int half = sm_count() / 2;
+    const int pairs = (int)(items2 < half ? items2 : half);
+    MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_fwd_tc2_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    sim_fwd_tc2_kernel<<<2 * pairs, FWD_THREADS, smem, st>>>(
+        ta, tb2, te, 0, e_flag, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind,
+        clamp_max, diag_offset, row_pm, row_pl, col_pm, col_pl, diag, flags, dot_bound);
+  } else
   sim_fwd_tc_kernel<<<g.grid, FWD_THREADS, smem, st>>>(
       ta, tb, te, e_out ? 1 : 0, e_flag, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind, clamp_max,
       diag_offset, row_pm, row_pl, col_pm, col_pl, diag, flags, dot_bound);
