@@ -12,6 +12,30 @@ import torch.multiprocessing as mp
 from conftest import ROOT
 
 
+def _np(obj):
+    """tensors -> numpy (recursively): results cross the process boundary BY VALUE.  A tensor put
+    on a multiprocessing queue travels as a shared-memory handle that dies with the sender, so a
+    worker that exits before the parent has rebuilt it raises FileNotFoundError in the parent."""
+    if torch.is_tensor(obj):
+        return ("__tensor__", obj.detach().cpu().numpy())
+    if isinstance(obj, dict):
+        return {k: _np(v) for k, v in obj.items()}
+    if isinstance(obj, (tuple, list)):
+        return type(obj)(_np(v) for v in obj)
+    return obj
+
+
+def _th(obj):
+    if isinstance(obj, tuple) and len(obj) == 2 and isinstance(obj[0], str) and \
+            obj[0] == "__tensor__":
+        return torch.from_numpy(obj[1].copy())
+    if isinstance(obj, dict):
+        return {k: _th(v) for k, v in obj.items()}
+    if isinstance(obj, (tuple, list)):
+        return type(obj)(_th(v) for v in obj)
+    return obj
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -34,7 +58,7 @@ def _run_world(target, world, args, attempts=2):
         for p in procs:
             p.start()
         try:
-            res = sorted([q.get(timeout=180) for _ in range(world)], key=lambda t: t[0])
+            res = sorted([_th(q.get(timeout=180)) for _ in range(world)], key=lambda t: t[0])
             ok = True
         except _queue.Empty as e:
             res, ok, last = None, False, e
@@ -68,7 +92,7 @@ def _worker(rank, world, port, q, eps, n, d, ls):
         crit = ShardedClipLoss(eps, backend=cpu_backend)
         loss = crit(xl, yl, lsp)
         (2.0 * loss).backward()
-        q.put((rank, float(loss.detach()), xl.grad.clone(), yl.grad.clone(), float(lsp.grad)))
+        q.put(_np((rank, float(loss.detach()), xl.grad.clone(), yl.grad.clone(), float(lsp.grad))))
     finally:
         dist.destroy_process_group()
 
@@ -112,9 +136,9 @@ def _worker_align(rank, world, port, q, semantic, n, d, dsem):
         out = crit(xl, yl, sc, output_dict=True, semantic_features=sem[sl] if semantic else None)
         out["total_loss"].backward()
         plain = ShardedAlignClipLoss(backend=cpu_backend)(xl.detach(), yl.detach(), sc.detach())
-        q.put((rank, float(out["total_loss"].detach()), float(out["clip_loss"].detach()),
+        q.put(_np((rank, float(out["total_loss"].detach()), float(out["clip_loss"].detach()),
                float(out["inModality_loss"].detach()), xl.grad.clone(), yl.grad.clone(),
-               float(sc.grad), float(plain)))
+               float(sc.grad), float(plain))))
     finally:
         dist.destroy_process_group()
 
@@ -183,7 +207,7 @@ def _worker_retrieval(rank, world, port, q, seed):
         y = x + 0.7 * torch.randn(n * world, d, generator=torch.Generator().manual_seed(4))
         sl = slice(rank * n, (rank + 1) * n)
         i2t, t2i = mdist.sharded_paired_ranks(x[sl], y[sl], 7.5, backend=cpu_backend)
-        q.put((rank, out, score, i2t, t2i))
+        q.put(_np((rank, out, score, i2t, t2i)))
     finally:
         dist.destroy_process_group()
 
@@ -260,7 +284,7 @@ def _worker_cloob(rank, world, port, q, n, d):
         yl = y[sl].clone().requires_grad_(True)
         loss = ShardedCLOOBLoss(30.0, 15.0, "cpu", backend=cpu_backend)(xl, yl)
         (3.0 * loss).backward()
-        q.put((rank, float(loss.detach()), xl.grad.clone(), yl.grad.clone()))
+        q.put(_np((rank, float(loss.detach()), xl.grad.clone(), yl.grad.clone())))
     finally:
         dist.destroy_process_group()
 
@@ -302,7 +326,7 @@ def _worker_sampled(rank, world, port, q, eps, S, n, d, ls):
         loss = crit.forward_sampled(xl, yl, lsp)
         w = torch.arange(1, S + 1, dtype=torch.float32)      # distinct upstream gradients
         (loss * w).sum().backward()
-        q.put((rank, loss.detach().clone(), xl.grad.clone(), yl.grad.clone(), float(lsp.grad)))
+        q.put(_np((rank, loss.detach().clone(), xl.grad.clone(), yl.grad.clone(), float(lsp.grad))))
     finally:
         dist.destroy_process_group()
 
@@ -359,8 +383,8 @@ def _worker_vclip(rank, world, port, q, n, d):
         out = crit(PowerSpherical(li, ki), PowerSpherical(lt, kt), 1.0 / ki, 1.0 / kt,
                    torch.tensor(2.6592), is_train=False)
         out["total_loss"].backward()
-        q.put((rank, {k: float(v.detach()) for k, v in out.items()}, li.grad.clone(),
-               ki.grad.clone(), kt.grad.clone()))
+        q.put(_np((rank, {k: float(v.detach()) for k, v in out.items()}, li.grad.clone(),
+               ki.grad.clone(), kt.grad.clone())))
     finally:
         dist.destroy_process_group()
 
