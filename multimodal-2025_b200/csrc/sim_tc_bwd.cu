@@ -267,6 +267,22 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
     const int grid = (int)(items < sms ? items : sms);
     if (dscale_part)
       MM25_CUDA_CHECK(cudaMemsetAsync(dscale_part, 0, sizeof(float) * bwd_nparts(B, M, N, d), st));
+    // opt-in experiment (MM25_SWEEP_2CTA=1), as in the panel loop below; pairs of row blocks
+    // must not straddle two batch entries
+    static const bool sweep2b = getenv("MM25_SWEEP_2CTA") != nullptr;
+    if (sweep2b && (M / BM) % 2 == 0 && sms >= 2) {
+      CUtensorMap tb2;
+      if ((rc = make_tmap_bf16(&tb2, b, (uint64_t)(B * N), (uint64_t)d, BN / 2, BK))) return rc;
+      const long items2 = (long)(num_rb / 2) * nseg;
+      const int pairs = (int)(items2 < sms / 2 ? items2 : sms / 2);
+      MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_grad_tc2_kernel,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)smem));
+      sim_grad_tc2_kernel<<<2 * pairs, FWD_THREADS, smem, st>>>(
+          ta, tb2, tg, M, N, (int)d, 0, num_rb, nseg, tps, scale, scale_kind, clamp_max,
+          diag_offset, row_lse, col_lse ? col_lse : cbuf, w_row, w_col, w_diag, w_all, gout,
+          dscale_part, Cc, dot_bound, nullptr, mask_diag);
+    } else
     sim_grad_tc_kernel<<<grid, FWD_THREADS, smem, st>>>(
         ta, tb, tg, M, N, (int)d, 0, num_rb, nseg, tps, scale, scale_kind, clamp_max, diag_offset,
         row_lse, col_lse ? col_lse : cbuf, w_row, w_col, w_diag, w_all, gout, dscale_part, Cc,
