@@ -2,8 +2,10 @@
 // unit test (tests/rank_keys_host_test.cc, built with g++ by tests/test_rank_keys_cpu.py) checks
 // exactly the code the kernel compiles.
 //
-// Sort order = torch's descending sort made total: larger value first, NaN above +inf, and among
-// equal keys the smaller position first (stable).  An entry is folded into ONE 64-bit composite
+// Sort order = torch's descending STABLE sort: larger value first, NaN above +inf, -0.0 == +0.0
+// (torch.argsort compares values, so the two zeros tie: AlignCLIP/main/train.py:348,
+// main/retrieval.py:69,85), and among equal values the smaller position first.
+// An entry is folded into ONE 64-bit composite
 //     (key << 32) | (0xFFFFFFFF - position)
 // so that "sorts ahead of the target" is a single unsigned 64-bit compare:
 //     ahead(e, t)  <=>  composite(e) > composite(t)
@@ -21,6 +23,7 @@
 // order-preserving key of an fp32 bit pattern: key(a) < key(b) <=> a sorts after b descending
 MM25_HD uint32_t mm25_rank_key_bits(uint32_t u) {
   if ((u & 0x7FFFFFFFu) > 0x7F800000u) return 0xFFFFFFFFu;  // NaN (either sign): largest
+  if ((u << 1) == 0u) u = 0u;                               // -0.0 ties with +0.0
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 MM25_HD uint64_t mm25_rank_composite(uint32_t key, uint32_t position) {

@@ -16,7 +16,8 @@ constexpr int TK_MAXK = 2048;
 
 __device__ __forceinline__ uint32_t order_key(float f) {
   if (f != f) return 0xFFFFFFFFu;  // NaN: largest
-  const uint32_t u = __float_as_uint(f);
+  uint32_t u = __float_as_uint(f);
+  if ((u << 1) == 0u) u = 0u;  // -0.0 ties with +0.0 (torch.topk compares values)
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 __device__ __forceinline__ float key_value(uint32_t k) {

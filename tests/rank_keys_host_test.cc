@@ -2,8 +2,8 @@
 // TEST INFRASTRUCTURE: built and run by tests/test_rank_keys_cpu.py with g++.
 // For random rows with heavy ties, +-0, +-inf and NaNs, the rank obtained by COUNTING
 // composites greater than the target's must equal the target's position in a stable
-// descending sort with torch's order (NaN first, then by value, ties by index; -0 after +0
-// as distinct keys — documented divergence: torch treats -0 == +0).
+// descending sort with torch's order (NaN first, then by VALUE — so -0.0 and +0.0 tie — and
+// ties by index).  The comparator below is torch's rule, written without the key transform.
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -19,11 +19,7 @@ static uint32_t bits(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
 static bool ref_before(float a, uint32_t ia, float b, uint32_t ib) {
   const bool na = std::isnan(a), nb = std::isnan(b);
   if (na != nb) return na;                 // NaN sorts first
-  if (!na) {
-    if (a != b) return a > b;
-    const bool sa = std::signbit(a), sb = std::signbit(b);
-    if (sa != sb) return !sa;              // +0 ahead of -0 (bit-pattern keys)
-  }
+  if (!na && a != b) return a > b;         // value compare: -0.0 == +0.0
   return ia < ib;                          // stable
 }
 

@@ -25,7 +25,8 @@ def test_library_exports_every_declared_symbol(lib_built):
         assert hasattr(h, s), "libmm25.so lacks %s" % s
         assert s in _lib.SIGNATURES, "ctypes signature missing for %s" % s
     assert set(_lib.SIGNATURES) == set(syms)
-    assert b"sm_100a" in h.mm25_version.__call__() if False else True
+    h.mm25_version.restype = ctypes.c_char_p
+    assert b"sm_100a" in h.mm25_version()
 
 
 def test_version_string(lib_built):

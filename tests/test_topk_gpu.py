@@ -35,6 +35,29 @@ def test_topk_ties_and_special_values(lib_built):
     assert torch.equal(val.cpu(), ref.values)       # as a set of values torch agrees
 
 
+def test_topk_signed_zeros_tie_like_torch(lib_built):
+    """torch.topk / argsort compare VALUES: -0.0 and +0.0 tie (lowest index first here), and
+    both zeros reach the top-k of these rows (metrics/topk.py:48; orthogonal or zero rows give
+    exactly such scores)."""
+    from multimodal_2025_b200 import ops
+    s = torch.tensor([[-1.0, -0.0, 0.0, -2.0, 0.0, -0.0, -3.0, -0.5],
+                      [0.0, -0.0, -0.0, 0.0, -1.0, 1.0, -0.0, 0.0]])
+    idx, val = ops.topk_rows(s.cuda(), 3)
+    assert idx[0].tolist() == [1, 2, 4]
+    assert idx[1].tolist() == [5, 0, 1]
+    order = torch.sort(s, dim=1, descending=True, stable=True).indices[:, :3]
+    assert torch.equal(idx.cpu(), order)
+    # the VALUES come back with their own sign bit (gathered from the row, not from the key)
+    assert torch.equal(torch.signbit(val.cpu()), torch.signbit(s.gather(1, order)))
+    g = torch.Generator().manual_seed(11)
+    big = torch.round(torch.randn(7, 5000, generator=g) * 2) / 2
+    big = torch.where(torch.rand(7, 5000, generator=g) < 0.3, -big, big)  # many -0.0
+    for k in (1, 17, 700):
+        idx, _ = ops.topk_rows(big.cuda(), k)
+        want = torch.sort(big, dim=1, descending=True, stable=True).indices[:, :k]
+        assert torch.equal(idx.cpu(), want)
+
+
 def test_topk_reference_golden_and_kat(lib_built):
     from multimodal_2025_b200.metrics import top_k_score, top_k_similarities
     G = load_golden("topk.npz")

@@ -50,7 +50,10 @@ def test_rank_both_ties_and_special_values(lib_built):
     s = torch.tensor([[1.0, 3.0, 3.0, -0.0, 0.0, float("inf"), 3.0, float("-inf")],
                       [2.0, 2.0, 2.0, 2.0, 2.0, 2.0, 2.0, 2.0],
                       [float("nan"), 1.0, float("inf"), float("nan"), 0.0, -1.0, 5.0, 5.0]]).cuda()
-    for tcol, want in (([2, 4, 3], [2, 4, 1]), ([3, 0, 7], [6, 0, 4]), ([5, 7, 0], [0, 7, 0])):
+    # -0.0 == +0.0 under torch.argsort: the -0.0 at column 3 sorts AHEAD of the +0.0 at column 4
+    for tcol, want in (([2, 4, 3], [2, 4, 1]), ([3, 0, 7], [5, 0, 4]), ([5, 7, 0], [0, 7, 0]),
+                       ([4, 3, 4], [6, 3, 6])):
+        assert MO.ranks_by_sort(s.cpu(), torch.tensor(tcol)).tolist() == want
         t = torch.tensor(tcol, device="cuda")
         rr = torch.zeros(3, dtype=torch.int32, device="cuda")
         ops.rank_both(s, 0, s.gather(1, t.view(-1, 1)).view(-1).contiguous(), t, None, None, rr,
