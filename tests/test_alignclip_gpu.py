@@ -40,6 +40,45 @@ def test_nonsemantic_and_openclip_vs_reference_golden(lib_built):
     assert rel_err(gs, g2["gs"]) < 1e-4
 
 
+SEM_CASES = ["sem_text_n64", "sem_both_n64", "sem_image_n96", "sem_text_n160",
+             "sem_both_n200_ragged"]
+
+
+@pytest.mark.parametrize("tag", SEM_CASES)
+def test_semantic_branch_vs_reference_golden(lib_built, tag):
+    """fp32 CUDA path against the UNMODIFIED reference class run on CPU
+    (tests/golden/make_golden_alignsem.py; AlignCLIP/align_clip/loss.py:226-255)."""
+    from multimodal_2025_b200.losses.align_clip_loss import ClipInModalityLoss
+    g = load_golden("alignclip_sem.npz")[tag]
+    x, y, sem = T(g["x"]), T(g["y"]), T(g["sem"]).cuda()
+    s = torch.tensor(float(g["s"]))
+    st, si = (bool(v) for v in g["flags"])
+    alpha, beta = (float(v) for v in g["ab"])
+    crit = ClipInModalityLoss(alpha=alpha, beta=beta, nl_semantic_supervision=True,
+                              separate_text=st, separate_image=si)
+    loss, (gx, gy, gs) = run_ours(lambda a, b, c: crit(a, b, c, semantic_features=sem), [x, y, s])
+    assert rel_err(loss, g["loss"]) < 1e-5
+    assert rel_err(gx, g["gx"]) < 1e-4 and rel_err(gy, g["gy"]) < 1e-4
+    assert rel_err(gs, g["gs"]) < 1e-4
+    d = crit(x.cuda(), y.cuda(), s.cuda(), output_dict=True, semantic_features=sem)
+    assert rel_err(d["clip_loss"].cpu(), g["clip_loss"]) < 1e-5
+    assert rel_err(d["inModality_loss"].cpu(), g["inmod_loss"]) < 1e-5
+
+
+def test_alignclip_wrapper_vs_reference_golden(lib_built):
+    """losses/alignCLIPLoss.py:2-8 itself (always the semantic branch), reference-run golden."""
+    from multimodal_2025_b200.losses import AlignCLIPLoss
+    G = load_golden("alignclip_sem.npz")
+    c, g = G["sem_text_n64"], G["wrapper_n64"]
+    sem = T(c["sem"]).cuda()
+    w = AlignCLIPLoss()
+    loss, (gx, gy, gs) = run_ours(lambda a, b, s_: w.forward(a, b, s_, semantic_features=sem),
+                                  [T(c["x"]), T(c["y"]), torch.tensor(float(c["s"]))])
+    assert rel_err(loss, g["loss"]) < 1e-5
+    assert rel_err(gx, g["gx"]) < 1e-4 and rel_err(gy, g["gy"]) < 1e-4
+    assert rel_err(gs, g["gs"]) < 1e-4
+
+
 @pytest.mark.parametrize("n,d,dsem,sep_img", [(64, 32, 16, False), (200, 96, 48, False),
                                               (257, 64, 768, True), (512, 512, 768, False)])
 def test_semantic_branch_vs_oracle(lib_built, n, d, dsem, sep_img):

@@ -88,3 +88,27 @@ def test_alignclip_semantic_branch_consistency():
     ref = 0.5 * torch.nn.functional.cross_entropy(zt, torch.arange(64))
     assert rel_err(inm, ref) < 1e-6
     assert rel_err(clip, 2 * O.openclip_loss(x, y, s)) < 1e-6
+
+
+SEM_CASES = ["sem_text_n64", "sem_both_n64", "sem_image_n96", "sem_text_n160",
+             "sem_both_n200_ragged"]
+
+
+@pytest.mark.parametrize("tag", SEM_CASES)
+def test_alignclip_semantic_oracle_matches_reference_golden(tag):
+    """the SEMANTIC branch (loss.py:226-255) pinned by the UNMODIFIED reference class run on CPU
+    (tests/golden/make_golden_alignsem.py patches Tensor.get_device for the call only)."""
+    g = load_golden("alignclip_sem.npz")[tag]
+    x, y, sem = (torch.from_numpy(g[k]) for k in ("x", "y", "sem"))
+    s = torch.tensor(float(g["s"]))
+    st, si = (bool(v) for v in g["flags"])
+    alpha, beta = (float(v) for v in g["ab"])
+    kw = dict(alpha=alpha, beta=beta, nl_semantic_supervision=True, separate_text=st,
+              separate_image=si)
+    loss, (gx, gy, gs) = O.loss_and_grads(
+        lambda a, b, c: O.inmodality_loss(a, b, c, sem, **kw)[0], [x, y, s])
+    assert rel_err(loss, g["loss"]) < 1e-6
+    assert rel_err(gx, g["gx"]) < 1e-5 and rel_err(gy, g["gy"]) < 1e-5
+    assert rel_err(gs, g["gs"]) < 1e-5
+    tot, clip, inm = O.inmodality_loss(x, y, s, sem, **kw)
+    assert rel_err(clip, g["clip_loss"]) < 1e-6 and rel_err(inm, g["inmod_loss"]) < 1e-6
