@@ -372,7 +372,7 @@ def kernel_roofline(r, args, peaks):
         sc = ls.detach().reshape(1).float()
         off = r["rank"] * M
 
-        keep = 2 * M * N <= ops.keep_e_bytes_limit()  # as the loss modules decide
+        keep = 2 * M * N <= ops.keep_e_bytes_limit(M, N, d)  # as the loss modules decide
         kept = [None, None]
 
         def fwd():

@@ -17,6 +17,7 @@ LIB_PATH = os.path.join(LIB_DIR, "libmm25.so")
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 
 SOURCES = ["prep.cu", "sim_simt.cu", "sim_tc.cu", "sim_tc_bwd.cu", "sim_tc_mod.cu", "gemm_tc.cu", "gemm_tc2.cu",
+           "gemm_te.cu",
            "api_sim.cu", "hopfield.cu", "samplers.cu", "beta_vmf.cu", "bessel.cu", "topk.cu", "rank.cu"]
 
 _lock = threading.Lock()
@@ -92,6 +93,8 @@ SIGNATURES = {
                                        _vp, _i64, _i64, _i64, _vp]),
     "mm25_debug_gemm_scatter": (_int, [_vp, _int, _vp, _int, _vp, _int, _i64, _int, _i64, _i64, _i64,
                                        _vp]),
+    "mm25_debug_gemm_te": (_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp,
+                                  _i64, _i64, _vp]),
     "mm25_debug_gemm_schedule": (_int, [_i64, _i64, _i64, _i64, _int, _vp]),
     "mm25_rownorm_colsum_floats": (_i64, [_i64, _i64, _i64]),
     "mm25_rownorm_fwd": (_int, [_vp, _int, _vp, _int, _vp, _vp, _i64, _i64, _i64, _int, _f32, _vp]),

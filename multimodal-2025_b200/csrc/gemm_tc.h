@@ -47,6 +47,36 @@ int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float
 int gemm_grouped2(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float* alpha_dev,
                   cudaStream_t st);
 
+// ---- kept-E backward GEMMs with the E -> G' transform fused into the A-operand load (gemm_te.cu)
+// One problem  C[batch * Mg, Ng] fp32 = T(E)op[Mg, K] * Bop[K, Ng]; E is the bf16 matrix the
+// forward kept, [batch * Mg, K] (a_mn = 0) or [batch * K, Mg] (a_mn = 1) with row pitch ldE;
+// B is MN-major [batch * K, Ng].  rowf / colf: per-row / per-column factors of E's storage.
+struct GemmTeDesc {
+  const void* E;
+  int64_t ldE;
+  const void* B;
+  float* C;
+  int64_t ldc;
+  int64_t Mg, K;
+  int a_mn;
+  int batch;
+  const float* rowf;
+  const float* colf;
+  int64_t diag_offset;        // positive of E's local row r: column r + diag_offset
+  float* const* peers;        // fused reduce-scatter as in GemmDesc (rows_per_rank % 256 == 0)
+  int npeers;
+  int64_t rows_per_rank;
+  int self_rank;
+};
+bool gemm_te_eligible(int64_t Mg, int64_t Ng, int64_t K);
+int gemm_te_grouped(const GemmTeDesc* d0, const GemmTeDesc* d1, int64_t Ng, const int* e_flag,
+                    const float* consts, int zero_c, cudaStream_t st);
+// rowf [B M], colf [B N], consts [B][2] = {gs w_all, gs w_diag} of the static-shift gradient
+int te_coef(const float* row_lse, const float* col_lse, int64_t B, int64_t M, int64_t N,
+            const float* scale, int scale_kind, float clamp_max, const float* gout, float w_row,
+            float w_col, float w_diag, float w_all, float dot_bound, float* rowf, float* colf,
+            float* consts, cudaStream_t st);
+
 // single problem (wrapper over gemm_grouped)
 int gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, float* C, int64_t ldc,
               int64_t Mg, int64_t Ng, int64_t K, float alpha, const float* alpha_dev,

@@ -196,7 +196,26 @@ static bool batched_fits(int64_t B, int64_t M, int64_t N) {
          B * M < (1ll << 31) && B * N < (1ll << 31);
 }
 
+// Kept-E backward with the transform fused into the GEMM's operand load (gemm_te.cu): default
+// whenever the shapes allow; MM25_TE=0 restores the in-place pass + grouped GEMM (A/B switch).
+static bool te_enabled() {
+  static const bool on = !(getenv("MM25_TE") && atoi(getenv("MM25_TE")) == 0);
+  return on;
+}
+static bool te_shapes_ok(int64_t M, int64_t N, int64_t d, int npeers) {
+  return gemm_te_eligible(M, d, N) && gemm_te_eligible(N, d, M) &&
+         (npeers <= 0 || (N % npeers == 0 && (N / npeers) % 256 == 0));
+}
+static size_t te_ws_bytes(int64_t B, int64_t M, int64_t N) {
+  return 256 + sizeof(float) * (size_t)(B * N + B * M + 2 * B + 64) + 256;
+}
+
 size_t bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, bool with_e) {
+  if (with_e && te_enabled() && te_shapes_ok(M, N, d, 0)) {
+    const size_t legacy = 256 + (size_t)N * sizeof(float) + 256;
+    const size_t te = te_ws_bytes(B, M, N);
+    return te > legacy ? te : legacy;
+  }
   // bf16 G panel (not needed when the forward kept E: G' is formed in place there) + the [N]
   // column factors of the static-shift epilogue
   if (!with_e && batched_fits(B, M, N))
@@ -228,6 +247,81 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   const bool use_e = e_buf && dot_bound > 0.f && (!dscale_part || da || (db && !db_peers));
   if (ws_bytes < bwd_workspace_bytes(B, M, N, d, use_e)) return MM25_ERR_WORKSPACE;
   const uintptr_t ws0 = (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255);
+  if (use_e && te_enabled() && te_shapes_ok(M, N, d, db_peers ? npeers : 0) &&
+      ws_bytes >= te_ws_bytes(B, M, N)) {
+    // ---- kept E, transform fused into the GEMM (gemm_te.cu) ---------------------------------
+    float* colf = reinterpret_cast<float*>(ws0);
+    float* rowf = colf + B * N;
+    float* consts = rowf + B * M;
+    int rc = te_coef(row_lse, col_lse, B, M, N, scale, scale_kind, clamp_max, gout, w_row, w_col,
+                     w_diag, w_all, dot_bound, rowf, colf, consts, st);
+    if (rc) return rc;
+    const int sms = tc_sm_count();
+    const __nv_bfloat16* ab = (const __nv_bfloat16*)a;
+    const __nv_bfloat16* bb = (const __nv_bfloat16*)b;
+    __nv_bfloat16* E = reinterpret_cast<__nv_bfloat16*>(e_buf);
+    if (dscale_part)
+      MM25_CUDA_CHECK(cudaMemsetAsync(dscale_part, 0, sizeof(float) * 2 * B * sms, st));
+    // The forward raises *e_flag only when its static-shift epilogue ran (decided on the device
+    // from the scale).  Otherwise E holds nothing: the recompute kernel fills the same buffer
+    // with G' (it returns at once when the flag is set) and the GEMM below copies instead of
+    // transforming.
+    {
+      const size_t smem = sizeof(GradSmem) + 1024;
+      MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_grad_tc_kernel,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      const int num_rb = (int)(M / BM), ntiles = (int)(N / BN);
+      int nseg = 1;
+      {
+        double best = 0.0;
+        const int max_seg = ntiles >= 8 ? ntiles / 4 : 1;
+        for (int ns = 1; ns <= max_seg && ns <= 64; ++ns) {
+          const int tps = (ntiles + ns - 1) / ns;
+          const int sg = (ntiles + tps - 1) / tps;
+          const long items = (long)num_rb * sg;
+          const double eff = (double)items / ((double)((items + sms - 1) / sms) * sms);
+          if (eff > best + 0.01) { best = eff; nseg = sg; }
+        }
+      }
+      const int tps = (ntiles + nseg - 1) / nseg;
+      nseg = (ntiles + tps - 1) / tps;
+      const long items = (long)num_rb * nseg;
+      const int grid = (int)(items < sms ? items : sms);
+      for (int64_t bz = 0; bz < B; ++bz) {
+        CUtensorMap ta, tb, tg;
+        if ((rc = make_tmap_bf16(&ta, ab + bz * M * d, (uint64_t)M, (uint64_t)d, BM, BK))) return rc;
+        if ((rc = make_tmap_bf16(&tb, bb + bz * N * d, (uint64_t)N, (uint64_t)d, BN, BK))) return rc;
+        if ((rc = make_tmap_bf16(&tg, E + bz * M * N, (uint64_t)M, (uint64_t)N, 32, 32, 64))) return rc;
+        sim_grad_tc_kernel<<<grid, FWD_THREADS, smem, st>>>(
+            ta, tb, tg, M, N, (int)d, 0, num_rb, nseg, tps, scale, scale_kind, clamp_max,
+            diag_offset, row_lse + bz * M, col_lse ? col_lse + bz * N : colf + bz * N, w_row,
+            w_col, w_diag, w_all, gout ? gout + bz : nullptr,
+            dscale_part ? dscale_part + 2 * bz * sms : nullptr, colf + bz * N, dot_bound, e_flag,
+            mask_diag);
+        MM25_LAUNCH_CHECK();
+      }
+    }
+    const bool have_db = db != nullptr || db_peers != nullptr;
+    GemmTeDesc ga{E, N, b, da, d, M, N, 0, (int)B, rowf, colf, diag_offset, nullptr, 0, 0, 0};
+    GemmTeDesc gb{E, N, a, db, d, N, M, 1, (int)B, rowf, colf, diag_offset, db_peers, npeers,
+                  db_peers ? N / npeers : 0,
+                  db_peers ? (int)((diag_offset / M) % npeers) : 0};
+    rc = gemm_te_grouped(da ? &ga : nullptr, have_db ? &gb : nullptr, d, e_flag, consts, 1, st);
+    if (rc) return rc;
+    if (dscale_part) {
+      for (int64_t bz = 0; bz < B; ++bz) {
+        float* part = dscale_part + (2 * bz + 1) * sms;
+        if (da)
+          dscale_from_grad_kernel<<<sms, 256, 0, st>>>(ab + bz * M * d, da + bz * M * d, M * d,
+                                                       e_flag, scale, scale_kind, clamp_max, part);
+        else
+          dscale_from_grad_kernel<<<sms, 256, 0, st>>>(bb + bz * N * d, db + bz * N * d, N * d,
+                                                       e_flag, scale, scale_kind, clamp_max, part);
+        MM25_LAUNCH_CHECK();
+      }
+    }
+    return MM25_OK;
+  }
   if (!use_e && !db_peers && batched_fits(B, M, N)) {
     __nv_bfloat16* G = reinterpret_cast<__nv_bfloat16*>(ws0);
     float* cbuf = reinterpret_cast<float*>(

@@ -167,7 +167,7 @@ class _ShardedClipFn(torch.autograd.Function):
         bound = 1.01 if normalize else 0.0
         keep = (hasattr(B, "sim_fwd_keep") and xhat.is_cuda and torch.is_grad_enabled()
                 and any(ctx.needs_input_grad[:3]) and bound > 0.0 and impl != 1
-                and B.tc_eligible_bwd(xhat, yall) and 2 * n * N <= B.keep_e_bytes_limit())
+                and B.tc_eligible_bwd(xhat, yall) and 2 * n * N <= B.keep_e_bytes_limit(n, N, xhat.shape[-1]))
         e_keep = e_flag = None
         if keep:  # E = exp(z - shift) of the local [n, N] block is kept for the backward
             row_lse, cmax, csum, diag, e_keep, e_flag = B.sim_fwd_keep(

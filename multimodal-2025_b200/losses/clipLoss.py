@@ -45,7 +45,7 @@ class _ClipLossFn(torch.autograd.Function):
         N = yhat.shape[1]
         keep = (torch.is_grad_enabled() and any(ctx.needs_input_grad[:3]) and bound > 0.0
                 and impl != ops.IMPL_SIMT and ops.tc_eligible_bwd(xhat, yhat)
-                and 2 * B * M * N <= ops.keep_e_bytes_limit())
+                and 2 * B * M * N <= ops.keep_e_bytes_limit(M, N, xhat.shape[-1]))
         e_keep = e_flag = None
         if keep:
             row_lse, cmax, csum, diag, e_keep, e_flag = ops.sim_fwd_keep(

@@ -143,14 +143,21 @@ def sim_fwd_keep(a: Tensor, b: Tensor, scale: Tensor, scale_kind: int, clamp_max
                          diag_offset, want_cols, impl, dot_bound, True)
 
 
-def keep_e_bytes_limit() -> int:
-    """Largest E buffer (bytes) the losses keep for the backward (MM25_KEEP_E_GB, default 0 =
-    always recompute).  Measured on one B200 at B = 32768 (profiles/r1_keep_e.md): the E store
-    costs the epilogue-bound forward +0.23 ms and saves the backward 0.32 ms, i.e. 3.86 vs
-    3.89 ms per step, while E's extra bf16 rounding adds ~40 % to the gradient error — so the
-    S-tile recompute stays the default and this is an opt-in memory/time trade."""
+def keep_e_bytes_limit(M: int = 0, N: int = 0, d: int = 0) -> int:
+    """Largest E buffer (bytes) the losses keep for the backward.  `MM25_KEEP_E_GB` overrides.
+
+    Default: 6 GiB for shapes the fused-transform GEMM covers (csrc/gemm_te.cu: M, N, d multiples
+    of 256) — the backward then reads E inside the GEMM's operand load and neither recomputes the
+    S tiles nor makes a separate E -> G' pass; 0 (always recompute) for other shapes, where the
+    kept-E path measured no better than the recompute (profiles/r1_keep_e.md)."""
     import os
-    return int(float(os.environ.get("MM25_KEEP_E_GB", "0")) * (1 << 30))
+    env = os.environ.get("MM25_KEEP_E_GB")
+    if env is not None:
+        return int(float(env) * (1 << 30))
+    if M > 0 and M % 256 == 0 and N % 256 == 0 and d % 256 == 0 and \
+            os.environ.get("MM25_TE", "1") != "0":
+        return 6 << 30
+    return 0
 
 
 # e_keep is scratch owned by the loss's autograd node and consumed here (never an autograd-visible

@@ -1,0 +1,31 @@
+#!/usr/bin/env bash
+# generic one-GPU session: each step under its own timeout, logs into gpurun_out/<tag>_*.log
+#   gpurun --timeout 1800 -- bash tools/gpu_session.sh <tag> <step> [<step> ...]
+set -u
+cd "${GRAFT_REPO_ROOT:-.}"
+mkdir -p gpurun_out
+TAG=$1; shift
+run() { local name=$1; shift; echo "=== $name"; ( timeout "$@" ) > "gpurun_out/${TAG}_$name.log" 2>&1; echo "$name rc=$?" | tee -a "gpurun_out/${TAG}_summary.txt"; }
+for step in "$@"; do
+  case $step in
+    tc)        run tc 900 python -m pytest tests/test_tc_gpu.py -m gpu -q -x ;;
+    pytest)    run pytest 1500 python -m pytest tests -m gpu -q -x ;;
+    bench)     run bench 600 python bench.py --steps 10 --warmup 3 ;;
+    bench20)   run bench20 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline ;;
+    bench_te0) run bench_te0 600 env MM25_TE=0 python bench.py --steps 10 --warmup 3 --no-cpu-baseline ;;
+    bench_2cta) run bench_2cta 600 env MM25_TE=0 MM25_GEMM_2CTA=1 python bench.py --steps 10 --warmup 3 --no-cpu-baseline ;;
+    paths)     run paths 1200 python tools/bench_paths.py ;;
+    launches)  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-graph > "gpurun_out/${TAG}_plain.log" 2>&1 && \
+               timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
+                 --log-file "gpurun_out/${TAG}_launches.csv" python bench.py --steps 2 --warmup 3 \
+                 --no-cpu-baseline --no-graph > "gpurun_out/${TAG}_ncu_launches.log" 2>&1
+               echo "launches rc=$?" | tee -a "gpurun_out/${TAG}_summary.txt" ;;
+    ncufull)   python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-graph > "gpurun_out/${TAG}_plain2.log" 2>&1 && \
+               timeout 1200 ncu --set full --clock-control none --import-source on \
+                 -k regex:"sim_fwd_tc|gemm_te|sim_grad_tc|gemm_grouped" -s 4 -c 3 -o "gpurun_out/${TAG}_prof" \
+                 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-graph > "gpurun_out/${TAG}_ncu_full.log" 2>&1
+               echo "ncufull rc=$?" | tee -a "gpurun_out/${TAG}_summary.txt" ;;
+    *) echo "unknown step $step" ;;
+  esac
+done
+cat "gpurun_out/${TAG}_summary.txt"
