@@ -38,6 +38,16 @@ enum {
   MM25_ERR_ARG = -7
 };
 
+/* slots of the per-kernel timing hook (mm25_debug_timing) */
+enum {
+  MM25_T_SIM_FWD = 0,      /* sim_fwd_tc_kernel */
+  MM25_T_GEMM_TE = 1,      /* gemm_te_kernel (kept-E backward GEMMs) */
+  MM25_T_SIM_GRAD = 2,     /* sim_grad_tc_kernel */
+  MM25_T_GEMM_GROUPED = 3, /* gemm_grouped_kernel / gemm_grouped2_kernel */
+  MM25_T_SIM_MOD = 4,      /* sim_mod_tc_kernel */
+  MM25_TIMING_SLOTS = 8
+};
+
 /* logit modes of the fused similarity kernels */
 enum {
   MM25_SIM_PLAIN = 0,    /* z = s * a_i.b_j                       (clipLoss.py:106; loss.py:215) */
@@ -56,6 +66,12 @@ const char* mm25_version(void);
 const char* mm25_last_cuda_error(void);
 /* number of kernels this library has launched in this process (all threads). */
 long long mm25_launch_count(void);
+/* measurement hook (bench.py `roofline`): while on, the launchers of the hot kernels bracket each
+ * launch with CUDA events on the launch stream (eager launches only; ignored during graph
+ * capture).  mm25_debug_timing(on) also clears the record.  Slots: the MM25_T_* enum above. */
+void mm25_debug_timing(int on);
+/* summed duration (ms) and number of recorded launches of a slot; synchronises on the events. */
+int mm25_debug_timing_read(int slot, double* ms_total, long long* launches);
 /* test hook: non-zero forces the robust (two-exp) epilogue path of the tcgen05 forward. */
 void mm25_debug_force_slow_epilogue(int on);
 /* test hook: cap (bytes) of the bf16 gradient panel of the tensor-core backward; 0 = default. */

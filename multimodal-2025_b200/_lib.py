@@ -86,6 +86,8 @@ SIGNATURES = {
     "mm25_last_cuda_error": (ctypes.c_char_p, []),
     "mm25_device_ok": (_int, []),
     "mm25_launch_count": (ctypes.c_longlong, []),
+    "mm25_debug_timing": (None, [_int]),
+    "mm25_debug_timing_read": (_int, [_int, _vp, _vp]),
     "mm25_debug_force_slow_epilogue": (None, [_int]),
     "mm25_debug_set_g_panel_bytes": (None, [_sz]),
     "mm25_debug_gemm_bf16": (_int, [_vp, _int, _vp, _int, _vp, _i64, _i64, _i64, _f32, _int, _vp]),

@@ -31,6 +31,11 @@ void count_launch();
     MM25_CUDA_CHECK(cudaGetLastError());    \
   } while (0)
 
+// kernel-timing hook (prep.cu): token = timing_begin(slot, stream); <launch>; timing_end(token, stream)
+bool timing_enabled();
+void* timing_begin(int slot, cudaStream_t st);
+void timing_end(void* tok, cudaStream_t st);
+
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
 

@@ -469,7 +469,9 @@ int gemm_grouped(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const float
   const size_t smem = sizeof(g::Smem) + 1024;
   MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_grouped_kernel<0>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  { void* tt_ = timing_begin(MM25_T_GEMM_GROUPED, st);
   gemm_grouped_kernel<0><<<ngroups * group, g::THREADS, smem, st>>>(P);
+  timing_end(tt_, st); }
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

@@ -357,7 +357,9 @@ int gemm_grouped2(const GemmDesc* d0, const GemmDesc* d1, int64_t Ng, const floa
   const size_t smem = sizeof(g2::Smem) + 1024;
   MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_grouped2_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  { void* tt_ = timing_begin(MM25_T_GEMM_GROUPED, st);
   gemm_grouped2_kernel<<<ngroups * group * 2, g2::THREADS, smem, st>>>(P);
+  timing_end(tt_, st); }
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

@@ -15,16 +15,18 @@
 // Ng = d = 512 every E element is loaded, transformed and staged exactly once per problem, and
 // the 512 TMEM columns hold the one accumulator (the K loop is thousands of k-blocks long; the
 // un-overlapped epilogue is < 1 % of a job).  Ng = 256 (mod 512) runs one MMA per k-step with
-// two accumulator stages.  Warp roles per CTA (448 threads):
+// two accumulator stages.  Warp roles per CTA (320 threads, 168 registers):
 //   warp 0      B producer: TMA loads of this CTA's half of the B tile (MN-major 64 x 64 boxes),
 //               bytes complete on the LEADER's `full` barrier (as gemm_tc2.cu);
 //   warp 1      MMA issuer (leader CTA only);
-//   warps 2-5   epilogue: TMEM -> registers -> fp32 C (plain store, or red.global.add for a
-//               tile whose K range is split between two pairs / for the fused reduce-scatter);
-//   warps 6-13  A producers: 16-byte global loads of E two k-blocks ahead (register ring),
+//   warps 2-9   A producers: 16-byte global loads of E two k-blocks ahead (register ring),
 //               transform in fp32, bf16 pack, st.shared into the SWIZZLE_128B image a TMA load
 //               of the same box would have produced, fence.proxy.async, one arrive per warp on
-//               the leader's `full` barrier (count 1 + 16).
+//               the leader's `full` barrier (count 1 + 16);
+//   warps 2-5   after the last k-block of a piece also run its epilogue (the one accumulator
+//               cannot overlap the next piece anyway): TMEM -> registers -> fp32 C (plain
+//               store, or red.global.add for a tile whose K range is split between two pairs /
+//               for the fused reduce-scatter).
 // Work: the (problem, batch entry, 256-row super-block, 512-column tile) jobs are flattened
 // into one sequence of k-blocks that is cut into equal contiguous ranges, one per pair
 // (stream-K): every pair executes the same number of k-blocks whatever the shapes, a job is
@@ -47,8 +49,8 @@ constexpr int A_BYTES = BM * BK * 2;        // 16 KB
 constexpr int BH_BYTES = 128 * BK * 2;      // 16 KB: this CTA's 128 columns of one 256-wide MMA
 constexpr int B_BYTES = 2 * BH_BYTES;       // up to two MMAs per k-step
 constexpr int NPROD = 8;                    // A-producer warps
-constexpr int PROD0 = 6;                    // first A-producer warp (epilogue: warps 2..5)
-constexpr int THREADS = 32 * (PROD0 + NPROD);   // 448
+constexpr int PROD0 = 2;                    // first A-producer warp; warps 2..5 also run the epilogue
+constexpr int THREADS = 32 * (PROD0 + NPROD);   // 320 (168 registers per thread)
 constexpr int NFULL = 1 + 2 * NPROD;        // arrivals on the leader's `full` barrier
 
 struct Smem {
@@ -346,7 +348,7 @@ __device__ __forceinline__ void produce_piece(ge::Smem& sm, const ge::Problem& p
   }
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(144)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(ge::THREADS, 1)
 gemm_te_kernel(const __grid_constant__ ge::Params P) {
   using namespace ge;
   extern __shared__ uint8_t smem_raw[];
@@ -429,13 +431,24 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
         if (++as == (uint32_t)nacc) { as = 0; accph ^= 1; }
       }
     }
-  } else if (warp < PROD0) {
-    // ------------------------------------------------------------------ epilogue
+  } else {
+    // ------------------------------------------------------ A producers (+ epilogue, warps 2-5)
+    const int ptid = (warp - PROD0) * 32 + lane;
+    const bool epi = warp < PROD0 + 4;
     const int q = warp & 3;
-    uint32_t as = 0, accph = 0;
+    const bool xform = P.e_flag ? (__ldg(P.e_flag) != 0) : true;
+    const uint32_t full_leader0 = mapa_u32(&sm.full[0], 0);
+    uint32_t st = 0, ph = 0, as = 0, accph = 0;
     Piece pc;
     for (int g = g_begin; next_piece(P, g, g_end, &pc);) {
       const Problem& pr = P.p[pc.prob];
+      const float k_all = (xform && P.consts) ? __ldg(P.consts + 2 * pc.bz) : 0.f;
+      const float k_diag = (xform && P.consts) ? __ldg(P.consts + 2 * pc.bz + 1) : 0.f;
+      if (pr.a_mn)
+        produce_piece<true>(sm, pr, pc, (int)rank, ptid, xform, k_all, k_diag, st, ph, full_leader0);
+      else
+        produce_piece<false>(sm, pr, pc, (int)rank, ptid, xform, k_all, k_diag, st, ph, full_leader0);
+      if (!epi) continue;
       const int lrow = pc.sb * 256 + (int)rank * BM + q * 32 + lane;   // row inside the entry
       const int n0 = pc.nt * 256 * nh;
       float* crow;
@@ -470,22 +483,6 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_u32(&sm.acc_empty[as], 0));
       if (++as == (uint32_t)nacc) { as = 0; accph ^= 1; }
-    }
-  } else {
-    // ------------------------------------------------------------------ A producers
-    const int ptid = (warp - PROD0) * 32 + lane;
-    const bool xform = P.e_flag ? (__ldg(P.e_flag) != 0) : true;
-    const uint32_t full_leader0 = mapa_u32(&sm.full[0], 0);
-    uint32_t st = 0, ph = 0;
-    Piece pc;
-    for (int g = g_begin; next_piece(P, g, g_end, &pc);) {
-      const Problem& pr = P.p[pc.prob];
-      const float k_all = (xform && P.consts) ? __ldg(P.consts + 2 * pc.bz) : 0.f;
-      const float k_diag = (xform && P.consts) ? __ldg(P.consts + 2 * pc.bz + 1) : 0.f;
-      if (pr.a_mn)
-        produce_piece<true>(sm, pr, pc, (int)rank, ptid, xform, k_all, k_diag, st, ph, full_leader0);
-      else
-        produce_piece<false>(sm, pr, pc, (int)rank, ptid, xform, k_all, k_diag, st, ph, full_leader0);
     }
   }
   tc_fence_before();
@@ -618,7 +615,9 @@ int gemm_te_grouped(const GemmTeDesc* d0, const GemmTeDesc* d1, int64_t Ng, cons
   const size_t smem = sizeof(ge::Smem) + 1024;
   MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_te_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
+  { void* tt_ = timing_begin(MM25_T_GEMM_TE, st);
   gemm_te_kernel<<<2 * pairs, ge::THREADS, smem, st>>>(P);
+  timing_end(tt_, st); }
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

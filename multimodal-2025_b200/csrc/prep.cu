@@ -4,6 +4,8 @@
 #include "common.cuh"
 
 #include <atomic>
+#include <mutex>
+#include <vector>
 
 namespace mm25 {
 
@@ -11,6 +13,35 @@ static thread_local cudaError_t g_last_err = cudaSuccess;
 void set_last_error(cudaError_t e) { g_last_err = e; }
 static std::atomic<long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// ---------------------------------------------------------------------------------------
+// Per-kernel timing hook (bench.py's roofline object): when switched on, the launchers of the
+// hot kernels record a CUDA event on THEIR launch stream before and after the launch, so the
+// duration of that kernel is measured inside a real step (eager launches only: events cannot be
+// recorded into a graph capture).  Off by default: zero overhead on the product path.
+// ---------------------------------------------------------------------------------------
+static std::atomic<int> g_timing_on{0};
+static std::mutex g_timing_mu;
+struct TimingSlot { std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev; };
+static TimingSlot g_slots[MM25_TIMING_SLOTS];
+
+bool timing_enabled() { return g_timing_on.load(std::memory_order_relaxed) != 0; }
+void* timing_begin(int slot, cudaStream_t st) {
+  if (!timing_enabled() || slot < 0 || slot >= MM25_TIMING_SLOTS) return nullptr;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone)
+    return nullptr;
+  cudaEvent_t a, b;
+  if (cudaEventCreate(&a) != cudaSuccess) return nullptr;
+  if (cudaEventCreate(&b) != cudaSuccess) { cudaEventDestroy(a); return nullptr; }
+  cudaEventRecord(a, st);
+  std::lock_guard<std::mutex> lk(g_timing_mu);
+  g_slots[slot].ev.emplace_back(a, b);
+  return (void*)b;
+}
+void timing_end(void* tok, cudaStream_t st) {
+  if (tok) cudaEventRecord((cudaEvent_t)tok, st);
+}
 
 // ---------------------------------------------------------------------------------------
 // row normalise: x [rows, d] -> xhat (TO), inv_norm.  Replaces F.normalize (clipLoss.py:95-96)
@@ -381,6 +412,30 @@ using namespace mm25;
 extern "C" const char* mm25_version(void) { return "mm25 0.1 (sm_100a)"; }
 extern "C" const char* mm25_last_cuda_error(void) { return cudaGetErrorString(g_last_err); }
 extern "C" long long mm25_launch_count(void) { return g_launches.load(); }
+extern "C" void mm25_debug_timing(int on) {
+  std::lock_guard<std::mutex> lk(mm25::g_timing_mu);
+  for (auto& s : mm25::g_slots) {
+    for (auto& e : s.ev) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    s.ev.clear();
+  }
+  mm25::g_timing_on.store(on ? 1 : 0);
+}
+extern "C" int mm25_debug_timing_read(int slot, double* ms_total, long long* launches) {
+  if (slot < 0 || slot >= MM25_TIMING_SLOTS || !ms_total || !launches) return MM25_ERR_ARG;
+  std::lock_guard<std::mutex> lk(mm25::g_timing_mu);
+  double tot = 0.0;
+  long long n = 0;
+  for (auto& e : mm25::g_slots[slot].ev) {
+    if (cudaEventSynchronize(e.second) != cudaSuccess) return MM25_ERR_CUDA;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e.first, e.second) != cudaSuccess) return MM25_ERR_CUDA;
+    tot += ms;
+    ++n;
+  }
+  *ms_total = tot;
+  *launches = n;
+  return MM25_OK;
+}
 extern "C" int mm25_device_ok(void) {
   int dev = 0, major = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 0;

@@ -297,9 +297,11 @@ int launch_fwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
         ta, tb2, te, 0, e_flag, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind,
         clamp_max, diag_offset, row_pm, row_pl, col_pm, col_pl, diag, flags, dot_bound);
   } else
+  { void* tt_ = timing_begin(MM25_T_SIM_FWD, st);
   sim_fwd_tc_kernel<<<g.grid, FWD_THREADS, smem, st>>>(
       ta, tb, te, e_out ? 1 : 0, e_flag, M, N, (int)d, g.nrb, g.total_rb, g.nseg, g.tps, scale, scale_kind, clamp_max,
       diag_offset, row_pm, row_pl, col_pm, col_pl, diag, flags, dot_bound);
+  timing_end(tt_, st); }
   MM25_LAUNCH_CHECK();
   const int64_t mx = M > N ? M : N;
   fwd_tc_merge_kernel<<<dim3((unsigned)ceil_div(mx, 32), (unsigned)B), 1024, 0, st>>>(

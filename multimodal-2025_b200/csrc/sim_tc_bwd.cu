@@ -377,10 +377,12 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
           diag_offset, row_lse, col_lse ? col_lse : cbuf, w_row, w_col, w_diag, w_all, gout,
           dscale_part, Cc, dot_bound, nullptr, mask_diag);
     } else
+    { void* tt_ = timing_begin(MM25_T_SIM_GRAD, st);
     sim_grad_tc_kernel<<<grid, FWD_THREADS, smem, st>>>(
         ta, tb, tg, M, N, (int)d, 0, num_rb, nseg, tps, scale, scale_kind, clamp_max, diag_offset,
         row_lse, col_lse ? col_lse : cbuf, w_row, w_col, w_diag, w_all, gout, dscale_part, Cc,
         dot_bound, nullptr, mask_diag);
+    timing_end(tt_, st); }
     MM25_LAUNCH_CHECK();
     GemmDesc ga{G, b, da, d, M, N, 0, 1, 0, 1.f, nullptr, 0, 0, 0, (int)B};
     GemmDesc gb{G, a, db, d, N, M, 1, 1, 0, 1.f, nullptr, 0, 0, 0, (int)B};
@@ -469,12 +471,14 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
             w_col, w_diag, w_all, gout ? gout + bz : nullptr,
             dscale_part ? dscale_part + part : nullptr, Cc, dot_bound, nullptr, mask_diag);
       } else
+      { void* tt_ = timing_begin(MM25_T_SIM_GRAD, st);
       sim_grad_tc_kernel<<<grid, FWD_THREADS, smem, st>>>(
           ta, tb, tg, M, N, (int)d, (int)(p0 / BM), num_rb, nseg, tps, scale, scale_kind, clamp_max,
           diag_offset, row_lse + bz * M, col_lse ? col_lse + bz * N : cbuf, w_row, w_col, w_diag,
           w_all,
           gout ? gout + bz : nullptr, dscale_part ? dscale_part + part : nullptr, Cc,
           dot_bound, use_e ? e_flag : nullptr, mask_diag);
+      timing_end(tt_, st); }
       MM25_LAUNCH_CHECK();
       part += sms;
       {

@@ -165,7 +165,7 @@ class _ShardedClipFn(torch.autograd.Function):
             yall, ykey, ygen = _all_gather_cat(yhat[0], group).unsqueeze(0), None, 0
         # (3) local block
         bound = 1.01 if normalize else 0.0
-        keep = (hasattr(B, "sim_fwd_keep") and xhat.is_cuda and torch.is_grad_enabled()
+        keep = (hasattr(B, "sim_fwd_keep") and xhat.is_cuda
                 and any(ctx.needs_input_grad[:3]) and bound > 0.0 and impl != 1
                 and B.tc_eligible_bwd(xhat, yall) and 2 * n * N <= B.keep_e_bytes_limit(n, N, xhat.shape[-1]))
         e_keep = e_flag = None

@@ -43,7 +43,7 @@ class _ClipLossFn(torch.autograd.Function):
         # Keep E = exp(z - shift) (bf16, the activation autograd would have saved) so the
         # backward forms G' from it instead of recomputing the S tiles (include/mm25.h e_keep).
         N = yhat.shape[1]
-        keep = (torch.is_grad_enabled() and any(ctx.needs_input_grad[:3]) and bound > 0.0
+        keep = (any(ctx.needs_input_grad[:3]) and bound > 0.0
                 and impl != ops.IMPL_SIMT and ops.tc_eligible_bwd(xhat, yhat)
                 and 2 * B * M * N <= ops.keep_e_bytes_limit(M, N, xhat.shape[-1]))
         e_keep = e_flag = None
