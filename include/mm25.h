@@ -90,13 +90,14 @@ int mm25_debug_gemm_grouped(const void* A0, int a0_mn, const void* B0, int b0_mn
  * (csrc/gemm_te.cu; replaces the autograd of `logits = scale * x @ y.T` + cross_entropy,
  * losses/clipLoss.py:106-119).  E [batch * Me, Ne] bf16; C0 [batch * Me, Ng] = T(E) B0 with
  * B0 [batch * Ne, Ng]; C1 [batch * Ne, Ng] = T(E)^T B1 with B1 [batch * Me, Ng] (bf16 row-major,
- * fp32 out; either C may be NULL).  T(E)_rc = E_rc (rowf_r + colf_c) - consts[2 z]
- * (- consts[2 z + 1] where c == r + diag_offset) for entry z when *e_flag != 0, identity
- * otherwise.  Me, Ne, Ng multiples of 256. */
+ * fp32 out; either C may be NULL).  For entry z, when *e_flag != 0:
+ * T(E)_rc = E_rc (rowf_r + colf_c) - consts[2 z], except T(E)_rc = gdiag_r (fp32 [batch * Me],
+ * may be NULL) where c == r + diag_offset; identity when *e_flag == 0.
+ * Me, Ne, Ng multiples of 256. */
 int mm25_debug_gemm_te(const void* E, int64_t Me, int64_t Ne, const float* rowf,
-                       const float* colf, const float* consts, const int* e_flag,
-                       int64_t diag_offset, const void* B0, float* C0, const void* B1, float* C1,
-                       int64_t Ng, int64_t batch, void* stream);
+                       const float* colf, const float* consts, const float* gdiag,
+                       const int* e_flag, int64_t diag_offset, const void* B0, float* C0,
+                       const void* B1, float* C1, int64_t Ng, int64_t batch, void* stream);
 /* test hook: the scatter-mode GEMM of the fused reduce-scatter (mm25_sim_bwd_rs) with the owner
  * buffers as a HOST array of `nowners` device pointers to [rows_per_rank, Ng] fp32: rows
  * [q R, (q+1) R) of op(A) op(B) are ADDED into owners[q].  On one GPU the owners are local

@@ -62,6 +62,7 @@ struct GemmTeDesc {
   int batch;
   const float* rowf;
   const float* colf;
+  const float* gdiag;         // exact fp32 G' of each E row's positive (NULL: none)
   int64_t diag_offset;        // positive of E's local row r: column r + diag_offset
   float* const* peers;        // fused reduce-scatter as in GemmDesc (rows_per_rank % 256 == 0)
   int npeers;
@@ -72,10 +73,12 @@ bool gemm_te_eligible(int64_t Mg, int64_t Ng, int64_t K);
 int gemm_te_grouped(const GemmTeDesc* d0, const GemmTeDesc* d1, int64_t Ng, const int* e_flag,
                     const float* consts, int zero_c, cudaStream_t st);
 // rowf [B M], colf [B N], consts [B][2] = {gs w_all, gs w_diag} of the static-shift gradient
-int te_coef(const float* row_lse, const float* col_lse, int64_t B, int64_t M, int64_t N,
+// + gdiag [B M]: exact G' of the positives, from a_i . b_{i + diag_offset} in fp32
+int te_coef(const void* a, const void* b, int64_t d, int64_t diag_offset, const float* row_lse,
+            const float* col_lse, int64_t B, int64_t M, int64_t N,
             const float* scale, int scale_kind, float clamp_max, const float* gout, float w_row,
             float w_col, float w_diag, float w_all, float dot_bound, float* rowf, float* colf,
-            float* consts, cudaStream_t st);
+            float* consts, float* gdiag, cudaStream_t st);
 
 // single problem (wrapper over gemm_grouped)
 int gemm_bf16(const void* A, int a_mn, const void* B, int b_mn, float* C, int64_t ldc,

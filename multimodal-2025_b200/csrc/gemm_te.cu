@@ -1,7 +1,7 @@
 // gemm_te.cu — the backward GEMMs of the kept-E path, with the E -> G' transform fused into the
 // A-operand load ("transform-on-load"):
-//     C[Mg, Ng] (fp32) = T(E)op[Mg, K] * Bop[K, Ng],   T(E)_rc = E_rc (rowf_r + colf_c) - k_all
-//                                                               (- k_diag on the positives)
+//     C[Mg, Ng] (fp32) = T(E)op[Mg, K] * Bop[K, Ng],   T(E)_rc = E_rc (rowf_r + colf_c) - k_all,
+//                                                     T(E)_rp = gdiag_r on the positive p of row r
 // E [rows, cols] bf16 is what the forward kept (E = 2^(z log2e - m), sim_tc.cu); rowf / colf are
 // the per-row / per-column factors gs w_row 2^(m - r_i log2e), gs w_col 2^(m - c_j log2e)
 // (te_coef_kernel).  The two problems of the backward read E in its natural storage:
@@ -19,10 +19,11 @@
 //   warp 0      B producer: TMA loads of this CTA's half of the B tile (MN-major 64 x 64 boxes),
 //               bytes complete on the LEADER's `full` barrier (as gemm_tc2.cu);
 //   warp 1      MMA issuer (leader CTA only);
-//   warps 2-9   A producers: 16-byte global loads of E two k-blocks ahead (register ring),
-//               transform in fp32, bf16 pack, st.shared into the SWIZZLE_128B image a TMA load
-//               of the same box would have produced, fence.proxy.async, one arrive per warp on
-//               the leader's `full` barrier (count 1 + 16);
+//   warps 2-9   A producers, four groups of two warps, group g fills ring stage g: 16-byte global
+//               loads of E one whole tile ahead (register ring), transform in fp32, bf16 pack,
+//               st.shared into the SWIZZLE_128B image a TMA load of the same box would have
+//               produced, fence.proxy.async, one arrive per warp on the leader's `full` barrier
+//               (count 1 + 4);
 //   warps 2-5   after the last k-block of a piece also run its epilogue (the one accumulator
 //               cannot overlap the next piece anyway): TMEM -> registers -> fp32 C (plain
 //               store, or red.global.add for a tile whose K range is split between two pairs /
@@ -45,13 +46,15 @@ namespace ge {
 constexpr int BM = 128;        // rows per CTA (pair: 256)
 constexpr int BK = 64;
 constexpr int NST = 4;
+constexpr int PF_DIST = 12;                 // L2 prefetch distance of the A tiles, in k-blocks
 constexpr int A_BYTES = BM * BK * 2;        // 16 KB
 constexpr int BH_BYTES = 128 * BK * 2;      // 16 KB: this CTA's 128 columns of one 256-wide MMA
 constexpr int B_BYTES = 2 * BH_BYTES;       // up to two MMAs per k-step
 constexpr int NPROD = 8;                    // A-producer warps
 constexpr int PROD0 = 2;                    // first A-producer warp; warps 2..5 also run the epilogue
 constexpr int THREADS = 32 * (PROD0 + NPROD);   // 320 (168 registers per thread)
-constexpr int NFULL = 1 + 2 * NPROD;        // arrivals on the leader's `full` barrier
+constexpr int NFULL = 1 + 2 * (NPROD / NST);  // arrivals on the leader's `full` barrier: the TMA
+                                            // thread + the two warps of the stage's group per CTA
 
 struct Smem {
   uint8_t a[NST][A_BYTES];
@@ -63,10 +66,12 @@ struct Smem {
 
 struct Problem {
   CUtensorMap tb;          // B operand, MN-major: [batch * K rows, Ng cols], 64 x 64 boxes
+  CUtensorMap te;          // E itself, only for L2 prefetches of the A tiles (128 x 64 / 64 x 64 boxes)
   const __nv_bfloat16* E;  // A source
   int64_t ldE;
   const float* rowf;       // [batch * e_rows]   factor of E's memory row
   const float* colf;       // [batch * e_cols]   factor of E's memory column
+  const float* gdiag;      // [batch * e_rows]   exact fp32 G' of the positive of each E row (or NULL)
   float* C;
   int64_t ldc;
   int64_t e_rows, e_cols;  // one batch entry of E
@@ -131,8 +136,10 @@ __device__ __forceinline__ uint32_t mapa_u32(const void* p, uint32_t rank) {
   return out;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr)
-               : "memory");
+  // default semantics (.release.cta): `.release.cluster` compiles to MEMBAR.ALL.GPU + ERRBAR per
+  // arrive (8 % of the kernel's stall samples, profiles/r2_gemm_te_notes.md); the data the
+  // barrier guards is made visible to the tensor core by fence.proxy.async before the arrive
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // wait with cluster-scope acquire: the data guarded by the barrier was written by BOTH CTAs
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
@@ -157,6 +164,13 @@ __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorM
       " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(smem_dst)),
       "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster), "r"(c0), "r"(c1)
       : "memory");
+}
+// bring one box of a tensor into L2 (no shared-memory destination, no completion to wait for)
+__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* m, int32_t c0, int32_t c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(c0), "r"(c1)
+               : "memory");
 }
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
@@ -213,138 +227,161 @@ __device__ __forceinline__ uint4 transform8(const uint4 v, const float rf, const
   }
   return make_uint4(o[0], o[1], o[2], o[3]);
 }
-// same with the positive at element `rel` (0..7) of the chunk
-__device__ __forceinline__ uint4 transform8_diag(const uint4 v, const float rf,
-                                                 const float (&cf)[8], const float k_all,
-                                                 const float k_diag, const int rel) {
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-  uint32_t o[4];
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const float e0 = __uint_as_float(w[k] << 16);
-    const float e1 = __uint_as_float(w[k] & 0xffff0000u);
-    float g0 = fmaf(e0, rf + cf[2 * k], -k_all), g1 = fmaf(e1, rf + cf[2 * k + 1], -k_all);
-    if (rel == 2 * k) g0 -= k_diag;
-    if (rel == 2 * k + 1) g1 -= k_diag;
-    o[k] = pack_bf16x2(g0, g1);
-  }
-  return make_uint4(o[0], o[1], o[2], o[3]);
-}
 }  // namespace ge
 
-// A producers of one piece.  Thread `ptid` (0..255) owns the 16-byte chunks
-//   (smem row sr = it * 32 + ptid / 8, chunk cc = ptid % 8),  it = 0..3
-// of the 128 x 128-byte tile image; 8 neighbouring threads read 128 contiguous bytes of one E row.
+// A producers of one piece.  The 8 producer warps form NST = 4 groups of two warps; group g owns
+// ring stage g, i.e. the tiles t = g (mod 4) of the pair's running tile count, and fills each of
+// them ALONE: thread `gtid` (0..63) owns the 16-byte chunks
+//   (smem row sr = i * 8 + gtid / 8, chunk cc = gtid % 8),  i = 0..15
+// of the 128 x 128-byte tile image (8 neighbouring threads read 128 contiguous bytes of one E
+// row).  All 16 loads of a thread's NEXT tile are issued as soon as the current one is staged, so
+// they have the rest of the group period (4 k-blocks of MMA time, ~2.5 us) to land, and the
+// proxy fence + barrier arrive are paid once per tile and warp.
 template <bool A_MN>
 __device__ __forceinline__ void produce_piece(ge::Smem& sm, const ge::Problem& pr,
-                                              const ge::Piece& pc, const int rank, const int ptid,
-                                              const bool xform, const float k_all,
-                                              const float k_diag, uint32_t& st, uint32_t& ph,
-                                              const uint32_t full_leader0) {
+                                              const ge::Piece& pc, const int rank, const int grp,
+                                              const int gtid, const bool xform, const float k_all,
+                                              const uint32_t t0, const uint32_t full_leader0) {
   using namespace ge;
-  const int r8 = ptid >> 3, cc = ptid & 7;
-  const uint32_t dst0 = (uint32_t)(r8 * 128 + ((cc ^ (r8 & 7)) << 4));  // + it * 4096 + stage
+  const int r8 = gtid >> 3, cc = gtid & 7;
+  const uint32_t dst0 = smem_u32(sm.a[grp]) + (uint32_t)(r8 * 128 + ((cc ^ r8) << 4));  // + i * 1024
   const int64_t erow0 = (int64_t)pc.bz * pr.e_rows;   // first E row of the batch entry
   const int64_t ccol0 = (int64_t)pc.bz * pr.e_cols;   // colf offset of the batch entry
   const int m0 = pc.sb * 256 + rank * BM;             // first C row (= M index) of this CTA
   const int64_t ldE = pr.ldE;
-  // E address of chunk (it, kb):
-  //   K-major:  row m0 + it * 32 + r8,              col kb * 64 + cc * 8
-  //   MN-major: row kb * 64 + (it & 1) * 32 + r8,   col m0 + (it >> 1) * 64 + cc * 8
+  const int nkb = pc.kb1 - pc.kb0;
+  // first tile of this piece that belongs to the group: running tile t0 + j with (t0 + j) % 4 == grp
+  int j = (int)((grp - t0) & 3u);
+  if (j >= nkb) return;
+  // E address of chunk (i, kb):
+  //   K-major:  row m0 + i * 8 + r8,                     col kb * 64 + cc * 8
+  //   MN-major: row kb * 64 + (i & 7) * 8 + r8,          col m0 + (i >> 3) * 64 + cc * 8
   const __nv_bfloat16* src0;
   int64_t step;                // elements per k-block
-  const int64_t it_stride = 32 * ldE;
-  int dg0;                     // position of the positive relative to chunk (it = 0, kb = 0)
-  float rf[4];                 // K-major: row factors, fixed per piece
-  float cfix[2][8];            // MN-major: column factors, fixed per piece (at = 0, 1)
+  const int64_t i_stride = 8 * ldE;
+  // position of the positive: element `rel` of chunk i holds it when
+  //   K-major:  rel = dg0 + i * 8 - kb * 64               is in [0, 8)
+  //   MN-major: rel = dg0 + kb * 64 + (i & 7) * 8 - (i >> 3) * 64
+  int dg0;
+  const bool patch = xform && pr.gdiag != nullptr;
   if (!A_MN) {
     src0 = pr.E + (erow0 + m0 + r8) * ldE + cc * 8;
     step = BK;
-#pragma unroll
-    for (int it = 0; it < 4; ++it)
-      rf[it] = xform ? __ldg(pr.rowf + erow0 + m0 + it * 32 + r8) : 0.f;
-    // rel(it, kb) = (m0 + it * 32 + r8) + off - (kb * 64 + cc * 8)
     const int64_t t = (int64_t)m0 + r8 + pr.diag_offset - cc * 8;
     dg0 = (int)(t < -(1ll << 30) ? -(1ll << 30) : (t > (1ll << 30) ? (1ll << 30) : t));
   } else {
     src0 = pr.E + (erow0 + r8) * ldE + m0 + cc * 8;
     step = (int64_t)BK * ldE;
-    if (xform) {
+    const int64_t t = (int64_t)r8 + pr.diag_offset - m0 - cc * 8;
+    dg0 = (int)(t < -(1ll << 30) ? -(1ll << 30) : (t > (1ll << 30) ? (1ll << 30) : t));
+  }
+  // factors that are fixed for the piece: K-major rows / MN-major columns
+  float fix[16];
+  if (xform) {
+    if (!A_MN) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) fix[i] = __ldg(pr.rowf + erow0 + m0 + i * 8 + r8);
+    } else {
 #pragma unroll
       for (int at = 0; at < 2; ++at) {
         const float* cp = pr.colf + ccol0 + m0 + at * 64 + cc * 8;
         const float4 x = __ldg(reinterpret_cast<const float4*>(cp));
         const float4 y = __ldg(reinterpret_cast<const float4*>(cp + 4));
-        cfix[at][0] = x.x; cfix[at][1] = x.y; cfix[at][2] = x.z; cfix[at][3] = x.w;
-        cfix[at][4] = y.x; cfix[at][5] = y.y; cfix[at][6] = y.z; cfix[at][7] = y.w;
+        fix[at * 8 + 0] = x.x; fix[at * 8 + 1] = x.y; fix[at * 8 + 2] = x.z; fix[at * 8 + 3] = x.w;
+        fix[at * 8 + 4] = y.x; fix[at * 8 + 5] = y.y; fix[at * 8 + 6] = y.z; fix[at * 8 + 7] = y.w;
       }
     }
-    // rel(it, kb) = (kb * 64 + (it & 1) * 32 + r8) + off - (m0 + (it >> 1) * 64 + cc * 8)
-    const int64_t t = (int64_t)r8 + pr.diag_offset - m0 - cc * 8;
-    dg0 = (int)(t < -(1ll << 30) ? -(1ll << 30) : (t > (1ll << 30) ? (1ll << 30) : t));
-  }
-  const int nkb = pc.kb1 - pc.kb0;
-  uint4 buf[3][4];
-  auto load = [&](uint4 (&b)[4], int kb) {
-    const __nv_bfloat16* p = src0 + (int64_t)kb * step;
+  } else {
 #pragma unroll
-    for (int it = 0; it < 4; ++it) {
-      if (!A_MN) b[it] = ld_stream16(p + it * it_stride);
-      else b[it] = ld_stream16(p + (it & 1) * it_stride + (it >> 1) * 64);
-    }
+    for (int i = 0; i < 16; ++i) fix[i] = 0.f;
+  }
+  auto src_of = [&](int i, int kb) -> const __nv_bfloat16* {
+    const __nv_bfloat16* p = src0 + (int64_t)kb * step;
+    if (!A_MN) return p + i * i_stride;
+    return p + (i & 7) * i_stride + (i >> 3) * 64;
   };
-  auto process = [&](uint4 (&b)[4], int kb) {
-    float cf[8];
-    float r0 = 0.f, r1 = 0.f;
+  // Two phases per tile, never mixed: (1) transform + st.shared of the 16 chunks whose loads were
+  // issued a whole group period earlier, (2) issue ALL loads of the group's next tile (16 chunks
+  // + the 8 per-tile factors).  A rolling prefetch inside the transform loop serialises on the
+  // load latency: the 6 scoreboard slots are counters, so the first use of any loaded register
+  // also waits for the prefetches just issued on the same slot (measured: 3x slower).
+  uint4 buf[16];
+  float var[8];   // per-tile factors: K-major columns / MN-major rows (i and i + 8 share a row)
+  auto issue = [&](int kb) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) buf[i] = ld_stream16(src_of(i, kb));
     if (xform) {
       if (!A_MN) {
         const float* cp = pr.colf + ccol0 + (int64_t)kb * BK + cc * 8;
         const float4 x = __ldg(reinterpret_cast<const float4*>(cp));
         const float4 y = __ldg(reinterpret_cast<const float4*>(cp + 4));
-        cf[0] = x.x; cf[1] = x.y; cf[2] = x.z; cf[3] = x.w;
-        cf[4] = y.x; cf[5] = y.y; cf[6] = y.z; cf[7] = y.w;
+        var[0] = x.x; var[1] = x.y; var[2] = x.z; var[3] = x.w;
+        var[4] = y.x; var[5] = y.y; var[6] = y.z; var[7] = y.w;
       } else {
         const float* rp = pr.rowf + erow0 + (int64_t)kb * BK + r8;
-        r0 = __ldg(rp);
-        r1 = __ldg(rp + 32);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) var[u] = __ldg(rp + u * 8);
       }
     }
-    mbar_wait(&sm.empty[st], ph ^ 1);  // the MMAs that read this slot have completed
-    const uint32_t base = smem_u32(sm.a[st]) + dst0;
+  };
+  issue(pc.kb0 + j);
+  for (; j < nkb; j += NST) {
+    const int kb = pc.kb0 + j;
+    // The positive of an E row is NOT formed from the bf16 E (on trained embeddings
+    // E_ii (R_i + C_i) nearly cancels against k_diag, so E's rounding would dominate): its exact
+    // fp32 G' comes from te_diag_kernel and is patched into the staged tile.  A thread holds at
+    // most one positive per tile.
+    float gd = 0.f;
+    uint32_t gd_addr = 0;
+    if (patch) {
+      int i_hit = -1, rel = 0;
+      int64_t row = 0;
+      if (!A_MN) {
+        const int t = kb * BK - dg0;           // need i * 8 - t in [0, 8)
+        const int i = (t + 7) >> 3;
+        if (i >= 0 && i < 16) { i_hit = i; rel = i * 8 - t; row = (int64_t)m0 + i * 8 + r8; }
+      } else {
 #pragma unroll
-    for (int it = 0; it < 4; ++it) {
-      uint4 o = b[it];
-      if (xform) {
-        if (!A_MN) {
-          const int rel = dg0 + it * 32 - kb * BK;
-          if (rel >= 0 && rel < 8) o = transform8_diag(o, rf[it], cf, k_all, k_diag, rel);
-          else o = transform8(o, rf[it], cf, k_all);
-        } else {
-          const int rel = dg0 + kb * BK + (it & 1) * 32 - (it >> 1) * 64;
-          const float rfi = (it & 1) ? r1 : r0;
-          if (rel >= 0 && rel < 8) o = transform8_diag(o, rfi, cfix[it >> 1], k_all, k_diag, rel);
-          else o = transform8(o, rfi, cfix[it >> 1], k_all);
+        for (int at = 0; at < 2; ++at) {
+          const int v = dg0 + kb * BK - at * 64;   // need v + 8 b in [0, 8)
+          const int bq = (7 - v) >> 3;
+          if (bq >= 0 && bq < 8) { i_hit = at * 8 + bq; rel = v + 8 * bq; row = (int64_t)kb * BK + bq * 8 + r8; }
         }
       }
-      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(base + it * 4096),
+      if (i_hit >= 0) {
+        gd = __ldg(pr.gdiag + erow0 + row);
+        gd_addr = dst0 + (uint32_t)i_hit * 1024 + (uint32_t)rel * 2;
+      }
+    }
+    // the MMAs that read this stage (tile t - 4) have completed
+    const uint32_t use = (t0 + (uint32_t)j) >> 2;       // how many times the group used its stage
+    mbar_wait(&sm.empty[grp], (use & 1u) ^ 1u);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      uint4 o = buf[i];
+      if (xform) {
+        if (!A_MN) {
+          o = transform8(o, fix[i], var, k_all);
+        } else {
+          float cf[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) cf[u] = fix[(i >> 3) * 8 + u];
+          o = transform8(o, var[i & 7], cf, k_all);
+        }
+      }
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst0 + i * 1024),
                    "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w)
+                   : "memory");
+    }
+    if (j + NST < nkb) issue(kb + NST);   // registers are free: next tile's loads go out now
+    if (gd_addr != 0) {
+      const __nv_bfloat16 h = __float2bfloat16_rn(gd);
+      asm volatile("st.shared.b16 [%0], %1;" ::"r"(gd_addr), "h"(*reinterpret_cast<const uint16_t*>(&h))
                    : "memory");
     }
     fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core (async proxy)
     __syncwarp();
-    if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(full_leader0 + st * 8);
-    if (++st == NST) { st = 0; ph ^= 1; }
-  };
-  load(buf[0], pc.kb0);
-  if (nkb > 1) load(buf[1], pc.kb0 + 1);
-  for (int i = 0; i < nkb; i += 3) {
-#pragma unroll
-    for (int u = 0; u < 3; ++u) {
-      if (i + u < nkb) {
-        if (i + u + 2 < nkb) load(buf[(u + 2) % 3], pc.kb0 + i + u + 2);
-        process(buf[u], pc.kb0 + i + u);
-      }
-    }
+    if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(full_leader0 + grp * 8);
   }
 }
 
@@ -377,14 +414,38 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
 
   if (warp == 0) {
     // ------------------------------------------------------------------ B producer (TMA)
+    // The same thread runs an L2 prefetch cursor PF_DIST tiles ahead of the loads over this
+    // CTA's A tiles (E is streamed from HBM exactly once; the producer warps' 16-byte loads then
+    // hit L2 instead of paying the HBM latency inside their short register ring).
     if (lane == 0) {
       uint32_t st = 0, ph = 0;
-      Piece pc;
+      Piece pc, pq;
+      int gq = g_begin, kbq = 0;
+      bool have_q = next_piece(P, gq, g_end, &pq);
+      if (have_q) kbq = pq.kb0;
+      auto prefetch_one = [&]() {
+        if (!have_q) return;
+        const Problem& prq = P.p[pq.prob];
+        const int mq = pq.sb * 256 + (int)rank * BM;
+        if (prq.a_mn) {
+          const int kr = pq.bz * prq.nk * BK + kbq * BK;
+          tma_prefetch_l2_2d(&prq.te, mq, kr);
+          tma_prefetch_l2_2d(&prq.te, mq + 64, kr);
+        } else {
+          tma_prefetch_l2_2d(&prq.te, kbq * BK, pq.bz * prq.sblocks * 256 + mq);
+        }
+        if (++kbq == pq.kb1) {
+          have_q = next_piece(P, gq, g_end, &pq);
+          if (have_q) kbq = pq.kb0;
+        }
+      };
+      for (int i = 0; i < PF_DIST; ++i) prefetch_one();
       for (int g = g_begin; next_piece(P, g, g_end, &pc);) {
         const Problem& pr = P.p[pc.prob];
         const int ncol0 = pc.nt * 256 * nh + (int)rank * 128;
         const int krow0 = pc.bz * pr.nk * BK;
         for (int kb = pc.kb0; kb < pc.kb1; ++kb) {
+          prefetch_one();
           mbar_wait(&sm.empty[st], ph ^ 1);
           const uint32_t fbar = mapa_u32(&sm.full[st], 0);
           if (leader) mbar_arrive_expect_tx(&sm.full[st], 2 * nh * BH_BYTES);
@@ -412,7 +473,7 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
         tc_fence_after();
         const uint32_t dcol = tmem + as * 256;
         for (int kb = pc.kb0; kb < pc.kb1; ++kb) {
-          mbar_wait_cluster(&sm.full[st], ph);   // TMA bytes + the 16 producer warps of the pair
+          mbar_wait_cluster(&sm.full[st], ph);   // TMA bytes + the stage's producer warps of the pair
           tc_fence_after();
           const uint32_t abase = smem_u32(sm.a[st]);
           const uint32_t bbase = smem_u32(sm.b[st]);
@@ -433,21 +494,21 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
     }
   } else {
     // ------------------------------------------------------ A producers (+ epilogue, warps 2-5)
-    const int ptid = (warp - PROD0) * 32 + lane;
+    const int grp = (warp - PROD0) >> 1, gtid = ((warp - PROD0) & 1) * 32 + lane;
     const bool epi = warp < PROD0 + 4;
     const int q = warp & 3;
     const bool xform = P.e_flag ? (__ldg(P.e_flag) != 0) : true;
     const uint32_t full_leader0 = mapa_u32(&sm.full[0], 0);
-    uint32_t st = 0, ph = 0, as = 0, accph = 0;
+    uint32_t t0 = 0, as = 0, accph = 0;   // t0: tiles (k-blocks) of the pieces before this one
     Piece pc;
     for (int g = g_begin; next_piece(P, g, g_end, &pc);) {
       const Problem& pr = P.p[pc.prob];
       const float k_all = (xform && P.consts) ? __ldg(P.consts + 2 * pc.bz) : 0.f;
-      const float k_diag = (xform && P.consts) ? __ldg(P.consts + 2 * pc.bz + 1) : 0.f;
       if (pr.a_mn)
-        produce_piece<true>(sm, pr, pc, (int)rank, ptid, xform, k_all, k_diag, st, ph, full_leader0);
+        produce_piece<true>(sm, pr, pc, (int)rank, grp, gtid, xform, k_all, t0, full_leader0);
       else
-        produce_piece<false>(sm, pr, pc, (int)rank, ptid, xform, k_all, k_diag, st, ph, full_leader0);
+        produce_piece<false>(sm, pr, pc, (int)rank, grp, gtid, xform, k_all, t0, full_leader0);
+      t0 += (uint32_t)(pc.kb1 - pc.kb0);
       if (!epi) continue;
       const int lrow = pc.sb * 256 + (int)rank * BM + q * 32 + lane;   // row inside the entry
       const int n0 = pc.nt * 256 * nh;
@@ -515,6 +576,50 @@ te_coef_kernel(const float* __restrict__ row_lse, const float* __restrict__ col_
   }
 }
 
+// gdiag[i] = exact fp32 G' of the positive of row i:
+//   gs (w_row e^{z_ii - r_i} + w_col e^{z_ii - c_p} - w_diag - w_all),  p = i + diag_offset,
+// with z_ii = s a_i . b_p recomputed from the bf16 operands in fp32 (one warp per row).  Rows
+// whose positive lies outside [0, N) get 0 and are never patched.
+__global__ void __launch_bounds__(256)
+te_diag_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+               int64_t M, int64_t N, int d, int64_t diag_offset,
+               const float* __restrict__ row_lse, const float* __restrict__ col_lse,
+               const float* __restrict__ scale, int scale_kind, float clamp_max,
+               const float* __restrict__ gout, float w_row, float w_col, float w_diag,
+               float w_all, float* __restrict__ gdiag) {
+  const int64_t bz = blockIdx.y;
+  const int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= M) return;
+  const int64_t p = i + diag_offset;
+  if (p < 0 || p >= N) {
+    if (lane == 0) gdiag[bz * M + i] = 0.f;
+    return;
+  }
+  const __nv_bfloat16* ar = a + (bz * M + i) * d;
+  const __nv_bfloat16* br = b + (bz * N + p) * d;
+  float acc = 0.f;
+  for (int k = lane * 8; k < d; k += 256) {
+    const uint4 x = __ldg(reinterpret_cast<const uint4*>(ar + k));
+    const uint4 y = __ldg(reinterpret_cast<const uint4*>(br + k));
+    const uint32_t xw[4] = {x.x, x.y, x.z, x.w}, yw[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      acc = fmaf(__uint_as_float(xw[u] << 16), __uint_as_float(yw[u] << 16), acc);
+      acc = fmaf(__uint_as_float(xw[u] & 0xffff0000u), __uint_as_float(yw[u] & 0xffff0000u), acc);
+    }
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) {
+    const float s = load_scale(scale, scale_kind, clamp_max);
+    const float gs = (gout ? __ldg(gout + bz) : 1.f) * s;
+    const float z = s * acc;
+    float g = w_row * expf(z - row_lse[bz * M + i]) - w_diag - w_all;
+    if (col_lse) g += w_col * expf(z - col_lse[bz * N + p]);
+    gdiag[bz * M + i] = gs * g;
+  }
+}
+
 static int sm_count_te() {
   static int n = 0;
   if (n == 0) {
@@ -536,10 +641,15 @@ static int fill_te(ge::Problem* p, const GemmTeDesc& d, int64_t Ng, int ntiles) 
   if (nb * d.K >= (1ll << 31) || nb * d.Mg >= (1ll << 31)) return MM25_ERR_SHAPE;
   int rc = make_tmap_bf16(&p->tb, d.B, (uint64_t)(nb * d.K), (uint64_t)Ng, 64, 64);
   if (rc) return rc;
+  if (d.ldE != (d.a_mn ? d.Mg : d.K)) return MM25_ERR_SHAPE;   // E is dense
+  if (d.a_mn) rc = make_tmap_bf16(&p->te, d.E, (uint64_t)(nb * d.K), (uint64_t)d.Mg, 64, 64);
+  else rc = make_tmap_bf16(&p->te, d.E, (uint64_t)(nb * d.Mg), (uint64_t)d.K, 128, 64);
+  if (rc) return rc;
   p->E = reinterpret_cast<const __nv_bfloat16*>(d.E);
   p->ldE = d.ldE;
   p->rowf = d.rowf;
   p->colf = d.colf;
+  p->gdiag = d.gdiag;
   p->C = d.C;
   p->ldc = d.ldc;
   p->e_rows = d.a_mn ? d.K : d.Mg;
@@ -622,10 +732,17 @@ int gemm_te_grouped(const GemmTeDesc* d0, const GemmTeDesc* d1, int64_t Ng, cons
   return MM25_OK;
 }
 
-int te_coef(const float* row_lse, const float* col_lse, int64_t B, int64_t M, int64_t N,
+int te_coef(const void* a, const void* b, int64_t d, int64_t diag_offset, const float* row_lse,
+            const float* col_lse, int64_t B, int64_t M, int64_t N,
             const float* scale, int scale_kind, float clamp_max, const float* gout, float w_row,
             float w_col, float w_diag, float w_all, float dot_bound, float* rowf, float* colf,
-            float* consts, cudaStream_t st) {
+            float* consts, float* gdiag, cudaStream_t st) {
+  if (d % 8 != 0) return MM25_ERR_SHAPE;
+  te_diag_kernel<<<dim3((unsigned)((M + 7) / 8), (unsigned)B), 256, 0, st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(b), M, N,
+      (int)d, diag_offset, row_lse, col_lse, scale, scale_kind, clamp_max, gout, w_row, w_col,
+      w_diag, w_all, gdiag);
+  MM25_LAUNCH_CHECK();
   const int64_t mx = M > N ? M : N;
   te_coef_kernel<<<dim3((unsigned)((mx + 255) / 256), (unsigned)B), 256, 0, st>>>(
       row_lse, col_lse, M, N, scale, scale_kind, clamp_max, gout, w_row, w_col, w_diag, w_all,
@@ -638,17 +755,19 @@ int te_coef(const float* row_lse, const float* col_lse, int64_t B, int64_t M, in
 }  // namespace mm25
 
 // debug / test entry (tests/test_tc_gpu.py): C0 = T(E) B0 and C1 = T(E)^T B1 for a bf16
-// E [Me, Ne], with T(E)_rc = E_rc (rowf_r + colf_c) - consts[0] (- consts[1] where
-// c == r + diag_offset) when *e_flag != 0, T = identity otherwise.  B0 [Ne, Ng], B1 [Me, Ng]
+// E [Me, Ne], with T(E)_rc = E_rc (rowf_r + colf_c) - consts[2 z], and T(E)_rc = gdiag_r where
+// c == r + diag_offset (gdiag may be NULL: no special positive), when *e_flag != 0;
+// T = identity otherwise.  B0 [Ne, Ng], B1 [Me, Ng]
 // bf16 row-major; C0 [Me, Ng], C1 [Ne, Ng] fp32.  Either C may be NULL.
 extern "C" int mm25_debug_gemm_te(const void* E, int64_t Me, int64_t Ne, const float* rowf,
-                                  const float* colf, const float* consts, const int* e_flag,
-                                  int64_t diag_offset, const void* B0, float* C0, const void* B1,
-                                  float* C1, int64_t Ng, int64_t batch, void* stream) {
+                                  const float* colf, const float* consts, const float* gdiag,
+                                  const int* e_flag, int64_t diag_offset, const void* B0,
+                                  float* C0, const void* B1, float* C1, int64_t Ng, int64_t batch,
+                                  void* stream) {
   if (!E || Me <= 0 || Ne <= 0 || Ng <= 0) return MM25_ERR_ARG;
   const int nb = batch > 1 ? (int)batch : 1;
-  mm25::tc::GemmTeDesc a{E, Ne, B0, C0, Ng, Me, Ne, 0, nb, rowf, colf, diag_offset, nullptr, 0, 0, 0};
-  mm25::tc::GemmTeDesc b{E, Ne, B1, C1, Ng, Ne, Me, 1, nb, rowf, colf, diag_offset, nullptr, 0, 0, 0};
+  mm25::tc::GemmTeDesc a{E, Ne, B0, C0, Ng, Me, Ne, 0, nb, rowf, colf, gdiag, diag_offset, nullptr, 0, 0, 0};
+  mm25::tc::GemmTeDesc b{E, Ne, B1, C1, Ng, Ne, Me, 1, nb, rowf, colf, gdiag, diag_offset, nullptr, 0, 0, 0};
   return mm25::tc::gemm_te_grouped(C0 ? &a : nullptr, C1 ? &b : nullptr, Ng, e_flag, consts, 1,
                                    (cudaStream_t)stream);
 }

@@ -207,7 +207,7 @@ static bool te_shapes_ok(int64_t M, int64_t N, int64_t d, int npeers) {
          (npeers <= 0 || (N % npeers == 0 && (N / npeers) % 256 == 0));
 }
 static size_t te_ws_bytes(int64_t B, int64_t M, int64_t N) {
-  return 256 + sizeof(float) * (size_t)(B * N + B * M + 2 * B + 64) + 256;
+  return 256 + sizeof(float) * (size_t)(B * N + 2 * B * M + 2 * B + 64) + 256;
 }
 
 size_t bwd_workspace_bytes(int64_t B, int64_t M, int64_t N, int64_t d, bool with_e) {
@@ -252,9 +252,10 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
     // ---- kept E, transform fused into the GEMM (gemm_te.cu) ---------------------------------
     float* colf = reinterpret_cast<float*>(ws0);
     float* rowf = colf + B * N;
-    float* consts = rowf + B * M;
-    int rc = te_coef(row_lse, col_lse, B, M, N, scale, scale_kind, clamp_max, gout, w_row, w_col,
-                     w_diag, w_all, dot_bound, rowf, colf, consts, st);
+    float* gdiag = rowf + B * M;
+    float* consts = gdiag + B * M;
+    int rc = te_coef(a, b, d, diag_offset, row_lse, col_lse, B, M, N, scale, scale_kind, clamp_max,
+                     gout, w_row, w_col, w_diag, w_all, dot_bound, rowf, colf, consts, gdiag, st);
     if (rc) return rc;
     const int sms = tc_sm_count();
     const __nv_bfloat16* ab = (const __nv_bfloat16*)a;
@@ -302,8 +303,8 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
       }
     }
     const bool have_db = db != nullptr || db_peers != nullptr;
-    GemmTeDesc ga{E, N, b, da, d, M, N, 0, (int)B, rowf, colf, diag_offset, nullptr, 0, 0, 0};
-    GemmTeDesc gb{E, N, a, db, d, N, M, 1, (int)B, rowf, colf, diag_offset, db_peers, npeers,
+    GemmTeDesc ga{E, N, b, da, d, M, N, 0, (int)B, rowf, colf, gdiag, diag_offset, nullptr, 0, 0, 0};
+    GemmTeDesc gb{E, N, a, db, d, N, M, 1, (int)B, rowf, colf, gdiag, diag_offset, db_peers, npeers,
                   db_peers ? N / npeers : 0,
                   db_peers ? (int)((diag_offset / M) % npeers) : 0};
     rc = gemm_te_grouped(da ? &ga : nullptr, have_db ? &gb : nullptr, d, e_flag, consts, 1, st);

@@ -154,7 +154,7 @@ def test_tc_gemm_grouped_pair(lib_built, M0, K0, M1, K1, Ng):
     # shapes of the fused-transform GEMM (csrc/gemm_te.cu: M, N, d multiples of 256)
     (1, 512, 1024, 512, 256, 2.6592),    # rectangular, shifted positives
     (2, 512, 512, 1024, 0, 3.0),         # d = 1024: two 512-column tiles; batched
-    (1, 1024, 768, 256, 0, 2.0),         # d = 256: one MMA per k-step, two accumulator stages
+    (1, 768, 1024, 256, 0, 2.0),         # d = 256: one MMA per k-step, two accumulator stages
     (1, 768, 1280, 768, 0, 2.6592),      # d = 768: three 256-column tiles
     (1, 4096, 4096, 512, 0, 2.6592),     # many pairs, tiles split between two pairs (red.add)
     (1, 512, 512, 512, 0, 4.6052),       # flag 0 on an eligible shape: recompute + copy mode
@@ -224,7 +224,7 @@ def test_tc_backward_kept_e_matches_recompute(lib_built, B, M, N, d, off, ls):
 ])
 def test_gemm_te_transform_on_load_vs_torch(lib_built, Me, Ne, Ng, batch, off, flag):
     """C-ABI test entry of csrc/gemm_te.cu: C0 = T(E) B0, C1 = T(E)^T B1 with
-    T(E) = E (rowf + colf) - k_all (- k_diag on the positives), against the same arithmetic in
+    T(E) = E (rowf + colf) - k_all, T(E) = gdiag on the positives, against the same arithmetic in
     torch (bf16-rounded T(E), fp32 products)."""
     import ctypes
     from multimodal_2025_b200 import _lib
@@ -233,15 +233,15 @@ def test_gemm_te_transform_on_load_vs_torch(lib_built, Me, Ne, Ng, batch, off, f
     E = torch.rand(batch * Me, Ne, generator=g).cuda().bfloat16()
     rowf = (torch.rand(batch * Me, generator=g) * 2e-3).cuda()
     colf = (torch.rand(batch * Ne, generator=g) * 2e-3).cuda()
-    consts = torch.tensor([[3e-5, 7e-4 * (z + 1)] for z in range(batch)]).cuda().contiguous()
-    consts[:, 0] *= torch.arange(1, batch + 1, device="cuda")
+    consts = torch.tensor([[3e-5 * (z + 1), 0.0] for z in range(batch)]).cuda().contiguous()
+    gdiag = (torch.rand(batch * Me, generator=g) * 1e-3 - 5e-4).cuda()   # exact G' of positives
     e_flag = torch.tensor([flag], dtype=torch.int32, device="cuda")
     B0 = torch.randn(batch * Ne, Ng, generator=g).cuda().bfloat16()
     B1 = torch.randn(batch * Me, Ng, generator=g).cuda().bfloat16()
     C0 = torch.full((batch * Me, Ng), 7.0, device="cuda")   # the entry zeroes C itself
     C1 = torch.full((batch * Ne, Ng), 7.0, device="cuda")
     rc = L.mm25_debug_gemm_te(E.data_ptr(), Me, Ne, rowf.data_ptr(), colf.data_ptr(),
-                              consts.data_ptr(), e_flag.data_ptr(), off, B0.data_ptr(),
+                              consts.data_ptr(), gdiag.data_ptr(), e_flag.data_ptr(), off, B0.data_ptr(),
                               C0.data_ptr(), B1.data_ptr(), C1.data_ptr(), Ng, batch,
                               torch.cuda.current_stream().cuda_stream)
     assert rc == 0, rc
@@ -253,7 +253,7 @@ def test_gemm_te_transform_on_load_vs_torch(lib_built, Me, Ne, Ng, batch, off, f
                 - consts[z, 0]
             r = torch.arange(Me, device="cuda")
             ok = (r + off >= 0) & (r + off < Ne)
-            T[r[ok], (r + off)[ok]] -= consts[z, 1]
+            T[r[ok], (r + off)[ok]] = gdiag[z * Me:(z + 1) * Me][ok]
             T = T.bfloat16().float()
         else:
             T = Ez
@@ -265,13 +265,13 @@ def test_gemm_te_transform_on_load_vs_torch(lib_built, Me, Ne, Ng, batch, off, f
     # one-sided calls (only da / only db requested)
     C0b = torch.empty_like(C0)
     rc = L.mm25_debug_gemm_te(E.data_ptr(), Me, Ne, rowf.data_ptr(), colf.data_ptr(),
-                              consts.data_ptr(), e_flag.data_ptr(), off, B0.data_ptr(),
+                              consts.data_ptr(), gdiag.data_ptr(), e_flag.data_ptr(), off, B0.data_ptr(),
                               C0b.data_ptr(), None, None, Ng, batch,
                               torch.cuda.current_stream().cuda_stream)
     assert rc == 0
     C1b = torch.empty_like(C1)
     rc = L.mm25_debug_gemm_te(E.data_ptr(), Me, Ne, rowf.data_ptr(), colf.data_ptr(),
-                              consts.data_ptr(), e_flag.data_ptr(), off, None, None,
+                              consts.data_ptr(), gdiag.data_ptr(), e_flag.data_ptr(), off, None, None,
                               B1.data_ptr(), C1b.data_ptr(), Ng, batch,
                               torch.cuda.current_stream().cuda_stream)
     assert rc == 0
@@ -288,9 +288,9 @@ def test_gemm_te_rejects_bad_shapes(lib_built):
     C0 = torch.zeros(256, 256, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
     # Me not a multiple of 256
-    rc = L.mm25_debug_gemm_te(E.data_ptr(), 128, 256, f.data_ptr(), f.data_ptr(), None, None, 0,
-                              B0.data_ptr(), C0.data_ptr(), None, None, 256, 1, st)
+    rc = L.mm25_debug_gemm_te(E.data_ptr(), 128, 256, f.data_ptr(), f.data_ptr(), None, None, None,
+                              0, B0.data_ptr(), C0.data_ptr(), None, None, 256, 1, st)
     assert rc != 0
-    rc = L.mm25_debug_gemm_te(None, 256, 256, f.data_ptr(), f.data_ptr(), None, None, 0,
+    rc = L.mm25_debug_gemm_te(None, 256, 256, f.data_ptr(), f.data_ptr(), None, None, None, 0,
                               B0.data_ptr(), C0.data_ptr(), None, None, 256, 1, st)
     assert rc != 0

@@ -14,6 +14,14 @@ for step in "$@"; do
     bench20)   run bench20 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline ;;
     bench_te0) run bench_te0 600 env MM25_TE=0 python bench.py --steps 10 --warmup 3 --no-cpu-baseline ;;
     bench_2cta) run bench_2cta 600 env MM25_TE=0 MM25_GEMM_2CTA=1 python bench.py --steps 10 --warmup 3 --no-cpu-baseline ;;
+    diag)      run diag 600 python tools/diag_te.py ;;
+    diag0)     run diag0 600 env MM25_TE=0 python tools/diag_te.py ;;
+    te)        run te 600 python tools/bench_te.py ;;
+    te2)       run te2 600 env MM25_GEMM_2CTA=1 python tools/bench_te.py ;;
+    ncu_te)    python tools/bench_te.py 16384 > "gpurun_out/${TAG}_te_plain.log" 2>&1 && \
+               timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_te -s 1 -c 1 \
+                 -o "gpurun_out/${TAG}_te_prof" python tools/bench_te.py 16384 > "gpurun_out/${TAG}_ncu_te.log" 2>&1
+               echo "ncu_te rc=$?" | tee -a "gpurun_out/${TAG}_summary.txt" ;;
     paths)     run paths 1200 python tools/bench_paths.py ;;
     launches)  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-graph > "gpurun_out/${TAG}_plain.log" 2>&1 && \
                timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
