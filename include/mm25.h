@@ -98,6 +98,9 @@ int mm25_debug_gemm_te(const void* E, int64_t Me, int64_t Ne, const float* rowf,
                        const float* colf, const float* consts, const float* gdiag,
                        const int* e_flag, int64_t diag_offset, const void* B0, float* C0,
                        const void* B1, float* C1, int64_t Ng, int64_t batch, void* stream);
+/* measurement hook: cycle counters of one A-producer thread of gemm_te_kernel (8 values:
+ * load wait, stage wait, stage fill, tiles, ...); enable != 0 allocates, 0 frees; out8 may be NULL. */
+int mm25_debug_te_stats(long long* out8, int enable);
 /* test hook: the scatter-mode GEMM of the fused reduce-scatter (mm25_sim_bwd_rs) with the owner
  * buffers as a HOST array of `nowners` device pointers to [rows_per_rank, Ng] fp32: rows
  * [q R, (q+1) R) of op(A) op(B) are ADDED into owners[q].  On one GPU the owners are local

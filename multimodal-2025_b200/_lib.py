@@ -97,6 +97,7 @@ SIGNATURES = {
                                        _vp]),
     "mm25_debug_gemm_te": (_int, [_vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp,
                                   _vp, _i64, _i64, _vp]),
+    "mm25_debug_te_stats": (_int, [_vp, _int]),
     "mm25_debug_gemm_schedule": (_int, [_i64, _i64, _i64, _i64, _int, _vp]),
     "mm25_rownorm_colsum_floats": (_i64, [_i64, _i64, _i64]),
     "mm25_rownorm_fwd": (_int, [_vp, _int, _vp, _int, _vp, _vp, _i64, _i64, _i64, _int, _f32, _vp]),

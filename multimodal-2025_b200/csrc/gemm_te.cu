@@ -46,7 +46,6 @@ namespace ge {
 constexpr int BM = 128;        // rows per CTA (pair: 256)
 constexpr int BK = 64;
 constexpr int NST = 4;
-constexpr int PF_DIST = 12;                 // L2 prefetch distance of the A tiles, in k-blocks
 constexpr int A_BYTES = BM * BK * 2;        // 16 KB
 constexpr int BH_BYTES = 128 * BK * 2;      // 16 KB: this CTA's 128 columns of one 256-wide MMA
 constexpr int B_BYTES = 2 * BH_BYTES;       // up to two MMAs per k-step
@@ -94,6 +93,9 @@ struct Params {
   int total;               // p[0].kb_total + p[1].kb_total
   const int* e_flag;       // device flag: 0 = E already holds G' (recompute path ran) -> copy
   const float* consts;     // device {k_all, k_diag} per batch entry
+  int debug_skip_a;        // measurement only (MM25_TE_DEBUG_SKIP_A): producers arrive without data
+  int pf_dist;             // L2 prefetch distance of the A tiles in k-blocks (0 = off)
+  long long* stats;        // measurement only: cycle sums of one producer thread (or NULL)
 };
 
 // One contiguous piece of a pair's range: k-blocks [kb0, kb1) of job `job` of problem `prob`.
@@ -241,7 +243,8 @@ template <bool A_MN>
 __device__ __forceinline__ void produce_piece(ge::Smem& sm, const ge::Problem& pr,
                                               const ge::Piece& pc, const int rank, const int grp,
                                               const int gtid, const bool xform, const float k_all,
-                                              const uint32_t t0, const uint32_t full_leader0) {
+                                              const uint32_t t0, const uint32_t full_leader0,
+                                              long long* stats) {
   using namespace ge;
   const int r8 = gtid >> 3, cc = gtid & 7;
   const uint32_t dst0 = smem_u32(sm.a[grp]) + (uint32_t)(r8 * 128 + ((cc ^ r8) << 4));  // + i * 1024
@@ -325,8 +328,18 @@ __device__ __forceinline__ void produce_piece(ge::Smem& sm, const ge::Problem& p
     }
   };
   issue(pc.kb0 + j);
+  long long t_issue = stats ? clock64() : 0;
   for (; j < nkb; j += NST) {
     const int kb = pc.kb0 + j;
+    if (stats) {  // [0] cycles from the end of the loads' issue until the tile's data is usable
+      unsigned acc = 0;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) acc |= buf[i].x ^ buf[i].w;
+      if (acc == 0x9e3779b9u) stats[7] = 1;   // consumes every load
+      const long long t = clock64();
+      stats[0] += t - t_issue;
+      t_issue = t;
+    }
     // The positive of an E row is NOT formed from the bf16 E (on trained embeddings
     // E_ii (R_i + C_i) nearly cancels against k_diag, so E's rounding would dominate): its exact
     // fp32 G' comes from te_diag_kernel and is patched into the staged tile.  A thread holds at
@@ -356,6 +369,11 @@ __device__ __forceinline__ void produce_piece(ge::Smem& sm, const ge::Problem& p
     // the MMAs that read this stage (tile t - 4) have completed
     const uint32_t use = (t0 + (uint32_t)j) >> 2;       // how many times the group used its stage
     mbar_wait(&sm.empty[grp], (use & 1u) ^ 1u);
+    if (stats) {  // [1] further wait for the stage to be free
+      const long long t = clock64();
+      stats[1] += t - t_issue;
+      t_issue = t;
+    }
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       uint4 o = buf[i];
@@ -382,6 +400,12 @@ __device__ __forceinline__ void produce_piece(ge::Smem& sm, const ge::Problem& p
     fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core (async proxy)
     __syncwarp();
     if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(full_leader0 + grp * 8);
+    if (stats) {  // [2] transform + stores + next issue + fence + arrive; [3] tiles
+      const long long t = clock64();
+      stats[2] += t - t_issue;
+      stats[3] += 1;
+      t_issue = t;
+    }
   }
 }
 
@@ -439,13 +463,13 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
           if (have_q) kbq = pq.kb0;
         }
       };
-      for (int i = 0; i < PF_DIST; ++i) prefetch_one();
+      for (int i = 0; i < P.pf_dist; ++i) prefetch_one();
       for (int g = g_begin; next_piece(P, g, g_end, &pc);) {
         const Problem& pr = P.p[pc.prob];
         const int ncol0 = pc.nt * 256 * nh + (int)rank * 128;
         const int krow0 = pc.bz * pr.nk * BK;
         for (int kb = pc.kb0; kb < pc.kb1; ++kb) {
-          prefetch_one();
+          if (P.pf_dist > 0) prefetch_one();
           mbar_wait(&sm.empty[st], ph ^ 1);
           const uint32_t fbar = mapa_u32(&sm.full[st], 0);
           if (leader) mbar_arrive_expect_tx(&sm.full[st], 2 * nh * BH_BYTES);
@@ -469,11 +493,13 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
         const int a_mn = pr.a_mn;
         const uint32_t idesc = make_idesc_bf16(2 * BM, 256, a_mn, 1);
         const uint32_t a_step = a_mn ? 2048 : 32, a_lbo = a_mn ? 8192 : 16;
-        mbar_wait_cluster(&sm.acc_empty[as], accph ^ 1);
+        mbar_wait(&sm.acc_empty[as], accph ^ 1);
         tc_fence_after();
         const uint32_t dcol = tmem + as * 256;
         for (int kb = pc.kb0; kb < pc.kb1; ++kb) {
-          mbar_wait_cluster(&sm.full[st], ph);   // TMA bytes + the stage's producer warps of the pair
+          // CTA-scope acquire: a cluster-scope one costs a CCTL.IVALL (L1 invalidate) per k-block;
+          // the operands were published to the async proxy by fence.proxy.async / TMA
+          mbar_wait(&sm.full[st], ph);   // TMA bytes + the stage's producer warps of the pair
           tc_fence_after();
           const uint32_t abase = smem_u32(sm.a[st]);
           const uint32_t bbase = smem_u32(sm.b[st]);
@@ -499,15 +525,30 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
     const int q = warp & 3;
     const bool xform = P.e_flag ? (__ldg(P.e_flag) != 0) : true;
     const uint32_t full_leader0 = mapa_u32(&sm.full[0], 0);
+    long long* st_ptr = (P.stats && blockIdx.x == 20 && threadIdx.x == PROD0 * 32) ? P.stats : nullptr;
+    long long clk0 = 0;
+    unsigned long long ns0 = 0;
+    if (st_ptr) {
+      clk0 = clock64();
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns0));
+    }
     uint32_t t0 = 0, as = 0, accph = 0;   // t0: tiles (k-blocks) of the pieces before this one
     Piece pc;
     for (int g = g_begin; next_piece(P, g, g_end, &pc);) {
       const Problem& pr = P.p[pc.prob];
       const float k_all = (xform && P.consts) ? __ldg(P.consts + 2 * pc.bz) : 0.f;
-      if (pr.a_mn)
-        produce_piece<true>(sm, pr, pc, (int)rank, grp, gtid, xform, k_all, t0, full_leader0);
+      if (P.debug_skip_a) {
+        const int nkb = pc.kb1 - pc.kb0;
+        for (int j = (int)((grp - t0) & 3u); j < nkb; j += NST) {
+          const uint32_t use = (t0 + (uint32_t)j) >> 2;
+          mbar_wait(&sm.empty[grp], (use & 1u) ^ 1u);
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(full_leader0 + grp * 8);
+        }
+      } else if (pr.a_mn)
+        produce_piece<true>(sm, pr, pc, (int)rank, grp, gtid, xform, k_all, t0, full_leader0, st_ptr);
       else
-        produce_piece<false>(sm, pr, pc, (int)rank, grp, gtid, xform, k_all, t0, full_leader0);
+        produce_piece<false>(sm, pr, pc, (int)rank, grp, gtid, xform, k_all, t0, full_leader0, st_ptr);
       t0 += (uint32_t)(pc.kb1 - pc.kb0);
       if (!epi) continue;
       const int lrow = pc.sb * 256 + (int)rank * BM + q * 32 + lane;   // row inside the entry
@@ -544,6 +585,12 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_u32(&sm.acc_empty[as], 0));
       if (++as == (uint32_t)nacc) { as = 0; accph ^= 1; }
+    }
+    if (st_ptr) {  // [4] SM cycles and [5] nanoseconds of this thread's whole run -> effective clock
+      unsigned long long ns1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns1));
+      st_ptr[4] += clock64() - clk0;
+      st_ptr[5] += (long long)(ns1 - ns0);
     }
   }
   tc_fence_before();
@@ -619,6 +666,9 @@ te_diag_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restr
     gdiag[bz * M + i] = gs * g;
   }
 }
+
+// measurement only: device buffer of 8 counters filled by one producer thread
+static long long* g_te_stats = nullptr;
 
 static int sm_count_te() {
   static int n = 0;
@@ -702,6 +752,11 @@ int gemm_te_grouped(const GemmTeDesc* d0, const GemmTeDesc* d1, int64_t Ng, cons
   }
   P.e_flag = e_flag;
   P.consts = consts;
+  static const bool skip_a = getenv("MM25_TE_DEBUG_SKIP_A") != nullptr;
+  P.debug_skip_a = skip_a ? 1 : 0;
+  static const int pf = getenv("MM25_TE_PF") ? atoi(getenv("MM25_TE_PF")) : 0;
+  P.pf_dist = pf;
+  P.stats = g_te_stats;
   P.total = P.p[0].kb_total + P.p[1].kb_total;
   const int maxpairs = sm_count_te() / 2;
   // equal contiguous ranges, not shorter than 8 k-blocks
@@ -753,6 +808,22 @@ int te_coef(const void* a, const void* b, int64_t d, int64_t diag_offset, const 
 
 }  // namespace tc
 }  // namespace mm25
+
+// measurement hook (tools/bench_te.py): allocate / read / clear the producer cycle counters
+extern "C" int mm25_debug_te_stats(long long* out8, int enable) {
+  using mm25::tc::g_te_stats;
+  if (enable && !g_te_stats) {
+    if (cudaMalloc(&g_te_stats, 8 * sizeof(long long)) != cudaSuccess) return MM25_ERR_CUDA;
+    cudaMemset(g_te_stats, 0, 8 * sizeof(long long));
+  }
+  if (g_te_stats && out8) {
+    cudaDeviceSynchronize();
+    cudaMemcpy(out8, g_te_stats, 8 * sizeof(long long), cudaMemcpyDeviceToHost);
+    cudaMemset(g_te_stats, 0, 8 * sizeof(long long));
+  }
+  if (!enable && g_te_stats) { cudaFree(g_te_stats); g_te_stats = nullptr; }
+  return MM25_OK;
+}
 
 // debug / test entry (tests/test_tc_gpu.py): C0 = T(E) B0 and C1 = T(E)^T B1 for a bf16
 // E [Me, Ne], with T(E)_rc = E_rc (rowf_r + colf_c) - consts[2 z], and T(E)_rc = gdiag_r where

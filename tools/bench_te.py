@@ -61,11 +61,22 @@ def timeit(fn, k=5):
 
 
 fl = 2.0 * M * N * d
+import ctypes
+STATS = os.environ.get('MM25_TE_STATS') == '1'
+if STATS:
+    L.mm25_debug_te_stats(None, 1)
 for name, fn, f in (("te both (transform)", lambda: te(one), 2 * fl),
                     ("te dA only", lambda: te(one, True, False), fl),
                     ("te dB only", lambda: te(one, False, True), fl),
                     ("te both (copy mode)", lambda: te(zero), 2 * fl),
                     ("grouped TMA 1-CTA / 2-CTA per env", grouped, 2 * fl)):
     ms = timeit(fn)
+    if STATS:
+        buf = (ctypes.c_longlong * 8)()
+        L.mm25_debug_te_stats(ctypes.cast(buf, ctypes.c_void_p), 1)
+        n = max(buf[3], 1)
+        print(json.dumps({"path": name, "cycles_per_tile": {"load_wait": buf[0] / n,
+              "stage_wait": buf[1] / n, "fill": buf[2] / n, "tiles": buf[3]},
+              "sm_ghz": buf[4] / max(buf[5], 1)}))
     print(json.dumps({"path": name, "M": M, "N": N, "d": d, "ms": ms,
                       "tflops": f / ms / 1e9}))

@@ -17,6 +17,10 @@ for step in "$@"; do
     diag)      run diag 600 python tools/diag_te.py ;;
     diag0)     run diag0 600 env MM25_TE=0 python tools/diag_te.py ;;
     te)        run te 600 python tools/bench_te.py ;;
+    te_skipa)  run te_skipa 600 env MM25_TE_DEBUG_SKIP_A=1 python tools/bench_te.py ;;
+    te_stats)  run te_stats 600 env MM25_TE_STATS=1 python tools/bench_te.py ;;
+    te_pf)     run te_pf 600 env MM25_TE_PF=12 python tools/bench_te.py ;;
+    te_stats_skipa) run te_stats_skipa 600 env MM25_TE_STATS=1 MM25_TE_DEBUG_SKIP_A=1 python tools/bench_te.py ;;
     te2)       run te2 600 env MM25_GEMM_2CTA=1 python tools/bench_te.py ;;
     ncu_te)    python tools/bench_te.py 16384 > "gpurun_out/${TAG}_te_plain.log" 2>&1 && \
                timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_te -s 1 -c 1 \
