@@ -33,6 +33,42 @@ def clip_loss(image_features, text_features, logits_scale, label_smoothing=0.1, 
     return (loss_img + loss_txt) / 2  # :119
 
 
+def clip_loss_slab(image_features, text_features, logits_scale, row0, rows, label_smoothing=0.1,
+                   normalize=True, dtype=torch.float32):
+    """The part of `clip_loss` (clipLoss.py:94-119) owned by image rows [row0, row0 + rows): the
+    [rows, N] slab of the logits (:106) with the same per-logit arithmetic.  Returns the pieces
+    that `clip_loss_from_slabs` combines into exactly the loss of the whole batch:
+      img_sum   = sum over the slab's rows of the image-side CE (:116, label smoothing included)
+      col_lse   = [N] logsumexp over the slab's rows of every column (partial column statistic)
+      col_lin   = [N] sum over the slab's rows of z_ij   (smoothing term of the text-side CE)
+      diag      = [rows] the positives z_ii
+    bench.py times this as a bounded sample of a batch too large to run whole on the host: a
+    slab of r rows is r / N of the N x N work with the per-pair work unchanged."""
+    if normalize:
+        image_features = F.normalize(image_features, dim=-1, p=2)
+        text_features = F.normalize(text_features, dim=-1, p=2)
+    logit_scale = logits_scale.clamp(max=4.6052).exp()
+    z = logit_scale.to(dtype) * image_features[row0:row0 + rows].to(dtype) @ text_features.t().to(dtype)
+    labels = torch.arange(row0, row0 + rows, device=z.device)
+    img_sum = F.cross_entropy(z, labels, label_smoothing=label_smoothing, reduction="sum")
+    col_lse = torch.logsumexp(z, dim=0)
+    col_lin = z.sum(dim=0)
+    diag = z[torch.arange(rows), labels]
+    return img_sum, col_lse, col_lin, diag
+
+
+def clip_loss_from_slabs(parts, n, label_smoothing=0.1):
+    """Combine the pieces of `clip_loss_slab` over a partition of the rows into clip_loss."""
+    img = sum(p[0] for p in parts) / n
+    col_lse = torch.logsumexp(torch.stack([p[1] for p in parts]), dim=0)
+    col_lin = torch.stack([p[2] for p in parts]).sum(dim=0)
+    diag = torch.cat([p[3] for p in parts])
+    eps = label_smoothing
+    # text-side CE with label smoothing: mean_j [ lse_j - (1 - eps) z_jj - eps / n * sum_i z_ij ]
+    txt = (col_lse - (1 - eps) * diag - eps / n * col_lin).mean()
+    return (img + txt) / 2
+
+
 def clip_loss_sampled(image_features, text_features, logits_scale, label_smoothing=0.1):
     """clipLoss.py:24-79 (ClipLoss.forward_sampled): [S,B,E] x2 -> [S]."""
     B1, B2, E = image_features.shape

@@ -112,3 +112,24 @@ def test_alignclip_semantic_oracle_matches_reference_golden(tag):
     assert rel_err(gs, g["gs"]) < 1e-5
     tot, clip, inm = O.inmodality_loss(x, y, s, sem, **kw)
     assert rel_err(clip, g["clip_loss"]) < 1e-6 and rel_err(inm, g["inmod_loss"]) < 1e-6
+
+
+@pytest.mark.parametrize("n,d,eps,nslab", [(256, 64, 0.1, 4), (96, 32, 0.0, 3), (130, 48, 0.1, 5)])
+def test_clip_loss_slabs_combine_to_the_pinned_clip_loss(n, d, eps, nslab):
+    """bench.py times `clip_loss_slab` (a bounded sample of a batch too big for the host); its
+    pieces over a partition of the rows must give exactly the golden-pinned `clip_loss`, value
+    and gradients."""
+    x, y = O.synth_embeddings(n, d, 4, correlated=True)
+    x = x * 1.7
+    ls = torch.tensor(2.9)
+    ref, (rx, ry, rl) = O.loss_and_grads(O.clip_loss, [x, y, ls], eps, True)
+    bounds = [round(i * n / nslab) for i in range(nslab + 1)]
+
+    def slabbed(a, b, c):
+        parts = [O.clip_loss_slab(a, b, c, bounds[i], bounds[i + 1] - bounds[i], eps, True)
+                 for i in range(nslab)]
+        return O.clip_loss_from_slabs(parts, n, eps)
+
+    got, (gx, gy, gl) = O.loss_and_grads(slabbed, [x, y, ls])
+    assert rel_err(got, ref) < 1e-6
+    assert rel_err(gx, rx) < 1e-5 and rel_err(gy, ry) < 1e-5 and rel_err(gl, rl) < 1e-5
