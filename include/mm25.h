@@ -134,6 +134,26 @@ int mm25_rownorm_fwd(const void* x, int dtype, void* xhat, int out_dtype, float*
                      float* colsum, int64_t B, int64_t M, int64_t d, int normalize, float eps,
                      void* stream);
 
+/* Allocation-free variant of mm25_rownorm_fwd with column sums.  NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot allocate (CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  Same kernels and results as
+ * mm25_rownorm_fwd, but the partials of the two-stage column sum live in a file-scope device
+ * array of the library (MM25_NOALLOC_MAX_FLOATS floats = 2.89 MiB, held by every GPU that loads
+ * the library until exit) instead of behind `colsum`: the caller passes inputs and outputs only,
+ * `colsum` is exactly [B, d] floats, and the call performs no cudaMalloc / cudaFree.
+ *   needs  d % 128 == 0, d <= 2048, M >= 64                       (else MM25_ERR_SHAPE)
+ *   and    mm25_rownorm_colsum_noalloc_floats(B, M, d) = B * d * min(ceil(M / 8), 740)
+ *          <= MM25_NOALLOC_MAX_FLOATS                             (else MM25_ERR_WORKSPACE;
+ *          e.g. B = 1: any M at d <= 1024, M <= 2960 at d = 2048)
+ * All calls on a device share the one array: it keeps the last call's partials (nothing needs
+ * to start at zero — stage 1 overwrites all it reads back), and two calls that overlap on the GPU
+ * (different streams, or graphs replayed concurrently) RACE on it — serialise them. */
+#define MM25_NOALLOC_MAX_FLOATS (740 * 1024)
+int64_t mm25_rownorm_colsum_noalloc_floats(int64_t B, int64_t M, int64_t d);
+int mm25_rownorm_colsum_noalloc(const void* x, int dtype, void* xhat, int out_dtype,
+                                float* inv_norm, float* colsum, int64_t B, int64_t M, int64_t d,
+                                int normalize, float eps, void* stream);
+
 /* Backward of the prologue: dx = inv_norm * (g - xhat (xhat.g)) (or a cast when !normalize).
  *   g [B,M,d] fp32 (gradient w.r.t. xhat), xhat [B,M,d] xhat_dtype, dx [B,M,d] out_dtype.
  *   gscale: optional device scalar multiplied into dx (upstream grad); NULL = 1.

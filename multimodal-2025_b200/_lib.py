@@ -101,6 +101,9 @@ SIGNATURES = {
     "mm25_debug_gemm_schedule": (_int, [_i64, _i64, _i64, _i64, _int, _vp]),
     "mm25_rownorm_colsum_floats": (_i64, [_i64, _i64, _i64]),
     "mm25_rownorm_fwd": (_int, [_vp, _int, _vp, _int, _vp, _vp, _i64, _i64, _i64, _int, _f32, _vp]),
+    "mm25_rownorm_colsum_noalloc_floats": (_i64, [_i64, _i64, _i64]),
+    "mm25_rownorm_colsum_noalloc": (_int, [_vp, _int, _vp, _int, _vp, _vp, _i64, _i64, _i64, _int,
+                                           _f32, _vp]),
     "mm25_rownorm_bwd": (_int, [_vp, _vp, _int, _vp, _vp, _int, _i64, _i64, _i64, _int, _vp, _int,
                                 _vp]),
     "mm25_sim_fwd_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64, _int, _int]),

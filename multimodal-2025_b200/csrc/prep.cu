@@ -654,3 +654,85 @@ extern "C" int mm25_clip_loss_finalize(const float* row_lse, const float* diag,
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant of mm25_rownorm_fwd with column sums (include/mm25.h).  The partials of
+// the deterministic two-stage column sum ([B][P][d] floats, P = colsum_parts(M) <= 740) live in a
+// file-scope device array instead of caller memory, so the caller hands over only inputs and
+// outputs.  Every device that loads the library holds the array (2.89 MiB) until exit.
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: the device address comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_noalloc_scratch[MM25_NOALLOC_MAX_FLOATS];
+
+static int noalloc_scratch_ptr(float** out) {
+  constexpr int MAXDEV = 64;
+  static std::mutex mu;
+  static float* ptrs[MAXDEV] = {nullptr};
+  int dev = 0;
+  MM25_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= MAXDEV) return MM25_ERR_ARG;
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    MM25_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    if (!p) return MM25_ERR_CUDA;
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return MM25_OK;
+}
+
+extern "C" int64_t mm25_rownorm_colsum_noalloc_floats(int64_t B, int64_t M, int64_t d) {
+  return B * d * (int64_t)colsum_parts(M);
+}
+
+extern "C" int mm25_rownorm_colsum_noalloc(const void* x, int dtype, void* xhat, int out_dtype,
+                                           float* inv_norm, float* colsum, int64_t B, int64_t M,
+                                           int64_t d, int normalize, float eps, void* stream) {
+  if (B <= 0 || M <= 0 || d <= 0) return MM25_ERR_SHAPE;
+  if (!x || !xhat || !colsum) return MM25_ERR_ARG;
+  if (dtype != MM25_F32 && dtype != MM25_BF16) return MM25_ERR_DTYPE;
+  if (out_dtype != MM25_F32 && out_dtype != MM25_BF16) return MM25_ERR_DTYPE;
+  // the fused vectorised kernel only (the shapes of every BASELINE config)
+  if (!(d % 128 == 0 && d <= RN_MAXIT * 128 && M >= 64)) return MM25_ERR_SHAPE;
+  // beyond the fixed scratch: MM25_ERR_WORKSPACE ("workspace too small"), nothing is launched
+  if (mm25_rownorm_colsum_noalloc_floats(B, M, d) > (int64_t)MM25_NOALLOC_MAX_FLOATS)
+    return MM25_ERR_WORKSPACE;
+  float* part = nullptr;
+  const int rc = noalloc_scratch_ptr(&part);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int P = colsum_parts(M);
+  dim3 g1((unsigned)P, (unsigned)B);
+  const size_t sh = sizeof(float) * 8 * (size_t)d;
+  // stage 1 overwrites every partial it owns ([B][P][d], all of them), so nothing has to start
+  // at zero; the array keeps the last call's partials afterwards
+#define NA2(TI, TO, NIT)                                                                      \
+  do {                                                                                        \
+    MM25_CUDA_CHECK(cudaFuncSetAttribute(rownorm_fused_kernel<TI, TO, true, NIT>,             \
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,         \
+                                         (int)sh));                                           \
+    rownorm_fused_kernel<TI, TO, true, NIT><<<g1, 256, sh, st>>>(                             \
+        (const TI*)x, (TO*)xhat, inv_norm, part, M, (int)d, normalize, eps);                  \
+  } while (0)
+#define NA(TI, TO)                                                                            \
+  do {                                                                                        \
+    const int nit_ = (int)(d >> 7);                                                           \
+    if (nit_ <= 2) NA2(TI, TO, 2);                                                            \
+    else if (nit_ <= 4) NA2(TI, TO, 4);                                                       \
+    else if (nit_ <= 8) NA2(TI, TO, 8);                                                       \
+    else NA2(TI, TO, 16);                                                                     \
+  } while (0)
+  if (dtype == MM25_F32 && out_dtype == MM25_F32) NA(float, float);
+  else if (dtype == MM25_F32 && out_dtype == MM25_BF16) NA(float, __nv_bfloat16);
+  else if (dtype == MM25_BF16 && out_dtype == MM25_BF16) NA(__nv_bfloat16, __nv_bfloat16);
+  else NA(__nv_bfloat16, float);
+#undef NA
+#undef NA2
+  MM25_LAUNCH_CHECK();
+  dim3 g2((unsigned)ceil_div(d, 32), (unsigned)B);
+  colsum_wide_kernel<<<g2, 1024, 0, st>>>(part, colsum, P, (int)d);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}

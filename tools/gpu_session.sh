@@ -8,6 +8,7 @@ TAG=$1; shift
 run() { local name=$1; shift; echo "=== $name"; ( timeout "$@" ) > "gpurun_out/${TAG}_$name.log" 2>&1; echo "$name rc=$?" | tee -a "gpurun_out/${TAG}_summary.txt"; }
 for step in "$@"; do
   case $step in
+    noalloc)   run noalloc 600 python -m pytest tests/test_zzz_no_alloc.py -m gpu -q ;;
     tc)        run tc 900 python -m pytest tests/test_tc_gpu.py -m gpu -q -x ;;
     pytest)    run pytest 1500 python -m pytest tests -m gpu -q -x ;;
     bench)     run bench 600 python bench.py --steps 10 --warmup 3 ;;
