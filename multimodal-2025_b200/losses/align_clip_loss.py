@@ -74,6 +74,36 @@ class _ModulatedCEFn(torch.autograd.Function):
         return dfeats, None, dpaired, dls, None
 
 
+def _sharded_args(mod):
+    """Map the reference's multi-process flags (loss.py:20-64, 103-114) onto the sharded
+    modules.  With `local_loss=False` the reference evaluates the GLOBAL loss on every rank:
+    `gather_with_grad=False` lets only the rank's own slot of the gathered features carry a
+    gradient (loss.py:55-58) -> d(global loss)/d(local shard), `grad_scale = 1`;
+    `gather_with_grad=True` back-propagates through `torch.distributed.nn.all_gather`, which
+    SUMS the P identical per-rank losses' gradients -> `grad_scale = world_size` (the open_clip
+    convention; DDP's gradient averaging then undoes the factor).  `local_loss=True` (per-rank
+    loss of the local rows) and Horovod are not built: they raise instead of silently returning
+    a different loss."""
+    import torch.distributed as dist
+    if mod.use_horovod:
+        raise NotImplementedError("use_horovod=True: Horovod collectives are out of scope "
+                                  "(torch.distributed only)")
+    if mod.local_loss:
+        raise NotImplementedError(
+            "local_loss=True (per-rank loss over the local rows, loss.py:108-110) is not "
+            "implemented by the sharded kernels; use local_loss=False (global loss, identical "
+            "on every rank)")
+    group = getattr(mod, "group", None)
+    if not dist.is_available() or not dist.is_initialized():
+        raise RuntimeError("world_size > 1 needs an initialised torch.distributed process group")
+    g = group if group is not None else dist.group.WORLD
+    ws, rk = dist.get_world_size(g), dist.get_rank(g)
+    if ws != int(mod.world_size) or rk != int(mod.rank):
+        raise ValueError("rank/world_size (%d/%d) do not match the process group (%d/%d)"
+                         % (mod.rank, mod.world_size, rk, ws))
+    return group, float(ws) if mod.gather_with_grad else 1.0
+
+
 class ClipLoss(nn.Module):
     """open_clip-style CLIP loss (reference AlignCLIP/align_clip/loss.py:67-132); world_size > 1
     delegates to dist.ShardedAlignClipLoss (needs an initialised process group)."""
@@ -87,15 +117,18 @@ class ClipLoss(nn.Module):
         self.rank = rank
         self.world_size = world_size
         self.use_horovod = use_horovod
+        self.group = None    # optional process group (attribute, not in the reference signature)
+        self._backend = None  # tests inject the CPU stand-in ops (gloo)
 
     def forward(self, image_features, text_features, logit_scale, output_dict=False,
                 semantic_features=None):
         if self.world_size > 1:
-            # global-batch loss from the local shards (what gather_with_grad=True,
-            # local_loss=False computes, loss.py:103-114) on the default process group
+            # global-batch loss from the local shards (local_loss=False, loss.py:103-114);
+            # gradient convention per gather_with_grad, see _sharded_args
             from ..dist import ShardedAlignClipLoss
-            return ShardedAlignClipLoss()(image_features, text_features, logit_scale,
-                                          output_dict=output_dict)
+            group, grad_scale = _sharded_args(self)
+            crit = ShardedAlignClipLoss(group, grad_scale, self._backend)
+            return crit(image_features, text_features, logit_scale, output_dict=output_dict)
         logit_scale = _as_scale(logit_scale, image_features)
         clip_loss = _ce_pair(image_features, text_features, logit_scale)
         return {"contrastive_loss": clip_loss} if output_dict else clip_loss
@@ -120,6 +153,8 @@ class ClipInModalityLoss(nn.Module):
         self.nl_semantic_supervision = nl_semantic_supervision
         self.separate_text = separate_text
         self.separate_image = separate_image
+        self.group = None    # optional process group (attribute, not in the reference signature)
+        self._backend = None  # tests inject the CPU stand-in ops (gloo)
 
     def forward(self, image_features, text_features, logit_scale, output_dict=False,
                 semantic_features=None):
@@ -127,8 +162,11 @@ class ClipInModalityLoss(nn.Module):
             # the reference's own branch never gathers the semantic features; the
             # sharded module evaluates the single-process formula on the concatenated batch
             from ..dist import ShardedClipInModalityLoss
+            group, grad_scale = _sharded_args(self)
             crit = ShardedClipInModalityLoss(self.alpha, self.beta, self.nl_semantic_supervision,
-                                             self.separate_text, self.separate_image)
+                                             self.separate_text, self.separate_image,
+                                             group=group, grad_scale=grad_scale,
+                                             backend=self._backend)
             return crit(image_features, text_features, logit_scale, output_dict=output_dict,
                         semantic_features=semantic_features)
         logit_scale = _as_scale(logit_scale, image_features)

@@ -415,3 +415,77 @@ def test_sharded_vclip_eval_path_world2_gloo():
         assert (gli - loc_i.grad[sl]).norm() < 1e-4 * loc_i.grad[sl].norm()
         assert (gki - k_i.grad[sl]).norm() < 1e-4 * k_i.grad[sl].norm()
         assert (gkt - k_t.grad[sl]).norm() < 1e-4 * k_t.grad[sl].norm()
+
+
+def _worker_flags(rank, world, port, q, n, d):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import torch.nn.functional as F
+        from torch.distributed.nn import all_gather as ag_with_grad
+        import cpu_backend
+        from multimodal_2025_b200.losses.align_clip_loss import ClipLoss
+        g = torch.Generator().manual_seed(11)
+        X = F.normalize(torch.randn(n * world, d, generator=g), dim=-1)
+        Y = F.normalize(X + 0.5 * torch.randn(n * world, d, generator=g), dim=-1)
+        sl = slice(rank * n, (rank + 1) * n)
+        out = {}
+        for gwg in (False, True):
+            # the reference's formula (loss.py:20-64, 103-130) written with the same collectives
+            x = X[sl].clone().requires_grad_(True)
+            y = Y[sl].clone().requires_grad_(True)
+            if gwg:
+                ax = torch.cat(ag_with_grad(x), dim=0)
+                ay = torch.cat(ag_with_grad(y), dim=0)
+            else:
+                gx = [torch.zeros_like(x) for _ in range(world)]
+                gy = [torch.zeros_like(y) for _ in range(world)]
+                dist.all_gather(gx, x.detach())
+                dist.all_gather(gy, y.detach())
+                gx[rank], gy[rank] = x, y
+                ax, ay = torch.cat(gx), torch.cat(gy)
+            z = 14.285 * ax @ ay.t()
+            lab = torch.arange(n * world)
+            ref = (F.cross_entropy(z, lab) + F.cross_entropy(z.t(), lab)) / 2
+            ref.backward()
+            crit = ClipLoss(gather_with_grad=gwg, rank=rank, world_size=world)
+            crit._backend = cpu_backend
+            xo = X[sl].clone().requires_grad_(True)
+            yo = Y[sl].clone().requires_grad_(True)
+            loss = crit(xo, yo, 14.285)
+            loss.backward()
+            out[gwg] = (ref.detach(), x.grad, y.grad, loss.detach(), xo.grad, yo.grad)
+        errs = []
+        for kw in (dict(local_loss=True), dict(use_horovod=True)):
+            try:
+                c = ClipLoss(rank=rank, world_size=world, **kw)
+                c._backend = cpu_backend
+                c(X[sl], Y[sl], 14.285)
+                errs.append(None)
+            except NotImplementedError as e:
+                errs.append(str(e))
+        try:
+            ClipLoss(rank=rank + 1, world_size=world)(X[sl], Y[sl], 14.285)
+            errs.append(None)
+        except ValueError as e:
+            errs.append(str(e))
+        q.put(_np((rank, out, errs)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_dropin_cliploss_distributed_flags_world2_gloo():
+    """the drop-in open_clip ClipLoss maps gather_with_grad onto the gradient
+    convention of the reference (own-slot gradient vs sum over ranks), and refuses local_loss /
+    horovod / a rank that does not match the group instead of silently ignoring them."""
+    res = _run_world(_worker_flags, 2, (12, 16))
+    for rank, out, errs in res:
+        for gwg, (ref, rx, ry, loss, gx, gy) in out.items():
+            assert abs(float(loss) - float(ref)) < 1e-5 * abs(float(ref)), gwg
+            assert (gx - rx).norm() < 1e-4 * rx.norm(), gwg
+            assert (gy - ry).norm() < 1e-4 * ry.norm(), gwg
+        assert all(e is not None for e in errs), errs
