@@ -44,8 +44,12 @@ enum {
   MM25_T_GEMM_TE = 1,      /* gemm_te_kernel (kept-E backward GEMMs) */
   MM25_T_SIM_GRAD = 2,     /* sim_grad_tc_kernel */
   MM25_T_GEMM_GROUPED = 3, /* gemm_grouped_kernel / gemm_grouped2_kernel */
-  MM25_T_SIM_MOD = 4,      /* sim_mod_tc_kernel */
-  MM25_TIMING_SLOTS = 8
+  MM25_T_SIM_MOD = 4,      /* sim_mod_tc_kernel (MODULATED fwd / grad, Hopfield backward sweep) */
+  MM25_T_SIMT_FWD = 5,     /* sim_fwd_kernel (fp32 FFMA path) */
+  MM25_T_SIMT_BWD = 6,     /* sim_bwd_kernel / hopfield_bwd_kernel (fp32 FFMA path) */
+  MM25_T_SAMPLER = 7,      /* projnormal_* / sphere_* sampler kernels */
+  MM25_T_SIM_RANK = 8,     /* sim_rank_tc_kernel */
+  MM25_TIMING_SLOTS = 12
 };
 
 /* logit modes of the fused similarity kernels */
@@ -401,6 +405,19 @@ int mm25_topk_rows(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_
 int mm25_rank_both(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_t row0,
                    const float* row_tval, const int64_t* row_tcol, const float* col_tval,
                    const int64_t* col_trow, int* row_rank, int* col_rank, void* stream);
+
+/* Retrieval ranks fused into the similarity GEMM: the scores a_q . b_j (bf16 rows, fp32
+ * accumulation on the tensor cores) are counted against the row's target as they leave TMEM and
+ * are never written (AlignCLIP/main/train.py:338-356 forms `logits_per_image` [N, N], copies it
+ * to the CPU and argsorts it per direction; main/retrieval.py:62-71; metrics/topk.py:64-82).
+ * a [Q, d], b [N, d] bf16 row-major (d % 64 == 0, 64 <= d <= 1024; any Q, N); ADDS into
+ *   rank[q] += #{ j != tcol[q] : a_q.b_j > tval[q], or == tval[q] and j < tcol[q] }
+ * (the stable descending order of mm25_rank_both; the caller zeroes `rank`).  tval[q] is the
+ * caller's value of the target score a_q . b_tcol[q] (its own column is excluded by position).
+ * The column direction of a paired batch is a second call with a and b swapped.  A positive
+ * logit scale does not change the order, so the raw dot products are ranked. */
+int mm25_sim_rank(const void* a, const void* b, int dtype, int64_t Q, int64_t N, int64_t d,
+                  const float* tval, const int64_t* tcol, int* rank, void* stream);
 
 #ifdef __cplusplus
 }

@@ -18,7 +18,7 @@ INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 
 SOURCES = ["prep.cu", "sim_simt.cu", "sim_tc.cu", "sim_tc_bwd.cu", "sim_tc_mod.cu", "gemm_tc.cu", "gemm_tc2.cu",
            "gemm_te.cu",
-           "api_sim.cu", "hopfield.cu", "samplers.cu", "beta_vmf.cu", "bessel.cu", "topk.cu", "rank.cu"]
+           "api_sim.cu", "hopfield.cu", "samplers.cu", "beta_vmf.cu", "bessel.cu", "topk.cu", "rank.cu", "sim_tc_rank.cu"]
 
 _lock = threading.Lock()
 _lib = None
@@ -134,6 +134,7 @@ SIGNATURES = {
                                _vp, _vp, _vp]),
     "mm25_topk_rows": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
     "mm25_rank_both": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "mm25_sim_rank": (_int, [_vp, _vp, _int, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "mm25_rowdot": (_int, [_vp, _vp, _vp, _i64, _i64, _vp]),
     "mm25_hopfield_bwd_pass": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _vp,
                                       _vp, _int, _vp, _vp]),

@@ -145,8 +145,10 @@ extern "C" int mm25_hopfield_bwd_pass(const float* a, const float* b, const floa
   MM25_CUDA_CHECK(cudaFuncSetAttribute(simt::hopfield_bwd_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)ceil_div(d, simt::HDC), (unsigned)ceil_div(M, simt::BM));
+  void* tt_ = timing_begin(MM25_T_SIMT_BWD, (cudaStream_t)stream);
   simt::hopfield_bwd_kernel<<<grid, simt::NT, smem, (cudaStream_t)stream>>>(
       a, b, a2, b2, bm1, bm2, M, N, (int)d, beta, lse, D, stat_by_col, out);
+  timing_end(tt_, (cudaStream_t)stream);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

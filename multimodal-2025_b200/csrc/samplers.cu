@@ -419,8 +419,10 @@ extern "C" int mm25_sample_projnormal_fwd(const float* mu, const float* sigma,
   const int64_t gpl = ceil_div(ceil_div(d, 4), 32);  // 4-element groups per lane
 #define PN(G) projnormal_fwd_kernel<G><<<grid, 256, 0, st>>>(mu, sigma, eps_in, seed, S, B, \
                                                              (int)d, out, inv_norm)
+  void* tt_ = timing_begin(MM25_T_SAMPLER, st);
   if (gpl <= 1) PN(1); else if (gpl <= 2) PN(2); else if (gpl <= 4) PN(4);
   else if (gpl <= 8) PN(8); else PN(0);
+  timing_end(tt_, st);
 #undef PN
   MM25_LAUNCH_CHECK();
   return MM25_OK;
@@ -435,8 +437,10 @@ extern "C" int mm25_sample_projnormal_bwd(const float* gout, const float* y,
   const size_t sh = sizeof(float) * 8 * 2 * (size_t)((d + 3) / 4 * 4);
   MM25_CUDA_CHECK(cudaFuncSetAttribute(projnormal_bwd_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+  void* tt_ = timing_begin(MM25_T_SAMPLER, (cudaStream_t)stream);
   projnormal_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, sh, (cudaStream_t)stream>>>(
       gout, y, inv_norm, eps_in, seed, S, B, (int)d, dmu, dsigma);
+  timing_end(tt_, (cudaStream_t)stream);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }
@@ -452,8 +456,10 @@ extern "C" int mm25_sphere_sample_fwd(const float* t, const float* loc, const fl
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t gpl = ceil_div(ceil_div(d, 4), 32);
 #define SP(G) sphere_fwd_kernel<G><<<grid, 256, 0, st>>>(t, loc, v_in, seed, S, B, (int)d, cfg, out)
+  void* tt_ = timing_begin(MM25_T_SAMPLER, st);
   if (gpl <= 1) SP(1); else if (gpl <= 2) SP(2); else if (gpl <= 4) SP(4);
   else if (gpl <= 8) SP(8); else SP(0);
+  timing_end(tt_, st);
 #undef SP
   MM25_LAUNCH_CHECK();
   return MM25_OK;
@@ -469,8 +475,10 @@ extern "C" int mm25_sphere_sample_bwd(const float* gout, const float* y, const f
   const size_t sh = sizeof(float) * 8 * (size_t)((d + 3) / 4 * 4);
   MM25_CUDA_CHECK(cudaFuncSetAttribute(sphere_bwd_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+  void* tt_ = timing_begin(MM25_T_SAMPLER, (cudaStream_t)stream);
   sphere_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, sh, (cudaStream_t)stream>>>(
       gout, y, t, loc, S, B, (int)d, cfg, dloc, dt);
+  timing_end(tt_, (cudaStream_t)stream);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

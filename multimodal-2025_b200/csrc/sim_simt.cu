@@ -349,9 +349,11 @@ static int launch_fwd_t(const T* a, const T* b, const float* u, const float* v,
                                                scale, scale_kind, clamp_max, diag_offset,     \
                                                row_pm, row_pl, col_pm, col_pl, diag, nsplit,  \
                                                jbps)
+  { void* tt_ = timing_begin(MM25_T_SIMT_FWD, st);
   if (mode == MM25_SIM_PLAIN) LAUNCH(MM25_SIM_PLAIN);
   else if (mode == MM25_SIM_MASKDIAG) LAUNCH(MM25_SIM_MASKDIAG);
   else LAUNCH(MM25_SIM_MODULATED);
+  timing_end(tt_, st); }
 #undef LAUNCH
   MM25_LAUNCH_CHECK();
   const int64_t mx = M > N ? M : N;
@@ -401,9 +403,11 @@ static int launch_bwd_pass_t(const T* a, const T* b, const float* u, const float
         clamp_max, diag_offset, row_lse, col_lse, w_row, w_col, w_diag, w_all, gout, dA,       \
         dscale_part, ddiag);                                                                   \
   } while (0)
+  void* tt_ = timing_begin(MM25_T_SIMT_BWD, st);
   if (mode == MM25_SIM_PLAIN) LAUNCH(MM25_SIM_PLAIN);
   else if (mode == MM25_SIM_MASKDIAG) LAUNCH(MM25_SIM_MASKDIAG);
   else LAUNCH(MM25_SIM_MODULATED);
+  timing_end(tt_, st);
 #undef LAUNCH
   MM25_LAUNCH_CHECK();
   return MM25_OK;

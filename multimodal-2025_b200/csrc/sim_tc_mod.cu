@@ -457,9 +457,11 @@ int launch_fwd(const void* a, const void* b, const float* u, const float* v,
   const int grid = (int)(items < sms ? items : sms);
   // rows whose positive lies outside [0, N) keep diag = 0
   MM25_CUDA_CHECK(cudaMemsetAsync(diag, 0, sizeof(float) * M, st));
+{ void* tt_ = timing_begin(MM25_T_SIM_MOD, st);
   sim_mod_tc_kernel<EPI_FWD><<<grid, MTHREADS, smem, st>>>(
       ta, tb, tu, tv, ta, ta, g, M, N, scale, scale_kind, clamp_max, diag_offset, diag_add, row_pm,
       row_pl, diag, nullptr, 0.f, 0.f, 0.f, nullptr, nullptr, nullptr);
+  timing_end(tt_, st); }
   MM25_LAUNCH_CHECK();
   mod_row_merge_kernel<<<(unsigned)ceil_div(M, 256), 256, 0, st>>>(row_pm, row_pl, 2 * g.nseg, M,
                                                                    row_lse);
@@ -504,10 +506,12 @@ int launch_bwd(const void* a, const void* b, const float* u, const float* v,
     if (dscale_part) MM25_CUDA_CHECK(cudaMemsetAsync(dscale_part + part, 0, sizeof(float) * sms, st));
     CUtensorMap tg;
     if ((rc = make_tmap_bf16(&tg, G, (uint64_t)rows, (uint64_t)N, 32, 32, 64))) return rc;
+{ void* tt_ = timing_begin(MM25_T_SIM_MOD, st);
     sim_mod_tc_kernel<EPI_GRAD><<<grid, MTHREADS, smem, st>>>(
         ta, tb, tu, tv, tg, tg, g, M, N, scale, scale_kind, clamp_max, diag_offset, diag_add, nullptr,
         nullptr, nullptr, row_lse, w_row, w_diag, w_all, gout,
         dscale_part ? dscale_part + part : nullptr, ddiag);
+  timing_end(tt_, st); }
     MM25_LAUNCH_CHECK();
     part += sms;
     GemmDesc ga{G, bb, da ? da + p0 * d : nullptr, d, rows, N, 0, 1, 0, 1.f, nullptr, 0, 0};
@@ -573,9 +577,11 @@ int launch_hopfield_bwd(const void* q, const void* k, const float* d_o, int64_t 
     CUtensorMap tg, tp;
     if ((rc = make_tmap_bf16(&tg, GZ, (uint64_t)rows, (uint64_t)N, 32, 32, 64))) return rc;
     if ((rc = make_tmap_bf16(&tp, GP, (uint64_t)rows, (uint64_t)N, 32, 32, 64))) return rc;
+{ void* tt_ = timing_begin(MM25_T_SIM_MOD, st);
     sim_mod_tc_kernel<EPI_HOPF><<<grid, MTHREADS, smem, st>>>(
         ta, tb, tu, tb, tg, tp, g, M, N, beta, MM25_SCALE_MUL, 0.f, 0, delta, nullptr, nullptr,
         nullptr, lse, 0.f, 0.f, 0.f, nullptr, nullptr, nullptr);
+  timing_end(tt_, st); }
     MM25_LAUNCH_CHECK();
     // dQ[panel] = dZ K  and  dK (+)= dZ^T Q[panel]  in one grouped launch, then dK += P^T dO
     GemmDesc ga{GZ, kb, dq ? dq + p0 * d : nullptr, d, rows, N, 0, 1, 0, 1.f, nullptr, 0, 0};

@@ -76,13 +76,47 @@ def _scores(logit_scale, a: Tensor, b: Tensor) -> Tensor:
     return (logit_scale * a @ b.t()) if logit_scale is not None else a @ b.t()
 
 
+def fused_ranks(queries: Tensor, gallery: Tensor, targets: Tensor) -> Tensor:
+    """0-based rank of gallery row `targets[q]` among the scores `queries[q] . gallery[j]`, with
+    the similarity GEMM and the count fused in one tcgen05 kernel (`mm25_sim_rank`): the
+    [Q, N] score matrix is never formed.  bf16 features (fp32 accumulation); the target's score
+    is an fp32 dot product of the same bf16 rows."""
+    q = queries.detach().to(torch.bfloat16).contiguous()
+    g = gallery.detach().to(torch.bfloat16).contiguous()
+    t = targets.to(device=q.device, dtype=torch.int64).contiguous()
+    tval = (q.float() * g[t].float()).sum(dim=-1).contiguous()
+    rank = _zeros_i32(q.shape[0], q)
+    _ops.sim_rank(q, g, tval, t, rank)
+    return rank
+
+
+def _use_fused(fused, x: Tensor, y: Tensor, logit_scale=None) -> bool:
+    """fused=None (auto): bf16 features of an eligible width take the fused kernel — the
+    reference's own bf16 matmul rounds every score to bf16, so no bit-level score parity exists
+    to preserve there; fp32 features keep the exact route (library GEMM in the reference's
+    expression + mm25_rank_both on identical fp32 scores)."""
+    ok = (hasattr(_ops, "sim_rank") and x.is_cuda and y.is_cuda and x.shape[-1] % 64 == 0
+          and 64 <= x.shape[-1] <= 1024 and x.shape[-1] == y.shape[-1])
+    if ok and logit_scale is not None and float(logit_scale) <= 0:
+        ok = False  # a non-positive scale changes the order: rank the scaled scores instead
+    if fused is None:
+        return bool(ok and x.dtype == torch.bfloat16 and y.dtype == torch.bfloat16)
+    if fused and not ok:
+        raise ValueError("fused ranks need CUDA features with d % 64 == 0, 64 <= d <= 1024 and "
+                         "a positive logit scale")
+    return bool(fused)
+
+
 def paired_ranks(image_features: Tensor, text_features: Tensor, logit_scale=None,
-                 max_score_bytes: Optional[int] = None) -> Tuple[Tensor, Tensor]:
+                 max_score_bytes: Optional[int] = None, fused=None) -> Tuple[Tensor, Tensor]:
     """(image_to_text, text_to_image) 0-based ranks of the paired item i <-> i (int32 [N])."""
     x, y = image_features.detach(), text_features.detach()
     if x.shape[0] != y.shape[0]:
         raise ValueError("paired ranks need as many images as texts")
     N = x.shape[0]
+    if _use_fused(fused, x, y, logit_scale):
+        ar = torch.arange(N, device=x.device, dtype=torch.int64)
+        return fused_ranks(x, y, ar), fused_ranks(y, x, ar)
     budget = MAX_SCORE_BYTES if max_score_bytes is None else int(max_score_bytes)
     ar = torch.arange(N, device=x.device, dtype=torch.int64)
     if N * N * 4 <= budget:
@@ -101,10 +135,10 @@ def paired_ranks(image_features: Tensor, text_features: Tensor, logit_scale=None
 
 
 def get_clip_metrics(image_features: Tensor, text_features: Tensor, logit_scale,
-                     max_score_bytes: Optional[int] = None) -> dict:
+                     max_score_bytes: Optional[int] = None, fused=None) -> dict:
     """Drop-in for train.py:338-356: mean / median rank and R@{1,5,10} of both directions, same
     keys, same numpy arithmetic on the ranks; only 2 N int32 ranks leave the device."""
-    i2t, t2i = paired_ranks(image_features, text_features, logit_scale, max_score_bytes)
+    i2t, t2i = paired_ranks(image_features, text_features, logit_scale, max_score_bytes, fused)
     metrics = {}
     for name, rank in (("image_to_text", i2t), ("text_to_image", t2i)):
         preds = rank.cpu().numpy().astype(np.int64)
@@ -117,7 +151,8 @@ def get_clip_metrics(image_features: Tensor, text_features: Tensor, logit_scale,
 
 def recall_at_k_from_encodings(image_encodings: Tensor, text_encodings: Tensor,
                                text_to_image_map: Tensor, image_to_text_map: Tensor,
-                               k_vals: Sequence[int]) -> Tuple[List[float], List[float]]:
+                               k_vals: Sequence[int], fused=None) -> Tuple[List[float],
+                                                                           List[float]]:
     """retrieval.py:59-102 after `encode_dataset`: (text_to_image_recall, image_to_text_recall),
     one entry per k.  `topk[:, :k]` contains the target iff its rank is < k, so one rank per text
     (row direction) and one per caption (column direction, one pass per caption slot) replace
@@ -125,6 +160,20 @@ def recall_at_k_from_encodings(image_encodings: Tensor, text_encodings: Tensor,
     num_text = text_encodings.shape[0]
     num_im = image_encodings.shape[0]
     captions_per_image = image_to_text_map.shape[1]
+    if captions_per_image > 0 and _use_fused(fused, text_encodings, image_encodings):
+        # fused GEMM + count: text -> image once; image -> text once per caption slot (the best
+        # caption's rank decides `topk[:, :k] == caption` for any k)
+        dev = text_encodings.device
+        text_rank = fused_ranks(text_encodings, image_encodings, text_to_image_map)
+        i2t_map = image_to_text_map.to(device=dev, dtype=torch.int64)
+        best = None
+        for c in range(captions_per_image):
+            cap_rank = fused_ranks(image_encodings, text_encodings, i2t_map[:, c])
+            best = cap_rank if best is None else torch.minimum(best, cap_rank)
+        ks = torch.tensor(list(k_vals), dtype=torch.int32, device=dev).view(-1, 1)
+        t_correct = (text_rank.view(1, -1) < ks).sum(dim=1).tolist()
+        i_correct = (best.view(1, -1) < ks).sum(dim=1).tolist()
+        return ([c / num_text for c in t_correct], [c / num_im for c in i_correct])
     dist_matrix = (text_encodings.detach() @ image_encodings.detach().T).float()
     dev = dist_matrix.device
     t2i_map = text_to_image_map.to(device=dev, dtype=torch.int64).contiguous()

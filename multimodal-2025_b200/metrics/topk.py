@@ -50,8 +50,11 @@ def top_k_indices_batched(text_emb: torch.Tensor, image_emb: torch.Tensor, k: in
                       for a in range(0, q.shape[0], rows)])
 
 
-def top_k_score(embedding_pairs, k=5):
-    """Fraction of images whose correct texts intersect their top-k texts (reference :54-82)."""
+def top_k_score(embedding_pairs, k=5, fused=None):
+    """Fraction of images whose correct texts intersect their top-k texts (reference :54-82).
+    `fused` (None = auto: bf16 CUDA embeddings): the image x text similarity GEMM and the rank
+    count run in one tcgen05 kernel (`mm25_sim_rank`, no score matrix) — an image hits iff the
+    best rank among its own texts is < k; cosine normalisation is done before the bf16 cast."""
     total_count = len(embedding_pairs)
     if total_count == 0:
         return 0.0, {"correct": 0, "total": 0}
@@ -59,6 +62,19 @@ def top_k_score(embedding_pairs, k=5):
     images = torch.stack([img for _, img in embedding_pairs])
     counts = torch.tensor([len(texts) for texts, _ in embedding_pairs], device=all_text.device)
     start = torch.cumsum(counts, 0) - counts  # `sofar` of the reference loop
+    from .retrieval import _use_fused, fused_ranks
+    if int(counts.min()) > 0 and _use_fused(fused, images, all_text):
+        t = all_text.float()
+        q = images.float()
+        t = (t / t.norm(dim=1, keepdim=True).clamp_min(1e-8)).to(torch.bfloat16)
+        q = (q / q.norm(dim=1, keepdim=True).clamp_min(1e-8)).to(torch.bfloat16)
+        best = None
+        for c in range(int(counts.max())):
+            tgt = start + torch.clamp(counts - 1, max=c)
+            r = fused_ranks(q, t, tgt)
+            best = r if best is None else torch.minimum(best, r)
+        correct_count = int((best < k).sum().item())
+        return correct_count / total_count, {"correct": correct_count, "total": total_count}
     idx = top_k_indices_batched(all_text, images, k)
     hit = ((idx >= start[:, None]) & (idx < (start + counts)[:, None])).any(dim=1)
     correct_count = int(hit.sum().item())

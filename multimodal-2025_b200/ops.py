@@ -533,6 +533,36 @@ def rank_both(scores: Tensor, row0: int, row_tval: Optional[Tensor], row_tcol: O
     _lib.check(rc, "mm25_rank_both")
 
 
+@torch.library.custom_op("mm25::sim_rank", mutates_args=("rank",), device_types="cuda")
+def sim_rank(a: Tensor, b: Tensor, tval: Tensor, tcol: Tensor, rank: Tensor) -> None:
+    """Ranks fused into the similarity GEMM (include/mm25.h mm25_sim_rank): ADDS into rank[q]
+    (int32) the number of gallery rows j != tcol[q] whose score a_q . b_j sorts ahead of the
+    target (tval[q], tcol[q]) in the stable descending order; the [Q, N] scores are never
+    written.  a [Q, d], b [N, d] bf16."""
+    if not (a.is_cuda and b.is_cuda):
+        raise _lib.MM25Error("sim_rank needs CUDA tensors: this path has no CPU fallback")
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or a.dim() != 2 or b.dim() != 2:
+        raise TypeError("a, b must be 2-D bf16")
+    a, b = a.contiguous(), b.contiguous()
+    Q, d = a.shape
+    N = b.shape[0]
+    for name, t, dt in (("tval", tval, torch.float32), ("tcol", tcol, torch.int64),
+                        ("rank", rank, torch.int32)):
+        if t.dtype != dt or t.numel() != Q or not t.is_contiguous() or t.device != a.device:
+            raise ValueError("%s must be a contiguous %s tensor of %d elements on %s"
+                             % (name, dt, Q, a.device))
+    with torch.cuda.device(a.device):
+        rc = _lib.lib().mm25_sim_rank(_p(a), _p(b), BF16, Q, N, d, _p(tval), _p(tcol), _p(rank),
+                                      _stream(a))
+    _lib.check(rc, "mm25_sim_rank")
+
+
+def sim_rank_eligible(a: Tensor, b: Tensor) -> bool:
+    d = a.shape[-1]
+    return (a.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and
+            d % 64 == 0 and 64 <= d <= 1024)
+
+
 @torch.library.custom_op("mm25::sim_bwd_rs", mutates_args=(), device_types="cuda")
 def sim_bwd_rs(a: Tensor, b: Tensor, scale: Tensor, scale_kind: int, clamp_max: float,
                diag_offset: int, row_lse: Tensor, col_lse: Tensor, w_row: float, w_col: float,

@@ -185,3 +185,41 @@ def test_modulated_tc_matches_simt(lib_built, M, N, d, d2, off):
         assert (got[k] - ref[k]).norm().item() <= 2e-2 * ref[k].norm().item(), k
     assert abs(got[4].item() - ref[4].item()) <= 2e-2 * abs(ref[4].item()) + 1e-6
     assert (got[5] - ref[5]).norm().item() <= 1e-3 * ref[5].norm().item() + 1e-7
+
+
+@pytest.mark.parametrize("dtype,k,b,d,tl,tg", [(torch.float32, 4, 96, 64, 1e-5, 1e-4),
+                                               (torch.bfloat16, 4, 256, 256, 2e-3, 2e-2),
+                                               (torch.bfloat16, 8, 256, 512, 2e-3, 2e-2)])
+@pytest.mark.parametrize("need_scale", [True, False])
+def test_cached_negatives_live_rows_vs_oracle(lib_built, dtype, k, b, d, tl, tg, need_scale):
+    """SURVEY §8f rank 4 (AlignCLIP/main/train.py:139-157): micro-step j of the accumulation loop;
+    loss of the spliced batch (oracle.openclip_loss) and gradients of the live rows only, fp32
+    SIMT and bf16 tcgen05 rectangular kernels (positives at column offset j b)."""
+    from multimodal_2025_b200.losses.negatives_cache import cached_negatives_clip_loss
+    j = k - 2
+    x, y = O.synth_embeddings(k * b, d, 12, correlated=True, dtype=dtype)
+    g = torch.Generator().manual_seed(3)
+    live = slice(j * b, (j + 1) * b)
+    li = torch.nn.functional.normalize(x[live].float() + 0.05 * torch.randn(b, d, generator=g),
+                                       dim=-1).to(dtype)
+    lt = torch.nn.functional.normalize(y[live].float() + 0.05 * torch.randn(b, d, generator=g),
+                                       dim=-1).to(dtype)
+    a = li.float().clone().requires_grad_(True)
+    t = lt.float().clone().requires_grad_(True)
+    s = torch.tensor(14.285, requires_grad=need_scale)
+    xi = torch.cat([x[:j * b].float(), a, x[(j + 1) * b:].float()])
+    xt = torch.cat([y[:j * b].float(), t, y[(j + 1) * b:].float()])
+    ref = O.openclip_loss(xi, xt, s)
+    ref.backward()
+    ci = [c.cuda() for c in x.split(b)]
+    ct = [c.cuda() for c in y.split(b)]
+    a2 = li.cuda().requires_grad_(True)
+    t2 = lt.cuda().requires_grad_(True)
+    s2 = torch.tensor(14.285, device="cuda", requires_grad=need_scale)
+    loss = cached_negatives_clip_loss(a2, t2, s2, ci, ct, j)
+    loss.backward()
+    assert rel_err(loss.detach().cpu(), ref.detach()) < tl
+    assert rel_err(a2.grad.float().cpu(), a.grad) < tg
+    assert rel_err(t2.grad.float().cpu(), t.grad) < tg
+    if need_scale:
+        assert rel_err(s2.grad.cpu(), s.grad) < tg

@@ -489,3 +489,39 @@ def test_dropin_cliploss_distributed_flags_world2_gloo():
             assert (gx - rx).norm() < 1e-4 * rx.norm(), gwg
             assert (gy - ry).norm() < 1e-4 * ry.norm(), gwg
         assert all(e is not None for e in errs), errs
+
+
+@pytest.mark.parametrize("need_scale", [True, False])
+def test_cached_negatives_host_logic_with_standin(need_scale):
+    """SURVEY §8f rank 4 (main/train.py:139-157): micro-step j of the accumulation loop — loss of
+    the spliced batch, gradients of the LIVE rows only — against autograd through the
+    reference formula on the spliced tensors; dense stand-in ops (the GPU test runs the kernels)."""
+    import torch.nn.functional as F
+    import cpu_backend
+    from multimodal_2025_b200.losses.negatives_cache import cached_negatives_clip_loss
+    g = torch.Generator().manual_seed(2)
+    k, b, d, j = 4, 6, 16, 2
+    ci = [F.normalize(torch.randn(b, d, generator=g), dim=-1) for _ in range(k)]
+    ct = [F.normalize(torch.randn(b, d, generator=g), dim=-1) for _ in range(k)]
+    li = F.normalize(ci[j] + 0.05 * torch.randn(b, d, generator=g), dim=-1)
+    lt = F.normalize(ct[j] + 0.05 * torch.randn(b, d, generator=g), dim=-1)
+    # reference: loss(**inputs) with inputs = cat(accumulated[:j] + [live] + accumulated[j+1:])
+    a = li.clone().requires_grad_(True)
+    t = lt.clone().requires_grad_(True)
+    s = torch.tensor(14.285, requires_grad=need_scale)
+    xi = torch.cat(ci[:j] + [a] + ci[j + 1:])
+    xt = torch.cat(ct[:j] + [t] + ct[j + 1:])
+    z = s * xi @ xt.T
+    lab = torch.arange(k * b)
+    ref = (F.cross_entropy(z, lab) + F.cross_entropy(z.T, lab)) / 2
+    ref.backward()
+    a2 = li.clone().requires_grad_(True)
+    t2 = lt.clone().requires_grad_(True)
+    s2 = torch.tensor(14.285, requires_grad=need_scale)
+    loss = cached_negatives_clip_loss(a2, t2, s2, ci, ct, j, backend=cpu_backend)
+    loss.backward()
+    assert abs(float(loss) - float(ref)) < 1e-5 * abs(float(ref))
+    assert (a2.grad - a.grad).norm() < 1e-4 * a.grad.norm()
+    assert (t2.grad - t.grad).norm() < 1e-4 * t.grad.norm()
+    if need_scale:
+        assert abs(float(s2.grad) - float(s.grad)) < 1e-4 * abs(float(s.grad))

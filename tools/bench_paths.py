@@ -212,6 +212,23 @@ def main():
     xt = torch.nn.functional.normalize(xi + 0.05 * torch.randn(n, dd, device=dev), dim=-1)
     ms = timeit(lambda: get_clip_metrics(xi, xt, 14.2857), reps=3, warm=1)
     emit(path="get_clip_metrics N=32768 d=512 fp32 (GEMM + rank_both + 2 x D2H of N ints)", ms=ms)
+    # fused GEMM + rank count (csrc/sim_tc_rank.cu): no score matrix; one sweep per direction
+    from multimodal_2025_b200.metrics.retrieval import fused_ranks
+    xb, tb = xi.bfloat16(), xt.bfloat16()
+    ar = torch.arange(n, device=dev)
+    ms = timeit(lambda: fused_ranks(xb, tb, ar), reps=5, warm=2)
+    tf = 2.0 * n * n * dd / (ms * 1e-3) / 1e12
+    emit(path="fused_ranks (sim_rank_tc_kernel, one direction) N=32768 d=512 bf16", ms=ms,
+         roofline={"bound": "tensor", "achieved": tf, "peak": PEAKS["bf16_tflops"],
+                   "unit": "TFLOP/s", "frac": tf / PEAKS["bf16_tflops"]},
+         note="includes the fp32 target dot products and the memset; scores never written")
+    ms = timeit(lambda: get_clip_metrics(xb, tb, 14.2857), reps=3, warm=1)
+    emit(path="get_clip_metrics N=32768 d=512 bf16 FUSED (2 sweeps + 2 x D2H of N ints)", ms=ms)
+    # small-Q top-k (the reference's call shape: one query against all texts)
+    for Q in (1, 16):
+        sc1 = torch.randn(Q, 1 << 20, generator=g).to(dev)
+        ms = timeit(lambda: ops.topk_rows(sc1, 5))
+        hbm_line("topk_rows k=5 Q=%d N_t=1048576" % Q, ms, Q * (1 << 20) * 4, "small-Q shape")
 
 
 if __name__ == "__main__":

@@ -15,6 +15,13 @@ for step in "$@"; do
     bench20)   run bench20 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline ;;
     bench_te0) run bench_te0 600 env MM25_TE=0 python bench.py --steps 10 --warmup 3 --no-cpu-baseline ;;
     bench_2cta) run bench_2cta 600 env MM25_TE=0 MM25_GEMM_2CTA=1 python bench.py --steps 10 --warmup 3 --no-cpu-baseline ;;
+    cfgs)      for c in cfg1 cfg3 cfg4 cfg5; do run bench_$c 900 python bench.py --config $c --steps 5 --warmup 3; done
+               run bench_cfg3_bf16 600 python bench.py --config cfg3 --precision bf16 --steps 5 --warmup 3 --no-cpu-baseline
+               run bench_cfg4_bf16 600 python bench.py --config cfg4 --precision bf16 --steps 5 --warmup 3 --no-cpu-baseline
+               run bench_cfg4_vmf 600 python bench.py --config cfg4 --vdist vmf --precision bf16 --steps 5 --warmup 3 --no-cpu-baseline
+               run bench_cfg4_pn 600 python bench.py --config cfg4 --vdist projected_normal --precision bf16 --steps 5 --warmup 3 --no-cpu-baseline ;;
+    newtests)  run newtests 1200 python -m pytest tests/test_config_sizes_gpu.py tests/test_alignclip_gpu.py -m gpu -q ;;
+    refarm)    run refarm 900 python bench.py --impl reference --steps 3 --warmup 1 ;;
     diag)      run diag 600 python tools/diag_te.py ;;
     diag0)     run diag0 600 env MM25_TE=0 python tools/diag_te.py ;;
     te)        run te 600 python tools/bench_te.py ;;

@@ -3,7 +3,7 @@ import os, sys
 import torch, torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from oracle import losses_oracle as O
+from bench import synth_pair
 from multimodal_2025_b200.dist import ShardedClipLoss
 
 rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); lr = int(os.environ["LOCAL_RANK"])
@@ -11,7 +11,7 @@ torch.cuda.set_device(lr); dev = torch.device("cuda", lr)
 dist.init_process_group("nccl", device_id=dev)
 N, d = 32768, 512
 n = N // world
-x32, y32 = O.synth_embeddings(N, d, 1234)
+x32, y32 = synth_pair(N, d, 1234)
 sl = slice(rank * n, (rank + 1) * n)
 x = x32[sl].bfloat16().to(dev).requires_grad_(True)
 y = y32[sl].bfloat16().to(dev).requires_grad_(True)
