@@ -21,6 +21,9 @@ for step in "$@"; do
                run bench_cfg4_vmf 600 python bench.py --config cfg4 --vdist vmf --precision bf16 --steps 5 --warmup 3 --no-cpu-baseline
                run bench_cfg4_pn 600 python bench.py --config cfg4 --vdist projected_normal --precision bf16 --steps 5 --warmup 3 --no-cpu-baseline ;;
     newtests)  run newtests 1200 python -m pytest tests/test_config_sizes_gpu.py tests/test_alignclip_gpu.py -m gpu -q ;;
+    fused)     run fused 900 python -m pytest tests/test_fused_rank_gpu.py -m gpu -q ;;
+    cfg5)      run bench_cfg5 900 python bench.py --config cfg5 --steps 5 --warmup 3 ;;
+    exper)     run exper 1800 env MM25_TEST_EXPERIMENTAL=1 python -m pytest tests/test_zz_retrieval_gpu.py -m gpu -q -k "scatter or two_cta or pair_kernels" ;;
     refarm)    run refarm 900 python bench.py --impl reference --steps 3 --warmup 1 ;;
     diag)      run diag 600 python tools/diag_te.py ;;
     diag0)     run diag0 600 env MM25_TE=0 python tools/diag_te.py ;;
