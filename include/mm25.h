@@ -386,6 +386,16 @@ int mm25_log_bessel(const double* kappa, int64_t n, double nu, double* log_i_nu,
  * ------------------------------------------------------------------------------------------ */
 int mm25_topk_rows(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_t k,
                    int64_t* out_idx, float* out_val, void* stream);
+/* The same result (bit for bit) through the sliced path: a row is cut into slices that one CTA
+ * each loads ONCE into shared memory (radix select, gather and sort never return to HBM), so a
+ * small-Q call — the reference's own shape, one query against all texts, metrics/topk.py:43-48
+ * — uses every SM; a merge kernel sorts the slices' candidates.  `workspace` holds them:
+ * mm25_topk_workspace_bytes(Q, N, k) bytes (0 when one slice per row suffices or when the shape
+ * falls back to mm25_topk_rows: k * slices > 8192, Q > 65535). */
+size_t mm25_topk_workspace_bytes(int64_t Q, int64_t N, int64_t k);
+int mm25_topk_rows_ws(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_t k,
+                      int64_t* out_idx, float* out_val, void* workspace, size_t workspace_bytes,
+                      void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Retrieval ranks without the sort (AlignCLIP/main/train.py:338-356 `get_clip_metrics`:

@@ -133,6 +133,8 @@ SIGNATURES = {
                                _f32, _f32, _f32, _f32, _vp, _vp, _vp, _i64, _vp, _vp, _sz, _f32,
                                _vp, _vp, _vp]),
     "mm25_topk_rows": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "mm25_topk_workspace_bytes": (_sz, [_i64, _i64, _i64]),
+    "mm25_topk_rows_ws": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _sz, _vp]),
     "mm25_rank_both": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "mm25_sim_rank": (_int, [_vp, _vp, _int, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "mm25_rowdot": (_int, [_vp, _vp, _vp, _i64, _i64, _vp]),

@@ -129,6 +129,199 @@ topk_rows_kernel(const float* __restrict__ scores, int64_t N, int64_t ld, int k,
   }
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Sliced path (round 2): a row is cut into C slices of at most TK_SLICE elements; one CTA per
+// (slice, row) loads its slice ONCE (16-byte loads when aligned) into shared memory as keys, so
+// the four radix passes, the gather and the sort never go back to HBM, and small-Q calls
+// (the reference's shape: one query against all texts, metrics/topk.py:43-48) spread over
+// every SM instead of one.  The top-k of the row is contained in the union of the slices'
+// top-k (the composite (key, ~index) order is total), so a merge kernel sorts the C k
+// candidates.  Same result as topk_rows_kernel, bit for bit.
+// ------------------------------------------------------------------------------------------
+constexpr int TK_SLICE = 16384;       // 64 KB of keys: two CTAs per SM
+constexpr int TK_HCOPIES = 8;
+constexpr int TK_MERGE_MAX = 8192;    // candidates the merge kernel sorts in shared memory
+
+struct SliceSmem {
+  uint32_t keys[TK_SLICE];
+  unsigned long long cand[TK_MAXK];
+  unsigned int hist[TK_HCOPIES][256];
+  unsigned int warp_cnt[TK_THREADS / 32];
+  unsigned int prefix, remaining, gt_count, eq_base;
+};
+
+__device__ __forceinline__ void bitonic_desc(unsigned long long* a, int P, int tid) {
+  for (int size = 2; size <= P; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int t = tid; t < P / 2; t += TK_THREADS) {
+        const int lo = 2 * t - (t & (stride - 1));
+        const int hi = lo + stride;
+        const bool desc = ((lo & size) == 0);
+        const unsigned long long x = a[lo], y = a[hi];
+        if ((x < y) == desc) { a[lo] = y; a[hi] = x; }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(TK_THREADS, 2)
+topk_slice_kernel(const float* __restrict__ scores, int64_t N, int64_t ld, int k, int C,
+                  int64_t slice_len, int64_t* __restrict__ out_idx, float* __restrict__ out_val,
+                  unsigned long long* __restrict__ ws) {
+  extern __shared__ __align__(16) uint8_t tk_smem[];
+  SliceSmem& sm = *reinterpret_cast<SliceSmem*>(tk_smem);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t rowi = blockIdx.y;
+  const float* row = scores + rowi * ld;
+  const int64_t s0 = (int64_t)blockIdx.x * slice_len;
+  const int n = (int)min(slice_len, N - s0);
+  const int kk = min(k, n);
+  const float* src = row + s0;
+
+  // ---- the one HBM pass: slice -> order-preserving keys in shared memory ----------------
+  if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    const int n4 = n >> 2;
+    for (int i = tid; i < n4; i += TK_THREADS) {
+      const float4 v = __ldg(s4 + i);
+      uint4 kq = make_uint4(order_key(v.x), order_key(v.y), order_key(v.z), order_key(v.w));
+      *reinterpret_cast<uint4*>(&sm.keys[4 * i]) = kq;
+    }
+    for (int i = 4 * n4 + tid; i < n; i += TK_THREADS) sm.keys[i] = order_key(src[i]);
+  } else {
+    for (int i = tid; i < n; i += TK_THREADS) sm.keys[i] = order_key(src[i]);
+  }
+  if (tid == 0) { sm.prefix = 0; sm.remaining = (unsigned)kk; }
+  __syncthreads();
+
+  // ---- radix select of the kk-th largest key of the slice (shared memory only) -----------
+  unsigned int* myhist = sm.hist[warp & (TK_HCOPIES - 1)];
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 24 - 8 * pass;
+    const uint32_t mask_hi = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + 8));
+    for (int i = tid; i < TK_HCOPIES * 256; i += TK_THREADS) (&sm.hist[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t prefix = sm.prefix;
+    for (int i0 = 0; i0 < n; i0 += TK_THREADS) {
+      const int i = i0 + tid;
+      const bool in = i < n && ((sm.keys[i] & mask_hi) == prefix);
+      const unsigned act = __ballot_sync(0xffffffffu, in);
+      if (in) {
+        const uint32_t bin = (sm.keys[i] >> shift) & 255u;
+        const unsigned peers = __match_any_sync(act, bin);   // one atomic per distinct bin
+        if (lane == __ffs(peers) - 1) atomicAdd(&myhist[bin], (unsigned)__popc(peers));
+      }
+    }
+    __syncthreads();
+    if (tid < 256) {
+      unsigned t = 0;
+#pragma unroll
+      for (int c = 0; c < TK_HCOPIES; ++c) t += sm.hist[c][tid];
+      sm.hist[0][tid] = t;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      unsigned rem = sm.remaining;
+      int b = 255;
+      for (; b > 0; --b) {
+        if (sm.hist[0][b] >= rem) break;
+        rem -= sm.hist[0][b];
+      }
+      sm.prefix = prefix | ((uint32_t)b << shift);
+      sm.remaining = rem;
+    }
+    __syncthreads();
+  }
+  const uint32_t T = sm.prefix;
+  const unsigned need_eq = sm.remaining;
+  if (tid == 0) { sm.gt_count = 0; sm.eq_base = 0; }
+  __syncthreads();
+
+  // ---- gather: keys > T in any order, then the first need_eq keys == T by index ----------
+  const unsigned n_gt = (unsigned)kk - need_eq;
+  for (int i0 = 0; i0 < n; i0 += TK_THREADS) {
+    const int i = i0 + tid;
+    uint32_t key = 0;
+    bool gt = false, eq = false;
+    if (i < n) { key = sm.keys[i]; gt = key > T; eq = key == T; }
+    const unsigned long long comp =
+        ((unsigned long long)key << 32) | (unsigned long long)(0xFFFFFFFFu - (uint32_t)(s0 + i));
+    if (gt) sm.cand[atomicAdd(&sm.gt_count, 1u)] = comp;
+    const unsigned bal = __ballot_sync(0xffffffffu, eq);
+    if (sm.eq_base < need_eq) {            // uniform: read before the barrier below
+      if (lane == 0) sm.warp_cnt[warp] = __popc(bal);
+      __syncthreads();
+      if (eq) {
+        unsigned before = sm.eq_base;
+        for (int w = 0; w < warp; ++w) before += sm.warp_cnt[w];
+        before += __popc(bal & ((1u << lane) - 1u));
+        if (before < need_eq) sm.cand[n_gt + before] = comp;
+      }
+      __syncthreads();
+      if (tid == 0) {
+        unsigned tot = 0;
+        for (int w = 0; w < TK_THREADS / 32; ++w) tot += sm.warp_cnt[w];
+        sm.eq_base += tot;
+      }
+      __syncthreads();
+    }
+  }
+  __syncthreads();
+
+  // ---- sort the slice's candidates, descending on (key, ~index) --------------------------
+  int P = 1;
+  while (P < kk) P <<= 1;
+  for (int i = kk + tid; i < P; i += TK_THREADS) sm.cand[i] = 0ull;
+  __syncthreads();
+  bitonic_desc(sm.cand, P, tid);
+  if (C == 1) {
+    for (int j = tid; j < k; j += TK_THREADS) {
+      const uint32_t idx = 0xFFFFFFFFu - (uint32_t)(sm.cand[j] & 0xFFFFFFFFull);
+      out_idx[rowi * k + j] = (int64_t)idx;
+      if (out_val) out_val[rowi * k + j] = row[idx];
+    }
+  } else {
+    unsigned long long* dst = ws + (rowi * C + blockIdx.x) * (int64_t)k;
+    for (int j = tid; j < k; j += TK_THREADS) dst[j] = j < kk ? sm.cand[j] : 0ull;  // 0 = pad
+  }
+}
+
+__global__ void __launch_bounds__(TK_THREADS)
+topk_merge_kernel(const unsigned long long* __restrict__ ws, int total, int k,
+                  const float* __restrict__ scores, int64_t ld, int64_t* __restrict__ out_idx,
+                  float* __restrict__ out_val) {
+  extern __shared__ __align__(16) uint8_t tk_smem[];
+  unsigned long long* a = reinterpret_cast<unsigned long long*>(tk_smem);
+  const int tid = threadIdx.x;
+  const int64_t rowi = blockIdx.x;
+  int P = 1;
+  while (P < total) P <<= 1;
+  for (int i = tid; i < P; i += TK_THREADS) a[i] = i < total ? ws[rowi * total + i] : 0ull;
+  __syncthreads();
+  bitonic_desc(a, P, tid);
+  const float* row = scores + rowi * ld;
+  for (int j = tid; j < k; j += TK_THREADS) {
+    const uint32_t idx = 0xFFFFFFFFu - (uint32_t)(a[j] & 0xFFFFFFFFull);
+    out_idx[rowi * k + j] = (int64_t)idx;
+    if (out_val) out_val[rowi * k + j] = row[idx];
+  }
+}
+
+// slices per row for the sliced path; 0 = not applicable (the one-CTA-per-row kernel runs)
+static int topk_slices(int64_t Q, int64_t N, int64_t k) {
+  if (Q > 65535) return 0;
+  const int64_t c_min = (N + TK_SLICE - 1) / TK_SLICE;
+  const int64_t c_fill = (2 * 148 + Q - 1) / Q;          // fill the SMs when Q is small
+  int64_t C = c_fill < N / 8192 ? c_fill : N / 8192;     // ... with slices of >= 8192 elements
+  if (C < c_min) C = c_min;
+  if (C < 1) C = 1;
+  if (C > 1 && C * k > TK_MERGE_MAX) C = TK_MERGE_MAX / k;
+  if (C < c_min) return 0;                               // merge would not fit: plain kernel
+  return (int)C;
+}
+
 }  // namespace mm25
 
 extern "C" int mm25_topk_rows(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_t k,
@@ -140,5 +333,47 @@ extern "C" int mm25_topk_rows(const float* scores, int64_t Q, int64_t N, int64_t
   mm25::topk_rows_kernel<<<(unsigned)Q, mm25::TK_THREADS, 0, (cudaStream_t)stream>>>(
       scores, N, ld, (int)k, out_idx, out_val);
   MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
+extern "C" size_t mm25_topk_workspace_bytes(int64_t Q, int64_t N, int64_t k) {
+  if (Q <= 0 || N <= 0 || k <= 0 || k > mm25::TK_MAXK) return 0;
+  const int C = mm25::topk_slices(Q, N, k);
+  return C > 1 ? sizeof(unsigned long long) * (size_t)Q * C * k : 0;
+}
+
+extern "C" int mm25_topk_rows_ws(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_t k,
+                                 int64_t* out_idx, float* out_val, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+  if (Q <= 0 || N <= 0 || k <= 0 || k > N || k > mm25::TK_MAXK || ld < N ||
+      N >= (1ll << 32))
+    return MM25_ERR_SHAPE;
+  if (!scores || !out_idx) return MM25_ERR_ARG;
+  const int C = mm25::topk_slices(Q, N, k);
+  if (C == 0) return mm25_topk_rows(scores, Q, N, ld, k, out_idx, out_val, stream);
+  if (C > 1 && (!workspace || workspace_bytes < mm25_topk_workspace_bytes(Q, N, k)))
+    return MM25_ERR_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t slice_len = ((N + C - 1) / C + 3) & ~int64_t(3);  // keeps 16-byte alignment
+  const int Cn = (int)((N + slice_len - 1) / slice_len);
+  const size_t smem = sizeof(mm25::SliceSmem);
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(mm25::topk_slice_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // the slice count of the launch may be smaller than C after rounding slice_len up; the
+  // workspace layout uses the launched count
+  mm25::topk_slice_kernel<<<dim3((unsigned)Cn, (unsigned)Q), mm25::TK_THREADS, smem, st>>>(
+      scores, N, ld, (int)k, Cn, slice_len, out_idx, out_val, (unsigned long long*)workspace);
+  MM25_LAUNCH_CHECK();
+  if (Cn > 1) {
+    const int total = Cn * (int)k;
+    int P = 1;
+    while (P < total) P <<= 1;
+    const size_t msmem = sizeof(unsigned long long) * (size_t)P;
+    MM25_CUDA_CHECK(cudaFuncSetAttribute(mm25::topk_merge_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+    mm25::topk_merge_kernel<<<(unsigned)Q, mm25::TK_THREADS, msmem, st>>>(
+        (const unsigned long long*)workspace, total, (int)k, scores, ld, out_idx, out_val);
+    MM25_LAUNCH_CHECK();
+  }
   return MM25_OK;
 }

@@ -6,6 +6,7 @@ kernels never allocate (include/mm25.h conventions).
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Tuple
 
 import torch
@@ -498,7 +499,14 @@ def topk_rows(scores: Tensor, k: int) -> Tuple[Tensor, Tensor]:
     with torch.cuda.device(s.device):
         idx = torch.empty((Q, k), dtype=torch.int64, device=s.device)
         val = torch.empty((Q, k), dtype=torch.float32, device=s.device)
-        rc = _lib.lib().mm25_topk_rows(_p(s), Q, N, N, k, _p(idx), _p(val), _stream(s))
+        L = _lib.lib()
+        if os.environ.get("MM25_TOPK_PLAIN"):   # A/B switch: the one-CTA-per-row kernel
+            rc = L.mm25_topk_rows(_p(s), Q, N, N, k, _p(idx), _p(val), _stream(s))
+        else:
+            wsb = int(L.mm25_topk_workspace_bytes(Q, N, k))
+            ws = torch.empty((max(wsb, 16),), dtype=torch.uint8, device=s.device)
+            rc = L.mm25_topk_rows_ws(_p(s), Q, N, N, k, _p(idx), _p(val), _p(ws), ws.numel(),
+                                     _stream(s))
     _lib.check(rc, "mm25_topk_rows")
     return idx, val
 
