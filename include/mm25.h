@@ -293,6 +293,13 @@ int mm25_col_merge_ld(const float* col_max, const float* col_sum, int64_t P, int
  * `torch.distributed.nn.all_gather` of the reference's gather_features (loss.py:49-51). */
 int mm25_peer_bcast(const void* src, int64_t bytes, void* const* peer_ptrs, int64_t npeers,
                     int64_t dst_offset_bytes, void* stream);
+/* The same gather through the NVSwitch multicast mapping of the symmetric buffer: one
+ * `multimem.st` per 16 bytes lands in every rank's copy (the sender's included), so each rank
+ * sends its shard once instead of `npeers` times.  `mc_ptr` = multicast address of the buffer
+ * (torch.distributed._symmetric_memory handle `multicast_ptr`); bytes, offset and pointers
+ * 16-byte aligned.  A cross-rank barrier must follow, as for mm25_peer_bcast. */
+int mm25_peer_bcast_mc(const void* src, int64_t bytes, void* mc_ptr, int64_t dst_offset_bytes,
+                       void* stream);
 /* Label-smoothing term of the row-sharded loss (clipLoss.py:111-117 in closed form):
  * loss[0] -= coef * s * (sum_p sx_p) . (sum_p sy_p), sx_p / sy_p = the [d] column sums of
  * xhat / yhat of rank p at column offsets ox / oy of a gathered [P, ld] payload.  One CTA. */

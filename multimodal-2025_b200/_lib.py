@@ -147,6 +147,7 @@ SIGNATURES = {
     "mm25_col_merge": (_int, [_vp, _vp, _i64, _i64, _vp, _vp]),
     "mm25_col_merge_ld": (_int, [_vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "mm25_peer_bcast": (_int, [_vp, _i64, _vp, _i64, _i64, _vp]),
+    "mm25_peer_bcast_mc": (_int, [_vp, _i64, _vp, _i64, _vp]),
     "mm25_smooth_term": (_int, [_vp, _i64, _i64, _i64, _i64, _i64, _vp, _int, _f32, _f32, _vp,
                                 _vp]),
     "mm25_scale_param_grad": (_int, [_vp, _vp, _int, _f32, _vp, _vp]),

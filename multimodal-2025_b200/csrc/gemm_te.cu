@@ -36,6 +36,7 @@
 #include "tc_common.cuh"
 #include "gemm_tc.h"
 
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 
@@ -52,6 +53,7 @@ constexpr int B_BYTES = 2 * BH_BYTES;       // up to two MMAs per k-step
 constexpr int NPROD = 8;                    // A-producer warps
 constexpr int PROD0 = 2;                    // first A-producer warp; warps 2..5 also run the epilogue
 constexpr int THREADS = 32 * (PROD0 + NPROD);   // 320 (168 registers per thread)
+constexpr int MAX_PAIRS = 96;               // >= SMs / 2
 constexpr int NFULL = 1 + 2 * (NPROD / NST);  // arrivals on the leader's `full` barrier: the TMA
                                             // thread + the two warps of the stage's group per CTA
 
@@ -89,7 +91,8 @@ struct Params {
   Problem p[2];
   int ntiles;              // column tiles of C (Ng / (256 NH))
   int nh;                  // 256-wide MMAs per k-step (1 or 2)
-  int share;               // k-blocks per pair
+  int share;               // k-blocks per pair (uniform split; start[] is what the kernel reads)
+  int start[MAX_PAIRS + 1];  // pair i executes k-blocks [start[i], start[i + 1]) of the sequence
   int total;               // p[0].kb_total + p[1].kb_total
   const int* e_flag;       // device flag: 0 = E already holds G' (recompute path ran) -> copy
   const float* consts;     // device {k_all, k_diag} per batch entry
@@ -420,7 +423,7 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
   const bool leader = rank == 0;
   const int pair = blockIdx.x >> 1;
   const int nh = P.nh, nacc = nh == 2 ? 1 : 2;
-  const int g_begin = pair * P.share, g_end = min(P.total, g_begin + P.share);
+  const int g_begin = P.start[pair], g_end = P.start[pair + 1];
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < NST; ++i) { mbar_init(&sm.full[i], NFULL); mbar_init(&sm.empty[i], 1); }
@@ -758,12 +761,41 @@ int gemm_te_grouped(const GemmTeDesc* d0, const GemmTeDesc* d1, int64_t Ng, cons
   P.pf_dist = pf;
   P.stats = g_te_stats;
   P.total = P.p[0].kb_total + P.p[1].kb_total;
-  const int maxpairs = sm_count_te() / 2;
+  int maxpairs = sm_count_te() / 2;
+  if (maxpairs > ge::MAX_PAIRS) maxpairs = ge::MAX_PAIRS;
   // equal contiguous ranges, not shorter than 8 k-blocks
   int share = (P.total + maxpairs - 1) / maxpairs;
   if (share < 8) share = 8;
   P.share = share;
   const int pairs = (P.total + share - 1) / share;
+  for (int i = 0; i <= pairs; ++i) P.start[i] = (int)std::min<int64_t>((int64_t)i * share, P.total);
+  // Fused reduce-scatter: the epilogue of a scatter job pushes its 256 x Ng fp32 tile over
+  // NVLink with red.global and is NOT overlapped with MMAs (one accumulator), so a job of the
+  // scatter problem costs nk + epi k-block times, not nk.  The cut points are placed at equal
+  // COST instead of equal k-block counts (epi in k-block units: MM25_TE_EPI_KB, default 40 —
+  // measured at 8 ranks, profiles/r2_n8_timeline.txt: ~41 us per epilogue, ~1 us per k-block).
+  {
+    static const int epi_env = getenv("MM25_TE_EPI_KB") ? atoi(getenv("MM25_TE_EPI_KB")) : 40;
+    const int ep[2] = {P.p[0].scatter ? epi_env : 0, P.p[1].scatter ? epi_env : 0};
+    if ((ep[0] > 0 || ep[1] > 0) && pairs > 1) {
+      const int64_t c0 = (int64_t)P.p[0].njobs * (P.p[0].nk + ep[0]);
+      const int64_t c1 = (int64_t)P.p[1].njobs * (P.p[1].nk + ep[1]);
+      const int64_t ctot = c0 + c1;
+      for (int i = 1; i < pairs; ++i) {
+        int64_t c = ctot * i / pairs;
+        const int pb = c < c0 ? 0 : 1;
+        if (pb) c -= c0;
+        const int64_t per = P.p[pb].nk + ep[pb];
+        const int64_t job = c / per;
+        int64_t kb = c - job * per;
+        if (kb > P.p[pb].nk) kb = P.p[pb].nk;   // a cut inside the epilogue share: after the job
+        int64_t g = (pb ? P.p[0].kb_total : 0) + job * P.p[pb].nk + kb;
+        if (g < P.start[i - 1]) g = P.start[i - 1];
+        P.start[i] = (int)std::min<int64_t>(g, P.total);
+      }
+      P.start[pairs] = P.total;
+    }
+  }
   if (zero_c) {
     const GemmTeDesc* ds[2] = {d0, d1};
     for (int i = 0; i < 2; ++i) {

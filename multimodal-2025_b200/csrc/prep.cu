@@ -610,6 +610,38 @@ extern "C" int mm25_peer_bcast(const void* src, int64_t bytes, void* const* peer
   return MM25_OK;
 }
 
+// NVSwitch multicast variant: ONE `multimem.st` per 16 bytes is replicated by the switch into
+// every rank's copy of the symmetric buffer (this rank's included), so a rank sends its shard
+// once instead of P times.  `mc_dst` is the multicast address of the buffer
+// (torch symmetric memory `multicast_ptr`; 0 where the fabric has no multicast support).
+__global__ void __launch_bounds__(256) peer_bcast_mc_kernel(const uint4* __restrict__ src,
+                                                            int64_t nvec, uint4* mc_dst) {
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * 256) {
+    const uint4 v = __ldg(src + i);
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_dst + i),
+                 "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)),
+                 "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                 : "memory");
+  }
+}
+
+extern "C" int mm25_peer_bcast_mc(const void* src, int64_t bytes, void* mc_ptr,
+                                  int64_t dst_offset_bytes, void* stream) {
+  if (!src || !mc_ptr || bytes <= 0) return MM25_ERR_ARG;
+  if ((bytes & 15) || (dst_offset_bytes & 15) || (reinterpret_cast<uintptr_t>(src) & 15) ||
+      (reinterpret_cast<uintptr_t>(mc_ptr) & 15))
+    return MM25_ERR_ALIGN;
+  const int64_t nvec = bytes / 16;
+  int64_t blocks = ceil_div(nvec, 256);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  peer_bcast_mc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)src, nvec,
+      reinterpret_cast<uint4*>(static_cast<char*>(mc_ptr) + dst_offset_bytes));
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
 extern "C" int mm25_col_merge_ld(const float* col_max, const float* col_sum, int64_t P,
                                  int64_t N, int64_t ld, float* col_lse, void* stream) {
   if (!col_max || !col_sum || !col_lse || P <= 0 || N <= 0 || ld < N) return MM25_ERR_ARG;

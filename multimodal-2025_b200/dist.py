@@ -85,6 +85,7 @@ def _symm_grad_buffer(n: int, d: int, device, group):
 
 
 _SYMM_GEN = {}
+_GRAD_CLEAN = {}  # symmetric dY buffer zeroed (and published) by the forward of the same step
 
 
 def _symm_buffer(tag, shape, dtype, device, group):
@@ -104,12 +105,14 @@ def _symm_buffer(tag, shape, dtype, device, group):
     return key, out
 
 
-def _peer_all_gather(B, t, tag, group):
+def _peer_all_gather(B, t, tag, group, barrier=True):
     """[n, ...] per rank -> [P n, ...]: every rank stores its shard straight into all peers'
     symmetric buffers over NVLink (one kernel) and one symmetric-memory barrier follows — no NCCL
     ring, no staging.  Returns (gathered buffer, key) or None when the fast path does not apply.
     The buffer is reused by the next call with the same shape: consume it (or check
     `_SYMM_GEN[key]`) before gathering again."""
+    if os.environ.get("MM25_DIST_LEGACY") and not barrier:
+        return None
     if not (hasattr(B, "peer_bcast") and t.is_cuda and dist.get_backend(group) == "nccl"):
         return None
     nbytes = t.numel() * t.element_size()
@@ -121,8 +124,15 @@ def _peer_all_gather(B, t, tag, group):
     if sb is None:
         return None
     buf, hdl = sb
-    B.peer_bcast(t, [int(p) for p in hdl.buffer_ptrs], rank * nbytes)
-    hdl.barrier(channel=0)
+    mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+    if (mc and nbytes % 16 == 0 and nbytes >= (1 << 16) and hasattr(B, "peer_bcast_mc")
+            and os.environ.get("MM25_MC", "0") == "1"):
+        # NVSwitch multicast: the shard is sent once and replicated in the switch
+        B.peer_bcast_mc(t, mc, rank * nbytes)
+    else:
+        B.peer_bcast(t, [int(p) for p in hdl.buffer_ptrs], rank * nbytes)
+    if barrier:  # barrier=False: the caller's next symmetric-memory barrier publishes the stores
+        hdl.barrier(channel=0)
     _SYMM_GEN[key] = _SYMM_GEN.get(key, 0) + 1
     return buf, key
 
@@ -176,22 +186,49 @@ class _ShardedClipFn(torch.autograd.Function):
             row_lse, cmax, csum, diag = B.sim_fwd(xhat, yall, None, None, None, scale32,
                                                   scale_kind, clamp_max, B.SIM_PLAIN, rank * n,
                                                   True, impl, bound)
-        # (4) ONE all-gather carries the column partials (max, sum)[N] and each rank's scalar
-        #     pieces (column sums of xhat / yhat for the smoothing term); everything is then
-        #     merged / summed locally in rank order (deterministic, one collective fewer)
+        # (4) ONE all-gather carries the column partials (max, sum)[N], each rank's column sums
+        #     of xhat / yhat (smoothing term) and the scalar loss piece of its own ROWS;
+        #     everything is then merged / summed locally in rank order (deterministic).  The
+        #     column part of the loss needs no exchange at all: after the merge every rank
+        #     holds all N column LSEs and sums them itself, so the forward has no scalar
+        #     all-reduce (one kernel + one barrier fewer than round 1).
+        legacy = bool(os.environ.get("MM25_DIST_LEGACY"))
         extra = torch.cat([sx.reshape(-1), sy.reshape(-1)]) if want_cs else cmax.new_zeros(0)
-        payload = torch.cat([cmax[0], csum[0], extra]).unsqueeze(0)
-        pg = _peer_all_gather(B, payload, "colstats", group)            # [P, 2N (+ 2d)]
+        if legacy:
+            payload = torch.cat([cmax[0], csum[0], extra]).unsqueeze(0)
+        else:
+            rowpart = B.clip_loss_finalize(row_lse, diag, None, None, None, N, scale32,
+                                           scale_kind, clamp_max, eps_ls)
+            payload = torch.cat([cmax[0], csum[0], extra, rowpart.reshape(1),
+                                 cmax.new_zeros(3)]).unsqueeze(0)   # 16-byte multiple
+        # the fused backward scatter-adds dY into this rank's symmetric buffer: zero it HERE so
+        # that the exchange below publishes the zeroing (the backward then starts without its
+        # own zero + barrier); _GRAD_CLEAN tells the backward whether that still holds
+        gkey = None
+        if (not legacy and any(ctx.needs_input_grad[:3]) and hasattr(B, "sim_bwd_rs")
+                and xhat.is_cuda and xhat.dtype == torch.bfloat16
+                and dist.get_backend(group) == "nccl" and B.tc_eligible_bwd(xhat, yall)):
+            symm = _symm_grad_buffer(n, xhat.shape[-1], xhat.device, group)
+            if symm is not None:
+                symm[0].zero_()
+                gkey = (n, xhat.shape[-1], xhat.device.index, id(group))
+                _GRAD_CLEAN[gkey] = True
+        pg = _peer_all_gather(B, payload, "colstats", group)            # [P, 2N (+ 2d) (+ 4)]
         gathered = pg[0] if pg is not None else _all_gather_cat(payload, group)
         if hasattr(B, "col_merge_ld"):
             col_lse = B.col_merge_ld(gathered, N)
         else:
             col_lse = B.col_merge(gathered[:, :N].contiguous(), gathered[:, N:2 * N].contiguous())
-        # (5) scalar pieces of the loss: local rows + local columns, then one small all-reduce
-        part = B.clip_loss_finalize(row_lse, diag, col_lse[rank * n:(rank + 1) * n]
-                                    .reshape(1, n).contiguous(), None, None, N, scale32,
-                                    scale_kind, clamp_max, eps_ls)
-        red = _all_reduce_scalar(B, part.reshape(1), "loss", group)
+        if legacy:
+            # (5) scalar pieces of the loss: local rows + local columns, then a small all-reduce
+            part = B.clip_loss_finalize(row_lse, diag, col_lse[rank * n:(rank + 1) * n]
+                                        .reshape(1, n).contiguous(), None, None, N, scale32,
+                                        scale_kind, clamp_max, eps_ls)
+            red = _all_reduce_scalar(B, part.reshape(1), "loss", group)
+        else:
+            off = 2 * N + (2 * d if want_cs else 0)
+            red = (gathered[:, off].sum(dtype=torch.float64) +
+                   col_lse.sum(dtype=torch.float64) * (0.5 / N)).to(torch.float32).reshape(1)
         if want_cs:
             coef = eps_ls / float(N) ** 2
             if hasattr(B, "smooth_term_"):
@@ -210,6 +247,7 @@ class _ShardedClipFn(torch.autograd.Function):
                    rank, n, N, scale_kind)
         ctx.kept = (e_keep, e_flag)
         ctx.ygen = (ykey, ygen)
+        ctx.gkey = gkey
         return loss
 
     @staticmethod
@@ -236,6 +274,7 @@ class _ShardedClipFn(torch.autograd.Function):
         if (hasattr(B, "sim_bwd_rs") and xhat.is_cuda and xhat.dtype == torch.bfloat16 and
                 dist.get_backend(group) == "nccl" and B.tc_eligible_bwd(xhat, yall)):
             symm = _symm_grad_buffer(n, xhat.shape[-1], xhat.device, group)
+        pgd = None
         global LAST_BACKWARD_PATH
         LAST_BACKWARD_PATH = ("fused gemm+reduce-scatter (NVLink peer memory)" if symm is not None
                               else "nccl reduce-scatter")
@@ -244,11 +283,17 @@ class _ShardedClipFn(torch.autograd.Function):
             # owner rank's buffer over NVLink peer memory (no NCCL reduce-scatter, no [N, d]
             # fp32 partial in HBM)
             buf, hdl = symm
-            buf.zero_()
-            hdl.barrier(channel=0)
+            if ctx.gkey is not None and _GRAD_CLEAN.get(ctx.gkey):
+                _GRAD_CLEAN[ctx.gkey] = False   # zeroed and published by this step's forward
+            else:
+                buf.zero_()
+                hdl.barrier(channel=0)
             da, dscale = B.sim_bwd_rs(xhat, yall, scale32, scale_kind, clamp_max, rank * n,
                                       row_lse, col_lse.reshape(1, N), *weights, g,
                                       [int(p) for p in hdl.buffer_ptrs], bound, *kept)
+            if ctx.needs_input_grad[2]:
+                # the d/dscale partial travels before the barrier that completes the scatter
+                pgd = _peer_all_gather(B, dscale.reshape(1, 1), "dscale", group, barrier=False)
             hdl.barrier(channel=1)
             dy_local = buf.unsqueeze(0)
         else:
@@ -262,7 +307,10 @@ class _ShardedClipFn(torch.autograd.Function):
         dtxt = B.rownorm_bwd(dy_local, yhat, invy, normalize, out_dt, None)[0].to(in_dtype)
         dls = None
         if ctx.needs_input_grad[2]:
-            dscale = _all_reduce_scalar(B, dscale.reshape(1), "dscale", group)
+            if pgd is not None:
+                dscale = pgd[0].sum(dim=0)
+            else:
+                dscale = _all_reduce_scalar(B, dscale.reshape(1), "dscale", group)
             dls = B.scale_param_grad(dscale, logits_scale, scale_kind, clamp_max)
         return dimg, dtxt, dls, None, None, None, None, None, None, None, None
 

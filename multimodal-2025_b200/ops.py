@@ -330,6 +330,18 @@ def peer_bcast(src: Tensor, peer_ptrs: List[int], dst_offset_bytes: int) -> None
     _lib.check(rc, "mm25_peer_bcast")
 
 
+def peer_bcast_mc(src: Tensor, mc_ptr: int, dst_offset_bytes: int) -> None:
+    """peer_bcast through the NVSwitch multicast mapping of the symmetric buffer: one
+    `multimem.st` reaches every rank's copy (include/mm25.h mm25_peer_bcast_mc)."""
+    import ctypes
+    src = src.contiguous()
+    with torch.cuda.device(src.device):
+        rc = _lib.lib().mm25_peer_bcast_mc(_p(src), src.numel() * src.element_size(),
+                                           ctypes.c_void_p(int(mc_ptr)), dst_offset_bytes,
+                                           _stream(src))
+    _lib.check(rc, "mm25_peer_bcast_mc")
+
+
 def col_merge_ld(payload: Tensor, N: int) -> Tensor:
     """col_merge on a gathered [P, ld] payload whose rows start with (col_max[N], col_sum[N])."""
     P, ld = payload.shape
