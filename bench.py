@@ -11,8 +11,10 @@ quoted on:
   cfg3  CLOOB N=4096  d=512  fp32 inputs   (InfoLOOB + 4 Hopfield retrievals)
   cfg4  vCLIP B=8192  d=512  S=20 samples  (--vdist power_spherical|vmf|projected_normal)
   cfg5  AlignCLIP N=65536 d=1024 d_sem=768 bf16 (row-sharded over the ranks)
-cfg3 / cfg4 run at the REFERENCE's precision (fp32 inputs -> fp32 arithmetic) unless
-`--precision bf16`, which feeds the tensor-core kernels bf16 operands and is labelled as such.
+cfg3 / cfg4 run at the REFERENCE's precision (fp32 inputs -> fp32-grade arithmetic: the CLIP /
+vCLIP similarity kernels on the tensor cores over two-term bf16 splits, CLOOB on the fp32 FFMA
+kernels) unless `--precision bf16`, which feeds the tensor-core kernels plain bf16 operands and
+is labelled as reduced precision.
 
 A "step" is one forward+backward of the loss over one synthetic batch.  `value` is timed with
 CUDA events per step, inputs resident in HBM, an L2 flush (256 MB write) before every step; `e2e`
@@ -118,7 +120,13 @@ def workload_name(cfg, args):
 def precision_note(c, args):
     if c["dtype"] == "f32" and args.precision == "bf16":
         return "fp32 inputs, similarity GEMMs on bf16 tensor-core operands (REDUCED precision)"
-    return "fp32 inputs and arithmetic (reference precision)" if c["dtype"] == "f32" else "bf16"
+    if c["dtype"] == "f32":
+        if c["loss"] in ("clip", "vclip") and os.environ.get("MM25_FP32_TC", "1") != "0":
+            return ("fp32 inputs, fp32-grade arithmetic (reference precision: similarity GEMMs "
+                    "on the tensor cores over two-term bf16 splits, 16 significant bits, fp32 "
+                    "accumulation; 1e-5 / 1e-4 contract)")
+        return "fp32 inputs and arithmetic (reference precision, fp32 FFMA kernels)"
+    return "bf16"
 
 
 def algorithmic_flops(c):

@@ -423,6 +423,34 @@ int mm25_rank_both(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_
                    const float* row_tval, const int64_t* row_tcol, const float* col_tval,
                    const int64_t* col_trow, int* row_rank, int* col_rank, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * fp32-grade similarity kernels on the tensor cores (losses/clipLoss.py:106 computes the logits
+ * in fp32: `.float()`; contract rel 1e-5 loss / 1e-4 gradients).  fp32 rows are split into two
+ * bf16 terms x = hi + lo (16 significant bits) and laid out so that ONE bf16 sweep over
+ * K = 4 d reproduces (hi_a + lo_a) . (hi_b + lo_b):
+ *   mm25_split_bf16x2(x [rows, d] fp32, role) -> out4 [rows, 4 d] bf16 = [hi hi lo lo] (role 0,
+ *   row operand) or [hi lo hi lo] (role 1, column operand), plus hi, lo [rows, d] bf16.
+ * Forward: mm25_sim_fwd(out4_a, out4_b, MM25_BF16, ..., d = 4 d, MM25_SIM_PLAIN).
+ * Backward: mm25_sim_bwd_split — the gradient panel is split the same way (the recompute sweep
+ * runs twice, the second pass emits g - bf16(g)) and dA = sum over the four (G term, Y term)
+ * products, accumulated in fp32 by four grouped-GEMM launches; likewise dB.  da [B, M, d],
+ * db [B, N, d] fp32 (either may be NULL); dscale_part: mm25_sim_bwd_split_nparts(B, M, N)
+ * floats (NULL: skip); workspace: mm25_sim_bwd_split_workspace_bytes(M, N).
+ * mm25_sim_split_eligible: 1 when the shape is covered (d % 256 == 0, d <= 1024, M % 128 == 0,
+ * N % 256 == 0). */
+int mm25_split_bf16x2(const float* x, int64_t rows, int64_t d, int role, void* out4, void* hi,
+                      void* lo, void* stream);
+int mm25_sim_split_eligible(int64_t B, int64_t M, int64_t N, int64_t d);
+size_t mm25_sim_bwd_split_workspace_bytes(int64_t M, int64_t N);
+int64_t mm25_sim_bwd_split_nparts(int64_t B, int64_t M, int64_t N);
+int mm25_sim_bwd_split(const void* a4, const void* b4, const void* a_hi, const void* a_lo,
+                       const void* b_hi, const void* b_lo, int64_t B, int64_t M, int64_t N,
+                       int64_t d, const float* scale, int scale_kind, float clamp_max,
+                       int64_t diag_offset, const float* row_lse, const float* col_lse,
+                       float w_row, float w_col, float w_diag, float w_all, const float* gout,
+                       float* da, float* db, float* dscale_part, void* workspace,
+                       size_t workspace_bytes, float dot_bound, void* stream);
+
 /* Retrieval ranks fused into the similarity GEMM: the scores a_q . b_j (bf16 rows, fp32
  * accumulation on the tensor cores) are counted against the row's target as they leave TMEM and
  * are never written (AlignCLIP/main/train.py:338-356 forms `logits_per_image` [N, N], copies it

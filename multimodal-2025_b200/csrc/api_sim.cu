@@ -208,3 +208,32 @@ extern "C" int mm25_sim_bwd_rs(const void* a, const void* b, int dtype, int64_t 
                       workspace_bytes, 2, dot_bound, db_peers, (int)npeers, e_keep, e_flag,
                       stream);
 }
+
+// fp32-grade backward on two-term bf16 splits (sim_tc_bwd.cu launch_bwd_split)
+extern "C" size_t mm25_sim_bwd_split_workspace_bytes(int64_t M, int64_t N) {
+  return tc::bwd_split_workspace_bytes(M, N);
+}
+extern "C" int64_t mm25_sim_bwd_split_nparts(int64_t B, int64_t M, int64_t N) {
+  return tc::bwd_split_nparts(B, M, N);
+}
+extern "C" int mm25_sim_split_eligible(int64_t B, int64_t M, int64_t N, int64_t d) {
+  return tc::eligible_fwd(B, M, N, 4 * d, MM25_BF16, MM25_SIM_PLAIN) && d % 256 == 0 &&
+                 tc::eligible_bwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)
+             ? 1 : 0;
+}
+extern "C" int mm25_sim_bwd_split(const void* a4, const void* b4, const void* a_hi,
+                                  const void* a_lo, const void* b_hi, const void* b_lo,
+                                  int64_t B, int64_t M, int64_t N, int64_t d, const float* scale,
+                                  int scale_kind, float clamp_max, int64_t diag_offset,
+                                  const float* row_lse, const float* col_lse, float w_row,
+                                  float w_col, float w_diag, float w_all, const float* gout,
+                                  float* da, float* db, float* dscale_part, void* workspace,
+                                  size_t workspace_bytes, float dot_bound, void* stream) {
+  if (!a4 || !b4 || !a_hi || !a_lo || !b_hi || !b_lo || !scale || !row_lse || !workspace)
+    return MM25_ERR_ARG;
+  if (!col_lse && w_col != 0.f) return MM25_ERR_ARG;
+  return tc::launch_bwd_split(a4, b4, a_hi, a_lo, b_hi, b_lo, B, M, N, d, scale, scale_kind,
+                              clamp_max, diag_offset, row_lse, col_lse, w_row, w_col, w_diag,
+                              w_all, gout, da, db, dscale_part, workspace, workspace_bytes,
+                              dot_bound, (cudaStream_t)stream);
+}

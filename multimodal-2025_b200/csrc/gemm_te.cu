@@ -53,6 +53,8 @@ constexpr int B_BYTES = 2 * BH_BYTES;       // up to two MMAs per k-step
 constexpr int NPROD = 8;                    // A-producer warps
 constexpr int PROD0 = 2;                    // first A-producer warp; warps 2..5 also run the epilogue
 constexpr int THREADS = 32 * (PROD0 + NPROD);   // 320 (168 registers per thread)
+constexpr int STG_LD = 36;                  // floats per staged row (128 B + 16 B pad)
+constexpr int STG_BYTES = 4 * 32 * STG_LD * 4;   // 4 epilogue warps x 32 rows
 constexpr int MAX_PAIRS = 96;               // >= SMs / 2
 constexpr int NFULL = 1 + 2 * (NPROD / NST);  // arrivals on the leader's `full` barrier: the TMA
                                             // thread + the two warps of the stage's group per CTA
@@ -97,6 +99,7 @@ struct Params {
   const int* e_flag;       // device flag: 0 = E already holds G' (recompute path ran) -> copy
   const float* consts;     // device {k_all, k_diag} per batch entry
   int debug_skip_a;        // measurement only (MM25_TE_DEBUG_SKIP_A): producers arrive without data
+  int rs_bulk;             // scatter epilogue: 128-byte TMA reductions through a staging row
   int pf_dist;             // L2 prefetch distance of the A tiles in k-blocks (0 = off)
   long long* stats;        // measurement only: cycle sums of one producer thread (or NULL)
 };
@@ -567,6 +570,37 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
       }
       mbar_wait(&sm.acc_full[as], accph);
       tc_fence_after();
+      if (pr.scatter && P.rs_bulk) {
+        // Fused reduce-scatter, staged: each lane parks the 32 floats of its row chunk in its
+        // own padded shared-memory row and sends them as ONE 128-byte TMA reduction
+        // (cp.reduce.async.bulk add.f32) into the owner's buffer over NVLink, instead of eight
+        // separate 16-byte red.global per lane (measured at 8 ranks on the grouped GEMM:
+        // 0.842 -> 0.693 ms per step, profiles/r2_ab_n8_summary.txt).
+        float* mine = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(&sm) +
+                                               ((sizeof(Smem) + 127) & ~size_t(127))) +
+                      (q * 32 + lane) * STG_LD;
+#pragma unroll 1
+        for (int ch = 0; ch < 8 * nh; ++ch) {
+          float v[32];
+          tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + as * 256 + ch * 32, v);
+          tma_store_wait_read<0>();   // my previous bulk reduction has read my row
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(mine + 4 * j) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          fence_proxy_async_smem();
+          asm volatile(
+              "cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], 128;" ::
+                  "l"(crow + ch * 32), "r"(smem_u32(mine))
+              : "memory");
+          tma_store_commit();
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_u32(&sm.acc_empty[as], 0));
+        if (++as == (uint32_t)nacc) { as = 0; accph ^= 1; }
+        continue;
+      }
 #pragma unroll 1
       for (int ch = 0; ch < 8 * nh; ++ch) {
         float v[32];
@@ -588,6 +622,10 @@ gemm_te_kernel(const __grid_constant__ ge::Params P) {
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_u32(&sm.acc_empty[as], 0));
       if (++as == (uint32_t)nacc) { as = 0; accph ^= 1; }
+    }
+    if (epi && P.rs_bulk) {  // every bulk reduction of this thread has completed before exit
+      tma_store_wait_all<0>();
+      __threadfence_system();
     }
     if (st_ptr) {  // [4] SM cycles and [5] nanoseconds of this thread's whole run -> effective clock
       unsigned long long ns1;
@@ -760,6 +798,8 @@ int gemm_te_grouped(const GemmTeDesc* d0, const GemmTeDesc* d1, int64_t Ng, cons
   static const int pf = getenv("MM25_TE_PF") ? atoi(getenv("MM25_TE_PF")) : 0;
   P.pf_dist = pf;
   P.stats = g_te_stats;
+  static const bool rs_bulk_env = !(getenv("MM25_TE_RS") && atoi(getenv("MM25_TE_RS")) == 0);
+  P.rs_bulk = (rs_bulk_env && (P.p[0].scatter || P.p[1].scatter)) ? 1 : 0;
   P.total = P.p[0].kb_total + P.p[1].kb_total;
   int maxpairs = sm_count_te() / 2;
   if (maxpairs > ge::MAX_PAIRS) maxpairs = ge::MAX_PAIRS;
@@ -772,10 +812,10 @@ int gemm_te_grouped(const GemmTeDesc* d0, const GemmTeDesc* d1, int64_t Ng, cons
   // Fused reduce-scatter: the epilogue of a scatter job pushes its 256 x Ng fp32 tile over
   // NVLink with red.global and is NOT overlapped with MMAs (one accumulator), so a job of the
   // scatter problem costs nk + epi k-block times, not nk.  The cut points are placed at equal
-  // COST instead of equal k-block counts (epi in k-block units: MM25_TE_EPI_KB, default 40 —
+  // COST instead of equal k-block counts (epi in k-block units: MM25_TE_EPI_KB, default 24 —
   // measured at 8 ranks, profiles/r2_n8_timeline.txt: ~41 us per epilogue, ~1 us per k-block).
   {
-    static const int epi_env = getenv("MM25_TE_EPI_KB") ? atoi(getenv("MM25_TE_EPI_KB")) : 40;
+    static const int epi_env = getenv("MM25_TE_EPI_KB") ? atoi(getenv("MM25_TE_EPI_KB")) : 24;
     const int ep[2] = {P.p[0].scatter ? epi_env : 0, P.p[1].scatter ? epi_env : 0};
     if ((ep[0] > 0 || ep[1] > 0) && pairs > 1) {
       const int64_t c0 = (int64_t)P.p[0].njobs * (P.p[0].nk + ep[0]);
@@ -809,7 +849,7 @@ int gemm_te_grouped(const GemmTeDesc* d0, const GemmTeDesc* d1, int64_t Ng, cons
       }
     }
   }
-  const size_t smem = sizeof(ge::Smem) + 1024;
+  const size_t smem = sizeof(ge::Smem) + 1024 + (P.rs_bulk ? ge::STG_BYTES + 128 : 0);
   MM25_CUDA_CHECK(cudaFuncSetAttribute(gemm_te_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
   { void* tt_ = timing_begin(MM25_T_GEMM_TE, st);

@@ -610,6 +610,46 @@ extern "C" int mm25_peer_bcast(const void* src, int64_t bytes, void* const* peer
   return MM25_OK;
 }
 
+// Two-term bf16 split of fp32 rows for the fp32-grade tensor-core path (sim_tc_bwd.cu
+// launch_bwd_split): x = hi + lo with hi = bf16(x), lo = bf16(x - hi) (16 significant bits).
+// out4 [rows, 4 d] holds [hi hi lo lo] (role 0, the row operand) or [hi lo hi lo] (role 1, the
+// column operand), so that out4_a . out4_b = (hi_a + lo_a) . (hi_b + lo_b) over K = 4 d.
+__global__ void __launch_bounds__(256) split_bf16x2_kernel(const float* __restrict__ x,
+                                                           int64_t rows, int d, int role,
+                                                           __nv_bfloat16* __restrict__ out4,
+                                                           __nv_bfloat16* __restrict__ hi,
+                                                           __nv_bfloat16* __restrict__ lo) {
+  const int64_t n2 = rows * (int64_t)(d / 2);
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n2;
+       i += (int64_t)gridDim.x * 256) {
+    const int64_t r = i / (d / 2);
+    const int c = (int)(i - r * (d / 2)) * 2;
+    const float2 v = *reinterpret_cast<const float2*>(x + r * d + c);
+    const __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+    const __nv_bfloat162 l = __floats2bfloat162_rn(v.x - __bfloat162float(h.x),
+                                                   v.y - __bfloat162float(h.y));
+    *reinterpret_cast<__nv_bfloat162*>(hi + r * d + c) = h;
+    *reinterpret_cast<__nv_bfloat162*>(lo + r * d + c) = l;
+    __nv_bfloat16* o = out4 + r * 4 * (int64_t)d + c;
+    *reinterpret_cast<__nv_bfloat162*>(o) = h;
+    *reinterpret_cast<__nv_bfloat162*>(o + d) = role ? l : h;
+    *reinterpret_cast<__nv_bfloat162*>(o + 2 * d) = role ? h : l;
+    *reinterpret_cast<__nv_bfloat162*>(o + 3 * d) = l;
+  }
+}
+
+extern "C" int mm25_split_bf16x2(const float* x, int64_t rows, int64_t d, int role, void* out4,
+                                 void* hi, void* lo, void* stream) {
+  if (!x || !out4 || !hi || !lo) return MM25_ERR_ARG;
+  if (rows <= 0 || d <= 0 || d % 2 != 0 || d > (1 << 20)) return MM25_ERR_SHAPE;
+  int64_t blocks = ceil_div(rows * (d / 2), 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  split_bf16x2_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      x, rows, (int)d, role, (__nv_bfloat16*)out4, (__nv_bfloat16*)hi, (__nv_bfloat16*)lo);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
 // NVSwitch multicast variant: ONE `multimem.st` per 16 bytes is replicated by the switch into
 // every rank's copy of the symmetric buffer (this rank's included), so a rank sends its shard
 // once instead of P times.  `mc_dst` is the multicast address of the buffer

@@ -33,6 +33,17 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
                float* const* db_peers, int npeers, void* e_buf, const int* e_flag,
                cudaStream_t st, int mask_diag = 0);
 
+// fp32-grade path on two-term bf16 splits (sim_tc_bwd.cu launch_bwd_split)
+size_t bwd_split_workspace_bytes(int64_t M, int64_t N);
+int64_t bwd_split_nparts(int64_t B, int64_t M, int64_t N);
+int launch_bwd_split(const void* a4, const void* b4, const void* a_hi, const void* a_lo,
+                     const void* b_hi, const void* b_lo, int64_t B, int64_t M, int64_t N,
+                     int64_t d, const float* scale, int scale_kind, float clamp_max,
+                     int64_t diag_offset, const float* row_lse, const float* col_lse,
+                     float w_row, float w_col, float w_diag, float w_all, const float* gout,
+                     float* da, float* db, float* dscale_part, void* ws, size_t ws_bytes,
+                     float dot_bound, cudaStream_t st);
+
 }  // namespace tc
 
 // sim_tc_mod.cu — MODULATED mode on the tensor cores (two TMEM accumulators per tile), B = 1,

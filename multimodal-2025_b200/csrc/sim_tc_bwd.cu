@@ -519,6 +519,113 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
   return MM25_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// fp32-grade backward on the tensor cores (SURVEY §7 hard part 1; clipLoss.py:106 `.float()`).
+// Operands are two-term bf16 splits x = x1 + x2 (16 significant bits, prep.cu split kernel):
+//   a4 = [a1 a1 a2 a2], b4 = [b1 b2 b1 b2]  ([rows, 4 d] bf16)  =>  a4 . b4 = (a1 + a2).(b1 + b2)
+// so the unchanged sweep recomputes fp32-grade logits with K = 4 d.  The gradient panel is split
+// the same way, G' = G1 + G2: the sweep runs twice per panel (second pass emits g - bf16(g)), and
+// every product G . Y becomes four accumulating grouped-GEMM launches
+//   dA = G1 Y1 + G1 Y2 + G2 Y1 + G2 Y2,   dB likewise with X1, X2.
+// Cost: 2 x 4 sweeps + 4 x GEMMs = 32 N^2 d tensor FLOPs against 8 on the bf16 path — and against
+// the FFMA kernels' 6 N^2 d at ~10 TFLOP/s.  B entries are walked one by one (panel loop).
+size_t bwd_split_workspace_bytes(int64_t M, int64_t N) {
+  return (size_t)panel_rows(M, N) * (size_t)N * 2 + 256 + (size_t)N * sizeof(float) + 256;
+}
+int64_t bwd_split_nparts(int64_t B, int64_t M, int64_t N) {
+  return B * ceil_div(M, panel_rows(M, N)) * tc_sm_count();
+}
+
+int launch_bwd_split(const void* a4, const void* b4, const void* a_hi, const void* a_lo,
+                     const void* b_hi, const void* b_lo, int64_t B, int64_t M, int64_t N,
+                     int64_t d, const float* scale, int scale_kind, float clamp_max,
+                     int64_t diag_offset, const float* row_lse, const float* col_lse,
+                     float w_row, float w_col, float w_diag, float w_all, const float* gout,
+                     float* da, float* db, float* dscale_part, void* ws, size_t ws_bytes,
+                     float dot_bound, cudaStream_t st) {
+  const int64_t d4 = 4 * d;
+  if (!eligible_fwd(B, M, N, d4, MM25_BF16, MM25_SIM_PLAIN) || d % 256 != 0 ||
+      !gemm_eligible(M >= 128 ? 128 : M, d, N))
+    return MM25_ERR_SHAPE;
+  if (ws_bytes < bwd_split_workspace_bytes(M, N)) return MM25_ERR_WORKSPACE;
+  const uintptr_t ws0 = (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255);
+  const int64_t R = panel_rows(M, N);
+  __nv_bfloat16* G = reinterpret_cast<__nv_bfloat16*>(ws0);
+  float* cbuf = reinterpret_cast<float*>((ws0 + (size_t)R * (size_t)N * 2 + 255) & ~uintptr_t(255));
+  float* Cc = dot_bound > 0.f ? cbuf : nullptr;
+  if (!col_lse) MM25_CUDA_CHECK(cudaMemsetAsync(cbuf, 0, sizeof(float) * N, st));
+  const int sms = tc_sm_count();
+  const size_t smem = sizeof(GradSmem) + 1024;
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_grad_tc_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const __nv_bfloat16* a4b = (const __nv_bfloat16*)a4;
+  const __nv_bfloat16* b4b = (const __nv_bfloat16*)b4;
+  const __nv_bfloat16* ah = (const __nv_bfloat16*)a_hi;
+  const __nv_bfloat16* al = (const __nv_bfloat16*)a_lo;
+  const __nv_bfloat16* bh = (const __nv_bfloat16*)b_hi;
+  const __nv_bfloat16* bl = (const __nv_bfloat16*)b_lo;
+  int64_t part = 0;
+  for (int64_t bz = 0; bz < B; ++bz) {
+    CUtensorMap ta, tb;
+    int rc = make_tmap_bf16(&ta, a4b + bz * M * d4, (uint64_t)M, (uint64_t)d4, BM, BK);
+    if (rc) return rc;
+    if ((rc = make_tmap_bf16(&tb, b4b + bz * N * d4, (uint64_t)N, (uint64_t)d4, BN, BK))) return rc;
+    if (Cc && col_lse) {
+      grad_col_coef_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(
+          col_lse + bz * N, N, scale, scale_kind, clamp_max, gout ? gout + bz : nullptr, w_col,
+          dot_bound, Cc);
+      MM25_LAUNCH_CHECK();
+    }
+    for (int64_t p0 = 0; p0 < M; p0 += R) {
+      const int64_t rows = (M - p0 < R) ? (M - p0) : R;
+      const int num_rb = (int)(rows / BM), ntiles = (int)(N / BN);
+      int nseg = 1;
+      {
+        double best = 0.0;
+        const int max_seg = ntiles >= 8 ? ntiles / 4 : 1;
+        for (int ns = 1; ns <= max_seg && ns <= 64; ++ns) {
+          const int tps = (ntiles + ns - 1) / ns;
+          const int sg = (ntiles + tps - 1) / tps;
+          const long items = (long)num_rb * sg;
+          const double eff = (double)items / ((double)((items + sms - 1) / sms) * sms);
+          if (eff > best + 0.01) { best = eff; nseg = sg; }
+        }
+      }
+      const int tps = (ntiles + nseg - 1) / nseg;
+      nseg = (ntiles + tps - 1) / tps;
+      const long items = (long)num_rb * nseg;
+      const int grid = (int)(items < sms ? items : sms);
+      if (dscale_part) MM25_CUDA_CHECK(cudaMemsetAsync(dscale_part + part, 0, sizeof(float) * sms, st));
+      CUtensorMap tg;
+      if ((rc = make_tmap_bf16(&tg, G, (uint64_t)rows, (uint64_t)N, 32, 32, 64))) return rc;
+      for (int lo = 0; lo < 2; ++lo) {
+        { void* tt_ = timing_begin(MM25_T_SIM_GRAD, st);
+        sim_grad_tc_kernel<<<grid, FWD_THREADS, smem, st>>>(
+            ta, tb, tg, M, N, (int)d4, (int)(p0 / BM), num_rb, nseg, tps, scale, scale_kind,
+            clamp_max, diag_offset, row_lse + bz * M, col_lse ? col_lse + bz * N : cbuf, w_row,
+            w_col, w_diag, w_all, gout ? gout + bz : nullptr,
+            (dscale_part && lo == 0) ? dscale_part + part : nullptr, Cc, dot_bound, nullptr,
+            lo ? 2 : 0);
+        timing_end(tt_, st); }
+        MM25_LAUNCH_CHECK();
+        for (int t = 0; t < 2; ++t) {   // second operand: hi term, then lo term
+          const __nv_bfloat16* yb = (t ? bl : bh) + bz * N * d;
+          const __nv_bfloat16* xb = (t ? al : ah) + (bz * M + p0) * d;
+          const int first = (lo == 0 && t == 0);
+          GemmDesc ga{G, yb, da ? da + (bz * M + p0) * d : nullptr, d, rows, N, 0, 1,
+                      first ? 0 : 1, 1.f, nullptr, 0, 0};
+          GemmDesc gb{G, xb, db ? db + bz * N * d : nullptr, d, N, rows, 1, 1,
+                      (first && p0 == 0) ? 0 : 1, 1.f, nullptr, 0, 0};
+          rc = gemm_grouped(da ? &ga : nullptr, db ? &gb : nullptr, d, nullptr, st);
+          if (rc) return rc;
+        }
+      }
+      part += sms;
+    }
+  }
+  return MM25_OK;
+}
+
 }  // namespace tc
 }  // namespace mm25
 

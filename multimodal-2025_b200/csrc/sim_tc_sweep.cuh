@@ -11,7 +11,7 @@ namespace mm25 {
 namespace tc {
 
 constexpr int BM = 128, BN = 256, BK = 64;
-constexpr int MAX_KC = 16;           // d <= 1024
+constexpr int MAX_KC = 64;           // K <= 4096 (d <= 1024 features, x4 for the split operands)
 constexpr int NST = 4;               // ring stages (A 16 KB + B 32 KB each)
 constexpr int NACC = 2;              // TMEM accumulator stages (256 columns each)
 constexpr int A_BYTES = BM * BK * 2;  // 16384

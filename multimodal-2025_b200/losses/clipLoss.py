@@ -11,6 +11,8 @@ which equals the reference's 0.5 * (CE_eps(Z, I) + CE_eps(Z^T, I)) (clipLoss.py:
 """
 from __future__ import annotations
 
+import os
+
 import torch
 from torch import nn
 
@@ -40,20 +42,36 @@ class _ClipLossFn(torch.autograd.Function):
         scale32 = logits_scale.detach().reshape(1).to(torch.float32).contiguous()
         B, M, _ = xhat.shape
         bound = ops.DOT_BOUND_NORMALIZED if normalize else 0.0
-        # Keep E = exp(z - shift) (bf16, the activation autograd would have saved) so the
-        # backward forms G' from it instead of recomputing the S tiles (include/mm25.h e_keep).
         N = yhat.shape[1]
-        keep = (any(ctx.needs_input_grad[:3]) and bound > 0.0
-                and impl != ops.IMPL_SIMT and ops.tc_eligible_bwd(xhat, yhat)
-                and 2 * B * M * N <= ops.keep_e_bytes_limit(M, N, xhat.shape[-1]))
+        # fp32 inputs keep the reference's fp32-grade arithmetic (clipLoss.py:106 `.float()`) ON
+        # THE TENSOR CORES when the shape allows: two-term bf16 splits of the normalised rows
+        # (16 significant bits) swept over K = 4 d (include/mm25.h mm25_split_bf16x2); otherwise
+        # the fp32 FFMA kernels.  MM25_FP32_TC=0 forces the FFMA kernels.
+        split = (cdt == ops.F32 and impl == ops.IMPL_AUTO and xhat.is_cuda
+                 and os.environ.get("MM25_FP32_TC", "1") != "0"
+                 and ops.sim_split_eligible(B, M, N, xhat.shape[-1]))
+        ctx.split = None
         e_keep = e_flag = None
-        if keep:
-            row_lse, cmax, csum, diag, e_keep, e_flag = ops.sim_fwd_keep(
-                xhat, yhat, scale32, scale_kind, clamp_max, 0, True, impl, bound)
-        else:
-            row_lse, cmax, csum, diag = ops.sim_fwd(xhat, yhat, None, None, None, scale32,
+        if split:
+            x4, xh, xl = ops.split_bf16x2(xhat, 0)
+            y4, yh, yl = ops.split_bf16x2(yhat, 1)
+            row_lse, cmax, csum, diag = ops.sim_fwd(x4, y4, None, None, None, scale32,
                                                     scale_kind, clamp_max, ops.SIM_PLAIN, 0,
                                                     True, impl, bound)
+            ctx.split = (x4, y4, xh, xl, yh, yl)
+        else:
+            # Keep E = exp(z - shift) (bf16, the activation autograd would have saved) so the
+            # backward forms G' from it instead of recomputing the S tiles (mm25.h e_keep).
+            keep = (any(ctx.needs_input_grad[:3]) and bound > 0.0
+                    and impl != ops.IMPL_SIMT and ops.tc_eligible_bwd(xhat, yhat)
+                    and 2 * B * M * N <= ops.keep_e_bytes_limit(M, N, xhat.shape[-1]))
+            if keep:
+                row_lse, cmax, csum, diag, e_keep, e_flag = ops.sim_fwd_keep(
+                    xhat, yhat, scale32, scale_kind, clamp_max, 0, True, impl, bound)
+            else:
+                row_lse, cmax, csum, diag = ops.sim_fwd(xhat, yhat, None, None, None, scale32,
+                                                        scale_kind, clamp_max, ops.SIM_PLAIN, 0,
+                                                        True, impl, bound)
         col_lse = ops.col_merge(cmax.reshape(1, -1), csum.reshape(1, -1)).reshape(B, -1)
         loss = ops.clip_loss_finalize(row_lse, diag, col_lse, sx if want_cs else None,
                                       sy if want_cs else None, M, scale32, scale_kind,
@@ -72,11 +90,19 @@ class _ClipLossFn(torch.autograd.Function):
         gout = gout.detach().to(torch.float32).reshape(B).contiguous()
         e_keep, e_flag = ctx.kept
         ctx.kept = (None, None)  # E is overwritten by G': a second backward recomputes
-        da, db, dscale, _ = ops.sim_bwd(
-            xhat, yhat, None, None, None, scale32, scale_kind, clamp_max, ops.SIM_PLAIN, 0,
-            row_lse, col_lse, 0.5 / n, 0.5 / n, (1.0 - eps_ls) / n, eps_ls / (n * n), gout,
-            ctx.needs_input_grad[0] or ctx.needs_input_grad[2], ctx.needs_input_grad[1], False,
-            impl, ops.DOT_BOUND_NORMALIZED if normalize else 0.0, e_keep, e_flag)
+        weights = (0.5 / n, 0.5 / n, (1.0 - eps_ls) / n, eps_ls / (n * n))
+        need_da = ctx.needs_input_grad[0] or ctx.needs_input_grad[2]
+        bound = ops.DOT_BOUND_NORMALIZED if normalize else 0.0
+        if ctx.split is not None:
+            x4, y4, xh, xl, yh, yl = ctx.split
+            da, db, dscale = ops.sim_bwd_split(x4, y4, xh, xl, yh, yl, scale32, scale_kind,
+                                               clamp_max, 0, row_lse, col_lse, *weights, gout,
+                                               need_da, ctx.needs_input_grad[1], bound)
+        else:
+            da, db, dscale, _ = ops.sim_bwd(
+                xhat, yhat, None, None, None, scale32, scale_kind, clamp_max, ops.SIM_PLAIN, 0,
+                row_lse, col_lse, *weights, gout, need_da, ctx.needs_input_grad[1], False,
+                impl, bound, e_keep, e_flag)
         out_dt = ops.BF16 if in_dtype == torch.bfloat16 else ops.F32
         dimg = dtxt = dls = None
         if ctx.needs_input_grad[0]:

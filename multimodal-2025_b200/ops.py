@@ -208,6 +208,62 @@ def sim_bwd(a: Tensor, b: Tensor, u: Optional[Tensor], v: Optional[Tensor],
     return da, db, dscale, ddiag
 
 
+def sim_split_eligible(B: int, M: int, N: int, d: int) -> bool:
+    """True when the fp32-grade tensor-core path covers the shape (include/mm25.h)."""
+    return bool(_lib.lib().mm25_sim_split_eligible(B, M, N, d))
+
+
+@torch.library.custom_op("mm25::split_bf16x2", mutates_args=(), device_types="cuda")
+def split_bf16x2(x: Tensor, role: int) -> Tuple[Tensor, Tensor, Tensor]:
+    """fp32 [B, rows, d] -> (out4 [B, rows, 4 d], hi, lo [B, rows, d]) bf16: the two-term split
+    x = hi + lo laid out for the K = 4 d sweep (role 0 = row operand [hi hi lo lo], role 1 =
+    column operand [hi lo hi lo]; include/mm25.h mm25_split_bf16x2)."""
+    x = _cuda3(x, "x")
+    if x.dtype != torch.float32:
+        raise TypeError("split_bf16x2 takes fp32 rows")
+    B, R, d = x.shape
+    with torch.cuda.device(x.device):
+        out4 = torch.empty((B, R, 4 * d), dtype=torch.bfloat16, device=x.device)
+        hi = torch.empty((B, R, d), dtype=torch.bfloat16, device=x.device)
+        lo = torch.empty((B, R, d), dtype=torch.bfloat16, device=x.device)
+        rc = _lib.lib().mm25_split_bf16x2(_p(x), B * R, d, role, _p(out4), _p(hi), _p(lo),
+                                          _stream(x))
+    _lib.check(rc, "mm25_split_bf16x2")
+    return out4, hi, lo
+
+
+@torch.library.custom_op("mm25::sim_bwd_split", mutates_args=(), device_types="cuda")
+def sim_bwd_split(a4: Tensor, b4: Tensor, a_hi: Tensor, a_lo: Tensor, b_hi: Tensor, b_lo: Tensor,
+                  scale: Tensor, scale_kind: int, clamp_max: float, diag_offset: int,
+                  row_lse: Tensor, col_lse: Optional[Tensor], w_row: float, w_col: float,
+                  w_diag: float, w_all: float, gout: Optional[Tensor], need_da: bool,
+                  need_db: bool, dot_bound: float) -> Tuple[Tensor, Tensor, Tensor]:
+    """fp32-grade PLAIN backward on the split operands (include/mm25.h mm25_sim_bwd_split);
+    returns (da [B, M, d], db [B, N, d], dscale[1]) fp32."""
+    B, M, d4 = a4.shape
+    N = b4.shape[1]
+    d = d4 // 4
+    dev = a4.device
+    L = _lib.lib()
+    with torch.cuda.device(dev):
+        da = torch.empty((B, M, d) if need_da else (0,), dtype=torch.float32, device=dev)
+        db = torch.empty((B, N, d) if need_db else (0,), dtype=torch.float32, device=dev)
+        parts = torch.zeros((max(int(L.mm25_sim_bwd_split_nparts(B, M, N)), 1),),
+                            dtype=torch.float32, device=dev)
+        dscale = torch.empty((1,), dtype=torch.float32, device=dev)
+        ws = torch.empty((max(int(L.mm25_sim_bwd_split_workspace_bytes(M, N)), 16),),
+                         dtype=torch.uint8, device=dev)
+        rc = L.mm25_sim_bwd_split(_p(a4), _p(b4), _p(a_hi), _p(a_lo), _p(b_hi), _p(b_lo), B, M, N,
+                                  d, _p(scale), scale_kind, clamp_max, diag_offset, _p(row_lse),
+                                  _p(col_lse), w_row, w_col, w_diag, w_all, _p(gout),
+                                  _p(da) if need_da else None, _p(db) if need_db else None,
+                                  _p(parts), _p(ws), ws.numel(), dot_bound, _stream(a4))
+        _lib.check(rc, "mm25_sim_bwd_split")
+        rc = L.mm25_sum_parts(_p(parts), parts.numel(), 1.0, _p(dscale), _stream(a4))
+    _lib.check(rc, "mm25_sum_parts")
+    return da, db, dscale
+
+
 @torch.library.custom_op("mm25::col_merge", mutates_args=(), device_types="cuda")
 def col_merge(col_max: Tensor, col_sum: Tensor) -> Tensor:
     """Merge [P, N] partial column (max, sum) in fixed order into col_lse [N]."""
