@@ -306,6 +306,15 @@ int mm25_peer_bcast_mc(const void* src, int64_t bytes, void* mc_ptr, int64_t dst
 int mm25_smooth_term(const float* payload, int64_t P, int64_t ld, int64_t ox, int64_t oy,
                      int64_t d, const float* scale, int scale_kind, float clamp_max, float coef,
                      float* loss, void* stream);
+/* The scalar tail of the row-sharded forward in one launch: loss[0] = sum_p payload[p, orow]
+ * (each rank's row part of the loss, rank order) + (0.5 / N) sum_j col_lse[j] (fp64, fixed
+ * order: identical bits on every rank) - coef * s * (sum_p sx_p).(sum_p sy_p) (the smoothing term
+ * of mm25_smooth_term; d = 0 skips it).  Replaces a scalar all-reduce: after the column
+ * statistics are merged every rank holds all N column LSEs (dist.ShardedClipLoss). */
+int mm25_sharded_loss(const float* payload, int64_t P, int64_t ld, int64_t orow,
+                      const float* col_lse, int64_t N, int64_t ox, int64_t oy, int64_t d,
+                      const float* scale, int scale_kind, float clamp_max, float coef,
+                      float* loss, void* stream);
 /* dL/d(raw scale parameter) from dL/ds (device scalars): MM25_SCALE_LOG: dscale * exp(l) when
  * l <= clamp_max else 0 (clipLoss.py:106 `clamp(max=4.6052).exp()`); MM25_SCALE_MUL: dscale. */
 int mm25_scale_param_grad(const float* dscale, const float* scale, int scale_kind,

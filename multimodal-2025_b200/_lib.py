@@ -157,6 +157,8 @@ SIGNATURES = {
     "mm25_peer_bcast_mc": (_int, [_vp, _i64, _vp, _i64, _vp]),
     "mm25_smooth_term": (_int, [_vp, _i64, _i64, _i64, _i64, _i64, _vp, _int, _f32, _f32, _vp,
                                 _vp]),
+    "mm25_sharded_loss": (_int, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _i64, _i64, _vp, _int,
+                                 _f32, _f32, _vp, _vp]),
     "mm25_scale_param_grad": (_int, [_vp, _vp, _int, _f32, _vp, _vp]),
     "mm25_clip_loss_finalize": (_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp,
                                        _int, _f32, _f32, _vp, _vp]),

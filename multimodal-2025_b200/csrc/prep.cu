@@ -349,6 +349,50 @@ __global__ void __launch_bounds__(256) smooth_term_kernel(
   }
 }
 
+// Whole scalar tail of the row-sharded forward in ONE launch (dist.ShardedClipLoss step 5):
+//   loss = sum_p payload[p, orow]                      (each rank's row part, rank order)
+//        + (0.5 / N) sum_j col_lse[j]                   (fp64, fixed-order tree: same bits on
+//                                                        every rank)
+//        - coef * s * (sum_p sx_p) . (sum_p sy_p)       (label smoothing; skipped when d == 0)
+__global__ void __launch_bounds__(256) sharded_loss_kernel(
+    const float* __restrict__ payload, int64_t P, int64_t ld, int64_t orow,
+    const float* __restrict__ col_lse, int64_t N, int64_t ox, int64_t oy, int d,
+    const float* __restrict__ scale, int scale_kind, float clamp_max, float coef,
+    float* __restrict__ loss) {
+  __shared__ double red[256];
+  double acc = 0.0;
+  for (int64_t j = threadIdx.x; j < N; j += 256) acc += (double)col_lse[j];
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+    __syncthreads();
+  }
+  const double colsum = red[0];
+  __syncthreads();
+  acc = 0.0;
+  for (int k = threadIdx.x; k < d; k += 256) {
+    float sx = 0.f, sy = 0.f;
+    for (int64_t p = 0; p < P; ++p) {
+      sx += payload[p * ld + ox + k];
+      sy += payload[p * ld + oy + k];
+    }
+    acc += (double)sx * (double)sy;
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    double rows = 0.0;
+    for (int64_t p = 0; p < P; ++p) rows += (double)payload[p * ld + orow];
+    const float s = load_scale(scale, scale_kind, clamp_max);
+    loss[0] = (float)(rows + colsum * (0.5 / (double)N) - (double)coef * (double)s * red[0]);
+  }
+}
+
 // dL/d(raw scale parameter) from dL/ds: s = exp(min(l, clamp)) passes gradient at equality
 // (torch.clamp semantics), multiplicative scales pass it through
 __global__ void scale_param_grad_kernel(const float* __restrict__ dscale,
@@ -698,6 +742,20 @@ extern "C" int mm25_smooth_term(const float* payload, int64_t P, int64_t ld, int
     return MM25_ERR_ARG;
   smooth_term_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(payload, P, ld, ox, oy, (int)d, scale,
                                                           scale_kind, clamp_max, coef, loss);
+  MM25_LAUNCH_CHECK();
+  return MM25_OK;
+}
+
+extern "C" int mm25_sharded_loss(const float* payload, int64_t P, int64_t ld, int64_t orow,
+                                 const float* col_lse, int64_t N, int64_t ox, int64_t oy,
+                                 int64_t d, const float* scale, int scale_kind, float clamp_max,
+                                 float coef, float* loss, void* stream) {
+  if (!payload || !col_lse || !scale || !loss || P <= 0 || N <= 0 || orow < 0 || orow >= ld)
+    return MM25_ERR_ARG;
+  if (d < 0 || (d > 0 && (ox + d > ld || oy + d > ld))) return MM25_ERR_ARG;
+  sharded_loss_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(payload, P, ld, orow, col_lse, N, ox,
+                                                           oy, (int)d, scale, scale_kind,
+                                                           clamp_max, coef, loss);
   MM25_LAUNCH_CHECK();
   return MM25_OK;
 }

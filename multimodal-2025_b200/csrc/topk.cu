@@ -215,22 +215,32 @@ topk_slice_kernel(const float* __restrict__ scores, int64_t N, int64_t ld, int k
       }
     }
     __syncthreads();
+    // bin b = the highest bin whose count, added to everything above it, reaches `remaining`:
+    // a parallel suffix scan over the 256 bins (thread t holds bin 255 - t) instead of a
+    // 256-step walk by one thread
+    unsigned cnt = 0, incl = 0;
+    const unsigned rem = sm.remaining;   // read by everyone before the barrier below; written after it
     if (tid < 256) {
-      unsigned t = 0;
 #pragma unroll
-      for (int c = 0; c < TK_HCOPIES; ++c) t += sm.hist[c][tid];
-      sm.hist[0][tid] = t;
+      for (int c = 0; c < TK_HCOPIES; ++c) cnt += sm.hist[c][255 - tid];
+      incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+      }
+      if (lane == 31) sm.warp_cnt[warp] = incl;
     }
     __syncthreads();
-    if (tid == 0) {
-      unsigned rem = sm.remaining;
-      int b = 255;
-      for (; b > 0; --b) {
-        if (sm.hist[0][b] >= rem) break;
-        rem -= sm.hist[0][b];
+    if (tid < 256) {
+      unsigned base = 0;
+      for (int w8 = 0; w8 < warp; ++w8) base += sm.warp_cnt[w8];
+      incl += base;
+      // bin 0 (tid 255) takes whatever is left, as the serial walk did
+      if ((incl >= rem && incl - cnt < rem) || (tid == 255 && incl < rem)) {
+        sm.prefix = prefix | ((uint32_t)(255 - tid) << shift);
+        sm.remaining = rem - (incl - cnt);
       }
-      sm.prefix = prefix | ((uint32_t)b << shift);
-      sm.remaining = rem;
     }
     __syncthreads();
   }
@@ -317,6 +327,8 @@ static int topk_slices(int64_t Q, int64_t N, int64_t k) {
   int64_t C = c_fill < N / 8192 ? c_fill : N / 8192;     // ... with slices of >= 8192 elements
   if (C < c_min) C = c_min;
   if (C < 1) C = 1;
+  if (c_min > 1 && Q >= 2 * 148) return 0;  // many long rows: the SMs are full already and the
+                                            // per-slice select + merge costs more than it saves
   if (C > 1 && C * k > TK_MERGE_MAX) C = TK_MERGE_MAX / k;
   if (C < c_min) return 0;                               // merge would not fit: plain kernel
   return (int)C;

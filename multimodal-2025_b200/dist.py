@@ -227,8 +227,14 @@ class _ShardedClipFn(torch.autograd.Function):
             red = _all_reduce_scalar(B, part.reshape(1), "loss", group)
         else:
             off = 2 * N + (2 * d if want_cs else 0)
-            red = (gathered[:, off].sum(dtype=torch.float64) +
-                   col_lse.sum(dtype=torch.float64) * (0.5 / N)).to(torch.float32).reshape(1)
+            if hasattr(B, "sharded_loss") and gathered.is_contiguous():
+                red = B.sharded_loss(gathered, off, col_lse, 2 * N, 2 * N + d,
+                                     d if want_cs else 0, scale32, scale_kind, clamp_max,
+                                     eps_ls / float(N) ** 2)
+                want_cs = False   # the smoothing term is inside the fused tail
+            else:
+                red = (gathered[:, off].sum(dtype=torch.float64) +
+                       col_lse.sum(dtype=torch.float64) * (0.5 / N)).to(torch.float32).reshape(1)
         if want_cs:
             coef = eps_ls / float(N) ** 2
             if hasattr(B, "smooth_term_"):

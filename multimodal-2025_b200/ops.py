@@ -386,6 +386,20 @@ def peer_bcast(src: Tensor, peer_ptrs: List[int], dst_offset_bytes: int) -> None
     _lib.check(rc, "mm25_peer_bcast")
 
 
+def sharded_loss(payload: Tensor, orow: int, col_lse: Tensor, ox: int, oy: int, d: int,
+                 scale: Tensor, scale_kind: int, clamp_max: float, coef: float) -> Tensor:
+    """Scalar tail of the row-sharded forward in one launch (include/mm25.h mm25_sharded_loss)."""
+    P, ld = payload.shape
+    col_lse = col_lse.contiguous()
+    with torch.cuda.device(payload.device):
+        loss = torch.empty((1,), dtype=torch.float32, device=payload.device)
+        rc = _lib.lib().mm25_sharded_loss(_p(payload), P, ld, orow, _p(col_lse), col_lse.numel(),
+                                          ox, oy, d, _p(scale), scale_kind, clamp_max, coef,
+                                          _p(loss), _stream(payload))
+    _lib.check(rc, "mm25_sharded_loss")
+    return loss
+
+
 def peer_bcast_mc(src: Tensor, mc_ptr: int, dst_offset_bytes: int) -> None:
     """peer_bcast through the NVSwitch multicast mapping of the symmetric buffer: one
     `multimem.st` reaches every rank's copy (include/mm25.h mm25_peer_bcast_mc)."""

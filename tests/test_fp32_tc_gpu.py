@@ -57,28 +57,20 @@ def test_clip_fp32_split_path_vs_oracle(lib_built, monkeypatch, n, d, ls, eps):
     assert rel_err(loss2, ref) < 1e-5 and rel_err(gx2, rx) < 1e-4
 
 
-def test_clip_fp32_split_reference_golden(lib_built):
-    """the reference-produced fp32 goldens whose shape is eligible go through the split path."""
+@pytest.mark.parametrize("case", ["n256_d512", "n256_d512_clamp"])
+def test_clip_fp32_split_reference_golden(lib_built, case):
+    """the reference-produced fp32 goldens of an eligible shape go through the split path."""
     import numpy as np
+    from multimodal_2025_b200 import _lib
     from multimodal_2025_b200.losses import ClipLoss
-    G = load_golden("clip.npz")
-    hit = 0
-    for key, g in G.items():
-        if not key or "x" not in g:
-            continue
-        x, y = torch.from_numpy(np.asarray(g["x"])), torch.from_numpy(np.asarray(g["y"]))
-        n, d = x.shape
-        if x.dtype != torch.float32 or n % 256 or d % 256 or d > 1024:
-            continue
-        hit += 1
-        eps = float(g["eps"]) if "eps" in g else 0.1
-        ls = torch.tensor(float(g["ls"]))
-        m = ClipLoss(eps).cuda()
-        loss, (gx, gy, gl) = _ours(lambda a, b, c: m(a, b, c), [x, y, ls])
-        assert rel_err(loss, g["loss"]) < 1e-5
-        assert rel_err(gx, g["gx"]) < 1e-4 and rel_err(gy, g["gy"]) < 1e-4
-    # the golden file is not required to hold an eligible case; the oracle test above is the gate
-    assert hit >= 0
+    g = load_golden("clip_forward.npz")[case]
+    x, y = torch.from_numpy(np.asarray(g["x"])), torch.from_numpy(np.asarray(g["y"]))
+    m = ClipLoss(float(g["eps"])).cuda()
+    loss, (gx, gy, gl) = _ours(lambda a, b, c: m(a, b, c), [x, y, torch.tensor(float(g["ls"]))])
+    assert _lib.lib().mm25_debug_last_sim_path() == 1
+    assert rel_err(loss, g["loss"]) < 1e-5
+    assert rel_err(gx, g["gx"]) < 1e-4 and rel_err(gy, g["gy"]) < 1e-4
+    assert abs(float(gl) - float(g["gl"])) <= 1e-4 * max(abs(float(g["gl"])), 1e-3)
 
 
 def test_forward_sampled_fp32_split_vs_oracle(lib_built):

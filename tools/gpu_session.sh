@@ -24,6 +24,9 @@ for step in "$@"; do
     fused)     run fused 900 python -m pytest tests/test_fused_rank_gpu.py -m gpu -q ;;
     cfg5)      run bench_cfg5 900 python bench.py --config cfg5 --steps 5 --warmup 3 ;;
     exper)     run exper 1800 env MM25_TEST_EXPERIMENTAL=1 python -m pytest tests/test_zz_retrieval_gpu.py -m gpu -q -k "scatter or two_cta or pair_kernels" ;;
+    fp32tc)    run fp32tc 900 python -m pytest tests/test_fp32_tc_gpu.py tests/test_topk_gpu.py tests/test_fused_rank_gpu.py -m gpu -q ;;
+    cfg4ref)   run bench_cfg4_ref 900 python bench.py --config cfg4 --steps 5 --warmup 3 --no-cpu-baseline
+               run bench_cfg1_ref 600 python bench.py --config cfg1 --steps 10 --warmup 3 --no-cpu-baseline ;;
     refarm)    run refarm 900 python bench.py --impl reference --steps 3 --warmup 1 ;;
     diag)      run diag 600 python tools/diag_te.py ;;
     diag0)     run diag0 600 env MM25_TE=0 python tools/diag_te.py ;;
