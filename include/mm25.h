@@ -444,7 +444,8 @@ int mm25_rank_both(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_
  * runs twice, the second pass emits g - bf16(g)) and dA = sum over the four (G term, Y term)
  * products, accumulated in fp32 by four grouped-GEMM launches; likewise dB.  da [B, M, d],
  * db [B, N, d] fp32 (either may be NULL); dscale_part: mm25_sim_bwd_split_nparts(B, M, N)
- * floats (NULL: skip); workspace: mm25_sim_bwd_split_workspace_bytes(M, N).
+ * floats (NULL: skip); workspace: mm25_sim_bwd_split_workspace_bytes(M, N); mode = MM25_SIM_PLAIN
+ * or MM25_SIM_MASKDIAG (InfoLOOB, cloobLoss.py:26-31).
  * mm25_sim_split_eligible: 1 when the shape is covered (d % 256 == 0, d <= 1024, M % 128 == 0,
  * N % 256 == 0). */
 int mm25_split_bf16x2(const float* x, int64_t rows, int64_t d, int role, void* out4, void* hi,
@@ -458,7 +459,18 @@ int mm25_sim_bwd_split(const void* a4, const void* b4, const void* a_hi, const v
                        int64_t diag_offset, const float* row_lse, const float* col_lse,
                        float w_row, float w_col, float w_diag, float w_all, const float* gout,
                        float* da, float* db, float* dscale_part, void* workspace,
-                       size_t workspace_bytes, float dot_bound, void* stream);
+                       size_t workspace_bytes, float dot_bound, int mode, void* stream);
+/* fp32-grade Hopfield backward (autograd of `hopfield`, losses/cloobLoss.py:43-47, at the fp32
+ * contract on the tensor cores): the dual-accumulator sweep of mm25_hopfield_bwd_tc on the split
+ * operands q4, k4 (mm25_split_bf16x2 roles 0 / 1) with the panels dZ and P split as well; d_o is
+ * fp32 [M, d] and is split inside.  dq [M, d], dk [N, d] fp32 (either may be NULL). */
+int mm25_hopfield_split_eligible(int64_t M, int64_t N, int64_t d);
+size_t mm25_hopfield_bwd_split_workspace_bytes(int64_t M, int64_t N, int64_t d);
+int mm25_hopfield_bwd_split(const void* q4, const void* k4, const void* q_hi, const void* q_lo,
+                            const void* k_hi, const void* k_lo, const float* d_o, int64_t M,
+                            int64_t N, int64_t d, const float* beta, const float* lse,
+                            const float* delta, float* dq, float* dk, void* workspace,
+                            size_t workspace_bytes, void* stream);
 
 /* Retrieval ranks fused into the similarity GEMM: the scores a_q . b_j (bf16 rows, fp32
  * accumulation on the tensor cores) are counted against the row's target as they leave TMEM and

@@ -142,7 +142,11 @@ SIGNATURES = {
     "mm25_sim_bwd_split_nparts": (_i64, [_i64, _i64, _i64]),
     "mm25_sim_bwd_split": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _int,
                                   _f32, _i64, _vp, _vp, _f32, _f32, _f32, _f32, _vp, _vp, _vp, _vp,
-                                  _vp, _sz, _f32, _vp]),
+                                  _vp, _sz, _f32, _int, _vp]),
+    "mm25_hopfield_split_eligible": (_int, [_i64, _i64, _i64]),
+    "mm25_hopfield_bwd_split_workspace_bytes": (_sz, [_i64, _i64, _i64]),
+    "mm25_hopfield_bwd_split": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp,
+                                       _vp, _vp, _vp, _vp, _sz, _vp]),
     "mm25_sim_rank": (_int, [_vp, _vp, _int, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "mm25_rowdot": (_int, [_vp, _vp, _vp, _i64, _i64, _vp]),
     "mm25_hopfield_bwd_pass": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _vp,

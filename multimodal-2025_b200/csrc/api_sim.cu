@@ -228,12 +228,34 @@ extern "C" int mm25_sim_bwd_split(const void* a4, const void* b4, const void* a_
                                   const float* row_lse, const float* col_lse, float w_row,
                                   float w_col, float w_diag, float w_all, const float* gout,
                                   float* da, float* db, float* dscale_part, void* workspace,
-                                  size_t workspace_bytes, float dot_bound, void* stream) {
+                                  size_t workspace_bytes, float dot_bound, int mode,
+                                  void* stream) {
+  if (mode != MM25_SIM_PLAIN && mode != MM25_SIM_MASKDIAG) return MM25_ERR_ARG;
   if (!a4 || !b4 || !a_hi || !a_lo || !b_hi || !b_lo || !scale || !row_lse || !workspace)
     return MM25_ERR_ARG;
   if (!col_lse && w_col != 0.f) return MM25_ERR_ARG;
   return tc::launch_bwd_split(a4, b4, a_hi, a_lo, b_hi, b_lo, B, M, N, d, scale, scale_kind,
                               clamp_max, diag_offset, row_lse, col_lse, w_row, w_col, w_diag,
                               w_all, gout, da, db, dscale_part, workspace, workspace_bytes,
-                              dot_bound, (cudaStream_t)stream);
+                              dot_bound, (cudaStream_t)stream, mode == MM25_SIM_MASKDIAG);
+}
+
+extern "C" int mm25_hopfield_split_eligible(int64_t M, int64_t N, int64_t d) {
+  return tcm::hopfield_split_eligible(M, N, d) ? 1 : 0;
+}
+extern "C" size_t mm25_hopfield_bwd_split_workspace_bytes(int64_t M, int64_t N, int64_t d) {
+  return tcm::hopfield_split_eligible(M, N, d) ? tcm::hopfield_split_workspace_bytes(M, N, d) : 0;
+}
+extern "C" int mm25_hopfield_bwd_split(const void* q4, const void* k4, const void* q_hi,
+                                       const void* q_lo, const void* k_hi, const void* k_lo,
+                                       const float* d_o, int64_t M, int64_t N, int64_t d,
+                                       const float* beta, const float* lse, const float* delta,
+                                       float* dq, float* dk, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+  if (!q4 || !k4 || !q_hi || !q_lo || !k_hi || !k_lo || !d_o || !beta || !lse || !delta ||
+      !workspace)
+    return MM25_ERR_ARG;
+  return tcm::launch_hopfield_bwd_split(q4, k4, q_hi, q_lo, k_hi, k_lo, d_o, M, N, d, beta, lse,
+                                        delta, dq, dk, workspace, workspace_bytes,
+                                        (cudaStream_t)stream);
 }

@@ -42,7 +42,7 @@ int launch_bwd_split(const void* a4, const void* b4, const void* a_hi, const voi
                      int64_t diag_offset, const float* row_lse, const float* col_lse,
                      float w_row, float w_col, float w_diag, float w_all, const float* gout,
                      float* da, float* db, float* dscale_part, void* ws, size_t ws_bytes,
-                     float dot_bound, cudaStream_t st);
+                     float dot_bound, cudaStream_t st, int mask_diag = 0);
 
 }  // namespace tc
 
@@ -63,5 +63,13 @@ int launch_bwd(const void* a, const void* b, const float* u, const float* v,
                const float* row_lse, float w_row, float w_diag, float w_all, const float* gout,
                float* da, float* db, float* dscale_part, float* ddiag, void* ws,
                size_t ws_bytes, cudaStream_t st);
+// fp32-grade Hopfield backward on two-term bf16 splits (sim_tc_mod.cu)
+bool hopfield_split_eligible(int64_t M, int64_t N, int64_t d);
+size_t hopfield_split_workspace_bytes(int64_t M, int64_t N, int64_t d);
+int launch_hopfield_bwd_split(const void* q4, const void* k4, const void* q_hi, const void* q_lo,
+                              const void* k_hi, const void* k_lo, const float* d_o, int64_t M,
+                              int64_t N, int64_t d, const float* beta, const float* lse,
+                              const float* delta, float* dq, float* dk, void* ws, size_t ws_bytes,
+                              cudaStream_t st);
 }  // namespace tcm
 }  // namespace mm25

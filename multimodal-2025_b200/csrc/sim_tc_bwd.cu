@@ -542,7 +542,7 @@ int launch_bwd_split(const void* a4, const void* b4, const void* a_hi, const voi
                      int64_t diag_offset, const float* row_lse, const float* col_lse,
                      float w_row, float w_col, float w_diag, float w_all, const float* gout,
                      float* da, float* db, float* dscale_part, void* ws, size_t ws_bytes,
-                     float dot_bound, cudaStream_t st) {
+                     float dot_bound, cudaStream_t st, int mask_diag) {
   const int64_t d4 = 4 * d;
   if (!eligible_fwd(B, M, N, d4, MM25_BF16, MM25_SIM_PLAIN) || d % 256 != 0 ||
       !gemm_eligible(M >= 128 ? 128 : M, d, N))
@@ -605,7 +605,7 @@ int launch_bwd_split(const void* a4, const void* b4, const void* a_hi, const voi
             clamp_max, diag_offset, row_lse + bz * M, col_lse ? col_lse + bz * N : cbuf, w_row,
             w_col, w_diag, w_all, gout ? gout + bz : nullptr,
             (dscale_part && lo == 0) ? dscale_part + part : nullptr, Cc, dot_bound, nullptr,
-            lo ? 2 : 0);
+            (lo ? 2 : 0) | (mask_diag ? 1 : 0));
         timing_end(tt_, st); }
         MM25_LAUNCH_CHECK();
         for (int t = 0; t < 2; ++t) {   // second operand: hi term, then lo term

@@ -205,6 +205,13 @@ sim_mod_tc_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 pq[u] = p;
                 zq[u] = s * p * (__uint_as_float(rw[j]) - Di);
               }
+              if (w_all != 0.f) {   // EPI_HOPF reuses w_all as the "emit the low split half" flag
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                  zq[u] -= __bfloat162float(__float2bfloat16_rn(zq[u]));
+                  pq[u] -= __bfloat162float(__float2bfloat16_rn(pq[u]));
+                }
+              }
               __nv_bfloat162 hz = __floats2bfloat162_rn(zq[0], zq[1]);
               __nv_bfloat162 hp = __floats2bfloat162_rn(pq[0], pq[1]);
               pz[j2] = *reinterpret_cast<uint32_t*>(&hz);
@@ -592,6 +599,94 @@ int launch_hopfield_bwd(const void* q, const void* k, const float* d_o, int64_t 
       GemmDesc gc{GP, dob + p0 * d, dk, d, N, rows, 1, 1, 1, 1.f, nullptr, 0, 0};
       rc = gemm_grouped(nullptr, &gc, d, nullptr, st);
       if (rc) return rc;
+    }
+  }
+  return MM25_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// fp32-grade Hopfield backward (cloobLoss.py:43-47 in fp32; contract 1e-5 / 1e-4): the same
+// dual-accumulator sweep on two-term bf16 splits.  q4 / do4 = [hi hi lo lo], k4 = [hi lo hi lo]
+// ([rows, 4 d], prep.cu split kernel), so S = Q K^T and T = dO K^T accumulate with 16 significant
+// bits per operand; the panels dZ and P are split too (second pass emits x - bf16(x)) and every
+// product with them becomes accumulating grouped-GEMM launches over the (hi, lo) operand terms.
+bool hopfield_split_eligible(int64_t M, int64_t N, int64_t d) {
+  return eligible(1, M, N, 4 * d, 4 * d, MM25_BF16, false) && d % 256 == 0 && d <= 1024 &&
+         N % 256 == 0 && gemm_eligible(128, d, N);
+}
+
+size_t hopfield_split_workspace_bytes(int64_t M, int64_t N, int64_t d) {
+  return 256 + align256((size_t)M * 4 * d * 2) + 2 * align256((size_t)M * d * 2) +
+         2 * align256((size_t)hopf_panel_rows(M, N) * (size_t)N * 2);
+}
+
+extern "C" int mm25_split_bf16x2(const float* x, int64_t rows, int64_t d, int role, void* out4,
+                                 void* hi, void* lo, void* stream);
+
+int launch_hopfield_bwd_split(const void* q4, const void* k4, const void* q_hi, const void* q_lo,
+                              const void* k_hi, const void* k_lo, const float* d_o, int64_t M,
+                              int64_t N, int64_t d, const float* beta, const float* lse,
+                              const float* delta, float* dq, float* dk, void* ws, size_t ws_bytes,
+                              cudaStream_t st) {
+  if (!hopfield_split_eligible(M, N, d)) return MM25_ERR_SHAPE;
+  if (ws_bytes < hopfield_split_workspace_bytes(M, N, d)) return MM25_ERR_WORKSPACE;
+  const int64_t d4 = 4 * d;
+  uintptr_t w0 = (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255);
+  __nv_bfloat16* do4 = reinterpret_cast<__nv_bfloat16*>(w0);
+  w0 += align256((size_t)M * d4 * 2);
+  __nv_bfloat16* doh = reinterpret_cast<__nv_bfloat16*>(w0);
+  w0 += align256((size_t)M * d * 2);
+  __nv_bfloat16* dol = reinterpret_cast<__nv_bfloat16*>(w0);
+  w0 += align256((size_t)M * d * 2);
+  const int64_t R = hopf_panel_rows(M, N);
+  __nv_bfloat16* GZ = reinterpret_cast<__nv_bfloat16*>(w0);
+  __nv_bfloat16* GP = reinterpret_cast<__nv_bfloat16*>(w0 + align256((size_t)R * (size_t)N * 2));
+  int rc = mm25_split_bf16x2(d_o, M, d, 0, do4, doh, dol, st);
+  if (rc) return rc;
+  const int sms = tc::tc_sm_count();
+  CUtensorMap ta, tb, tu;
+  if ((rc = make_tmap_bf16(&ta, q4, (uint64_t)M, (uint64_t)d4, MBM, MBK))) return rc;
+  if ((rc = make_tmap_bf16(&tb, k4, (uint64_t)N, (uint64_t)d4, MBN, MBK))) return rc;
+  if ((rc = make_tmap_bf16(&tu, do4, (uint64_t)M, (uint64_t)d4, MBM, MBK))) return rc;
+  const size_t smem = sizeof(ModSmem) + 1024;
+  MM25_CUDA_CHECK(cudaFuncSetAttribute(sim_mod_tc_kernel<EPI_HOPF>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const __nv_bfloat16* qs[2] = {(const __nv_bfloat16*)q_hi, (const __nv_bfloat16*)q_lo};
+  const __nv_bfloat16* ks[2] = {(const __nv_bfloat16*)k_hi, (const __nv_bfloat16*)k_lo};
+  const __nv_bfloat16* dos[2] = {doh, dol};
+  for (int64_t p0 = 0; p0 < M; p0 += R) {
+    const int64_t rows = (M - p0 < R) ? (M - p0) : R;
+    ModGeom g;
+    g.KC1 = g.KC2 = (int)(d4 / MBK); g.ntiles = (int)(N / MBN);
+    g.first_rb = (int)(p0 / MBM); g.num_rb = (int)(rows / MBM);
+    pick_segments(g.num_rb, g.ntiles, sms, &g.nseg, &g.tps);
+    const long items = (long)g.num_rb * g.nseg;
+    const int grid = (int)(items < sms ? items : sms);
+    CUtensorMap tg, tp;
+    if ((rc = make_tmap_bf16(&tg, GZ, (uint64_t)rows, (uint64_t)N, 32, 32, 64))) return rc;
+    if ((rc = make_tmap_bf16(&tp, GP, (uint64_t)rows, (uint64_t)N, 32, 32, 64))) return rc;
+    for (int lo = 0; lo < 2; ++lo) {
+      { void* tt_ = timing_begin(MM25_T_SIM_MOD, st);
+      sim_mod_tc_kernel<EPI_HOPF><<<grid, MTHREADS, smem, st>>>(
+          ta, tb, tu, tb, tg, tp, g, M, N, beta, MM25_SCALE_MUL, 0.f, 0, delta, nullptr, nullptr,
+          nullptr, lse, 0.f, 0.f, lo ? 1.f : 0.f, nullptr, nullptr, nullptr);
+      timing_end(tt_, st); }
+      MM25_LAUNCH_CHECK();
+      for (int t = 0; t < 2; ++t) {
+        const int first = (lo == 0 && t == 0);
+        // dQ[panel] (+)= dZ K_t  and  dK (+)= dZ^T Q_t[panel]
+        GemmDesc ga{GZ, ks[t], dq ? dq + p0 * d : nullptr, d, rows, N, 0, 1, first ? 0 : 1, 1.f,
+                    nullptr, 0, 0};
+        GemmDesc gb{GZ, qs[t] + p0 * d, dk, d, N, rows, 1, 1, (first && p0 == 0) ? 0 : 1, 1.f,
+                    nullptr, 0, 0};
+        rc = gemm_grouped(dq ? &ga : nullptr, dk ? &gb : nullptr, d, nullptr, st);
+        if (rc) return rc;
+        if (dk) {   // dK += P^T dO_t[panel]
+          GemmDesc gc{GP, dos[t] + p0 * d, dk, d, N, rows, 1, 1, 1, 1.f, nullptr, 0, 0};
+          rc = gemm_grouped(nullptr, &gc, d, nullptr, st);
+          if (rc) return rc;
+        }
+      }
     }
   }
   return MM25_OK;

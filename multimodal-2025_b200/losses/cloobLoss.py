@@ -40,6 +40,21 @@ def _tc_operands(x, y):
 COMPUTE_DTYPE = None
 
 
+def _split_ok(ops, x, y, hopfield):
+    """fp32 inputs keep the reference's fp32-grade arithmetic on the tensor cores when the shape
+    is covered (two-term bf16 splits, include/mm25.h mm25_split_bf16x2); MM25_FP32_TC=0 or a
+    stand-in backend (CPU tests) take the fp32 FFMA / dense route."""
+    import os
+    if not (x.is_cuda and hasattr(ops, "split_bf16x2")) or os.environ.get("MM25_FP32_TC", "1") == "0":
+        return False
+    if x.dtype == torch.bfloat16 or COMPUTE_DTYPE == torch.bfloat16 or x.dim() != 2:
+        return False
+    M, d = x.shape
+    N = y.shape[0]
+    return bool(ops.hopfield_split_eligible(M, N, d) if hopfield
+                else ops.sim_split_eligible(1, M, N, d))
+
+
 class _HopfieldFn(torch.autograd.Function):
     """U[Nq, d] = rownorm(softmax(beta Q K^T) K)."""
 
@@ -71,6 +86,20 @@ class _HopfieldFn(torch.autograd.Function):
         qf = q.detach().float().contiguous()
         kf = k.detach().float().contiguous()
         sc = _scalar(beta, q.device)
+        if _split_ok(ops, qf, kf, True):
+            # fp32-grade on the tensor cores: split operands swept over K = 4 d
+            q4, qh, ql = ops.split_bf16x2(qf.unsqueeze(0), 0)
+            k4, kh, kl = ops.split_bf16x2(kf.unsqueeze(0), 1)
+            lse, _, _, _ = ops.sim_fwd(q4, k4, None, None, None, sc, ops.SCALE_MUL, 0.0,
+                                       ops.SIM_PLAIN, 0, False, ops.IMPL_AUTO)
+            o, _, _ = ops.sim_bwd_split(q4, k4, qh, ql, kh, kl, sc, ops.SCALE_MUL, 0.0, 0, lse,
+                                        None, 1.0, 0.0, 0.0, 0.0, None, True, False, 0.0)
+            o = o / float(beta)
+            u, inv, _ = ops.rownorm_fwd(o, True, 1e-30, ops.F32, False)
+            ctx.save_for_backward(q4[0], k4[0], qh[0], ql[0], kh[0], kl[0], o[0], u[0], inv,
+                                  lse[0], sc)
+            ctx.beta, ctx.in_dtype, ctx.tc = float(beta), in_dtype, "split"
+            return u[0].to(in_dtype)
         q3, k3 = qf.unsqueeze(0), kf.unsqueeze(0)
         lse, _, _, _ = ops.sim_fwd(q3, k3, None, None, None, sc, ops.SCALE_MUL, 0.0,
                                    ops.SIM_PLAIN, 0, False, ops.IMPL_SIMT)
@@ -88,6 +117,15 @@ class _HopfieldFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, du):
         ops = ctx.ops
+        if ctx.tc == "split":
+            q4, k4, qh, ql, kh, kl, o, u, inv, lse, sc = ctx.saved_tensors
+            du = du.detach().float().contiguous()
+            do = ops.rownorm_bwd(du.unsqueeze(0), u.unsqueeze(0), inv, True, ops.F32, None)[0]
+            delta = ops.rowdot(do, o)
+            dq, dk = ops.hopfield_bwd_split(q4, k4, qh, ql, kh, kl, do, sc, lse, delta,
+                                            ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+            return (dq.to(ctx.in_dtype) if ctx.needs_input_grad[0] else None,
+                    dk.to(ctx.in_dtype) if ctx.needs_input_grad[1] else None, None, None)
         if ctx.tc:
             qb, kb, o, u, inv, lse, sc = ctx.saved_tensors
             du = du.detach().float().contiguous()
@@ -125,9 +163,15 @@ class _InfoLoobFn(torch.autograd.Function):
         in_dtype = x.dtype
         tc = _tc_operands(x, y)
         impl = ops.IMPL_SIMT if tc is None else ops.IMPL_TC
+        ctx.split = None
         if tc is None:
             xf = x.detach().float().contiguous().unsqueeze(0)
             yf = y.detach().float().contiguous().unsqueeze(0)
+            if _split_ok(ops, xf[0], yf[0], False):
+                x4, xh, xl = ops.split_bf16x2(xf, 0)
+                y4, yh, yl = ops.split_bf16x2(yf, 1)
+                ctx.split = (xh, xl, yh, yl)
+                xf, yf, impl = x4, y4, ops.IMPL_AUTO
         else:
             xf, yf = tc[0].unsqueeze(0), tc[1].unsqueeze(0)
         sc = _scalar(inv_tau, x.device)
@@ -149,6 +193,15 @@ class _InfoLoobFn(torch.autograd.Function):
         xf, yf, lse, sc = ctx.saved_tensors
         n = float(ctx.n_norm)
         g = gout.detach().float().reshape(1).contiguous()
+        if ctx.split is not None:
+            xh, xl, yh, yl = ctx.split
+            da, db, _ = ops.sim_bwd_split(xf, yf, xh, xl, yh, yl, sc, ops.SCALE_MUL, 0.0, ctx.off,
+                                          lse, None, 1.0 / n, 0.0, 1.0 / n, 0.0, g,
+                                          ctx.needs_input_grad[0], ctx.needs_input_grad[1], 0.0,
+                                          ops.SIM_MASKDIAG)
+            dx = da[0].to(ctx.in_dtype) if ctx.needs_input_grad[0] else None
+            dy = db[0].to(ctx.in_dtype) if ctx.needs_input_grad[1] else None
+            return dx, dy, None, None, None, None
         da, db, _, _ = ops.sim_bwd(xf, yf, None, None, None, sc, ops.SCALE_MUL, 0.0,
                                    ops.SIM_MASKDIAG, ctx.off, lse, None, 1.0 / n, 0.0, 1.0 / n,
                                    0.0, g, ctx.needs_input_grad[0], ctx.needs_input_grad[1],

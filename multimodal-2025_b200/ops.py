@@ -237,8 +237,9 @@ def sim_bwd_split(a4: Tensor, b4: Tensor, a_hi: Tensor, a_lo: Tensor, b_hi: Tens
                   scale: Tensor, scale_kind: int, clamp_max: float, diag_offset: int,
                   row_lse: Tensor, col_lse: Optional[Tensor], w_row: float, w_col: float,
                   w_diag: float, w_all: float, gout: Optional[Tensor], need_da: bool,
-                  need_db: bool, dot_bound: float) -> Tuple[Tensor, Tensor, Tensor]:
-    """fp32-grade PLAIN backward on the split operands (include/mm25.h mm25_sim_bwd_split);
+                  need_db: bool, dot_bound: float,
+                  mode: int = 0) -> Tuple[Tensor, Tensor, Tensor]:
+    """fp32-grade PLAIN / MASKDIAG backward on the split operands (include/mm25.h mm25_sim_bwd_split);
     returns (da [B, M, d], db [B, N, d], dscale[1]) fp32."""
     B, M, d4 = a4.shape
     N = b4.shape[1]
@@ -257,11 +258,41 @@ def sim_bwd_split(a4: Tensor, b4: Tensor, a_hi: Tensor, a_lo: Tensor, b_hi: Tens
                                   d, _p(scale), scale_kind, clamp_max, diag_offset, _p(row_lse),
                                   _p(col_lse), w_row, w_col, w_diag, w_all, _p(gout),
                                   _p(da) if need_da else None, _p(db) if need_db else None,
-                                  _p(parts), _p(ws), ws.numel(), dot_bound, _stream(a4))
+                                  _p(parts), _p(ws), ws.numel(), dot_bound, mode, _stream(a4))
         _lib.check(rc, "mm25_sim_bwd_split")
         rc = L.mm25_sum_parts(_p(parts), parts.numel(), 1.0, _p(dscale), _stream(a4))
     _lib.check(rc, "mm25_sum_parts")
     return da, db, dscale
+
+
+def hopfield_split_eligible(M: int, N: int, d: int) -> bool:
+    return bool(_lib.lib().mm25_hopfield_split_eligible(M, N, d))
+
+
+@torch.library.custom_op("mm25::hopfield_bwd_split", mutates_args=(), device_types="cuda")
+def hopfield_bwd_split(q4: Tensor, k4: Tensor, q_hi: Tensor, q_lo: Tensor, k_hi: Tensor,
+                       k_lo: Tensor, d_o: Tensor, beta: Tensor, lse: Tensor, delta: Tensor,
+                       need_dq: bool, need_dk: bool) -> Tuple[Tensor, Tensor]:
+    """fp32-grade Hopfield backward on the split operands (include/mm25.h
+    mm25_hopfield_bwd_split); q4 [M, 4 d], k4 [N, 4 d] bf16, d_o [M, d] fp32."""
+    M, d4 = q4.shape
+    N = k4.shape[0]
+    d = d4 // 4
+    dev = q4.device
+    L = _lib.lib()
+    d_o = d_o.detach().float().contiguous()
+    with torch.cuda.device(dev):
+        dq = torch.empty((M, d) if need_dq else (0,), dtype=torch.float32, device=dev)
+        dk = torch.empty((N, d) if need_dk else (0,), dtype=torch.float32, device=dev)
+        ws = torch.empty((max(int(L.mm25_hopfield_bwd_split_workspace_bytes(M, N, d)), 16),),
+                         dtype=torch.uint8, device=dev)
+        rc = L.mm25_hopfield_bwd_split(_p(q4), _p(k4), _p(q_hi), _p(q_lo), _p(k_hi), _p(k_lo),
+                                       _p(d_o), M, N, d, _p(beta), _p(lse.contiguous()),
+                                       _p(delta.contiguous()), _p(dq) if need_dq else None,
+                                       _p(dk) if need_dk else None, _p(ws), ws.numel(),
+                                       _stream(q4))
+    _lib.check(rc, "mm25_hopfield_bwd_split")
+    return dq, dk
 
 
 @torch.library.custom_op("mm25::col_merge", mutates_args=(), device_types="cuda")

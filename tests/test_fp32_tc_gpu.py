@@ -120,3 +120,43 @@ def test_clip_fp32_split_full_size_slab(lib_built):
     xr = xd[rows]                       # already unit norm: d/dx of normalise at |x| = 1
     want = gx_hat - xr * (xr * gx_hat).sum(-1, keepdim=True)
     assert rel_err(xc.grad[rows].double().cpu(), want.cpu()) < 1e-4
+
+
+@pytest.mark.parametrize("n,d", [(512, 256), (1024, 512), (768, 1024)])
+def test_cloob_fp32_split_path_vs_oracle(lib_built, monkeypatch, n, d):
+    """CLOOB with fp32 inputs of an eligible shape: the four Hopfield retrievals (forward P K and
+    the dual-accumulator backward) and both InfoLOOB terms run the split tensor-core kernels and
+    meet the fp32 contract; MM25_FP32_TC=0 (FFMA kernels) agrees."""
+    from multimodal_2025_b200 import _lib
+    from multimodal_2025_b200.losses import CLOOBLoss
+    x, y = O.synth_embeddings(n, d, 8, correlated=True)
+    ref, (rx, ry) = O.loss_and_grads(lambda a, b: O.cloob_loss(a, b, 30.0, 15.0), [x, y])
+    crit = CLOOBLoss(30.0, 15.0, "cuda")
+    loss, (gx, gy) = _ours(lambda a, b: crit(a, b), [x, y])
+    assert _lib.lib().mm25_debug_last_sim_path() == 1
+    assert rel_err(loss, ref) < 1e-5
+    assert rel_err(gx, rx) < 1e-4 and rel_err(gy, ry) < 1e-4
+    monkeypatch.setenv("MM25_FP32_TC", "0")
+    loss2, (gx2, gy2) = _ours(lambda a, b: crit(a, b), [x, y])
+    assert _lib.lib().mm25_debug_last_sim_path() == 0
+    assert rel_err(loss2, ref) < 1e-5 and rel_err(gx2, rx) < 1e-4
+
+
+def test_hopfield_fp32_split_pieces_vs_dense(lib_built):
+    """hopfield(Q, K) and its gradients on a rectangular problem against dense fp64 autograd."""
+    from multimodal_2025_b200.losses import hopfield
+    g = torch.Generator().manual_seed(6)
+    q = torch.nn.functional.normalize(torch.randn(256, 256, generator=g), dim=-1)
+    k = torch.nn.functional.normalize(torch.randn(512, 256, generator=g), dim=-1)
+    w = torch.randn(256, 256, generator=g)
+
+    def dense(a, b):
+        p = torch.softmax(15.0 * a @ b.T, dim=1) @ b
+        return torch.nn.functional.normalize(p, dim=-1)
+    a, b = q.double().requires_grad_(True), k.double().requires_grad_(True)
+    (dense(a, b) * w.double()).sum().backward()
+    qc, kc = q.cuda().requires_grad_(True), k.cuda().requires_grad_(True)
+    u = hopfield(qc, kc, 15.0).T
+    (u * w.cuda()).sum().backward()
+    assert rel_err(u.detach().cpu(), dense(q.double(), k.double())) < 1e-5
+    assert rel_err(qc.grad.cpu(), a.grad) < 1e-4 and rel_err(kc.grad.cpu(), b.grad) < 1e-4
