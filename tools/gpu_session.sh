@@ -27,6 +27,7 @@ for step in "$@"; do
     fp32tc)    run fp32tc 900 python -m pytest tests/test_fp32_tc_gpu.py tests/test_topk_gpu.py tests/test_fused_rank_gpu.py -m gpu -q ;;
     cfg4ref)   run bench_cfg4_ref 900 python bench.py --config cfg4 --steps 5 --warmup 3 --no-cpu-baseline
                run bench_cfg1_ref 600 python bench.py --config cfg1 --steps 10 --warmup 3 --no-cpu-baseline ;;
+    cfg3ref)   run bench_cfg3_ref 900 python bench.py --config cfg3 --steps 5 --warmup 3 --no-cpu-baseline ;;
     refarm)    run refarm 900 python bench.py --impl reference --steps 3 --warmup 1 ;;
     diag)      run diag 600 python tools/diag_te.py ;;
     diag0)     run diag0 600 env MM25_TE=0 python tools/diag_te.py ;;
