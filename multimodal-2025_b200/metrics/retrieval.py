@@ -91,16 +91,20 @@ def fused_ranks(queries: Tensor, gallery: Tensor, targets: Tensor) -> Tensor:
 
 
 def _use_fused(fused, x: Tensor, y: Tensor, logit_scale=None) -> bool:
-    """fused=None (auto): bf16 features of an eligible width take the fused kernel — the
-    reference's own bf16 matmul rounds every score to bf16, so no bit-level score parity exists
-    to preserve there; fp32 features keep the exact route (library GEMM in the reference's
-    expression + mm25_rank_both on identical fp32 scores)."""
+    """fused=None: the exact route (library GEMM in the reference's expression +
+    `mm25_rank_both` on identical scores) unless the environment sets MM25_FUSED_RANKS=1; the
+    fused kernel ranks fp32-accumulated dot products of the bf16 rows, which is not the order of
+    the reference's own bf16-ROUNDED scores wherever the rounding creates ties, so it is an
+    explicit choice: `fused=True` (any CUDA features of an eligible width; fp32 features are
+    rounded to bf16 first) or the environment switch."""
     ok = (hasattr(_ops, "sim_rank") and x.is_cuda and y.is_cuda and x.shape[-1] % 64 == 0
           and 64 <= x.shape[-1] <= 1024 and x.shape[-1] == y.shape[-1])
     if ok and logit_scale is not None and float(logit_scale) <= 0:
         ok = False  # a non-positive scale changes the order: rank the scaled scores instead
     if fused is None:
-        return bool(ok and x.dtype == torch.bfloat16 and y.dtype == torch.bfloat16)
+        import os
+        return bool(ok and os.environ.get("MM25_FUSED_RANKS") == "1"
+                    and x.dtype == torch.bfloat16 and y.dtype == torch.bfloat16)
     if fused and not ok:
         raise ValueError("fused ranks need CUDA features with d % 64 == 0, 64 <= d <= 1024 and "
                          "a positive logit scale")

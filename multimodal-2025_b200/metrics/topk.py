@@ -52,7 +52,7 @@ def top_k_indices_batched(text_emb: torch.Tensor, image_emb: torch.Tensor, k: in
 
 def top_k_score(embedding_pairs, k=5, fused=None):
     """Fraction of images whose correct texts intersect their top-k texts (reference :54-82).
-    `fused` (None = auto: bf16 CUDA embeddings): the image x text similarity GEMM and the rank
+    `fused=True` (or MM25_FUSED_RANKS=1 with bf16 CUDA embeddings): the image x text similarity GEMM and the rank
     count run in one tcgen05 kernel (`mm25_sim_rank`, no score matrix) — an image hits iff the
     best rank among its own texts is < k; cosine normalisation is done before the bf16 cast."""
     total_count = len(embedding_pairs)

@@ -79,7 +79,7 @@ def test_sim_rank_accumulates_and_is_repeatable(lib_built):
 
 
 def test_get_clip_metrics_fused_vs_unfused_and_oracle(lib_built):
-    """bf16 features: auto-selects the fused kernel; the metrics agree with the unfused route
+    """bf16 features, fused=True: the metrics agree with the unfused route
     (library GEMM + mm25_rank_both on fp32 features of the same bf16 values) and the oracle."""
     from multimodal_2025_b200.metrics import get_clip_metrics
     from multimodal_2025_b200.metrics.retrieval import paired_ranks
@@ -88,14 +88,14 @@ def test_get_clip_metrics_fused_vs_unfused_and_oracle(lib_built):
     x = torch.nn.functional.normalize(torch.randn(N, d, generator=g), dim=-1)
     y = torch.nn.functional.normalize(x + 0.9 * torch.randn(N, d, generator=g), dim=-1)
     xb, yb = x.bfloat16().cuda(), y.bfloat16().cuda()
-    fused = get_clip_metrics(xb, yb, torch.tensor(14.3, device="cuda"))
+    fused = get_clip_metrics(xb, yb, torch.tensor(14.3, device="cuda"), fused=True)
     plain = get_clip_metrics(xb.float(), yb.float(), torch.tensor(14.3, device="cuda"),
                              fused=False)
     want = MO.get_clip_metrics(xb.float().cpu(), yb.float().cpu(), torch.tensor(14.3))
     for k in want:
         assert abs(float(fused[k]) - float(want[k])) <= 2e-3 * max(1.0, abs(float(want[k]))), k
         assert abs(float(plain[k]) - float(want[k])) <= 2e-3 * max(1.0, abs(float(want[k]))), k
-    i2t, t2i = paired_ranks(xb, yb)
+    i2t, t2i = paired_ranks(xb, yb, fused=True)
     j2t, u2i = paired_ranks(xb.float(), yb.float(), fused=False)
     assert float((i2t != j2t).float().mean()) < 5e-3 and float((t2i != u2i).float().mean()) < 5e-3
     assert int((i2t - j2t).abs().max()) <= 2 and int((t2i - u2i).abs().max()) <= 2
@@ -113,13 +113,13 @@ def test_recall_at_k_and_top_k_score_fused(lib_built):
     i2t = torch.arange(n_im * cap).view(n_im, cap)
     imb, txb = im.bfloat16().cuda(), tx.bfloat16().cuda()
     ks = [1, 5, 10, 50]
-    got = recall_at_k_from_encodings(imb, txb, t2i, i2t, ks)
+    got = recall_at_k_from_encodings(imb, txb, t2i, i2t, ks, fused=True)
     want = MO.recall_at_k(imb.float().cpu(), txb.float().cpu(), t2i, i2t, ks)
     for a, b in zip(got[0] + got[1], list(want[0]) + list(want[1])):
         assert abs(a - b) <= 4e-3
     pairs = [([txb[i * cap + c] for c in range(cap)], imb[i]) for i in range(n_im)]
     for k in (1, 5, 10):
-        acc_f, info_f = top_k_score(pairs, k)                # auto: fused (bf16 CUDA)
+        acc_f, info_f = top_k_score(pairs, k, fused=True)
         acc_p, info_p = top_k_score(pairs, k, fused=False)
         assert info_f["total"] == info_p["total"] == n_im
         assert abs(info_f["correct"] - info_p["correct"]) <= 2
