@@ -118,6 +118,8 @@ def _peer_all_gather(B, t, tag, group, barrier=True):
     nbytes = t.numel() * t.element_size()
     if nbytes % 4 or os.environ.get("MM25_NCCL_GATHER"):
         return None
+    if nbytes % 16 and nbytes > (1 << 20):
+        return None   # mm25_peer_bcast moves large payloads as 16-byte vectors only: NCCL path
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     key, sb = _symm_buffer(tag, (world * t.shape[0],) + tuple(t.shape[1:]), t.dtype, t.device,
                            group)
@@ -126,7 +128,7 @@ def _peer_all_gather(B, t, tag, group, barrier=True):
     buf, hdl = sb
     mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
     if (mc and nbytes % 16 == 0 and nbytes >= (1 << 16) and hasattr(B, "peer_bcast_mc")
-            and os.environ.get("MM25_MC", "0") == "1"):
+            and os.environ.get("MM25_MC", "1") == "1"):
         # NVSwitch multicast: the shard is sent once and replicated in the switch
         B.peer_bcast_mc(t, mc, rank * nbytes)
     else:

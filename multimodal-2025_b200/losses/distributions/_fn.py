@@ -9,8 +9,23 @@ from ... import ops
 
 def fresh_seed() -> int:
     """A 63-bit Philox key drawn from torch's default CPU generator: reproducible under
-    torch.manual_seed, no device synchronisation."""
-    return int(torch.empty((), dtype=torch.int64).random_().item())
+    torch.manual_seed, no device synchronisation.  In a multi-process run every rank usually
+    calls torch.manual_seed with the SAME seed (AlignCLIP/main/train.py does), and the sampler
+    kernels index their counters by LOCAL row — so the rank is folded into the key
+    (splitmix64 of the draw and the rank): the rows of a sharded global batch then see
+    independent noise instead of P copies of the same stream."""
+    key = int(torch.empty((), dtype=torch.int64).random_().item())
+    try:
+        import torch.distributed as dist
+        rank = dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+    except Exception:  # noqa: BLE001 - no process group: single-process key
+        rank = 0
+    if rank:
+        z = (key + 0x9E3779B97F4A7C15 * (rank + 1)) & 0xFFFFFFFFFFFFFFFF
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+        key = (z ^ (z >> 31)) & 0x7FFFFFFFFFFFFFFF
+    return key
 
 
 class RowNormFn(torch.autograd.Function):

@@ -525,3 +525,28 @@ def test_cached_negatives_host_logic_with_standin(need_scale):
     assert (t2.grad - t.grad).norm() < 1e-4 * t.grad.norm()
     if need_scale:
         assert abs(float(s2.grad) - float(s.grad)) < 1e-4 * abs(float(s.grad))
+
+
+def _worker_seed(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from multimodal_2025_b200.losses.distributions._fn import fresh_seed
+        torch.manual_seed(1234)          # every rank seeds identically (main/train.py does)
+        a = fresh_seed()
+        torch.manual_seed(1234)
+        b = fresh_seed()
+        q.put((rank, a, b))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_philox_key_differs_across_ranks_and_is_reproducible():
+    """identical torch.manual_seed on every rank must not give the ranks identical
+    sampler noise; the key stays reproducible per rank."""
+    res = _run_world(_worker_seed, 2, ())
+    (r0, a0, b0), (r1, a1, b1) = res
+    assert a0 == b0 and a1 == b1 and a0 != a1
+    assert 0 <= a1 < 2 ** 63
