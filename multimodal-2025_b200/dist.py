@@ -65,11 +65,40 @@ _SYMM_CACHE = {}
 LAST_BACKWARD_PATH = None  # "fused gemm+reduce-scatter (peer memory)" or "nccl reduce-scatter"
 
 
+def _agree(ok: bool, device, group) -> bool:
+    """All ranks take the symmetric-memory fast path or none does: a rendezvous that failed on
+    one rank only would leave that rank in NCCL collectives while the others wait in peer
+    barriers.  One MIN all-reduce per buffer creation (results are cached)."""
+    try:
+        flag = torch.tensor([1 if ok else 0], device=device, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        return bool(int(flag.item()))
+    except Exception:  # noqa: BLE001 - no usable collective: stay on the conservative path
+        return False
+
+
+def _group_key(group):
+    """Cache key of a process group that survives garbage collection of the Python object
+    (id() values are reused): its global ranks."""
+    try:
+        return tuple(dist.get_process_group_ranks(group))
+    except Exception:  # noqa: BLE001
+        return id(group)
+
+
+def release_symmetric_buffers():
+    """Drop every cached symmetric-memory buffer (they are created once per shape and group and
+    otherwise live until exit)."""
+    _SYMM_CACHE.clear()
+    _SYMM_GEN.clear()
+    _GRAD_CLEAN.clear()
+
+
 def _symm_grad_buffer(n: int, d: int, device, group):
     """[n, d] fp32 buffer in symmetric memory (peer-mapped on every rank of `group`) that the
     fused backward scatter-adds dY into.  Returns (tensor, handle) or None when symmetric
     memory cannot be set up (then the NCCL reduce-scatter is used)."""
-    key = (n, d, device.index, id(group))
+    key = (n, d, device.index, _group_key(group))
     if key in _SYMM_CACHE:
         return _SYMM_CACHE[key]
     out = None
@@ -79,6 +108,8 @@ def _symm_grad_buffer(n: int, d: int, device, group):
         hdl = symm_mem.rendezvous(buf, group)
         out = (buf, hdl)
     except Exception:  # no NVLink peer access / unsupported allocator: keep the NCCL path
+        out = None
+    if not _agree(out is not None, device, group):
         out = None
     _SYMM_CACHE[key] = out
     return out
@@ -90,7 +121,7 @@ _GRAD_CLEAN = {}  # symmetric dY buffer zeroed (and published) by the forward of
 
 def _symm_buffer(tag, shape, dtype, device, group):
     """Cached symmetric-memory tensor + handle (peer-mapped on every rank), or None."""
-    key = (tag, tuple(shape), dtype, device.index, id(group))
+    key = (tag, tuple(shape), dtype, device.index, _group_key(group))
     if key in _SYMM_CACHE:
         return key, _SYMM_CACHE[key]
     out = None
@@ -100,6 +131,8 @@ def _symm_buffer(tag, shape, dtype, device, group):
         hdl = symm_mem.rendezvous(buf, group)
         out = (buf, hdl)
     except Exception:  # no peer access / unsupported allocator: callers keep the NCCL path
+        out = None
+    if not _agree(out is not None, device, group):
         out = None
     _SYMM_CACHE[key] = out
     return key, out
@@ -213,7 +246,7 @@ class _ShardedClipFn(torch.autograd.Function):
             symm = _symm_grad_buffer(n, xhat.shape[-1], xhat.device, group)
             if symm is not None:
                 symm[0].zero_()
-                gkey = (n, xhat.shape[-1], xhat.device.index, id(group))
+                gkey = (n, xhat.shape[-1], xhat.device.index, _group_key(group))
                 _GRAD_CLEAN[gkey] = True
         pg = _peer_all_gather(B, payload, "colstats", group)            # [P, 2N (+ 2d) (+ 4)]
         gathered = pg[0] if pg is not None else _all_gather_cat(payload, group)

@@ -28,6 +28,11 @@ for step in "$@"; do
     cfg4ref)   run bench_cfg4_ref 900 python bench.py --config cfg4 --steps 5 --warmup 3 --no-cpu-baseline
                run bench_cfg1_ref 600 python bench.py --config cfg1 --steps 10 --warmup 3 --no-cpu-baseline ;;
     cfg3ref)   run bench_cfg3_ref 900 python bench.py --config cfg3 --steps 5 --warmup 3 --no-cpu-baseline ;;
+    ncunew)    python tools/profile_new_kernels.py > "gpurun_out/${TAG}_new_plain.log" 2>&1 && \
+               timeout 1200 ncu --set full --clock-control none --import-source on \
+                 -k regex:"sim_rank_tc|topk_slice|topk_merge|sim_fwd_tc_kernel|sim_grad_tc_kernel|gemm_grouped|sim_mod_tc" -s 16 -c 14 -o "gpurun_out/${TAG}_new_prof" \
+                 python tools/profile_new_kernels.py > "gpurun_out/${TAG}_ncu_new.log" 2>&1
+               echo "ncunew rc=$?" | tee -a "gpurun_out/${TAG}_summary.txt" ;;
     refarm)    run refarm 900 python bench.py --impl reference --steps 3 --warmup 1 ;;
     diag)      run diag 600 python tools/diag_te.py ;;
     diag0)     run diag0 600 env MM25_TE=0 python tools/diag_te.py ;;
