@@ -214,7 +214,20 @@ class _ShardedClipFn(torch.autograd.Function):
                 and any(ctx.needs_input_grad[:3]) and bound > 0.0 and impl != 1
                 and B.tc_eligible_bwd(xhat, yall) and 2 * n * N <= B.keep_e_bytes_limit(n, N, xhat.shape[-1]))
         e_keep = e_flag = None
-        if keep:  # E = exp(z - shift) of the local [n, N] block is kept for the backward
+        # fp32 shards of an eligible shape keep fp32-grade arithmetic on the tensor cores (two-term
+        # bf16 splits, include/mm25.h mm25_split_bf16x2) instead of the FFMA kernels
+        split = (cdt == B.F32 and impl == 0 and xhat.is_cuda and hasattr(B, "split_bf16x2")
+                 and os.environ.get("MM25_FP32_TC", "1") != "0"
+                 and B.sim_split_eligible(1, n, N, xhat.shape[-1]))
+        ctx.split = None
+        if split:
+            x4, xh, xl = B.split_bf16x2(xhat, 0)
+            y4, yh, yl = B.split_bf16x2(yall, 1)
+            row_lse, cmax, csum, diag = B.sim_fwd(x4, y4, None, None, None, scale32, scale_kind,
+                                                  clamp_max, B.SIM_PLAIN, rank * n, True, impl,
+                                                  bound)
+            ctx.split = (x4, y4, xh, xl, yh, yl)
+        elif keep:  # E = exp(z - shift) of the local [n, N] block is kept for the backward
             row_lse, cmax, csum, diag, e_keep, e_flag = B.sim_fwd_keep(
                 xhat, yall, scale32, scale_kind, clamp_max, rank * n, True, impl, bound)
         else:
@@ -319,7 +332,14 @@ class _ShardedClipFn(torch.autograd.Function):
         global LAST_BACKWARD_PATH
         LAST_BACKWARD_PATH = ("fused gemm+reduce-scatter (NVLink peer memory)" if symm is not None
                               else "nccl reduce-scatter")
-        if symm is not None:
+        if ctx.split is not None:
+            x4, y4, xh, xl, yh, yl = ctx.split
+            da, db, dscale = B.sim_bwd_split(x4, y4, xh, xl, yh, yl, scale32, scale_kind,
+                                             clamp_max, rank * n, row_lse, col_lse.reshape(1, N),
+                                             *weights, g, True, True, bound)
+            dy_local = _reduce_scatter_sum(db[0], group).unsqueeze(0)
+            LAST_BACKWARD_PATH = "fp32 split kernels + nccl reduce-scatter"
+        elif symm is not None:
             # GEMM -> reduce-scatter in ONE kernel: the dB tiles are added straight into the
             # owner rank's buffer over NVLink peer memory (no NCCL reduce-scatter, no [N, d]
             # fp32 partial in HBM)

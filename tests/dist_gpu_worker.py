@@ -20,6 +20,7 @@ def main():
     from oracle import losses_oracle as O
     ok = True
     for dtype, n, d, tl, tg in ((torch.float32, 96, 64, 1e-5, 1e-4),
+                                (torch.float32, 256, 256, 1e-5, 1e-4),   # split tensor-core path
                                 (torch.bfloat16, 512, 512, 2e-3, 2e-2)):
         N = n * world
         x, y = O.synth_embeddings(N, d, 11, correlated=True, dtype=dtype)
