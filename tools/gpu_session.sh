@@ -33,6 +33,7 @@ for step in "$@"; do
                  -k regex:"sim_rank_tc|topk_slice|topk_merge|sim_fwd_tc_kernel|sim_grad_tc_kernel|gemm_grouped|sim_mod_tc" -s 16 -c 14 -o "gpurun_out/${TAG}_new_prof" \
                  python tools/profile_new_kernels.py > "gpurun_out/${TAG}_ncu_new.log" 2>&1
                echo "ncunew rc=$?" | tee -a "gpurun_out/${TAG}_summary.txt" ;;
+    smoke)     run smoke 600 python __graft_entry__.py smoke ;;
     refarm)    run refarm 900 python bench.py --impl reference --steps 3 --warmup 1 ;;
     diag)      run diag 600 python tools/diag_te.py ;;
     diag0)     run diag0 600 env MM25_TE=0 python tools/diag_te.py ;;
