@@ -34,6 +34,11 @@ for step in "$@"; do
                  python tools/profile_new_kernels.py > "gpurun_out/${TAG}_ncu_new.log" 2>&1
                echo "ncunew rc=$?" | tee -a "gpurun_out/${TAG}_summary.txt" ;;
     smoke)     run smoke 600 python __graft_entry__.py smoke ;;
+    ncurank)   python tools/profile_new_kernels.py > "gpurun_out/${TAG}_rank_plain.log" 2>&1 && \
+               timeout 900 ncu --set full --clock-control none --import-source on \
+                 -k regex:"sim_rank_tc|topk_slice|topk_merge" -s 4 -c 4 -o "gpurun_out/${TAG}_rank_prof" \
+                 python tools/profile_new_kernels.py > "gpurun_out/${TAG}_ncu_rank.log" 2>&1
+               echo "ncurank rc=$?" | tee -a "gpurun_out/${TAG}_summary.txt" ;;
     refarm)    run refarm 900 python bench.py --impl reference --steps 3 --warmup 1 ;;
     diag)      run diag 600 python tools/diag_te.py ;;
     diag0)     run diag0 600 env MM25_TE=0 python tools/diag_te.py ;;
