@@ -693,6 +693,10 @@ def roofline_object(args, r, peaks):
 def main():
     args = parse_args()
     if args.impl == "reference":
+        # under torchrun only rank 0 measures; the other ranks leave before importing torch so
+        # that their start-up does not compete with the timed CPU run for the host cores
+        if int(os.environ.get("RANK", "0")) != 0:
+            return
         run_reference(args)
         return
     peaks = load_peaks()
