@@ -354,24 +354,24 @@ __global__ void __launch_bounds__(256) smooth_term_kernel(
 //        + (0.5 / N) sum_j col_lse[j]                   (fp64, fixed-order tree: same bits on
 //                                                        every rank)
 //        - coef * s * (sum_p sx_p) . (sum_p sy_p)       (label smoothing; skipped when d == 0)
-__global__ void __launch_bounds__(256) sharded_loss_kernel(
+__global__ void __launch_bounds__(1024) sharded_loss_kernel(
     const float* __restrict__ payload, int64_t P, int64_t ld, int64_t orow,
     const float* __restrict__ col_lse, int64_t N, int64_t ox, int64_t oy, int d,
     const float* __restrict__ scale, int scale_kind, float clamp_max, float coef,
     float* __restrict__ loss) {
-  __shared__ double red[256];
+  __shared__ double red[1024];
   double acc = 0.0;
-  for (int64_t j = threadIdx.x; j < N; j += 256) acc += (double)col_lse[j];
+  for (int64_t j = threadIdx.x; j < N; j += 1024) acc += (double)col_lse[j];
   red[threadIdx.x] = acc;
   __syncthreads();
-  for (int w = 128; w > 0; w >>= 1) {
+  for (int w = 512; w > 0; w >>= 1) {
     if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
     __syncthreads();
   }
   const double colsum = red[0];
   __syncthreads();
   acc = 0.0;
-  for (int k = threadIdx.x; k < d; k += 256) {
+  for (int k = threadIdx.x; k < d; k += 1024) {
     float sx = 0.f, sy = 0.f;
     for (int64_t p = 0; p < P; ++p) {
       sx += payload[p * ld + ox + k];
@@ -381,7 +381,7 @@ __global__ void __launch_bounds__(256) sharded_loss_kernel(
   }
   red[threadIdx.x] = acc;
   __syncthreads();
-  for (int w = 128; w > 0; w >>= 1) {
+  for (int w = 512; w > 0; w >>= 1) {
     if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
     __syncthreads();
   }
@@ -753,7 +753,7 @@ extern "C" int mm25_sharded_loss(const float* payload, int64_t P, int64_t ld, in
   if (!payload || !col_lse || !scale || !loss || P <= 0 || N <= 0 || orow < 0 || orow >= ld)
     return MM25_ERR_ARG;
   if (d < 0 || (d > 0 && (ox + d > ld || oy + d > ld))) return MM25_ERR_ARG;
-  sharded_loss_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(payload, P, ld, orow, col_lse, N, ox,
+  sharded_loss_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(payload, P, ld, orow, col_lse, N, ox,
                                                            oy, (int)d, scale, scale_kind,
                                                            clamp_max, coef, loss);
   MM25_LAUNCH_CHECK();
