@@ -9,6 +9,8 @@
 // tie-free rows).  NaN ranks above +inf as in torch.  Integer work: bit-exact.
 #include "common.cuh"
 
+#include <cstdlib>
+
 namespace mm25 {
 
 constexpr int TK_THREADS = 1024;
@@ -27,7 +29,10 @@ __device__ __forceinline__ float key_value(uint32_t k) {
 
 __global__ void __launch_bounds__(TK_THREADS)
 topk_rows_kernel(const float* __restrict__ scores, int64_t N, int64_t ld, int k,
-                 int64_t* __restrict__ out_idx, float* __restrict__ out_val) {
+                 int64_t* __restrict__ out_idx, float* __restrict__ out_val,
+                 const int* __restrict__ only_if = nullptr) {
+  // only_if: per-row flags of the compaction kernel below — rows it finished are skipped
+  if (only_if && only_if[blockIdx.x] == 0) return;
   __shared__ unsigned int hist[256];
   __shared__ unsigned long long cand[TK_MAXK];
   __shared__ unsigned int warp_cnt[TK_THREADS / 32];
@@ -319,6 +324,222 @@ topk_merge_kernel(const unsigned long long* __restrict__ ws, int total, int k,
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Many long rows (Q >= 2 SMs-worth, N > one slice): one CTA per row, two passes over the row
+// instead of five.  Pass 1 histograms the top 12 key bits (sign, exponent, 3 mantissa bits:
+// 4096 bins); a parallel suffix scan finds the bin b0 holding the k-th largest key.  Pass 2
+// (L2-resident for rows up to a few MB) sends every key above b0 straight to the candidates and
+// COMPACTS bin b0, in index order, into shared memory; the remaining 20 key bits are resolved
+// there (radix passes, gather of the lowest-index equals, bitonic sort) exactly as the slice
+// kernel does on its keys.  A bin that does not fit (heavy ties) raises the row's flag in
+// `redo` and the five-pass kernel repeats that row.  Same result, bit for bit.
+// ------------------------------------------------------------------------------------------
+constexpr int TK_BCAP = 8192;   // compacted keys per row held in shared memory
+
+struct BigSmem {
+  uint32_t keys[TK_BCAP];
+  uint32_t idxs[TK_BCAP];
+  unsigned long long cand[TK_MAXK];
+  unsigned int hist[4096];
+  unsigned int wcnt[2][TK_THREADS / 32];
+  unsigned int b0, rem, nb, gt_count, prefix, remaining, eq_base;
+};
+
+__global__ void __launch_bounds__(TK_THREADS, 2)
+topk_rows_compact_kernel(const float* __restrict__ scores, int64_t N, int64_t ld, int k,
+                         int64_t* __restrict__ out_idx, float* __restrict__ out_val,
+                         int* __restrict__ redo) {
+  extern __shared__ __align__(16) uint8_t tk_smem[];
+  BigSmem& sm = *reinterpret_cast<BigSmem*>(tk_smem);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t rowi = blockIdx.x;
+  const float* row = scores + rowi * ld;
+  const bool vec = (reinterpret_cast<uintptr_t>(row) & 15) == 0;
+  const int64_t n4 = vec ? (N >> 2) : 0;
+
+  // ---- pass 1: 4096-bin histogram of the top 12 key bits ---------------------------------
+  for (int i = tid; i < 4096; i += TK_THREADS) sm.hist[i] = 0;
+  __syncthreads();
+  for (int64_t i = tid; i < n4; i += TK_THREADS) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(row) + i);
+    atomicAdd(&sm.hist[order_key(v.x) >> 20], 1u);
+    atomicAdd(&sm.hist[order_key(v.y) >> 20], 1u);
+    atomicAdd(&sm.hist[order_key(v.z) >> 20], 1u);
+    atomicAdd(&sm.hist[order_key(v.w) >> 20], 1u);
+  }
+  for (int64_t i = 4 * n4 + tid; i < N; i += TK_THREADS)
+    atomicAdd(&sm.hist[order_key(row[i]) >> 20], 1u);
+  __syncthreads();
+  // suffix scan from the top: thread t owns bins 4095 - 4t .. 4092 - 4t
+  {
+    unsigned c[4], tot = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { c[j] = sm.hist[4095 - 4 * tid - j]; tot += c[j]; }
+    unsigned incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += up;
+    }
+    if (lane == 31) sm.wcnt[0][warp] = incl;
+    __syncthreads();
+    unsigned base = 0;
+    for (int w8 = 0; w8 < warp; ++w8) base += sm.wcnt[0][w8];
+    unsigned run = base + incl - tot;      // keys strictly above this thread's first bin
+    const unsigned kk = (unsigned)k;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (run < kk && run + c[j] >= kk) {  // the k-th largest key lies in this bin
+        sm.b0 = (unsigned)(4095 - 4 * tid - j);
+        sm.rem = kk - run;                 // how many keys of the bin belong to the top-k
+        sm.nb = c[j];
+      }
+      run += c[j];
+    }
+    if (tid == 0) { sm.gt_count = 0; }
+    __syncthreads();
+  }
+  const unsigned b0 = sm.b0, nb = sm.nb;
+  if (nb > (unsigned)TK_BCAP) {            // heavy ties: the five-pass kernel repeats this row
+    if (tid == 0) redo[rowi] = 1;
+    return;
+  }
+  if (tid == 0) redo[rowi] = 0;
+
+  // ---- pass 2: keys above b0 -> candidates; bin b0 -> shared memory, in index order --------
+  unsigned listn = 0;   // every thread tracks the running length itself (same value everywhere)
+  int buf = 0;
+  for (int64_t i0 = 0; i0 < N; i0 += TK_THREADS) {
+    const int64_t i = i0 + tid;
+    uint32_t key = 0;
+    bool in_bin = false;
+    if (i < N) {
+      key = order_key(row[i]);
+      const uint32_t bin = key >> 20;
+      if (bin > b0)
+        sm.cand[atomicAdd(&sm.gt_count, 1u)] =
+            ((unsigned long long)key << 32) | (unsigned long long)(0xFFFFFFFFu - (uint32_t)i);
+      in_bin = bin == b0;
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, in_bin);
+    if (lane == 0) sm.wcnt[buf][warp] = __popc(bal);
+    __syncthreads();
+    unsigned before = 0, total = 0;
+#pragma unroll
+    for (int w8 = 0; w8 < TK_THREADS / 32; ++w8) {
+      const unsigned c = sm.wcnt[buf][w8];
+      before += w8 < warp ? c : 0u;
+      total += c;
+    }
+    if (in_bin) {
+      const unsigned pos = listn + before + __popc(bal & ((1u << lane) - 1u));
+      sm.keys[pos] = key;
+      sm.idxs[pos] = (uint32_t)i;
+    }
+    listn += total;
+    buf ^= 1;   // the next iteration writes the other counter array: one barrier per iteration
+  }
+  __syncthreads();
+  const int n = (int)listn;                // == nb
+  const unsigned n_above = (unsigned)k - sm.rem;
+  if (tid == 0) { sm.prefix = b0 << 20; sm.remaining = sm.rem; }
+  __syncthreads();
+
+  // ---- radix select of the rem-th largest key of the list on the low 20 bits ---------------
+  for (int pass = 0; pass < 3; ++pass) {
+    const int shift = pass == 0 ? 12 : (pass == 1 ? 4 : 0);
+    const int bits = pass == 2 ? 4 : 8;
+    const uint32_t mask_hi = 0xFFFFFFFFu << (shift + bits);
+    for (int i = tid; i < 256; i += TK_THREADS) sm.hist[i] = 0;
+    __syncthreads();
+    const uint32_t prefix = sm.prefix;
+    for (int i = tid; i < n; i += TK_THREADS) {
+      const uint32_t key = sm.keys[i];
+      if ((key & mask_hi) == (prefix & mask_hi))
+        atomicAdd(&sm.hist[(key >> shift) & ((1u << bits) - 1u)], 1u);
+    }
+    __syncthreads();
+    if (warp == 0) {
+      // warp-parallel walk from the top bin: lane l owns m consecutive bins
+      const int nbins = 1 << bits, m = nbins >= 32 ? nbins / 32 : 1;
+      const unsigned rem = sm.remaining;
+      unsigned c[8], tot = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int b = nbins - 1 - lane * m - j;
+        c[j] = (j < m && b >= 0) ? sm.hist[b] : 0u;
+        tot += c[j];
+      }
+      unsigned incl = tot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+      }
+      unsigned run = incl - tot;
+      const unsigned all = __shfl_sync(0xffffffffu, incl, 31);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int b = nbins - 1 - lane * m - j;
+        if (j < m && b >= 0) {
+          // bin 0 takes whatever is left, as the serial walk did
+          if ((run < rem && run + c[j] >= rem) || (b == 0 && all < rem)) {
+            sm.prefix = prefix | ((uint32_t)b << shift);
+            sm.remaining = rem - run;
+          }
+          run += c[j];
+        }
+      }
+    }
+    __syncthreads();
+  }
+  const uint32_t T = sm.prefix;
+  const unsigned need_eq = sm.remaining;
+  if (tid == 0) sm.eq_base = 0;
+  __syncthreads();
+  // ---- gather from the list: keys > T, then the first need_eq keys == T in list (= index) order
+  const unsigned n_gt_list = sm.rem - need_eq;      // keys of the bin strictly above T
+  unsigned eqn = 0;
+  for (int i0 = 0; i0 < n; i0 += TK_THREADS) {
+    const int i = i0 + tid;
+    uint32_t key = 0, idx = 0;
+    bool gt = false, eq = false;
+    if (i < n) { key = sm.keys[i]; idx = sm.idxs[i]; gt = key > T; eq = key == T; }
+    const unsigned long long comp =
+        ((unsigned long long)key << 32) | (unsigned long long)(0xFFFFFFFFu - idx);
+    if (gt) sm.cand[atomicAdd(&sm.gt_count, 1u)] = comp;
+    const unsigned bal = __ballot_sync(0xffffffffu, eq);
+    if (lane == 0) sm.wcnt[buf][warp] = __popc(bal);
+    __syncthreads();
+    unsigned before = 0, total = 0;
+#pragma unroll
+    for (int w8 = 0; w8 < TK_THREADS / 32; ++w8) {
+      const unsigned c = sm.wcnt[buf][w8];
+      before += w8 < warp ? c : 0u;
+      total += c;
+    }
+    if (eq) {
+      const unsigned pos = eqn + before + __popc(bal & ((1u << lane) - 1u));
+      if (pos < need_eq) sm.cand[n_above + n_gt_list + pos] = comp;
+    }
+    eqn += total;
+    buf ^= 1;
+  }
+  __syncthreads();
+
+  // ---- sort the k candidates, descending on (key, ~index) ----------------------------------
+  int P = 1;
+  while (P < k) P <<= 1;
+  for (int i = k + tid; i < P; i += TK_THREADS) sm.cand[i] = 0ull;
+  __syncthreads();
+  bitonic_desc(sm.cand, P, tid);
+  for (int j = tid; j < k; j += TK_THREADS) {
+    const uint32_t idx = 0xFFFFFFFFu - (uint32_t)(sm.cand[j] & 0xFFFFFFFFull);
+    out_idx[rowi * k + j] = (int64_t)idx;
+    if (out_val) out_val[rowi * k + j] = row[idx];
+  }
+}
+
 // slices per row for the sliced path; 0 = not applicable (the one-CTA-per-row kernel runs)
 static int topk_slices(int64_t Q, int64_t N, int64_t k) {
   if (Q > 65535) return 0;
@@ -351,6 +572,7 @@ extern "C" int mm25_topk_rows(const float* scores, int64_t Q, int64_t N, int64_t
 extern "C" size_t mm25_topk_workspace_bytes(int64_t Q, int64_t N, int64_t k) {
   if (Q <= 0 || N <= 0 || k <= 0 || k > mm25::TK_MAXK) return 0;
   const int C = mm25::topk_slices(Q, N, k);
+  if (C == 0) return Q <= 65535ll * 32768 ? sizeof(int) * (size_t)Q : 0;  // per-row redo flags
   return C > 1 ? sizeof(unsigned long long) * (size_t)Q * C * k : 0;
 }
 
@@ -362,10 +584,26 @@ extern "C" int mm25_topk_rows_ws(const float* scores, int64_t Q, int64_t N, int6
     return MM25_ERR_SHAPE;
   if (!scores || !out_idx) return MM25_ERR_ARG;
   const int C = mm25::topk_slices(Q, N, k);
-  if (C == 0) return mm25_topk_rows(scores, Q, N, ld, k, out_idx, out_val, stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (C == 0) {
+    // many long rows: two-pass compaction kernel, five-pass kernel for the rows it hands back
+    static const bool plain_env = getenv("MM25_TOPK_NO_COMPACT") != nullptr;
+    if (plain_env || !workspace || workspace_bytes < sizeof(int) * (size_t)Q || Q >= (1ll << 31))
+      return mm25_topk_rows(scores, Q, N, ld, k, out_idx, out_val, stream);
+    int* redo = (int*)workspace;
+    const size_t bsm = sizeof(mm25::BigSmem);
+    MM25_CUDA_CHECK(cudaFuncSetAttribute(mm25::topk_rows_compact_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsm));
+    mm25::topk_rows_compact_kernel<<<(unsigned)Q, mm25::TK_THREADS, bsm, st>>>(
+        scores, N, ld, (int)k, out_idx, out_val, redo);
+    MM25_LAUNCH_CHECK();
+    mm25::topk_rows_kernel<<<(unsigned)Q, mm25::TK_THREADS, 0, st>>>(scores, N, ld, (int)k,
+                                                                      out_idx, out_val, redo);
+    MM25_LAUNCH_CHECK();
+    return MM25_OK;
+  }
   if (C > 1 && (!workspace || workspace_bytes < mm25_topk_workspace_bytes(Q, N, k)))
     return MM25_ERR_WORKSPACE;
-  cudaStream_t st = (cudaStream_t)stream;
   const int64_t slice_len = ((N + C - 1) / C + 3) & ~int64_t(3);  // keeps 16-byte alignment
   const int Cn = (int)((N + slice_len - 1) / slice_len);
   const size_t smem = sizeof(mm25::SliceSmem);

@@ -105,3 +105,29 @@ def test_topk_sliced_path_equals_plain_kernel_and_stable_sort(lib_built, monkeyp
     idx_v, _ = ops.topk_rows(v, min(k, N - 1))
     want_v = torch.sort(s[:, 1:], dim=1, descending=True, stable=True).indices[:, :min(k, N - 1)]
     assert torch.equal(idx_v.cpu(), want_v)
+
+
+@pytest.mark.parametrize("Q,N,k", [(300, 40000, 1), (300, 40000, 100), (296, 65536, 2048),
+                                   (310, 20001, 37)])
+def test_topk_compaction_path_many_long_rows(lib_built, monkeypatch, Q, N, k):
+    """round 2: many long rows take the two-pass kernel (12-bit histogram, bin compacted into
+    shared memory); rows whose bin overflows (heavy ties) are repeated by the five-pass kernel.
+    Mixed here: even rows tie-free (compaction), odd rows tie-heavy with signed zeros / inf
+    (hand-back) — all bit-identical to the plain kernel and to the stable descending sort."""
+    from multimodal_2025_b200 import ops
+    g = torch.Generator().manual_seed(N + k)
+    base = torch.linspace(-4.0, 4.0, N)
+    s = torch.stack([base[torch.randperm(N, generator=g)] for _ in range(Q)])
+    t = torch.round(torch.randn(Q, N, generator=g) * 4) / 4
+    t = torch.where(torch.rand(Q, N, generator=g) < 0.2, -t, t)
+    t[:, ::5003] = float("inf")
+    s[1::2] = t[1::2]
+    s[0, :50] = 3.999                      # a run of equal keys inside a compacted bin
+    sc = s.cuda()
+    idx, val = ops.topk_rows(sc, k)
+    monkeypatch.setenv("MM25_TOPK_PLAIN", "1")
+    idx_p, val_p = ops.topk_rows(sc, k)
+    monkeypatch.delenv("MM25_TOPK_PLAIN")
+    assert torch.equal(idx, idx_p) and torch.equal(val, val_p)
+    want = torch.sort(s, dim=1, descending=True, stable=True).indices[:, :k]
+    assert torch.equal(idx.cpu(), want)
