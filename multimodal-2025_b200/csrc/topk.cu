@@ -407,13 +407,18 @@ topk_rows_compact_kernel(const float* __restrict__ scores, int64_t N, int64_t ld
   if (tid == 0) redo[rowi] = 0;
 
   // ---- pass 2: keys above b0 -> candidates; bin b0 -> shared memory, in index order --------
-  unsigned listn = 0;   // every thread tracks the running length itself (same value everywhere)
-  int buf = 0;
-  for (int64_t i0 = 0; i0 < N; i0 += TK_THREADS) {
-    const int64_t i = i0 + tid;
+  // Warp w owns the contiguous elements [w L, (w + 1) L) and appends its bin-b0 keys to its own
+  // region of TK_BCAP / 32 slots with a warp-private counter: no block barrier inside the pass.
+  // Slot order (warp, position) is index order.  A region that overflows hands the row back.
+  constexpr int WCAP = TK_BCAP / (TK_THREADS / 32);   // 256 slots per warp
+  const int64_t L = (N + (TK_THREADS / 32) - 1) / (TK_THREADS / 32);
+  const int64_t w0 = (int64_t)warp * L, w1 = min(N, w0 + L);
+  unsigned wn = 0;   // this warp's count (same value in every lane)
+  for (int64_t i0 = w0; i0 < w1; i0 += 32) {
+    const int64_t i = i0 + lane;
     uint32_t key = 0;
     bool in_bin = false;
-    if (i < N) {
+    if (i < w1) {
       key = order_key(row[i]);
       const uint32_t bin = key >> 20;
       if (bin > b0)
@@ -422,28 +427,29 @@ topk_rows_compact_kernel(const float* __restrict__ scores, int64_t N, int64_t ld
       in_bin = bin == b0;
     }
     const unsigned bal = __ballot_sync(0xffffffffu, in_bin);
-    if (lane == 0) sm.wcnt[buf][warp] = __popc(bal);
-    __syncthreads();
-    unsigned before = 0, total = 0;
-#pragma unroll
-    for (int w8 = 0; w8 < TK_THREADS / 32; ++w8) {
-      const unsigned c = sm.wcnt[buf][w8];
-      before += w8 < warp ? c : 0u;
-      total += c;
-    }
     if (in_bin) {
-      const unsigned pos = listn + before + __popc(bal & ((1u << lane) - 1u));
-      sm.keys[pos] = key;
-      sm.idxs[pos] = (uint32_t)i;
+      const unsigned pos = wn + __popc(bal & ((1u << lane) - 1u));
+      if (pos < (unsigned)WCAP) {
+        sm.keys[warp * WCAP + pos] = key;
+        sm.idxs[warp * WCAP + pos] = (uint32_t)i;
+      }
     }
-    listn += total;
-    buf ^= 1;   // the next iteration writes the other counter array: one barrier per iteration
+    wn += __popc(bal);
   }
+  if (lane == 0) sm.wcnt[0][warp] = wn;
   __syncthreads();
-  const int n = (int)listn;                // == nb
+  bool over = false;
+#pragma unroll
+  for (int w8 = 0; w8 < TK_THREADS / 32; ++w8) over |= sm.wcnt[0][w8] > (unsigned)WCAP;
+  if (over) {              // uniform: every thread read the same counters
+    if (tid == 0) redo[rowi] = 1;
+    return;
+  }
   const unsigned n_above = (unsigned)k - sm.rem;
   if (tid == 0) { sm.prefix = b0 << 20; sm.remaining = sm.rem; }
   __syncthreads();
+  // slot s = (warp s / WCAP, position s % WCAP) is live when position < that warp's count
+  auto live = [&](int slot) { return (unsigned)(slot & (WCAP - 1)) < sm.wcnt[0][slot / WCAP]; };
 
   // ---- radix select of the rem-th largest key of the list on the low 20 bits ---------------
   for (int pass = 0; pass < 3; ++pass) {
@@ -453,8 +459,9 @@ topk_rows_compact_kernel(const float* __restrict__ scores, int64_t N, int64_t ld
     for (int i = tid; i < 256; i += TK_THREADS) sm.hist[i] = 0;
     __syncthreads();
     const uint32_t prefix = sm.prefix;
-    for (int i = tid; i < n; i += TK_THREADS) {
-      const uint32_t key = sm.keys[i];
+    for (int slot = tid; slot < TK_BCAP; slot += TK_THREADS) {
+      if (!live(slot)) continue;
+      const uint32_t key = sm.keys[slot];
       if ((key & mask_hi) == (prefix & mask_hi))
         atomicAdd(&sm.hist[(key >> shift) & ((1u << bits) - 1u)], 1u);
     }
@@ -495,26 +502,25 @@ topk_rows_compact_kernel(const float* __restrict__ scores, int64_t N, int64_t ld
   }
   const uint32_t T = sm.prefix;
   const unsigned need_eq = sm.remaining;
-  if (tid == 0) sm.eq_base = 0;
   __syncthreads();
-  // ---- gather from the list: keys > T, then the first need_eq keys == T in list (= index) order
+  // ---- gather from the list: keys > T, then the first need_eq keys == T in slot (= index) order
   const unsigned n_gt_list = sm.rem - need_eq;      // keys of the bin strictly above T
   unsigned eqn = 0;
-  for (int i0 = 0; i0 < n; i0 += TK_THREADS) {
-    const int i = i0 + tid;
+  for (int s0 = 0; s0 < TK_BCAP; s0 += TK_THREADS) {
+    const int slot = s0 + tid;
     uint32_t key = 0, idx = 0;
     bool gt = false, eq = false;
-    if (i < n) { key = sm.keys[i]; idx = sm.idxs[i]; gt = key > T; eq = key == T; }
+    if (live(slot)) { key = sm.keys[slot]; idx = sm.idxs[slot]; gt = key > T; eq = key == T; }
     const unsigned long long comp =
         ((unsigned long long)key << 32) | (unsigned long long)(0xFFFFFFFFu - idx);
     if (gt) sm.cand[atomicAdd(&sm.gt_count, 1u)] = comp;
     const unsigned bal = __ballot_sync(0xffffffffu, eq);
-    if (lane == 0) sm.wcnt[buf][warp] = __popc(bal);
+    if (lane == 0) sm.wcnt[1][warp] = __popc(bal);   // wcnt[1]: wcnt[0] holds the list counts
     __syncthreads();
     unsigned before = 0, total = 0;
 #pragma unroll
     for (int w8 = 0; w8 < TK_THREADS / 32; ++w8) {
-      const unsigned c = sm.wcnt[buf][w8];
+      const unsigned c = sm.wcnt[1][w8];
       before += w8 < warp ? c : 0u;
       total += c;
     }
@@ -523,7 +529,7 @@ topk_rows_compact_kernel(const float* __restrict__ scores, int64_t N, int64_t ld
       if (pos < need_eq) sm.cand[n_above + n_gt_list + pos] = comp;
     }
     eqn += total;
-    buf ^= 1;
+    __syncthreads();       // wcnt[1] is rewritten by the next iteration
   }
   __syncthreads();
 
