@@ -360,12 +360,21 @@ topk_rows_compact_kernel(const float* __restrict__ scores, int64_t N, int64_t ld
   // ---- pass 1: 4096-bin histogram of the top 12 key bits ---------------------------------
   for (int i = tid; i < 4096; i += TK_THREADS) sm.hist[i] = 0;
   __syncthreads();
-  for (int64_t i = tid; i < n4; i += TK_THREADS) {
+  for (int64_t i = tid; i < n4; i += 2 * TK_THREADS) {
+    // two 16-byte loads in flight per thread
     const float4 v = __ldg(reinterpret_cast<const float4*>(row) + i);
+    const bool two = i + TK_THREADS < n4;
+    const float4 u = two ? __ldg(reinterpret_cast<const float4*>(row) + i + TK_THREADS) : v;
     atomicAdd(&sm.hist[order_key(v.x) >> 20], 1u);
     atomicAdd(&sm.hist[order_key(v.y) >> 20], 1u);
     atomicAdd(&sm.hist[order_key(v.z) >> 20], 1u);
     atomicAdd(&sm.hist[order_key(v.w) >> 20], 1u);
+    if (two) {
+      atomicAdd(&sm.hist[order_key(u.x) >> 20], 1u);
+      atomicAdd(&sm.hist[order_key(u.y) >> 20], 1u);
+      atomicAdd(&sm.hist[order_key(u.z) >> 20], 1u);
+      atomicAdd(&sm.hist[order_key(u.w) >> 20], 1u);
+    }
   }
   for (int64_t i = 4 * n4 + tid; i < N; i += TK_THREADS)
     atomicAdd(&sm.hist[order_key(row[i]) >> 20], 1u);
@@ -414,27 +423,38 @@ topk_rows_compact_kernel(const float* __restrict__ scores, int64_t N, int64_t ld
   const int64_t L = (N + (TK_THREADS / 32) - 1) / (TK_THREADS / 32);
   const int64_t w0 = (int64_t)warp * L, w1 = min(N, w0 + L);
   unsigned wn = 0;   // this warp's count (same value in every lane)
-  for (int64_t i0 = w0; i0 < w1; i0 += 32) {
-    const int64_t i = i0 + lane;
-    uint32_t key = 0;
-    bool in_bin = false;
-    if (i < w1) {
-      key = order_key(row[i]);
-      const uint32_t bin = key >> 20;
-      if (bin > b0)
-        sm.cand[atomicAdd(&sm.gt_count, 1u)] =
-            ((unsigned long long)key << 32) | (unsigned long long)(0xFFFFFFFFu - (uint32_t)i);
-      in_bin = bin == b0;
+  for (int64_t i0 = w0; i0 < w1; i0 += 128) {
+    // four independent loads in flight per lane (the pass is L2-latency bound otherwise); the
+    // four 32-element chunks are then appended in order
+    float v[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int64_t i = i0 + 32 * c + lane;
+      v[c] = i < w1 ? __ldg(row + i) : 0.f;
     }
-    const unsigned bal = __ballot_sync(0xffffffffu, in_bin);
-    if (in_bin) {
-      const unsigned pos = wn + __popc(bal & ((1u << lane) - 1u));
-      if (pos < (unsigned)WCAP) {
-        sm.keys[warp * WCAP + pos] = key;
-        sm.idxs[warp * WCAP + pos] = (uint32_t)i;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int64_t i = i0 + 32 * c + lane;
+      uint32_t key = 0;
+      bool in_bin = false;
+      if (i < w1) {
+        key = order_key(v[c]);
+        const uint32_t bin = key >> 20;
+        if (bin > b0)
+          sm.cand[atomicAdd(&sm.gt_count, 1u)] =
+              ((unsigned long long)key << 32) | (unsigned long long)(0xFFFFFFFFu - (uint32_t)i);
+        in_bin = bin == b0;
       }
+      const unsigned bal = __ballot_sync(0xffffffffu, in_bin);
+      if (in_bin) {
+        const unsigned pos = wn + __popc(bal & ((1u << lane) - 1u));
+        if (pos < (unsigned)WCAP) {
+          sm.keys[warp * WCAP + pos] = key;
+          sm.idxs[warp * WCAP + pos] = (uint32_t)i;
+        }
+      }
+      wn += __popc(bal);
     }
-    wn += __popc(bal);
   }
   if (lane == 0) sm.wcnt[0][warp] = wn;
   __syncthreads();
