@@ -444,9 +444,20 @@ class _ShardedModCEFn(torch.autograd.Function):
         f = f.contiguous()
         n = f.shape[0]
         N = n * world
-        fall = _all_gather_cat(f, group).unsqueeze(0)
+        # both gathers go through NVLink peer memory when it is available (one store kernel +
+        # one barrier each, as in _ShardedClipFn); NCCL all-gather otherwise
         u = sem_hat.detach().float().contiguous()
-        uall = _all_gather_cat(u, group).unsqueeze(0)
+        pf = _peer_all_gather(B, f, "mod_f", group, barrier=False)
+        pu = _peer_all_gather(B, u, "mod_u", group) if pf is not None else None
+        if pf is not None and pu is not None:
+            fall, uall = pf[0].unsqueeze(0), pu[0].unsqueeze(0)
+            ctx.gens = ((pf[1], _SYMM_GEN[pf[1]]), (pu[1], _SYMM_GEN[pu[1]]))
+        else:
+            if pf is not None:   # the first gather was issued without its barrier: complete it
+                dist.barrier(group=group)
+            fall = _all_gather_cat(f, group).unsqueeze(0)
+            uall = _all_gather_cat(u, group).unsqueeze(0)
+            ctx.gens = None
         D = paired.detach().float().contiguous().reshape(1, n)
         sc = logit_scale.detach().reshape(1).float().contiguous()
         row_lse, _, _, diag = B.sim_fwd(f.unsqueeze(0), fall, u.unsqueeze(0), uall, D, sc,
@@ -454,8 +465,7 @@ class _ShardedModCEFn(torch.autograd.Function):
         # (1/N) sum_i (r_i - z_ii) over the local rows, then one scalar all-reduce
         part = B.clip_loss_finalize(row_lse * 2.0, diag, None, None, None, N, sc, B.SCALE_MUL,
                                     0.0, 0.0)
-        red = part.reshape(1).clone()
-        dist.all_reduce(red, group=group)
+        red = _all_reduce_scalar(B, part.reshape(1).clone(), "mod_loss", group)
         ctx.save_for_backward(f, fall, u, uall, D, sc, row_lse, logit_scale)
         ctx.cfg = (group, B, grad_scale, impl, in_dtype, rank, n, N)
         return red.reshape(())
@@ -464,6 +474,10 @@ class _ShardedModCEFn(torch.autograd.Function):
     def backward(ctx, gout):
         f, fall, u, uall, D, sc, row_lse, logit_scale = ctx.saved_tensors
         group, B, grad_scale, impl, in_dtype, rank, n, N = ctx.cfg
+        if ctx.gens is not None and any(_SYMM_GEN.get(k) != gen for k, gen in ctx.gens):
+            # another forward reused the symmetric gather buffers since: gather again
+            fall = _all_gather_cat(f, group).unsqueeze(0)
+            uall = _all_gather_cat(u, group).unsqueeze(0)
         g = (gout.detach().float().reshape(1) * grad_scale).contiguous()
         nn_ = float(N)
         da, db, dscale, ddiag = B.sim_bwd(f.unsqueeze(0), fall, u.unsqueeze(0), uall, D, sc,
