@@ -64,8 +64,11 @@ def parse_args():
                         "operands in bf16 (labelled reduced precision)")
     p.add_argument("--vdist", default="power_spherical",
                    choices=["power_spherical", "vmf", "projected_normal"])
-    p.add_argument("--n", type=int, default=0, help="override the batch (pairs)")
-    p.add_argument("--d", type=int, default=0)
+    # --batch / --dim: `--n`, `--d` are kept for plain runs, but torchrun's own parser rejects them
+    # as ambiguous abbreviations of its options
+    p.add_argument("--n", "--batch", dest="n", type=int, default=0,
+                   help="override the batch (pairs)")
+    p.add_argument("--d", "--dim", dest="d", type=int, default=0)
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="eager launches instead of a CUDA graph")
     p.add_argument("--serial-e2e", action="store_true",
