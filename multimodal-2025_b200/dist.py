@@ -426,6 +426,76 @@ def _sharded_ce_pair(a, b, logit_scale, group, backend, grad_scale, impl):
                                 float(grad_scale), int(impl), backend.SCALE_MUL)
 
 
+class _ShardedLocalCEFn(torch.autograd.Function):
+    """open_clip `local_loss=True` (loss.py:108-110, 94-95): rank r's OWN loss
+        0.5 [CE(s X_r Y_all^T, labels + r n) + CE(s Y_r X_all^T, labels + r n)]
+    from two rectangular [n, N] sweeps (row statistics only, positives at column offset r n).
+    `gather_with_grad=True`: the gathered operands carry gradient, i.e. the partial dX_all /
+    dY_all of every rank's loss are summed into their owners (reduce-scatter), as
+    torch.distributed.nn.all_gather back-propagates; False: only the row operands do."""
+
+    @staticmethod
+    def forward(ctx, img, txt, logit_scale, group, backend, gather_with_grad, impl):
+        B = backend
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        in_dtype = img.dtype
+        x, y = img.detach(), txt.detach()
+        if x.dtype not in (torch.float32, torch.bfloat16):
+            x, y = x.float(), y.float()
+        if y.dtype != x.dtype:
+            y = y.to(x.dtype)
+        x, y = x.contiguous(), y.contiguous()
+        n = x.shape[0]
+        xall = _all_gather_cat(x, group).unsqueeze(0)
+        yall = _all_gather_cat(y, group).unsqueeze(0)
+        sc = logit_scale.detach().reshape(1).float().contiguous()
+        x3, y3 = x.unsqueeze(0), y.unsqueeze(0)
+        r1, _, _, d1 = B.sim_fwd(x3, yall, None, None, None, sc, B.SCALE_MUL, 0.0, B.SIM_PLAIN,
+                                 rank * n, False, impl)
+        r2, _, _, d2 = B.sim_fwd(y3, xall, None, None, None, sc, B.SCALE_MUL, 0.0, B.SIM_PLAIN,
+                                 rank * n, False, impl)
+        # mean_i (r_i - z_ii) per direction: the CLIP finalize with weights 1/(2n) on 2 r_i
+        l1 = B.clip_loss_finalize(r1 * 2.0, d1, None, None, None, n, sc, B.SCALE_MUL, 0.0, 0.0)
+        l2 = B.clip_loss_finalize(r2 * 2.0, d2, None, None, None, n, sc, B.SCALE_MUL, 0.0, 0.0)
+        ctx.save_for_backward(x3, y3, xall, yall, sc, r1, r2, logit_scale)
+        ctx.cfg = (group, B, bool(gather_with_grad), impl, in_dtype, rank, n)
+        return (0.5 * (l1 + l2)).reshape(())
+
+    @staticmethod
+    def backward(ctx, gout):
+        x3, y3, xall, yall, sc, r1, r2, logit_scale = ctx.saved_tensors
+        group, B, gwg, impl, in_dtype, rank, n = ctx.cfg
+        g = (gout.detach().float().reshape(1) * 0.5).contiguous()
+        w = 1.0 / float(n)
+        dx1, dyall, ds1, _ = B.sim_bwd(x3, yall, None, None, None, sc, B.SCALE_MUL, 0.0,
+                                       B.SIM_PLAIN, rank * n, r1, None, w, 0.0, w, 0.0, g, True,
+                                       gwg, False, impl)
+        dy2, dxall, ds2, _ = B.sim_bwd(y3, xall, None, None, None, sc, B.SCALE_MUL, 0.0,
+                                       B.SIM_PLAIN, rank * n, r2, None, w, 0.0, w, 0.0, g, True,
+                                       gwg, False, impl)
+        dx, dy = dx1[0], dy2[0]
+        if gwg:
+            dx = dx + _reduce_scatter_sum(dxall[0], group)
+            dy = dy + _reduce_scatter_sum(dyall[0], group)
+        dls = None
+        if ctx.needs_input_grad[2]:
+            dls = B.scale_param_grad(ds1 + ds2, logit_scale, B.SCALE_MUL, 0.0)
+        return (dx.to(in_dtype) if ctx.needs_input_grad[0] else None,
+                dy.to(in_dtype) if ctx.needs_input_grad[1] else None, dls, None, None, None, None)
+
+
+def sharded_local_clip_loss(image_local, text_local, logit_scale, group=None, backend=None,
+                            gather_with_grad=False, impl=0):
+    """open_clip `ClipLoss(local_loss=True, ...)` on this rank's shard (see _ShardedLocalCEFn)."""
+    if backend is None:
+        from . import ops as backend
+    group = group if group is not None else dist.group.WORLD
+    if not torch.is_tensor(logit_scale):
+        logit_scale = torch.tensor(float(logit_scale), device=image_local.device)
+    return _ShardedLocalCEFn.apply(image_local, text_local, logit_scale, group, backend,
+                                   bool(gather_with_grad), int(impl))
+
+
 class _ShardedModCEFn(torch.autograd.Function):
     """mean over the GLOBAL rows of LSE_j z_ij - z_ii with
     z = s [(F F^T) o (1 - S S^T) + diag(D)] (loss.py:229-242): rank r holds rows

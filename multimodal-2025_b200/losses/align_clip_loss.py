@@ -81,17 +81,17 @@ def _sharded_args(mod):
     gradient (loss.py:55-58) -> d(global loss)/d(local shard), `grad_scale = 1`;
     `gather_with_grad=True` back-propagates through `torch.distributed.nn.all_gather`, which
     SUMS the P identical per-rank losses' gradients -> `grad_scale = world_size` (the open_clip
-    convention; DDP's gradient averaging then undoes the factor).  `local_loss=True` (per-rank
-    loss of the local rows) and Horovod are not built: they raise instead of silently returning
-    a different loss."""
+    convention; DDP's gradient averaging then undoes the factor).  `local_loss=True` (each rank's
+    own loss over its local rows, loss.py:108-110) is built for `ClipLoss`
+    (dist.sharded_local_clip_loss) and raises for `ClipInModalityLoss`; Horovod raises."""
     import torch.distributed as dist
     if mod.use_horovod:
         raise NotImplementedError("use_horovod=True: Horovod collectives are out of scope "
                                   "(torch.distributed only)")
-    if mod.local_loss:
+    if mod.local_loss and not getattr(mod, "_local_loss_ok", False):
         raise NotImplementedError(
-            "local_loss=True (per-rank loss over the local rows, loss.py:108-110) is not "
-            "implemented by the sharded kernels; use local_loss=False (global loss, identical "
+            "local_loss=True (per-rank loss over the local rows, loss.py:191-200) is not "
+            "implemented for ClipInModalityLoss; use local_loss=False (global loss, identical "
             "on every rank)")
     group = getattr(mod, "group", None)
     if not dist.is_available() or not dist.is_initialized():
@@ -125,8 +125,13 @@ class ClipLoss(nn.Module):
         if self.world_size > 1:
             # global-batch loss from the local shards (local_loss=False, loss.py:103-114);
             # gradient convention per gather_with_grad, see _sharded_args
-            from ..dist import ShardedAlignClipLoss
+            from ..dist import ShardedAlignClipLoss, sharded_local_clip_loss
+            self._local_loss_ok = True
             group, grad_scale = _sharded_args(self)
+            if self.local_loss:   # this rank's own loss over its local rows (loss.py:108-110)
+                loss = sharded_local_clip_loss(image_features, text_features, logit_scale,
+                                               group, self._backend, self.gather_with_grad)
+                return {"contrastive_loss": loss} if output_dict else loss
             crit = ShardedAlignClipLoss(group, grad_scale, self._backend)
             return crit(image_features, text_features, logit_scale, output_dict=output_dict)
         logit_scale = _as_scale(logit_scale, image_features)

@@ -148,6 +148,32 @@ def main():
         print("rank %d cloob %s N=%d loss_rel=%.2e gx=%.2e gy=%.2e %s" %
               (rank, dtype, N, el, egx, egy, "OK" if good else "FAIL"), flush=True)
         ok = ok and good
+    # open_clip ClipLoss(local_loss=True): this rank's own loss over its rows (loss.py:108-110)
+    import torch.nn.functional as F
+    from multimodal_2025_b200.losses.align_clip_loss import ClipLoss as OpenClipLoss
+    for dtype, n, d, tl, tg in ((torch.float32, 96, 64, 1e-5, 1e-4),
+                                (torch.bfloat16, 256, 256, 2e-3, 2e-2)):
+        N = n * world
+        x, y = O.synth_embeddings(N, d, 31, correlated=True, dtype=dtype)
+        sl = slice(rank * n, (rank + 1) * n)
+        a = x[sl].float().clone().requires_grad_(True)
+        b = y[sl].float().clone().requires_grad_(True)
+        lab = torch.arange(n) + n * rank
+        ref = (F.cross_entropy(14.285 * a @ y.float().t(), lab) +
+               F.cross_entropy(14.285 * b @ x.float().t(), lab)) / 2
+        ref.backward()
+        xl = x[sl].to(dev).requires_grad_(True)
+        yl = y[sl].to(dev).requires_grad_(True)
+        loss = OpenClipLoss(local_loss=True, rank=rank, world_size=world)(xl, yl, 14.285)
+        loss.backward()
+        torch.cuda.synchronize()
+        el = abs(float(loss) - float(ref)) / abs(float(ref))
+        egx = float((xl.grad.float().cpu() - a.grad).norm() / a.grad.norm())
+        egy = float((yl.grad.float().cpu() - b.grad).norm() / b.grad.norm())
+        good = el < tl and egx < tg and egy < tg
+        print("rank %d local_loss %s N=%d loss_rel=%.2e gx=%.2e gy=%.2e %s" %
+              (rank, dtype, N, el, egx, egy, "OK" if good else "FAIL"), flush=True)
+        ok = ok and good
     # full-size check of the fused GEMM -> reduce-scatter: N = 32768, d = 512, bf16;
     # loss, dX, dY, d/dscale of the sharded module against the single-GPU module on the same
     # batch (same kernels, different tiling / summation order), run twice: the fp32 adds into

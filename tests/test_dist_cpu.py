@@ -459,8 +459,32 @@ def _worker_flags(rank, world, port, q, n, d):
             loss = crit(xo, yo, 14.285)
             loss.backward()
             out[gwg] = (ref.detach(), x.grad, y.grad, loss.detach(), xo.grad, yo.grad)
+        # local_loss=True: each rank's own loss (loss.py:108-110, labels + n * rank :94-95)
+        for gwg in (False, True):
+            x = X[sl].clone().requires_grad_(True)
+            y = Y[sl].clone().requires_grad_(True)
+            if gwg:
+                ax = torch.cat(ag_with_grad(x), dim=0)
+                ay = torch.cat(ag_with_grad(y), dim=0)
+            else:
+                gx = [torch.zeros_like(x) for _ in range(world)]
+                gy = [torch.zeros_like(y) for _ in range(world)]
+                dist.all_gather(gx, x.detach())
+                dist.all_gather(gy, y.detach())
+                ax, ay = torch.cat(gx), torch.cat(gy)
+            lab = torch.arange(n) + n * rank
+            ref = (F.cross_entropy(14.285 * x @ ay.t(), lab) +
+                   F.cross_entropy(14.285 * y @ ax.t(), lab)) / 2
+            (ref * (1.0 + rank)).backward()     # a different upstream gradient on every rank
+            crit = ClipLoss(local_loss=True, gather_with_grad=gwg, rank=rank, world_size=world)
+            crit._backend = cpu_backend
+            xo = X[sl].clone().requires_grad_(True)
+            yo = Y[sl].clone().requires_grad_(True)
+            loss = crit(xo, yo, 14.285)
+            (loss * (1.0 + rank)).backward()
+            out[("local", gwg)] = (ref.detach(), x.grad, y.grad, loss.detach(), xo.grad, yo.grad)
         errs = []
-        for kw in (dict(local_loss=True), dict(use_horovod=True)):
+        for kw in (dict(use_horovod=True),):
             try:
                 c = ClipLoss(rank=rank, world_size=world, **kw)
                 c._backend = cpu_backend
@@ -473,6 +497,13 @@ def _worker_flags(rank, world, port, q, n, d):
             errs.append(None)
         except ValueError as e:
             errs.append(str(e))
+        try:
+            from multimodal_2025_b200.losses.align_clip_loss import ClipInModalityLoss
+            c = ClipInModalityLoss(local_loss=True, rank=rank, world_size=world)
+            c(X[sl], Y[sl], 14.285)
+            errs.append(None)
+        except NotImplementedError as e:
+            errs.append(str(e))
         q.put(_np((rank, out, errs)))
     finally:
         dist.destroy_process_group()
@@ -480,8 +511,9 @@ def _worker_flags(rank, world, port, q, n, d):
 
 def test_dropin_cliploss_distributed_flags_world2_gloo():
     """the drop-in open_clip ClipLoss maps gather_with_grad onto the gradient
-    convention of the reference (own-slot gradient vs sum over ranks), and refuses local_loss /
-    horovod / a rank that does not match the group instead of silently ignoring them."""
+    convention of the reference (own-slot gradient vs sum over ranks), computes the per-rank
+    loss for local_loss=True (both gradient conventions, distinct upstream gradients), and
+    refuses horovod / a rank that does not match the group instead of silently ignoring them."""
     res = _run_world(_worker_flags, 2, (12, 16))
     for rank, out, errs in res:
         for gwg, (ref, rx, ry, loss, gx, gy) in out.items():
