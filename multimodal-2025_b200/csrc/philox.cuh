@@ -40,17 +40,26 @@ __device__ __forceinline__ float u01(uint32_t x) {
   return ((float)(x >> 8) + 1.0f) * (1.0f / 16777216.0f);
 }
 
-// 4 standard normals (Box-Muller) for counter (idx, stream)
+// 4 standard normals (Box-Muller) for counter (idx, stream).  The samplers are bound by integer
+// and special-function work, not by HBM (profiles/r2_paths.jsonl), so the transform is kept to
+// the minimum: uniforms from the mantissa trick (no I2F: conversions share the MUFU pipe),
+// rad = sqrt(-2 ln2 lg2 u1) with lg2.approx / sqrt.approx, and the angle 2 pi u2' with u2' in
+// [1, 2) fed to sin.approx / cos.approx unreduced (one period further along: same values).
 __device__ __forceinline__ void normal4(uint64_t seed, uint64_t idx, uint64_t stream,
                                         float (&z)[4]) {
   uint32_t r[4];
   philox4(seed, idx, stream, r);
 #pragma unroll
   for (int p = 0; p < 2; ++p) {
-    const float u1 = u01(r[2 * p]), u2 = u01(r[2 * p + 1]);
-    const float rad = sqrtf(-2.0f * __logf(u1));
-    float sn, cs;
-    __sincosf(6.283185307179586f * u2, &sn, &cs);
+    // u1 in (0, 1]: 2 - [1, 2); u2' in [1, 2)
+    const float u1 = 2.0f - __uint_as_float(0x3f800000u | (r[2 * p] >> 9));
+    const float t2 = __uint_as_float(0x3f800000u | (r[2 * p + 1] >> 9));
+    float l2, rad, sn, cs;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(u1));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(rad) : "f"(-1.3862943611198906f * l2));
+    const float ang = 6.283185307179586f * t2;
+    asm("sin.approx.ftz.f32 %0, %1;" : "=f"(sn) : "f"(ang));
+    asm("cos.approx.ftz.f32 %0, %1;" : "=f"(cs) : "f"(ang));
     z[2 * p] = rad * cs;
     z[2 * p + 1] = rad * sn;
   }
