@@ -52,6 +52,10 @@ enum {
   MM25_TIMING_SLOTS = 12
 };
 
+/* number of [rows, d] blocks of the concatenated two-term bf16 split operands of the fp32-grade
+ * path (mm25_split_bf16x2): hi.hi + hi.lo + lo.hi; the lo x lo product is dropped */
+#define MM25_SPLIT_K 3
+
 /* logit modes of the fused similarity kernels */
 enum {
   MM25_SIM_PLAIN = 0,    /* z = s * a_i.b_j                       (clipLoss.py:106; loss.py:215) */
@@ -436,18 +440,21 @@ int mm25_rank_both(const float* scores, int64_t Q, int64_t N, int64_t ld, int64_
  * fp32-grade similarity kernels on the tensor cores (losses/clipLoss.py:106 computes the logits
  * in fp32: `.float()`; contract rel 1e-5 loss / 1e-4 gradients).  fp32 rows are split into two
  * bf16 terms x = hi + lo (16 significant bits) and laid out so that ONE bf16 sweep over
- * K = 4 d reproduces (hi_a + lo_a) . (hi_b + lo_b):
- *   mm25_split_bf16x2(x [rows, d] fp32, role) -> out4 [rows, 4 d] bf16 = [hi hi lo lo] (role 0,
- *   row operand) or [hi lo hi lo] (role 1, column operand), plus hi, lo [rows, d] bf16.
- * Forward: mm25_sim_fwd(out4_a, out4_b, MM25_BF16, ..., d = 4 d, MM25_SIM_PLAIN).
+ * K = 3 d reproduces hi_a.hi_b + hi_a.lo_b + lo_a.hi_b (the lo x lo product, 2^-18 of the dot
+ * product, is dropped):
+ *   mm25_split_bf16x2(x [rows, d] fp32, role) -> out4 [rows, 3 d] bf16 = [hi hi lo] (role 0,
+ *   row operand) or [hi lo hi] (role 1, column operand), plus hi, lo [rows, d] bf16.
+ * Forward: mm25_sim_fwd(out4_a, out4_b, MM25_BF16, ..., d = 3 d, MM25_SIM_PLAIN).
  * Backward: mm25_sim_bwd_split — the gradient panel is split the same way (the recompute sweep
- * runs twice, the second pass emits g - bf16(g)) and dA = sum over the four (G term, Y term)
- * products, accumulated in fp32 by four grouped-GEMM launches; likewise dB.  da [B, M, d],
+ * runs twice, the second pass emits g - bf16(g)) and dA = G_hi Y_hi + G_hi Y_lo + G_lo Y_hi,
+ * accumulated in fp32 by three grouped-GEMM launches; likewise dB.  da [B, M, d],
  * db [B, N, d] fp32 (either may be NULL); dscale_part: mm25_sim_bwd_split_nparts(B, M, N)
  * floats (NULL: skip); workspace: mm25_sim_bwd_split_workspace_bytes(M, N); mode = MM25_SIM_PLAIN
  * or MM25_SIM_MASKDIAG (InfoLOOB, cloobLoss.py:26-31).
  * mm25_sim_split_eligible: 1 when the shape is covered (d % 256 == 0, d <= 1024, M % 128 == 0,
  * N % 256 == 0). */
+/* MM25_SPLIT_K (defined with the enums above) as a call, for bindings that cannot read macros */
+int mm25_split_width(void);
 int mm25_split_bf16x2(const float* x, int64_t rows, int64_t d, int role, void* out4, void* hi,
                       void* lo, void* stream);
 int mm25_sim_split_eligible(int64_t B, int64_t M, int64_t N, int64_t d);

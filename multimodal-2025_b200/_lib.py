@@ -136,6 +136,7 @@ SIGNATURES = {
     "mm25_topk_workspace_bytes": (_sz, [_i64, _i64, _i64]),
     "mm25_topk_rows_ws": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _sz, _vp]),
     "mm25_rank_both": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "mm25_split_width": (_int, []),
     "mm25_split_bf16x2": (_int, [_vp, _i64, _i64, _int, _vp, _vp, _vp, _vp]),
     "mm25_sim_split_eligible": (_int, [_i64, _i64, _i64, _i64]),
     "mm25_sim_bwd_split_workspace_bytes": (_sz, [_i64, _i64]),

@@ -217,7 +217,7 @@ extern "C" int64_t mm25_sim_bwd_split_nparts(int64_t B, int64_t M, int64_t N) {
   return tc::bwd_split_nparts(B, M, N);
 }
 extern "C" int mm25_sim_split_eligible(int64_t B, int64_t M, int64_t N, int64_t d) {
-  return tc::eligible_fwd(B, M, N, 4 * d, MM25_BF16, MM25_SIM_PLAIN) && d % 256 == 0 &&
+  return tc::eligible_fwd(B, M, N, MM25_SPLIT_K * d, MM25_BF16, MM25_SIM_PLAIN) && d % 256 == 0 &&
                  tc::eligible_bwd(B, M, N, d, MM25_BF16, MM25_SIM_PLAIN)
              ? 1 : 0;
 }

@@ -656,8 +656,9 @@ extern "C" int mm25_peer_bcast(const void* src, int64_t bytes, void* const* peer
 
 // Two-term bf16 split of fp32 rows for the fp32-grade tensor-core path (sim_tc_bwd.cu
 // launch_bwd_split): x = hi + lo with hi = bf16(x), lo = bf16(x - hi) (16 significant bits).
-// out4 [rows, 4 d] holds [hi hi lo lo] (role 0, the row operand) or [hi lo hi lo] (role 1, the
-// column operand), so that out4_a . out4_b = (hi_a + lo_a) . (hi_b + lo_b) over K = 4 d.
+// out4 [rows, 3 d] holds [hi hi lo] (role 0, the row operand) or [hi lo hi] (role 1, the column
+// operand), so that out4_a . out4_b = hi_a.hi_b + hi_a.lo_b + lo_a.hi_b over K = 3 d; the
+// lo x lo product (2^-18 of the dot product per element, random sign) is dropped.
 __global__ void __launch_bounds__(256) split_bf16x2_kernel(const float* __restrict__ x,
                                                            int64_t rows, int d, int role,
                                                            __nv_bfloat16* __restrict__ out4,
@@ -674,13 +675,14 @@ __global__ void __launch_bounds__(256) split_bf16x2_kernel(const float* __restri
                                                    v.y - __bfloat162float(h.y));
     *reinterpret_cast<__nv_bfloat162*>(hi + r * d + c) = h;
     *reinterpret_cast<__nv_bfloat162*>(lo + r * d + c) = l;
-    __nv_bfloat16* o = out4 + r * 4 * (int64_t)d + c;
+    __nv_bfloat16* o = out4 + r * MM25_SPLIT_K * (int64_t)d + c;
     *reinterpret_cast<__nv_bfloat162*>(o) = h;
     *reinterpret_cast<__nv_bfloat162*>(o + d) = role ? l : h;
     *reinterpret_cast<__nv_bfloat162*>(o + 2 * d) = role ? h : l;
-    *reinterpret_cast<__nv_bfloat162*>(o + 3 * d) = l;
   }
 }
+
+extern "C" int mm25_split_width(void) { return MM25_SPLIT_K; }
 
 extern "C" int mm25_split_bf16x2(const float* x, int64_t rows, int64_t d, int role, void* out4,
                                  void* hi, void* lo, void* stream) {

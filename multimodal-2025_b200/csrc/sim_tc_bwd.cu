@@ -524,12 +524,13 @@ int launch_bwd(const void* a, const void* b, int64_t B, int64_t M, int64_t N, in
 // ------------------------------------------------------------------------------------------
 // fp32-grade backward on the tensor cores (SURVEY §7 hard part 1; clipLoss.py:106 `.float()`).
 // Operands are two-term bf16 splits x = x1 + x2 (16 significant bits, prep.cu split kernel):
-//   a4 = [a1 a1 a2 a2], b4 = [b1 b2 b1 b2]  ([rows, 4 d] bf16)  =>  a4 . b4 = (a1 + a2).(b1 + b2)
-// so the unchanged sweep recomputes fp32-grade logits with K = 4 d.  The gradient panel is split
+//   a4 = [a1 a1 a2], b4 = [b1 b2 b1]  ([rows, 3 d] bf16)  =>  a4 . b4 = a1.b1 + a1.b2 + a2.b1
+// (the a2.b2 product, 2^-18 of the dot product, is dropped) so the unchanged sweep recomputes
+// fp32-grade logits with K = 3 d.  The gradient panel is split
 // the same way, G' = G1 + G2: the sweep runs twice per panel (second pass emits g - bf16(g)), and
-// every product G . Y becomes four accumulating grouped-GEMM launches
-//   dA = G1 Y1 + G1 Y2 + G2 Y1 + G2 Y2,   dB likewise with X1, X2.
-// Cost: 2 x 4 sweeps + 4 x GEMMs = 32 N^2 d tensor FLOPs against 8 on the bf16 path — and against
+// every product G . Y becomes three accumulating grouped-GEMM launches
+//   dA = G1 Y1 + G1 Y2 + G2 Y1,   dB likewise with X1, X2.
+// Cost: 2 x 3 sweeps + 3 x GEMMs = 24 N^2 d tensor FLOPs against 6 on the bf16 path — and against
 // the FFMA kernels' 6 N^2 d at ~10 TFLOP/s.  B entries are walked one by one (panel loop).
 size_t bwd_split_workspace_bytes(int64_t M, int64_t N) {
   return (size_t)panel_rows(M, N) * (size_t)N * 2 + 256 + (size_t)N * sizeof(float) + 256;
@@ -545,7 +546,7 @@ int launch_bwd_split(const void* a4, const void* b4, const void* a_hi, const voi
                      float w_row, float w_col, float w_diag, float w_all, const float* gout,
                      float* da, float* db, float* dscale_part, void* ws, size_t ws_bytes,
                      float dot_bound, cudaStream_t st, int mask_diag) {
-  const int64_t d4 = 4 * d;
+  const int64_t d4 = MM25_SPLIT_K * d;   // width of the concatenated split operands
   if (!eligible_fwd(B, M, N, d4, MM25_BF16, MM25_SIM_PLAIN) || d % 256 != 0 ||
       !gemm_eligible(M >= 128 ? 128 : M, d, N))
     return MM25_ERR_SHAPE;
@@ -611,6 +612,7 @@ int launch_bwd_split(const void* a4, const void* b4, const void* a_hi, const voi
         timing_end(tt_, st); }
         MM25_LAUNCH_CHECK();
         for (int t = 0; t < 2; ++t) {   // second operand: hi term, then lo term
+          if (lo && t) continue;       // G_lo Y_lo: 2^-18 of the product, dropped
           const __nv_bfloat16* yb = (t ? bl : bh) + bz * N * d;
           const __nv_bfloat16* xb = (t ? al : ah) + (bz * M + p0) * d;
           const int first = (lo == 0 && t == 0);

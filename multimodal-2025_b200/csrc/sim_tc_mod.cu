@@ -606,17 +606,18 @@ int launch_hopfield_bwd(const void* q, const void* k, const float* d_o, int64_t 
 
 // ------------------------------------------------------------------------------------------
 // fp32-grade Hopfield backward (cloobLoss.py:43-47 in fp32; contract 1e-5 / 1e-4): the same
-// dual-accumulator sweep on two-term bf16 splits.  q4 / do4 = [hi hi lo lo], k4 = [hi lo hi lo]
-// ([rows, 4 d], prep.cu split kernel), so S = Q K^T and T = dO K^T accumulate with 16 significant
+// dual-accumulator sweep on two-term bf16 splits.  q4 / do4 = [hi hi lo], k4 = [hi lo hi]
+// ([rows, 3 d], prep.cu split kernel), so S = Q K^T and T = dO K^T accumulate with 16 significant
 // bits per operand; the panels dZ and P are split too (second pass emits x - bf16(x)) and every
 // product with them becomes accumulating grouped-GEMM launches over the (hi, lo) operand terms.
 bool hopfield_split_eligible(int64_t M, int64_t N, int64_t d) {
-  return eligible(1, M, N, 4 * d, 4 * d, MM25_BF16, false) && d % 256 == 0 && d <= 1024 &&
+  return eligible(1, M, N, MM25_SPLIT_K * d, MM25_SPLIT_K * d, MM25_BF16, false) &&
+         d % 256 == 0 && d <= 1024 &&
          N % 256 == 0 && gemm_eligible(128, d, N);
 }
 
 size_t hopfield_split_workspace_bytes(int64_t M, int64_t N, int64_t d) {
-  return 256 + align256((size_t)M * 4 * d * 2) + 2 * align256((size_t)M * d * 2) +
+  return 256 + align256((size_t)M * MM25_SPLIT_K * d * 2) + 2 * align256((size_t)M * d * 2) +
          2 * align256((size_t)hopf_panel_rows(M, N) * (size_t)N * 2);
 }
 
@@ -630,7 +631,7 @@ int launch_hopfield_bwd_split(const void* q4, const void* k4, const void* q_hi, 
                               cudaStream_t st) {
   if (!hopfield_split_eligible(M, N, d)) return MM25_ERR_SHAPE;
   if (ws_bytes < hopfield_split_workspace_bytes(M, N, d)) return MM25_ERR_WORKSPACE;
-  const int64_t d4 = 4 * d;
+  const int64_t d4 = MM25_SPLIT_K * d;
   uintptr_t w0 = (reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255);
   __nv_bfloat16* do4 = reinterpret_cast<__nv_bfloat16*>(w0);
   w0 += align256((size_t)M * d4 * 2);
@@ -673,6 +674,7 @@ int launch_hopfield_bwd_split(const void* q4, const void* k4, const void* q_hi, 
       timing_end(tt_, st); }
       MM25_LAUNCH_CHECK();
       for (int t = 0; t < 2; ++t) {
+        if (lo && t) continue;   // lo x lo products: 2^-18, dropped
         const int first = (lo == 0 && t == 0);
         // dQ[panel] (+)= dZ K_t  and  dK (+)= dZ^T Q_t[panel]
         GemmDesc ga{GZ, ks[t], dq ? dq + p0 * d : nullptr, d, rows, N, 0, 1, first ? 0 : 1, 1.f,

@@ -215,15 +215,16 @@ def sim_split_eligible(B: int, M: int, N: int, d: int) -> bool:
 
 @torch.library.custom_op("mm25::split_bf16x2", mutates_args=(), device_types="cuda")
 def split_bf16x2(x: Tensor, role: int) -> Tuple[Tensor, Tensor, Tensor]:
-    """fp32 [B, rows, d] -> (out4 [B, rows, 4 d], hi, lo [B, rows, d]) bf16: the two-term split
-    x = hi + lo laid out for the K = 4 d sweep (role 0 = row operand [hi hi lo lo], role 1 =
-    column operand [hi lo hi lo]; include/mm25.h mm25_split_bf16x2)."""
+    """fp32 [B, rows, d] -> (out4 [B, rows, W d], hi, lo [B, rows, d]) bf16: the two-term split
+    x = hi + lo laid out for the K = W d sweep (W = mm25_split_width() = 3: role 0 = row operand
+    [hi hi lo], role 1 = column operand [hi lo hi]; include/mm25.h mm25_split_bf16x2)."""
     x = _cuda3(x, "x")
     if x.dtype != torch.float32:
         raise TypeError("split_bf16x2 takes fp32 rows")
     B, R, d = x.shape
     with torch.cuda.device(x.device):
-        out4 = torch.empty((B, R, 4 * d), dtype=torch.bfloat16, device=x.device)
+        W = int(_lib.lib().mm25_split_width())
+        out4 = torch.empty((B, R, W * d), dtype=torch.bfloat16, device=x.device)
         hi = torch.empty((B, R, d), dtype=torch.bfloat16, device=x.device)
         lo = torch.empty((B, R, d), dtype=torch.bfloat16, device=x.device)
         rc = _lib.lib().mm25_split_bf16x2(_p(x), B * R, d, role, _p(out4), _p(hi), _p(lo),
@@ -243,7 +244,7 @@ def sim_bwd_split(a4: Tensor, b4: Tensor, a_hi: Tensor, a_lo: Tensor, b_hi: Tens
     returns (da [B, M, d], db [B, N, d], dscale[1]) fp32."""
     B, M, d4 = a4.shape
     N = b4.shape[1]
-    d = d4 // 4
+    d = d4 // int(_lib.lib().mm25_split_width())
     dev = a4.device
     L = _lib.lib()
     with torch.cuda.device(dev):
@@ -274,10 +275,10 @@ def hopfield_bwd_split(q4: Tensor, k4: Tensor, q_hi: Tensor, q_lo: Tensor, k_hi:
                        k_lo: Tensor, d_o: Tensor, beta: Tensor, lse: Tensor, delta: Tensor,
                        need_dq: bool, need_dk: bool) -> Tuple[Tensor, Tensor]:
     """fp32-grade Hopfield backward on the split operands (include/mm25.h
-    mm25_hopfield_bwd_split); q4 [M, 4 d], k4 [N, 4 d] bf16, d_o [M, d] fp32."""
+    mm25_hopfield_bwd_split); q4 [M, W d], k4 [N, W d] bf16, d_o [M, d] fp32."""
     M, d4 = q4.shape
     N = k4.shape[0]
-    d = d4 // 4
+    d = d4 // int(_lib.lib().mm25_split_width())
     dev = q4.device
     L = _lib.lib()
     d_o = d_o.detach().float().contiguous()
