@@ -45,7 +45,7 @@ class _ClipLossFn(torch.autograd.Function):
         N = yhat.shape[1]
         # fp32 inputs keep the reference's fp32-grade arithmetic (clipLoss.py:106 `.float()`) ON
         # THE TENSOR CORES when the shape allows: two-term bf16 splits of the normalised rows
-        # (16 significant bits) swept over K = 4 d (include/mm25.h mm25_split_bf16x2); otherwise
+        # (16 significant bits) swept over K = 3 d (include/mm25.h mm25_split_bf16x2); otherwise
         # the fp32 FFMA kernels.  MM25_FP32_TC=0 forces the FFMA kernels.
         split = (cdt == ops.F32 and impl == ops.IMPL_AUTO and xhat.is_cuda
                  and os.environ.get("MM25_FP32_TC", "1") != "0"
