@@ -87,7 +87,7 @@ class _HopfieldFn(torch.autograd.Function):
         kf = k.detach().float().contiguous()
         sc = _scalar(beta, q.device)
         if _split_ok(ops, qf, kf, True):
-            # fp32-grade on the tensor cores: split operands swept over K = 4 d
+            # fp32-grade on the tensor cores: split operands swept over K = 3 d
             q4, qh, ql = ops.split_bf16x2(qf.unsqueeze(0), 0)
             k4, kh, kl = ops.split_bf16x2(kf.unsqueeze(0), 1)
             lse, _, _, _ = ops.sim_fwd(q4, k4, None, None, None, sc, ops.SCALE_MUL, 0.0,
